@@ -1,0 +1,294 @@
+/* amrvr.h -- C ABI of libamrvr_b200.so, the B200-native (sm_100a) replacement for
+ * amrVolumeRenderer's per-ray hot path and sort-last DirectSend composite.
+ *
+ * The reference has no FFI layer; its seams are C++ classes.  Each entry point
+ * below names the reference interface it replaces (paths relative to the
+ * reference tree).  amrvolumerenderer_b200/adapters/ holds thin C++ classes with
+ * the reference's own names and signatures that forward here.
+ *
+ * Conventions: plain pointers and sizes only; every function returns an int
+ * status (AMRVR_OK = 0); no exception crosses the ABI; amrvr_last_error() gives
+ * the message the C++ adapters rethrow (std::invalid_argument for
+ * AMRVR_ERR_INVALID, std::runtime_error otherwise).  One amrvr_ctx per GPU, used
+ * from one thread at a time (the reference path is single-threaded per rank).
+ * There is NO CPU fallback: every compute entry point fails with
+ * AMRVR_ERR_CUDA when no sm_100 device is usable.  Entry points marked
+ * [host-only] never touch the GPU and work on a machine without one.
+ */
+#ifndef AMRVR_H
+#define AMRVR_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AMRVR_ABI_VERSION 1
+
+enum {
+  AMRVR_OK = 0,
+  AMRVR_ERR_INVALID = 1, /* bad argument (reference: std::invalid_argument)  */
+  AMRVR_ERR_RUNTIME = 2, /* data problem (reference: std::runtime_error)     */
+  AMRVR_ERR_CUDA = 3,    /* CUDA / device failure, or no usable GPU          */
+  AMRVR_ERR_NCCL = 4     /* NCCL failure or NCCL not loadable                */
+};
+
+#define AMRVR_COLOR_TABLE_SIZE 256 /* Common/VolumePainter.cpp:35 */
+#define AMRVR_NCCL_ID_BYTES 128
+
+typedef struct amrvr_ctx amrvr_ctx;
+typedef struct amrvr_scene amrvr_scene;
+typedef struct amrvr_layers amrvr_layers;
+
+/* volume::AmrBox (Common/VolumeTypes.hpp:69-76) flattened together with the
+ * amrex::Array4<Real const> view it carries.  `data` may be a host pointer
+ * (pageable or pinned) or a device pointer; element (i,j,k,n) lives at
+ *   data[(i-begin[0]) + (j-begin[1])*jstride + (k-begin[2])*kstride + n*nstride]
+ * exactly as amrex::Array4::operator().  Real is double (reference default). */
+typedef struct amrvr_box {
+  double min_corner[3];
+  double max_corner[3];
+  int32_t dims[3];  /* cellDimensions */
+  int32_t lo[3];    /* validBox.smallEnd() */
+  const double* data;
+  int64_t jstride, kstride, nstride;
+  int32_t begin[3]; /* Array4::begin */
+  int32_t component;
+} amrvr_box;
+
+/* volume::ScalarTransform (Common/VolumeTypes.hpp:21-31). */
+typedef struct amrvr_scalar_transform {
+  int32_t log_scale_input;
+  int32_t normalize_to_unit_range;
+  double positive_floor;
+  double processed_min;
+  double processed_max;
+  double inverse_processed_span;
+  double normalization_min;
+  double normalization_max;
+  double inverse_normalization_span;
+} amrvr_scalar_transform;
+
+/* volume::CameraParameters (Common/VolumeTypes.hpp:83-90). */
+typedef struct amrvr_camera {
+  double eye[3];
+  double look_at[3];
+  double up[3];
+  float fov_y_degrees;
+  float near_plane;
+  float far_plane;
+} amrvr_camera;
+
+/* volume::ColorMapControlPoint (Common/VolumeTypes.hpp:92-98). */
+typedef struct amrvr_colormap_pt {
+  float value, red, green, blue, alpha;
+} amrvr_colormap_pt;
+
+/* One global box record, identical on every rank after amrvr_scene_upload():
+ * what VisibilityOrdering.cpp:85-152 allgathers (bounds, owner) plus what
+ * DirectSendBase.cpp:329-376 needs (owner-local layer index). */
+typedef struct amrvr_box_record {
+  double min_corner[3];
+  double max_corner[3];
+  int32_t dims[3];
+  int32_t owner;       /* rank that paints this box */
+  int32_t local_index; /* index within the owner's box list (= layer index) */
+  int32_t reserved;
+} amrvr_box_record;
+
+/* Per-frame statistics of one amrvr_raymarch() call. */
+typedef struct amrvr_march_stats {
+  int64_t samples;          /* executions of VolumePainter.cpp:869-894 (0 unless counting on) */
+  int64_t rays;             /* (pixel, box) pairs inside a footprint rectangle */
+  int64_t fragment_pixels;  /* pixels stored in all footprint layers */
+  float kernel_ms;          /* CUDA-event time of the march kernel */
+} amrvr_march_stats;
+
+/* ------------------------------------------------------------------ context */
+
+/* [host-only] Version of this ABI. */
+int amrvr_abi_version(void);
+
+/* [host-only] Create an NCCL unique id (rank 0 calls it and ships the
+ * AMRVR_NCCL_ID_BYTES to the other ranks with whatever the host already has:
+ * MPI_Bcast in the reference's world, torch.distributed here). */
+int amrvr_nccl_unique_id(void* id_out);
+
+/* Replaces the implicit per-rank state of the reference (MPI_COMM_WORLD rank /
+ * size read in VolumeRenderer::VolumeRenderer(), VolumeRenderer.cpp:557-560).
+ * nccl_unique_id may be NULL iff nranks == 1. */
+int amrvr_ctx_create(int cuda_device, int rank, int nranks,
+                     const void* nccl_unique_id, amrvr_ctx** out);
+void amrvr_ctx_destroy(amrvr_ctx* ctx);
+/* Message of the last failure on this ctx (or of the last failed call that had
+ * no ctx when ctx == NULL).  Never NULL. */
+const char* amrvr_last_error(const amrvr_ctx* ctx);
+/* The CUDA stream every kernel of this ctx is launched on (cudaStream_t). */
+void* amrvr_ctx_stream(amrvr_ctx* ctx);
+/* Number of kernels this ctx has launched so far. */
+int64_t amrvr_ctx_kernel_launches(const amrvr_ctx* ctx);
+
+/* ------------------------------------------------------------------- scene */
+
+/* K2.  Replaces reduceLocalScalarStats (VolumeRenderer/SceneBuilder.cpp:53-94):
+ * min, max, min-positive and finite count over all cells of the given boxes. */
+int amrvr_brick_stats(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                      double* min_value, double* max_value,
+                      double* min_positive, int64_t* finite_count);
+
+/* K5.  Replaces the zero-copy Array4 views BuildSceneGeometry hands to the
+ * painter (SceneBuilder.cpp:160-187): each FAB becomes a device-resident brick
+ * of one byte per cell holding the colour-table index the reference computes
+ * per sample (VolumeTypes.hpp:33-67 applyScalarTransform, VolumePainter.cpp:
+ * 75-105 saturateSoftTail, :873-883 normalise/quantise).  Also allgathers the
+ * box records of all ranks (collective when nranks > 1). */
+int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                       const amrvr_scalar_transform* transform,
+                       float range_min, float range_max, amrvr_scene** out);
+int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene);
+/* Global box table (all ranks, owner-major, owner-local order). */
+int amrvr_scene_global_boxes(const amrvr_scene* scene, int* nglobal,
+                             const amrvr_box_record** records);
+/* Copy brick `local_box` (dims[0]*dims[1]*dims[2] bytes, i fastest) to host. */
+int amrvr_scene_read_brick(amrvr_ctx* ctx, const amrvr_scene* scene,
+                           int local_box, uint8_t* dst);
+
+/* ---------------------------------------------------------------- ordering */
+
+/* a10.  Replaces BuildVisibilityOrderedGroup (Common/VisibilityOrdering.hpp:
+ * 14-23, .cpp:63-632): rank_order[i] = rank that owns image piece i.  The
+ * MPI_Group of the reference is this int array.  Depth keys are sorted by the
+ * device radix sort; returns identity order when use_graph == 0 or the graph
+ * cannot be ordered (same fallback as :610-627, *graph_failed set to 1). */
+int amrvr_order_boxes(amrvr_ctx* ctx, const amrvr_scene* scene,
+                      const amrvr_camera* camera, float aspect, int use_graph,
+                      int* rank_order /*[nranks]*/, int* graph_failed);
+
+/* [host-only] Same computation on the host from an explicit global table;
+ * used by the CPU tests and by amrvr_order_boxes for the sequential part. */
+int amrvr_order_boxes_host(int nranks, int nglobal,
+                           const amrvr_box_record* records,
+                           const amrvr_camera* camera, float aspect,
+                           int use_graph, int* rank_order, int* graph_failed);
+
+/* [host-only] a6 + a11.  computeBoxDepthHint (VolumeRenderer.cpp:541-553) for
+ * every global box and the layer order of DirectSendBase.cpp:363-388:
+ * order[k] = index into the global table of the k-th layer to blend. */
+int amrvr_layer_order_host(int nglobal, const amrvr_box_record* records,
+                           const amrvr_camera* camera, float* depth_hints,
+                           int* order);
+
+/* [host-only] a12.  getPieceRange (DirectSendBase.cpp:59-74). */
+int amrvr_piece_range(int num_pixels, int piece, int num_pieces, int* begin,
+                      int* end);
+
+/* [host-only] a7.  referenceSampleDistance (VolumeRenderer.cpp:1138-1190). */
+int amrvr_reference_sample_distance(int nglobal,
+                                    const amrvr_box_record* records,
+                                    const double bounds_min[3],
+                                    const double bounds_max[3], float* out);
+
+/* [host-only] a2.  buildColorTable (VolumePainter.cpp:442-516): 256 RGBA
+ * entries for one normalisation factor. */
+int amrvr_color_table(float alpha_scale, float normalization_factor,
+                      float range_min, float range_max,
+                      const amrvr_colormap_pt* pts, int npts,
+                      float* table_rgba /*[256*4]*/);
+
+/* --------------------------------------------------------------- ray-march */
+
+/* a1-a5.  Replaces the loop of VolumePainter::paint calls in
+ * renderSingleTrial (VolumeRenderer.cpp:1201-1219, Common/VolumePainter.cpp:
+ * 548-961): all local boxes in one launch, each into a layer that stores only
+ * the box's screen-space footprint rectangle.  count_samples != 0 turns the
+ * per-sample counter on (slightly slower kernel). */
+int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene,
+                   const amrvr_camera* camera, int width, int height,
+                   float box_transparency, float reference_sample_distance,
+                   const amrvr_colormap_pt* pts, int npts, int count_samples,
+                   amrvr_layers** out);
+int amrvr_layers_free(amrvr_ctx* ctx, amrvr_layers* layers);
+int amrvr_layers_count(const amrvr_layers* layers);
+int amrvr_layers_stats(const amrvr_layers* layers, amrvr_march_stats* stats);
+/* Footprint rectangle of a layer: pixels [x0,x0+w) x [y0,y0+h). */
+int amrvr_layers_rect(const amrvr_layers* layers, int layer, int* x0, int* y0,
+                      int* w, int* h);
+/* Dense materialisation of one layer as the reference's
+ * ImageRGBAFloatColorDepthSort buffer: width*height*5 floats
+ * [r,g,b,a,depth], premultiplied, +inf depth where empty
+ * (Common/ImageRGBAFloatColorDepthSort.hpp:9-44).  dst5 is a HOST pointer. */
+int amrvr_layers_read(amrvr_ctx* ctx, const amrvr_layers* layers, int layer,
+                      float* dst5);
+
+/* --------------------------------------------------------------- composite */
+
+/* a11-a13.  Replaces Compositor::compose / DirectSendBase::composeLayered
+ * (Common/Compositor.hpp:35-37, DirectSend/Base/DirectSendBase.cpp:316-458):
+ * this rank's fully blended piece, pixels [*region_begin, *region_end) of the
+ * row-major frame, 5 floats per pixel, left on the device
+ * (*piece5_device, owned by ctx, valid until the next composite). Collective. */
+int amrvr_composite(amrvr_ctx* ctx, const amrvr_scene* scene,
+                    const amrvr_layers* layers, const amrvr_camera* camera,
+                    const int* rank_order, int* region_begin, int* region_end,
+                    float** piece5_device);
+/* a14.  Replaces ImageColorOnly::Gather (Common/ImageColorOnly.hpp:220-270).
+ * full5_device (root only) receives width*height*5 floats. Collective. */
+int amrvr_gather(amrvr_ctx* ctx, const float* piece5_device, int region_begin,
+                 int region_end, int num_pixels, int root,
+                 float* full5_device);
+/* a15.  Replaces downsampleImage (VolumeRenderer.cpp:479-528). */
+int amrvr_downsample(amrvr_ctx* ctx, const float* full5_device, int width,
+                     int height, int sqrt_aa, float* out5_device);
+/* a16.  Color::GetComponentAsByte (Common/Color.hpp:66-91) + the bottom-up row
+ * order of SavePPM/SavePNG (Common/SavePPM.cpp:25-32): RGB8, top row first. */
+int amrvr_quantize_rgb8(amrvr_ctx* ctx, const float* full5_device, int width,
+                        int height, uint8_t* rgb8_device);
+
+/* Device <-> host helpers so hosts without a CUDA runtime of their own (ctypes,
+ * plain C++) can move results; all on the ctx stream, blocking. */
+int amrvr_device_alloc(amrvr_ctx* ctx, size_t bytes, void** out);
+int amrvr_device_free(amrvr_ctx* ctx, void* ptr);
+int amrvr_copy_to_host(amrvr_ctx* ctx, void* dst_host, const void* src_device,
+                       size_t bytes);
+int amrvr_copy_to_device(amrvr_ctx* ctx, void* dst_device, const void* src_host,
+                         size_t bytes);
+int amrvr_host_alloc_pinned(size_t bytes, void** out);
+int amrvr_host_free_pinned(void* ptr);
+int amrvr_synchronize(amrvr_ctx* ctx);
+
+/* ------------------------------------------------------------ whole frame */
+
+typedef struct amrvr_frame_params {
+  int32_t width, height;       /* RenderParameters (VolumeRenderer.hpp:33-44) */
+  float box_transparency;
+  int32_t antialiasing;        /* perfect square */
+  int32_t use_visibility_graph;
+  int32_t count_samples;
+  int32_t draw_bounding_box;   /* renderBoundingBoxLayer, VolumeRenderer.cpp:1311-1314 */
+  int32_t reserved;
+} amrvr_frame_params;
+
+typedef struct amrvr_frame_stats {
+  float march_ms, order_ms, composite_ms, gather_ms, post_ms;
+  int64_t samples;
+  int64_t exchanged_bytes; /* bytes this rank sent to other ranks */
+} amrvr_frame_stats;
+
+/* a1-a17 in one call = VolumeRenderer::renderSingleTrial
+ * (VolumeRenderer.cpp:1103-1339) without the file write: on `root`,
+ * rgba5_host (may be NULL) receives width*height*5 floats after downsample and
+ * overlay, rgb8_host (may be NULL) the width*height*3 bytes SavePPM would
+ * write.  Collective. */
+int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
+                       const amrvr_camera* camera,
+                       const amrvr_frame_params* params,
+                       const amrvr_colormap_pt* pts, int npts, int root,
+                       float* rgba5_host, uint8_t* rgb8_host,
+                       amrvr_frame_stats* stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AMRVR_H */

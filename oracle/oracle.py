@@ -1,0 +1,289 @@
+"""oracle/oracle.py -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+
+ctypes wrappers over
+  * oracle/liboracle.so          the plain-C restatement (oracle/restate/*.c)   -> class Oracle
+  * oracle/_ref/libamrvr_ref.so  the reference's own sources built against the
+                                 AMReX/MPI shim (oracle/Makefile)               -> class Ref
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may import
+this module.  Nothing under amrvolumerenderer_b200/ does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+from amrvolumerenderer_b200 import ctypes_api as api
+
+HERE = Path(__file__).resolve().parent
+RESTATE_LIB = HERE / "liboracle.so"
+REF_LIB = HERE / "_ref" / "libamrvr_ref.so"
+REFERENCE_ROOT = Path("/root/reference")
+
+_P = C.POINTER
+_f32p = _P(C.c_float)
+
+
+def build(ref: bool | None = None) -> None:
+    """Compile the restatement and, when the reference tree is present, _ref."""
+    subprocess.run(["make", "-s", "-C", str(HERE), "restate"], check=True)
+    if ref is None:
+        ref = REFERENCE_ROOT.exists()
+    if ref:
+        subprocess.run(["make", "-s", "-j8", "-C", str(HERE), "ref"], check=True)
+
+
+def _fptr(a: np.ndarray):
+    return a.ctypes.data_as(_f32p)
+
+
+def _d3(a):
+    return (C.c_double * 3)(*[float(x) for x in a])
+
+
+class _Base:
+    def _cmap(self, colormap):
+        return api.colormap_array(colormap)
+
+
+class Oracle(_Base):
+    """Plain-C restatement."""
+
+    def __init__(self):
+        if not RESTATE_LIB.exists():
+            build(ref=False)
+        self.lib = C.CDLL(str(RESTATE_LIB))
+        L = self.lib
+        L.orc_depth_hint.restype = C.c_float
+        L.orc_reference_sample_distance.restype = C.c_float
+        L.orc_cell_index.restype = C.c_int
+        L.orc_cell_index.argtypes = [C.c_double, _P(api.ScalarTransform), C.c_float, C.c_float]
+        L.orc_order.restype = C.c_int
+
+    def color_table(self, alpha_scale, norm, rmin, rmax, colormap=None) -> np.ndarray:
+        out = np.zeros((256, 4), np.float32)
+        pts, n = self._cmap(colormap)
+        self.lib.orc_color_table(C.c_float(alpha_scale), C.c_float(norm), C.c_float(rmin),
+                                 C.c_float(rmax), pts, n, _fptr(out))
+        return out
+
+    def quantize_box(self, cbox, transform, rmin, rmax) -> np.ndarray:
+        n = cbox.dims[0] * cbox.dims[1] * cbox.dims[2]
+        out = np.zeros(n, np.uint8)
+        self.lib.orc_quantize_box(C.byref(cbox), C.byref(transform), C.c_float(rmin),
+                                  C.c_float(rmax), out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def cell_index(self, raw, transform, rmin, rmax) -> int:
+        return self.lib.orc_cell_index(float(raw), C.byref(transform), rmin, rmax)
+
+    def paint(self, cbox, transform, rmin, rmax, box_transparency, ref_dist, width, height,
+              camera, colormap=None):
+        out = np.zeros((height, width, 5), np.float32)
+        samples = C.c_longlong(0)
+        pts, n = self._cmap(colormap)
+        self.lib.orc_paint(C.byref(cbox), C.byref(transform), C.c_float(rmin), C.c_float(rmax),
+                           C.c_float(box_transparency), C.c_float(ref_dist), width, height,
+                           C.byref(camera), pts, n, _fptr(out), C.byref(samples))
+        return out, samples.value
+
+    def depth_hint(self, record, camera) -> float:
+        return float(self.lib.orc_depth_hint(C.byref(record), C.byref(camera)))
+
+    def layer_order(self, records, n, camera):
+        hints = np.zeros(max(n, 1), np.float32)
+        order = np.zeros(max(n, 1), np.int32)
+        self.lib.orc_layer_order(n, records, C.byref(camera), _fptr(hints),
+                                 order.ctypes.data_as(_P(C.c_int)))
+        return hints[:n], order[:n]
+
+    def reference_sample_distance(self, records, n, bmin, bmax) -> float:
+        return float(self.lib.orc_reference_sample_distance(n, records, _d3(bmin), _d3(bmax)))
+
+    def order(self, nranks, records, n, camera, aspect, use_graph=True):
+        out = np.zeros(nranks, np.int32)
+        ok = self.lib.orc_order(nranks, n, records, C.byref(camera), C.c_float(aspect),
+                                int(use_graph), out.ctypes.data_as(_P(C.c_int)))
+        return out, bool(ok)
+
+    def piece_range(self, npix, piece, npieces):
+        b, e = C.c_int(0), C.c_int(0)
+        self.lib.orc_piece_range(npix, piece, npieces, C.byref(b), C.byref(e))
+        return b.value, e.value
+
+    def blend(self, top, bottom) -> np.ndarray:
+        t = np.ascontiguousarray(top, np.float32)
+        b = np.ascontiguousarray(bottom, np.float32)
+        out = np.zeros(5, np.float32)
+        self.lib.orc_blend(_fptr(t), _fptr(b), _fptr(out))
+        return out
+
+    def compose(self, nranks, width, height, layers, owners, hints, rank_order):
+        n = len(layers)
+        layers = [np.ascontiguousarray(l, np.float32) for l in layers]
+        ptrs = (_f32p * max(n, 1))(*[_fptr(l) for l in layers])
+        own = np.ascontiguousarray(owners, np.int32)
+        hin = np.ascontiguousarray(hints, np.float32)
+        ro = np.ascontiguousarray(rank_order, np.int32)
+        full = np.zeros((height, width, 5), np.float32)
+        piece_owner = np.zeros(height * width, np.int32)
+        self.lib.orc_compose(nranks, width, height, n, own.ctypes.data_as(_P(C.c_int)), ptrs,
+                             _fptr(hin), ro.ctypes.data_as(_P(C.c_int)), _fptr(full),
+                             piece_owner.ctypes.data_as(_P(C.c_int)))
+        return full, piece_owner
+
+    def downsample(self, src5, width, height, sqrt_aa):
+        src = np.ascontiguousarray(src5, np.float32)
+        out = np.zeros((height, width, 5), np.float32)
+        self.lib.orc_downsample(_fptr(src), width, height, sqrt_aa, _fptr(out))
+        return out
+
+    def overlay(self, image5, tight_min, tight_max, camera, sqrt_aa=1):
+        img = np.ascontiguousarray(image5, np.float32).copy()
+        h, w = img.shape[:2]
+        self.lib.orc_overlay(_d3(tight_min), _d3(tight_max), C.byref(camera), sqrt_aa, w, h,
+                             _fptr(img))
+        return img
+
+    def quantize_rgb8(self, image5):
+        img = np.ascontiguousarray(image5, np.float32)
+        h, w = img.shape[:2]
+        out = np.zeros((h, w, 3), np.uint8)
+        self.lib.orc_quantize_rgb8(_fptr(img), w, h, out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def auto_camera(self, bmin, bmax, azimuth, altitude, up=None) -> api.Camera:
+        cam = api.Camera()
+        self.lib.orc_auto_camera(_d3(bmin), _d3(bmax), C.c_float(azimuth), C.c_float(altitude),
+                                 _d3(up) if up is not None else None, C.byref(cam))
+        return cam
+
+    def render_frame(self, scene, camera, params, colormap=None):
+        """scene: amrvolumerenderer_b200.scenes.Scene.  Returns dict."""
+        cboxes, n, _keep = scene.c_boxes()
+        owners = scene.owners()
+        final = np.zeros((params.height, params.width, 5), np.float32)
+        rgb = np.zeros((params.height, params.width, 3), np.uint8)
+        order = np.zeros(scene.nranks, np.int32)
+        samples = C.c_longlong(0)
+        pts, npts = self._cmap(colormap)
+        self.lib.orc_render_frame(
+            scene.nranks, n, cboxes, owners.ctypes.data_as(_P(C.c_int32)),
+            C.byref(scene.transform), C.c_float(scene.scalar_range[0]),
+            C.c_float(scene.scalar_range[1]), _d3(scene.bounds_min), _d3(scene.bounds_max),
+            C.byref(camera), C.byref(params), pts, npts, _fptr(final),
+            rgb.ctypes.data_as(C.c_void_p), order.ctypes.data_as(_P(C.c_int)),
+            C.byref(samples))
+        return {"final5": final, "rgb8": rgb, "rank_order": order, "samples": samples.value}
+
+
+class RefLevel(C.Structure):
+    _fields_ = [
+        ("prob_lo", C.c_double * 3),
+        ("cell_size", C.c_double * 3),
+        ("nboxes", C.c_int32),
+        ("ncomp", C.c_int32),
+        ("lo", _P(C.c_int32)),
+        ("hi", _P(C.c_int32)),
+        ("owner", _P(C.c_int32)),
+        ("data", _P(C.c_void_p)),
+    ]
+
+
+class RefUnavailable(RuntimeError):
+    pass
+
+
+class Ref(_Base):
+    """The reference's own code (oracle/_ref)."""
+
+    def __init__(self):
+        if not REF_LIB.exists():
+            if REFERENCE_ROOT.exists():
+                build(ref=True)
+            else:
+                raise RefUnavailable(f"{REF_LIB} not built and {REFERENCE_ROOT} is absent")
+        self.lib = C.CDLL(str(REF_LIB))
+        self.lib.ref_last_error.restype = C.c_char_p
+
+    def _check(self, status):
+        if status != 0:
+            raise api.AmrvrError(status, self.lib.ref_last_error().decode())
+
+    def paint(self, cbox, transform, rmin, rmax, box_transparency, ref_dist, width, height,
+              camera, colormap=None):
+        out = np.zeros((height, width, 5), np.float32)
+        samples = C.c_longlong(0)
+        pts, n = self._cmap(colormap)
+        self._check(self.lib.ref_paint(
+            C.byref(cbox), C.byref(transform), C.c_float(rmin), C.c_float(rmax),
+            C.c_float(box_transparency), C.c_float(ref_dist), width, height, C.byref(camera),
+            pts, n, _fptr(out), C.byref(samples)))
+        return out, samples.value
+
+    def order(self, nranks, records, n, camera, aspect, use_graph=True):
+        out = np.zeros(nranks, np.int32)
+        log = C.create_string_buffer(1 << 16)
+        self._check(self.lib.ref_order(nranks, n, records, C.byref(camera), C.c_float(aspect),
+                                       int(use_graph), out.ctypes.data_as(_P(C.c_int)), log,
+                                       len(log)))
+        return out, log.value.decode()
+
+    def compose(self, nranks, width, height, layers, owners, hints, rank_order):
+        n = len(layers)
+        layers = [np.ascontiguousarray(l, np.float32) for l in layers]
+        ptrs = (_f32p * max(n, 1))(*[_fptr(l) for l in layers])
+        own = np.ascontiguousarray(owners, np.int32)
+        hin = np.ascontiguousarray(hints, np.float32)
+        ro = np.ascontiguousarray(rank_order, np.int32)
+        full = np.zeros((height, width, 5), np.float32)
+        piece_owner = np.full(height * width, -1, np.int32)
+        seconds = C.c_double(0)
+        self._check(self.lib.ref_compose(
+            nranks, width, height, n, own.ctypes.data_as(_P(C.c_int)), ptrs, _fptr(hin),
+            ro.ctypes.data_as(_P(C.c_int)), _fptr(full),
+            piece_owner.ctypes.data_as(_P(C.c_int)), C.byref(seconds)))
+        return full, piece_owner, seconds.value
+
+    def render_scene(self, scene, camera, params, out_path, colormap=None, pin_cores=False):
+        """Real VolumeRenderer::renderScene -> PPM at out_path (rank 0)."""
+        cboxes, n, _keep = scene.c_boxes()
+        owners = scene.owners()
+        samples = C.c_longlong(0)
+        wall = C.c_double(0)
+        log = C.create_string_buffer(1 << 16)
+        pts, npts = self._cmap(colormap)
+        self._check(self.lib.ref_render_scene(
+            scene.nranks, n, cboxes, owners.ctypes.data_as(_P(C.c_int32)),
+            C.byref(scene.transform), C.c_float(scene.scalar_range[0]),
+            C.c_float(scene.scalar_range[1]), 1, _d3(scene.bounds_min), _d3(scene.bounds_max),
+            C.byref(camera) if camera is not None else None, C.byref(params), pts, npts,
+            str(out_path).encode(), int(pin_cores), C.byref(samples), C.byref(wall), log,
+            len(log)))
+        return {"samples": samples.value, "wall_s": wall.value, "log": log.value.decode()}
+
+    @staticmethod
+    def stage_seconds(log: str) -> dict:
+        """Parse the three 'Render: <stage> took X s' lines (VolumeRenderer.cpp:1121-1136)."""
+        import re
+
+        out = {}
+        for label, key in (("per-box rendering", "march_s"),
+                           ("visibility graph computation", "order_s"),
+                           ("compositing", "composite_s")):
+            m = re.search(rf"Render: {label} took ([0-9.eE+-]+) s", log)
+            if m:
+                out[key] = float(m.group(1))
+        return out
+
+
+def read_ppm(path) -> np.ndarray:
+    """P6 reader for the files SavePPM writes (top row first)."""
+    raw = Path(path).read_bytes()
+    parts = raw.split(b"\n", 3)
+    assert parts[0] == b"P6", parts[0]
+    w, h = [int(x) for x in parts[1].split()]
+    assert parts[2] == b"255"
+    return np.frombuffer(parts[3], np.uint8, count=w * h * 3).reshape(h, w, 3).copy()
