@@ -1,0 +1,1344 @@
+// api.cu -- the C ABI of libamrvr_b200.so (include/amrvr.h): contexts, scene
+// upload, ray-march, ordering, sort-last composite, post-processing.  No CPU
+// fallback: compute entry points need an sm_100 device.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#include "internal.hpp"
+#include "nccl_dyn.hpp"
+
+using namespace amrvr;
+
+// ---------------------------------------------------------------------------
+// objects
+// ---------------------------------------------------------------------------
+
+struct DeviceBuffer {  // grow-only device allocation
+  void* ptr = nullptr;
+  size_t bytes = 0;
+  cudaError_t reserve(size_t want) {
+    if (want <= bytes) return cudaSuccess;
+    if (ptr != nullptr) {
+      cudaError_t e = cudaFree(ptr);
+      ptr = nullptr;
+      bytes = 0;
+      if (e != cudaSuccess) return e;
+    }
+    const size_t rounded = (want + (1u << 20) - 1) & ~static_cast<size_t>((1u << 20) - 1);
+    cudaError_t e = cudaMalloc(&ptr, rounded);
+    if (e == cudaSuccess) bytes = rounded;
+    return e;
+  }
+  void release() {
+    if (ptr != nullptr) cudaFree(ptr);
+    ptr = nullptr;
+    bytes = 0;
+  }
+  template <class T>
+  T* as() const {
+    return static_cast<T*>(ptr);
+  }
+};
+
+struct amrvr_ctx {
+  int device = 0, rank = 0, nranks = 1;
+  cudaStream_t stream = nullptr;
+  int64_t launches = 0;
+  std::string error;
+  ncclComm_t comm = nullptr;
+  cudaEvent_t ev[8] = {};
+  // per-frame parameter blocks and scratch
+  DeviceBuffer stage;        // FAB doubles waiting for quantisation
+  DeviceBuffer march_boxes;  // MarchBox[]
+  DeviceBuffer tables;       // float[ntables*1024]
+  DeviceBuffer counter;      // sample counter + misc small results
+  DeviceBuffer fold_layers;  // FoldLayer[]
+  DeviceBuffer copy_jobs;    // CopyJob[]
+  DeviceBuffer send_buf, recv_buf;
+  DeviceBuffer piece;        // composited piece (5 floats / pixel)
+  DeviceBuffer full, small, rgb8;  // gathered frame, downsampled frame, bytes
+  DeviceBuffer order_boxes, order_scratch_a, order_scratch_b, order_priority, order_edges;
+  DeviceBuffer stats_partials;
+  std::vector<DeviceBuffer> layer_pools;  // recycled layer pools
+};
+
+struct LocalBox {
+  double min_corner[3], max_corner[3];
+  int32_t dims[3];
+  uint64_t brick_off;
+};
+
+struct amrvr_scene {
+  std::vector<amrvr_box_record> global;
+  std::vector<LocalBox> local;
+  int first_global = 0;  // global index of local box 0
+  DeviceBuffer bricks;
+  float range_min = 0.f, range_max = 1.f;
+};
+
+struct amrvr_layers {
+  int width = 0, height = 0;
+  amrvr_camera camera{};
+  std::vector<Rect> rects;
+  std::vector<uint64_t> offs;  // float offsets into pool
+  DeviceBuffer pool;
+  uint64_t pool_floats = 0;
+  bool counted = false;
+  cudaEvent_t t0 = nullptr, t1 = nullptr;
+  amrvr_march_stats stats{};
+  bool stats_ready = false;
+};
+
+namespace {
+
+thread_local std::string g_error = "";
+
+int fail(amrvr_ctx* ctx, int status, const std::string& msg) {
+  if (ctx != nullptr) ctx->error = msg;
+  g_error = msg;
+  return status;
+}
+
+#define CUDA_TRY(ctx, expr)                                                              \
+  do {                                                                                   \
+    const cudaError_t err__ = (expr);                                                    \
+    if (err__ != cudaSuccess)                                                            \
+      return fail(ctx, AMRVR_ERR_CUDA,                                                   \
+                  std::string(#expr) + ": " + cudaGetErrorString(err__));                \
+  } while (0)
+
+#define LAUNCH_TRY(ctx, expr)                                                            \
+  do {                                                                                   \
+    const int err__ = (expr);                                                            \
+    if (err__ != 0)                                                                      \
+      return fail(ctx, AMRVR_ERR_CUDA,                                                   \
+                  std::string(#expr) + ": " +                                            \
+                      cudaGetErrorString(static_cast<cudaError_t>(err__)));              \
+  } while (0)
+
+#define NCCL_TRY(ctx, expr)                                                              \
+  do {                                                                                   \
+    const ncclResult_t err__ = (expr);                                                   \
+    if (err__ != ncclSuccess)                                                            \
+      return fail(ctx, AMRVR_ERR_NCCL,                                                   \
+                  std::string(#expr) + ": " + nccl_api().GetErrorString(err__));         \
+  } while (0)
+
+#define REQUIRE(ctx, cond, msg) \
+  do {                          \
+    if (!(cond)) return fail(ctx, AMRVR_ERR_INVALID, msg); \
+  } while (0)
+
+bool is_pow2_float(float v) {
+  if (!(v > 0.0f) || !std::isfinite(v)) return false;
+  int e;
+  return std::frexp(v, &e) == 0.5f;
+}
+
+struct DeviceOrderBackend final : OrderBackend {
+  amrvr_ctx* ctx;
+  int status = 0;
+  int nranks;
+  explicit DeviceOrderBackend(amrvr_ctx* c) : ctx(c), nranks(c->nranks) {}
+
+  int upload(const std::vector<OrderBox>& boxes) {
+    const size_t n = boxes.size();
+    if (ctx->order_boxes.reserve(n * sizeof(OrderBox)) != cudaSuccess) return AMRVR_ERR_CUDA;
+    if (cudaMemcpyAsync(ctx->order_boxes.ptr, boxes.data(), n * sizeof(OrderBox),
+                        cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess)
+      return AMRVR_ERR_CUDA;
+    return 0;
+  }
+  void rank_boxes(const std::vector<OrderBox>& boxes, std::vector<int32_t>& priority) override {
+    const int n = static_cast<int>(boxes.size());
+    priority.assign(n, 0);
+    if (status != 0 || n == 0) return;
+    // the boxes were uploaded by pair_edges() of the same round
+    if (ctx->order_scratch_a.reserve(static_cast<size_t>(n) * 16) != cudaSuccess ||
+        ctx->order_scratch_b.reserve(static_cast<size_t>(n) * 16) != cudaSuccess ||
+        ctx->order_priority.reserve(static_cast<size_t>(n) * 4) != cudaSuccess) {
+      status = AMRVR_ERR_CUDA;
+      return;
+    }
+    int max_owner = 0;
+    for (const OrderBox& b : boxes) max_owner = std::max(max_owner, b.owner);
+    int owner_bits = 0;
+    while ((1 << owner_bits) <= max_owner) ++owner_bits;
+    if (launch_order_rank(ctx->order_boxes.as<OrderBox>(), n, ctx->order_scratch_a.ptr,
+                          ctx->order_scratch_b.ptr, owner_bits, ctx->order_priority.as<int32_t>(),
+                          ctx->stream, &ctx->launches) != 0 ||
+        cudaMemcpyAsync(priority.data(), ctx->order_priority.ptr, static_cast<size_t>(n) * 4,
+                        cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+        cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+      status = AMRVR_ERR_CUDA;
+  }
+  void pair_edges(const std::vector<OrderBox>& boxes, const float* dir,
+                  std::vector<OrderEdge>& edges) override {
+    edges.clear();
+    const int n = static_cast<int>(boxes.size());
+    if (status != 0 || n == 0) return;
+    if ((status = upload(boxes)) != 0) return;
+    int capacity = 16 * n + 64;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+      if (ctx->order_edges.reserve(static_cast<size_t>(capacity) * sizeof(OrderEdge) + 16) !=
+          cudaSuccess) {
+        status = AMRVR_ERR_CUDA;
+        return;
+      }
+      // count lives in the first 16 bytes
+      int32_t* count_dev = ctx->order_edges.as<int32_t>();
+      OrderEdge* edges_dev = reinterpret_cast<OrderEdge*>(ctx->order_edges.as<char>() + 16);
+      int count = 0;
+      if (cudaMemsetAsync(count_dev, 0, 16, ctx->stream) != cudaSuccess ||
+          launch_order_pairs(ctx->order_boxes.as<OrderBox>(), n, dir[0], dir[1], dir[2], edges_dev,
+                             capacity, count_dev, ctx->stream, &ctx->launches) != 0 ||
+          cudaMemcpyAsync(&count, count_dev, 4, cudaMemcpyDeviceToHost, ctx->stream) !=
+              cudaSuccess ||
+          cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+        status = AMRVR_ERR_CUDA;
+        return;
+      }
+      if (count <= capacity) {
+        edges.resize(static_cast<size_t>(count));
+        if (count > 0 &&
+            cudaMemcpy(edges.data(), edges_dev, static_cast<size_t>(count) * sizeof(OrderEdge),
+                       cudaMemcpyDeviceToHost) != cudaSuccess)
+          status = AMRVR_ERR_CUDA;
+        return;
+      }
+      capacity = count;  // rare: dense contact graph; retry once with room
+    }
+    status = AMRVR_ERR_RUNTIME;
+  }
+};
+
+// Everything the composite needs to know about the frame, identical on every
+// rank: blend order, run ids, footprints, pieces.
+struct FramePlan {
+  std::vector<int> order;       // blend position -> global box
+  std::vector<int> run_of;      // global box -> run id
+  std::vector<Rect> rects;      // global box -> footprint
+  std::vector<int> piece_of_rank, begin, end;  // per rank: piece index, pixel range
+};
+
+void make_frame_plan(const amrvr_scene& scene, const amrvr_camera& cam, int width, int height,
+                     int nranks, const int* rank_order, FramePlan& plan) {
+  const int n = static_cast<int>(scene.global.size());
+  plan.order.assign(n, 0);
+  layer_order(n, scene.global.data(), cam, nullptr, plan.order.data());
+  plan.run_of.assign(n, 0);
+  int run = -1, prev_owner = -1;
+  for (int pos = 0; pos < n; ++pos) {  // DirectSendBase.cpp:400-407
+    const int g = plan.order[pos];
+    if (pos == 0 || scene.global[g].owner != prev_owner) ++run;
+    prev_owner = scene.global[g].owner;
+    plan.run_of[g] = run;
+  }
+  CameraBasis basis;
+  make_camera_basis(cam, basis);
+  plan.rects.resize(n);
+  for (int g = 0; g < n; ++g)
+    plan.rects[g] = box_footprint(scene.global[g].min_corner, scene.global[g].max_corner,
+                                  scene.global[g].dims, basis, cam, width, height);
+  plan.piece_of_rank.assign(nranks, 0);
+  plan.begin.assign(nranks, 0);
+  plan.end.assign(nranks, 0);
+  for (int piece = 0; piece < nranks; ++piece) {
+    const int r = rank_order[piece];
+    plan.piece_of_rank[r] = piece;
+    piece_range(width * height, piece, nranks, &plan.begin[r], &plan.end[r]);
+  }
+}
+
+// rows [s0,s1) of rect r needed by the pixel range [begin,end) of a W-wide frame
+bool slice_rows(const Rect& r, int begin, int end, int width, int* s0, int* s1) {
+  if (end <= begin || r.w <= 0 || r.h <= 0) return false;
+  const int yb = begin / width, ye = (end - 1) / width;
+  *s0 = std::max(r.y0, yb);
+  *s1 = std::min(r.y0 + r.h, ye + 1);
+  return *s1 > *s0;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------
+
+extern "C" int amrvr_abi_version(void) { return AMRVR_ABI_VERSION; }
+
+extern "C" int amrvr_nccl_unique_id(void* id_out) {
+  if (id_out == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "id_out is NULL");
+  static_assert(sizeof(ncclUniqueId) == AMRVR_NCCL_ID_BYTES, "NCCL id size");
+  const std::string why = nccl_api().load();
+  if (!why.empty()) return fail(nullptr, AMRVR_ERR_NCCL, why);
+  ncclUniqueId id;
+  NCCL_TRY(nullptr, nccl_api().GetUniqueId(&id));
+  std::memcpy(id_out, &id, sizeof(id));
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const void* nccl_unique_id,
+                                amrvr_ctx** out) {
+  if (out == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "out is NULL");
+  *out = nullptr;
+  if (nranks < 1 || rank < 0 || rank >= nranks)
+    return fail(nullptr, AMRVR_ERR_INVALID, "rank/nranks out of range");
+  if (nranks > 1 && nccl_unique_id == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "nccl_unique_id required when nranks > 1");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+    (void)cudaGetLastError();
+    return fail(nullptr, AMRVR_ERR_CUDA,
+                "no CUDA device visible: libamrvr_b200 has no CPU fallback");
+  }
+  if (cuda_device < 0 || cuda_device >= ndev)
+    return fail(nullptr, AMRVR_ERR_INVALID, "cuda_device out of range");
+  cudaDeviceProp prop;
+  CUDA_TRY(nullptr, cudaGetDeviceProperties(&prop, cuda_device));
+  if (prop.major != 10)
+    return fail(nullptr, AMRVR_ERR_CUDA,
+                std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                    std::to_string(prop.minor) + "; this library carries sm_100a code only");
+  CUDA_TRY(nullptr, cudaSetDevice(cuda_device));
+  std::unique_ptr<amrvr_ctx> ctx(new amrvr_ctx);
+  ctx->device = cuda_device;
+  ctx->rank = rank;
+  ctx->nranks = nranks;
+  CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  for (auto& e : ctx->ev) CUDA_TRY(nullptr, cudaEventCreate(&e));
+  CUDA_TRY(nullptr, ctx->counter.reserve(256));
+  if (nranks > 1) {
+    const std::string why = nccl_api().load();
+    if (!why.empty()) return fail(nullptr, AMRVR_ERR_NCCL, why);
+    ncclUniqueId id;
+    std::memcpy(&id, nccl_unique_id, sizeof(id));
+    NCCL_TRY(nullptr, nccl_api().CommInitRank(&ctx->comm, nranks, id, rank));
+  }
+  *out = ctx.release();
+  return AMRVR_OK;
+}
+
+extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
+  if (ctx == nullptr) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->comm != nullptr) nccl_api().CommDestroy(ctx->comm);
+  for (DeviceBuffer* b :
+       {&ctx->stage, &ctx->march_boxes, &ctx->tables, &ctx->counter, &ctx->fold_layers,
+        &ctx->copy_jobs, &ctx->send_buf, &ctx->recv_buf, &ctx->piece, &ctx->full, &ctx->small,
+        &ctx->rgb8, &ctx->order_boxes, &ctx->order_scratch_a, &ctx->order_scratch_b,
+        &ctx->order_priority, &ctx->order_edges, &ctx->stats_partials})
+    b->release();
+  for (auto& p : ctx->layer_pools) p.release();
+  for (auto& e : ctx->ev)
+    if (e != nullptr) cudaEventDestroy(e);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+extern "C" const char* amrvr_last_error(const amrvr_ctx* ctx) {
+  return (ctx != nullptr) ? ctx->error.c_str() : g_error.c_str();
+}
+extern "C" void* amrvr_ctx_stream(amrvr_ctx* ctx) { return ctx ? ctx->stream : nullptr; }
+extern "C" int64_t amrvr_ctx_kernel_launches(const amrvr_ctx* ctx) {
+  return ctx ? ctx->launches : 0;
+}
+
+// ---------------------------------------------------------------------------
+// scene
+// ---------------------------------------------------------------------------
+namespace {
+
+struct StagedBox {
+  const double* dev;  // device-visible pointer to the first valid cell
+  int64_t jstride, kstride;
+};
+
+// Make the valid region of every box device-visible.  Host FABs are copied
+// into ctx->stage (compacted, no ghost cells); device FABs are used in place.
+int stage_boxes(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes, std::vector<StagedBox>& out) {
+  out.resize(static_cast<size_t>(std::max(nboxes, 0)));
+  size_t need = 0;
+  std::vector<char> on_device(out.size(), 0);
+  for (int b = 0; b < nboxes; ++b) {
+    const amrvr_box& B = boxes[b];
+    const size_t cells = static_cast<size_t>(std::max(B.dims[0], 0)) * std::max(B.dims[1], 0) *
+                         std::max(B.dims[2], 0);
+    if (cells == 0) continue;
+    REQUIRE(ctx, B.data != nullptr, "box data pointer is NULL");
+    cudaPointerAttributes attr;
+    const cudaError_t e = cudaPointerGetAttributes(&attr, B.data);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    on_device[b] =
+        (e == cudaSuccess && (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged));
+    if (!on_device[b]) need += (cells * sizeof(double) + 255) & ~static_cast<size_t>(255);
+  }
+  CUDA_TRY(ctx, ctx->stage.reserve(need));
+  size_t cursor = 0;
+  for (int b = 0; b < nboxes; ++b) {
+    const amrvr_box& B = boxes[b];
+    const int nx = B.dims[0], ny = B.dims[1], nz = B.dims[2];
+    const size_t cells = static_cast<size_t>(std::max(nx, 0)) * std::max(ny, 0) * std::max(nz, 0);
+    if (cells == 0) {
+      out[b] = StagedBox{nullptr, 0, 0};
+      continue;
+    }
+    const double* first = B.data + (B.lo[0] - B.begin[0]) + (B.lo[1] - B.begin[1]) * B.jstride +
+                          (B.lo[2] - B.begin[2]) * B.kstride + B.component * B.nstride;
+    if (on_device[b]) {
+      out[b] = StagedBox{first, B.jstride, B.kstride};
+      continue;
+    }
+    double* dst = reinterpret_cast<double*>(ctx->stage.as<char>() + cursor);
+    cursor += (cells * sizeof(double) + 255) & ~static_cast<size_t>(255);
+    if (B.jstride == nx && B.kstride == static_cast<int64_t>(nx) * ny) {
+      CUDA_TRY(ctx, cudaMemcpyAsync(dst, first, cells * sizeof(double), cudaMemcpyHostToDevice,
+                                    ctx->stream));
+    } else {
+      for (int k = 0; k < nz; ++k)  // one pitched copy per k-slab
+        CUDA_TRY(ctx, cudaMemcpy2DAsync(dst + static_cast<size_t>(k) * nx * ny, nx * sizeof(double),
+                                        first + k * B.kstride, B.jstride * sizeof(double),
+                                        nx * sizeof(double), ny, cudaMemcpyHostToDevice,
+                                        ctx->stream));
+    }
+    out[b] = StagedBox{dst, nx, static_cast<int64_t>(nx) * ny};
+  }
+  return AMRVR_OK;
+}
+
+}  // namespace
+
+extern "C" int amrvr_brick_stats(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                                 double* min_value, double* max_value, double* min_positive,
+                                 int64_t* finite_count) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, nboxes >= 0 && (nboxes == 0 || boxes != nullptr), "bad box list");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  std::vector<StagedBox> staged;
+  const int st = stage_boxes(ctx, nboxes, boxes, staged);
+  if (st != AMRVR_OK) return st;
+  const int blocks_per_box = 148 * 2;
+  CUDA_TRY(ctx, ctx->stats_partials.reserve(
+                    (static_cast<size_t>(std::max(nboxes, 1)) * blocks_per_box + 1) * 32));
+  double* partials = ctx->stats_partials.as<double>();
+  int nparts = 0;
+  for (int b = 0; b < nboxes; ++b) {
+    const amrvr_box& B = boxes[b];
+    const long long cells = 1LL * B.dims[0] * B.dims[1] * B.dims[2];
+    if (staged[b].dev == nullptr || cells <= 0) continue;
+    const int blocks = static_cast<int>(std::min<long long>(blocks_per_box, (cells + 255) / 256));
+    LAUNCH_TRY(ctx, launch_brick_stats(staged[b].dev, staged[b].jstride, staged[b].kstride,
+                                       B.dims[0], B.dims[1], B.dims[2], partials + 4 * nparts,
+                                       blocks, ctx->stream, &ctx->launches));
+    nparts += blocks;
+  }
+  double* out4 = partials + 4 * static_cast<size_t>(std::max(nboxes, 1)) * blocks_per_box;
+  LAUNCH_TRY(ctx, launch_brick_stats_final(partials, nparts, out4, ctx->stream, &ctx->launches));
+  double host4[4];
+  CUDA_TRY(ctx, cudaMemcpyAsync(host4, out4, sizeof(host4), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (min_value) *min_value = host4[0];
+  if (max_value) *max_value = host4[1];
+  if (min_positive) *min_positive = host4[2];
+  if (finite_count) std::memcpy(finite_count, &host4[3], 8);
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                                  const amrvr_scalar_transform* transform, float range_min,
+                                  float range_max, amrvr_scene** out) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, out != nullptr, "out is NULL");
+  *out = nullptr;
+  REQUIRE(ctx, nboxes >= 0 && (nboxes == 0 || boxes != nullptr), "bad box list");
+  REQUIRE(ctx, transform != nullptr, "transform is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  std::unique_ptr<amrvr_scene> scene(new amrvr_scene);
+  scene->range_min = range_min;
+  scene->range_max = range_max;
+  scene->local.resize(static_cast<size_t>(nboxes));
+  size_t brick_bytes = 0;
+  for (int b = 0; b < nboxes; ++b) {
+    LocalBox& L = scene->local[b];
+    for (int d = 0; d < 3; ++d) {
+      L.min_corner[d] = boxes[b].min_corner[d];
+      L.max_corner[d] = boxes[b].max_corner[d];
+      L.dims[d] = boxes[b].dims[d];
+    }
+    L.brick_off = brick_bytes;
+    const size_t cells = static_cast<size_t>(std::max(L.dims[0], 0)) * std::max(L.dims[1], 0) *
+                         std::max(L.dims[2], 0);
+    brick_bytes += (cells + 255) & ~static_cast<size_t>(255);
+  }
+  CUDA_TRY(ctx, scene->bricks.reserve(std::max<size_t>(brick_bytes, 256)));
+  std::vector<StagedBox> staged;
+  int st = stage_boxes(ctx, nboxes, boxes, staged);
+  if (st != AMRVR_OK) {
+    scene->bricks.release();
+    return st;
+  }
+  for (int b = 0; b < nboxes; ++b) {
+    if (staged[b].dev == nullptr) continue;
+    const int err = launch_brick_quantise(
+        staged[b].dev, staged[b].jstride, staged[b].kstride, boxes[b].dims[0], boxes[b].dims[1],
+        boxes[b].dims[2], *transform, range_min, range_max,
+        scene->bricks.as<uint8_t>() + scene->local[b].brick_off, ctx->stream, &ctx->launches);
+    if (err != 0) {
+      scene->bricks.release();
+      return fail(ctx, AMRVR_ERR_CUDA, cudaGetErrorString(static_cast<cudaError_t>(err)));
+    }
+  }
+
+  // global table: every rank's records, owner-major (VisibilityOrdering.cpp:85-152)
+  std::vector<amrvr_box_record> mine(static_cast<size_t>(nboxes));
+  for (int b = 0; b < nboxes; ++b) {
+    std::memset(&mine[b], 0, sizeof(amrvr_box_record));
+    for (int d = 0; d < 3; ++d) {
+      mine[b].min_corner[d] = boxes[b].min_corner[d];
+      mine[b].max_corner[d] = boxes[b].max_corner[d];
+      mine[b].dims[d] = boxes[b].dims[d];
+    }
+    mine[b].owner = ctx->rank;
+    mine[b].local_index = b;
+  }
+  if (ctx->nranks == 1) {
+    scene->global = mine;
+    scene->first_global = 0;
+  } else {
+    NcclApi& nc = nccl_api();
+    const int P = ctx->nranks;
+    DeviceBuffer tmp;
+    CUDA_TRY(ctx, tmp.reserve(static_cast<size_t>(P + 1) * sizeof(int)));
+    int* counts_dev = tmp.as<int>();
+    CUDA_TRY(ctx, cudaMemcpyAsync(counts_dev + P, &nboxes, sizeof(int), cudaMemcpyHostToDevice,
+                                  ctx->stream));
+    NCCL_TRY(ctx, nc.AllGather(counts_dev + P, counts_dev, sizeof(int), ncclChar, ctx->comm,
+                               ctx->stream));
+    std::vector<int> counts(static_cast<size_t>(P));
+    CUDA_TRY(ctx, cudaMemcpyAsync(counts.data(), counts_dev, sizeof(int) * P,
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    const int most = *std::max_element(counts.begin(), counts.end());
+    const size_t slot = static_cast<size_t>(std::max(most, 1)) * sizeof(amrvr_box_record);
+    DeviceBuffer table;
+    CUDA_TRY(ctx, table.reserve(slot * (P + 1)));
+    char* send = table.as<char>() + slot * P;
+    if (nboxes > 0)
+      CUDA_TRY(ctx, cudaMemcpyAsync(send, mine.data(), sizeof(amrvr_box_record) * nboxes,
+                                    cudaMemcpyHostToDevice, ctx->stream));
+    NCCL_TRY(ctx, nc.AllGather(send, table.ptr, slot, ncclChar, ctx->comm, ctx->stream));
+    std::vector<char> all(slot * P);
+    CUDA_TRY(ctx, cudaMemcpyAsync(all.data(), table.ptr, all.size(), cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < P; ++r) {
+      if (r == ctx->rank) scene->first_global = static_cast<int>(scene->global.size());
+      const amrvr_box_record* recs = reinterpret_cast<const amrvr_box_record*>(all.data() + slot * r);
+      scene->global.insert(scene->global.end(), recs, recs + counts[r]);
+    }
+    tmp.release();
+    table.release();
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // host FABs may be reused on return
+  *out = scene.release();
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene) {
+  if (scene == nullptr) return AMRVR_OK;
+  if (ctx != nullptr) {
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+  }
+  scene->bricks.release();
+  delete scene;
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_scene_global_boxes(const amrvr_scene* scene, int* nglobal,
+                                        const amrvr_box_record** records) {
+  if (scene == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "scene is NULL");
+  if (nglobal) *nglobal = static_cast<int>(scene->global.size());
+  if (records) *records = scene->global.data();
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_scene_read_brick(amrvr_ctx* ctx, const amrvr_scene* scene, int local_box,
+                                      uint8_t* dst) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, scene != nullptr && dst != nullptr, "NULL argument");
+  REQUIRE(ctx, local_box >= 0 && local_box < static_cast<int>(scene->local.size()),
+          "local_box out of range");
+  const LocalBox& L = scene->local[local_box];
+  const size_t cells = static_cast<size_t>(std::max(L.dims[0], 0)) * std::max(L.dims[1], 0) *
+                       std::max(L.dims[2], 0);
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst, scene->bricks.as<uint8_t>() + L.brick_off, cells,
+                                cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return AMRVR_OK;
+}
+
+// ---------------------------------------------------------------------------
+// ordering
+// ---------------------------------------------------------------------------
+
+extern "C" int amrvr_order_boxes(amrvr_ctx* ctx, const amrvr_scene* scene,
+                                 const amrvr_camera* camera, float aspect, int use_graph,
+                                 int* rank_order, int* graph_failed) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, scene != nullptr && camera != nullptr && rank_order != nullptr, "NULL argument");
+  return amrvr_order_records(ctx, ctx->nranks, static_cast<int>(scene->global.size()),
+                             scene->global.data(), camera, aspect, use_graph, rank_order,
+                             graph_failed);
+}
+
+extern "C" int amrvr_order_records(amrvr_ctx* ctx, int nranks, int nglobal,
+                                   const amrvr_box_record* records, const amrvr_camera* camera,
+                                   float aspect, int use_graph, int* rank_order,
+                                   int* graph_failed) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, nranks >= 1 && nglobal >= 0 && (nglobal == 0 || records != nullptr) &&
+                   camera != nullptr && rank_order != nullptr,
+          "bad argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  DeviceOrderBackend backend(ctx);
+  const bool ok = order_ranks(nranks, nglobal, records, *camera, aspect, use_graph != 0, backend,
+                              rank_order);
+  if (backend.status != 0) return fail(ctx, backend.status, "device ordering failed");
+  if (graph_failed) *graph_failed = ok ? 0 : 1;
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_order_boxes_host(int nranks, int nglobal, const amrvr_box_record* records,
+                                      const amrvr_camera* camera, float aspect, int use_graph,
+                                      int* rank_order, int* graph_failed) {
+  if (nranks < 1 || nglobal < 0 || (nglobal > 0 && records == nullptr) || camera == nullptr ||
+      rank_order == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "bad argument");
+  const bool ok = order_ranks(nranks, nglobal, records, *camera, aspect, use_graph != 0,
+                              *host_order_backend(), rank_order);
+  if (graph_failed) *graph_failed = ok ? 0 : 1;
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_layer_order_host(int nglobal, const amrvr_box_record* records,
+                                      const amrvr_camera* camera, float* depth_hints, int* order) {
+  if (nglobal < 0 || (nglobal > 0 && (records == nullptr || order == nullptr)) || camera == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "bad argument");
+  layer_order(nglobal, records, *camera, depth_hints, order);
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_piece_range(int num_pixels, int piece, int num_pieces, int* begin, int* end) {
+  if (num_pieces < 1 || piece < 0 || piece >= num_pieces || begin == nullptr || end == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "bad argument");
+  piece_range(num_pixels, piece, num_pieces, begin, end);
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_reference_sample_distance(int nglobal, const amrvr_box_record* records,
+                                               const double bounds_min[3],
+                                               const double bounds_max[3], float* out) {
+  if (nglobal < 0 || (nglobal > 0 && records == nullptr) || bounds_min == nullptr ||
+      bounds_max == nullptr || out == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "bad argument");
+  *out = reference_sample_distance(nglobal, records, bounds_min, bounds_max);
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_color_table(float alpha_scale, float normalization_factor, float range_min,
+                                 float range_max, const amrvr_colormap_pt* pts, int npts,
+                                 float* table_rgba) {
+  if (table_rgba == nullptr || npts < 0 || (npts > 0 && pts == nullptr))
+    return fail(nullptr, AMRVR_ERR_INVALID, "bad argument");
+  build_color_table(alpha_scale, normalization_factor, range_min, range_max, pts, npts, table_rgba);
+  return AMRVR_OK;
+}
+
+// ---------------------------------------------------------------------------
+// ray-march
+// ---------------------------------------------------------------------------
+
+extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
+                              int width, int height, float box_transparency,
+                              float reference_sample_distance_, const amrvr_colormap_pt* pts,
+                              int npts, int count_samples, amrvr_layers** out) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, out != nullptr, "out is NULL");
+  *out = nullptr;
+  REQUIRE(ctx, scene != nullptr && camera != nullptr, "NULL argument");
+  REQUIRE(ctx, width > 0 && height > 0, "width and height must be positive");
+  REQUIRE(ctx, npts >= 0 && (npts == 0 || pts != nullptr), "bad colour map");
+  REQUIRE(ctx, static_cast<int64_t>(width) * height < (1LL << 31), "frame too large");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+
+  const int n = static_cast<int>(scene->local.size());
+  std::unique_ptr<amrvr_layers> L(new amrvr_layers);
+  L->width = width;
+  L->height = height;
+  L->camera = *camera;
+  L->rects.resize(n);
+  L->offs.resize(n);
+  L->counted = count_samples != 0;
+
+  CameraBasis basis;
+  make_camera_basis(*camera, basis);
+  MarchFrame frame{};
+  for (int d = 0; d < 3; ++d) {
+    frame.eye[d] = basis.eye[d];
+    frame.fwd[d] = basis.fwd[d];
+    frame.right[d] = basis.right[d];
+    frame.up[d] = basis.up[d];
+  }
+  frame.aspect = static_cast<float>(width) / static_cast<float>(std::max(height, 1));
+  frame.tan_half = std::tan(camera->fov_y_degrees * 0.5f * 3.14159265358979323846f / 180.0f);
+  frame.inv_w = 1.0f / static_cast<float>(width);
+  frame.inv_h = 1.0f / static_cast<float>(height);
+  frame.width = width;
+  frame.height = height;
+  frame.nboxes = n;
+
+  const float alpha_scale = std::min(std::max(1.0f - box_transparency, 0.0f), 1.0f);
+  std::vector<MarchBox> mb(static_cast<size_t>(n));
+  std::vector<float> table_norm;  // one table per distinct normalisation factor
+  std::vector<float> tables;
+  uint64_t floats = 0;
+  int tiles = 0;
+  int64_t rays = 0;
+  for (int b = 0; b < n; ++b) {
+    const LocalBox& B = scene->local[b];
+    MarchBox& M = mb[b];
+    std::memset(&M, 0, sizeof(M));
+    float step, norm;
+    box_sampling(B.min_corner, B.max_corner, B.dims, reference_sample_distance_, &step, &norm);
+    int which = -1;
+    for (size_t t = 0; t < table_norm.size(); ++t)
+      if (std::memcmp(&table_norm[t], &norm, sizeof(float)) == 0) which = static_cast<int>(t);
+    if (which < 0) {
+      which = static_cast<int>(table_norm.size());
+      table_norm.push_back(norm);
+      tables.resize(tables.size() + 4 * AMRVR_COLOR_TABLE_SIZE);
+      build_color_table(alpha_scale, norm, scene->range_min, scene->range_max, pts, npts,
+                        tables.data() + static_cast<size_t>(which) * 4 * AMRVR_COLOR_TABLE_SIZE);
+    }
+    M.table = which;
+    M.step = step;
+    float diag2 = 0.0f;
+    bool pow2 = true;
+    for (int d = 0; d < 3; ++d) {
+      M.lo[d] = static_cast<float>(B.min_corner[d]);
+      M.hi[d] = static_cast<float>(B.max_corner[d]);
+      M.n[d] = B.dims[d];
+      M.cell[d] = (M.hi[d] - M.lo[d]) / static_cast<float>(B.dims[d]);  // VolumePainter.cpp:676-678
+      pow2 = pow2 && is_pow2_float(M.cell[d]);
+      M.inv_cell[d] = 1.0f / M.cell[d];
+    }
+    {  // :680-683 extent, float, x then y then z
+      const float ex = M.hi[0] - M.lo[0], ey = M.hi[1] - M.lo[1], ez = M.hi[2] - M.lo[2];
+      diag2 = ex * ex + ey * ey + ez * ez;
+    }
+    M.eps = std::sqrt(diag2) * 0.0001f;
+    M.exact_recip = pow2 ? 1 : 0;
+    const Rect r = box_footprint(B.min_corner, B.max_corner, B.dims, basis, *camera, width, height);
+    L->rects[b] = r;
+    M.rx0 = r.x0;
+    M.ry0 = r.y0;
+    M.rw = r.w;
+    M.rh = r.h;
+    M.tiles_x = (r.w + 15) / 16;
+    M.tile_base = tiles;
+    tiles += M.tiles_x * ((r.h + 15) / 16);
+    M.brick_off = B.brick_off;
+    M.layer_off = floats;
+    L->offs[b] = floats;
+    floats += static_cast<uint64_t>(r.w) * r.h * 5;
+    rays += static_cast<int64_t>(r.w) * r.h;
+  }
+  frame.ntiles = tiles;
+  L->pool_floats = floats;
+  L->stats.rays = rays;
+  L->stats.fragment_pixels = rays;
+
+  // layer pool: reuse a recycled one when it is large enough
+  const size_t need = std::max<size_t>(floats * sizeof(float), 256);
+  for (size_t i = 0; i < ctx->layer_pools.size(); ++i)
+    if (ctx->layer_pools[i].bytes >= need) {
+      L->pool = ctx->layer_pools[i];
+      ctx->layer_pools.erase(ctx->layer_pools.begin() + static_cast<long>(i));
+      break;
+    }
+  if (L->pool.ptr == nullptr) CUDA_TRY(ctx, L->pool.reserve(need));
+
+  if (n > 0) {
+    CUDA_TRY(ctx, ctx->march_boxes.reserve(mb.size() * sizeof(MarchBox)));
+    CUDA_TRY(ctx, ctx->tables.reserve(tables.size() * sizeof(float)));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->march_boxes.ptr, mb.data(), mb.size() * sizeof(MarchBox),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->tables.ptr, tables.data(), tables.size() * sizeof(float),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+  }
+  CUDA_TRY(ctx, cudaEventCreate(&L->t0));
+  CUDA_TRY(ctx, cudaEventCreate(&L->t1));
+  unsigned long long* counter = ctx->counter.as<unsigned long long>();
+  if (count_samples) CUDA_TRY(ctx, cudaMemsetAsync(counter, 0, 8, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(L->t0, ctx->stream));
+  if (n > 0)
+    LAUNCH_TRY(ctx, launch_raymarch(frame, ctx->march_boxes.as<MarchBox>(),
+                                    scene->bricks.as<uint8_t>(), ctx->tables.as<float>(),
+                                    L->pool.as<float>(), counter, count_samples != 0, ctx->stream,
+                                    &ctx->launches));
+  CUDA_TRY(ctx, cudaEventRecord(L->t1, ctx->stream));
+  if (count_samples) {
+    unsigned long long host = 0;
+    CUDA_TRY(ctx, cudaMemcpyAsync(&host, counter, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    L->stats.samples = static_cast<int64_t>(host);
+  }
+  *out = L.release();
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_layers_free(amrvr_ctx* ctx, amrvr_layers* layers) {
+  if (layers == nullptr) return AMRVR_OK;
+  if (ctx != nullptr) {
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (layers->pool.ptr != nullptr && ctx->layer_pools.size() < 4) {
+      ctx->layer_pools.push_back(layers->pool);
+      layers->pool = DeviceBuffer{};
+    }
+  }
+  layers->pool.release();
+  if (layers->t0) cudaEventDestroy(layers->t0);
+  if (layers->t1) cudaEventDestroy(layers->t1);
+  delete layers;
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_layers_count(const amrvr_layers* layers) {
+  return layers ? static_cast<int>(layers->rects.size()) : 0;
+}
+
+extern "C" int amrvr_layers_stats(const amrvr_layers* layers, amrvr_march_stats* stats) {
+  if (layers == nullptr || stats == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "NULL argument");
+  amrvr_layers* L = const_cast<amrvr_layers*>(layers);
+  if (!L->stats_ready) {
+    if (cudaEventSynchronize(L->t1) != cudaSuccess ||
+        cudaEventElapsedTime(&L->stats.kernel_ms, L->t0, L->t1) != cudaSuccess)
+      return fail(nullptr, AMRVR_ERR_CUDA, "event timing failed");
+    L->stats_ready = true;
+  }
+  *stats = L->stats;
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_layers_rect(const amrvr_layers* layers, int layer, int* x0, int* y0, int* w,
+                                 int* h) {
+  if (layers == nullptr || layer < 0 || layer >= static_cast<int>(layers->rects.size()))
+    return fail(nullptr, AMRVR_ERR_INVALID, "layer out of range");
+  const Rect& r = layers->rects[layer];
+  if (x0) *x0 = r.x0;
+  if (y0) *y0 = r.y0;
+  if (w) *w = r.w;
+  if (h) *h = r.h;
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_layers_read(amrvr_ctx* ctx, const amrvr_layers* layers, int layer,
+                                 float* dst5) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, layers != nullptr && dst5 != nullptr, "NULL argument");
+  REQUIRE(ctx, layer >= 0 && layer < static_cast<int>(layers->rects.size()), "layer out of range");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const Rect& r = layers->rects[layer];
+  const int W = layers->width, H = layers->height;
+  const size_t npix = static_cast<size_t>(W) * H;
+  for (size_t p = 0; p < npix; ++p) {  // ImageRGBAFloatColorDepthSort::clear
+    float* o = dst5 + 5 * p;
+    o[0] = o[1] = o[2] = o[3] = 0.0f;
+    o[4] = INFINITY;
+  }
+  const size_t count = static_cast<size_t>(r.w) * r.h * 5;
+  if (count == 0) return AMRVR_OK;
+  std::vector<float> host(count);
+  CUDA_TRY(ctx, cudaMemcpyAsync(host.data(), layers->pool.as<float>() + layers->offs[layer],
+                                count * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int y = 0; y < r.h; ++y) {
+    const float* row = host.data() + static_cast<size_t>(y) * r.w * 5;
+    for (int x = 0; x < r.w; ++x) {
+      const int px = r.x0 + x, py = r.y0 + y;
+      if (px >= W || py >= H) continue;
+      float* o = dst5 + 5 * (static_cast<size_t>(py) * W + px);
+      o[0] = row[4 * x + 0];
+      o[1] = row[4 * x + 1];
+      o[2] = row[4 * x + 2];
+      o[3] = row[4 * x + 3];
+      o[4] = row[4 * r.w + x];
+    }
+  }
+  return AMRVR_OK;
+}
+
+// ---------------------------------------------------------------------------
+// composite
+// ---------------------------------------------------------------------------
+namespace {
+
+int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers* layers,
+                   const amrvr_camera* camera, const int* rank_order, int* region_begin,
+                   int* region_end, float** piece_out, int64_t* exchanged_bytes) {
+  const int P = ctx->nranks, me = ctx->rank;
+  const int W = layers->width, H = layers->height;
+  {
+    std::vector<char> seen(static_cast<size_t>(P), 0);
+    for (int i = 0; i < P; ++i) {
+      REQUIRE(ctx, rank_order[i] >= 0 && rank_order[i] < P && !seen[rank_order[i]],
+              "rank_order is not a permutation");
+      seen[rank_order[i]] = 1;
+    }
+  }
+  FramePlan plan;
+  make_frame_plan(*scene, *camera, W, H, P, rank_order, plan);
+  const int n = static_cast<int>(scene->global.size());
+  REQUIRE(ctx, static_cast<int>(layers->rects.size()) == static_cast<int>(scene->local.size()),
+          "layers do not belong to this scene");
+  for (size_t l = 0; l < layers->rects.size(); ++l) {
+    const Rect& a = layers->rects[l];
+    const Rect& b = plan.rects[scene->first_global + static_cast<int>(l)];
+    if (a.x0 != b.x0 || a.y0 != b.y0 || a.w != b.w || a.h != b.h)
+      return fail(ctx, AMRVR_ERR_INVALID, "camera differs from the one the layers were marched with");
+  }
+  const int my_begin = plan.begin[me], my_end = plan.end[me];
+
+  // exchange plan (P > 1): slices of my layers other pieces need, slices of
+  // other ranks' layers my piece needs
+  std::vector<uint64_t> send_off(P + 1, 0), recv_off(P + 1, 0);
+  std::vector<CopyJob> jobs;
+  std::vector<uint64_t> recv_slot(static_cast<size_t>(n), 0);  // float offset in recv_buf per global box
+  if (P > 1) {
+    std::vector<uint64_t> send_len(P, 0), recv_len(P, 0);
+    for (int g = 0; g < n; ++g) {
+      const int owner = scene->global[g].owner;
+      const Rect& r = plan.rects[g];
+      int s0, s1;
+      if (owner == me) {
+        for (int q = 0; q < P; ++q) {
+          if (q == me || !slice_rows(r, plan.begin[q], plan.end[q], W, &s0, &s1)) continue;
+          send_len[q] += static_cast<uint64_t>(s1 - s0) * r.w * 5;
+        }
+      } else if (slice_rows(r, my_begin, my_end, W, &s0, &s1)) {
+        recv_len[owner] += static_cast<uint64_t>(s1 - s0) * r.w * 5;
+      }
+    }
+    for (int q = 0; q < P; ++q) {
+      send_off[q + 1] = send_off[q] + send_len[q];
+      recv_off[q + 1] = recv_off[q] + recv_len[q];
+    }
+    std::vector<uint64_t> send_cur(send_off.begin(), send_off.end() - 1);
+    std::vector<uint64_t> recv_cur(recv_off.begin(), recv_off.end() - 1);
+    const uint32_t kChunk = 16384;  // floats per copy job
+    for (int g = 0; g < n; ++g) {
+      const int owner = scene->global[g].owner;
+      const Rect& r = plan.rects[g];
+      int s0, s1;
+      if (owner == me) {
+        const uint64_t base = layers->offs[g - scene->first_global];
+        for (int q = 0; q < P; ++q) {
+          if (q == me || !slice_rows(r, plan.begin[q], plan.end[q], W, &s0, &s1)) continue;
+          uint64_t src = base + static_cast<uint64_t>(s0 - r.y0) * r.w * 5;
+          uint64_t left = static_cast<uint64_t>(s1 - s0) * r.w * 5;
+          while (left > 0) {
+            const uint32_t c = static_cast<uint32_t>(std::min<uint64_t>(left, kChunk));
+            jobs.push_back(CopyJob{src, send_cur[q], c, 0});
+            src += c;
+            send_cur[q] += c;
+            left -= c;
+          }
+        }
+      } else if (slice_rows(r, my_begin, my_end, W, &s0, &s1)) {
+        recv_slot[g] = recv_cur[owner];
+        recv_cur[owner] += static_cast<uint64_t>(s1 - s0) * r.w * 5;
+      }
+    }
+    CUDA_TRY(ctx, ctx->send_buf.reserve(std::max<uint64_t>(send_off[P], 4) * sizeof(float)));
+    CUDA_TRY(ctx, ctx->recv_buf.reserve(std::max<uint64_t>(recv_off[P], 4) * sizeof(float)));
+    if (!jobs.empty()) {
+      CUDA_TRY(ctx, ctx->copy_jobs.reserve(jobs.size() * sizeof(CopyJob)));
+      CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, jobs.data(), jobs.size() * sizeof(CopyJob),
+                                    cudaMemcpyHostToDevice, ctx->stream));
+      LAUNCH_TRY(ctx, launch_pack(ctx->copy_jobs.as<CopyJob>(), static_cast<int>(jobs.size()),
+                                  layers->pool.as<float>(), ctx->send_buf.as<float>(), ctx->stream,
+                                  &ctx->launches));
+    }
+    NcclApi& nc = nccl_api();
+    NCCL_TRY(ctx, nc.GroupStart());
+    for (int q = 0; q < P; ++q) {
+      if (q == me) continue;
+      if (send_len[q] > 0)
+        NCCL_TRY(ctx, nc.Send(ctx->send_buf.as<float>() + send_off[q], send_len[q], ncclFloat, q,
+                              ctx->comm, ctx->stream));
+      if (recv_len[q] > 0)
+        NCCL_TRY(ctx, nc.Recv(ctx->recv_buf.as<float>() + recv_off[q], recv_len[q], ncclFloat, q,
+                              ctx->comm, ctx->stream));
+    }
+    NCCL_TRY(ctx, nc.GroupEnd());
+    if (exchanged_bytes) *exchanged_bytes = static_cast<int64_t>(send_off[P] * sizeof(float));
+  } else if (exchanged_bytes) {
+    *exchanged_bytes = 0;
+  }
+
+  // fold table in blend order, only layers that reach my piece
+  std::vector<FoldLayer> fold;
+  fold.reserve(static_cast<size_t>(n));
+  for (int pos = 0; pos < n; ++pos) {
+    const int g = plan.order[pos];
+    const Rect& r = plan.rects[g];
+    int s0, s1;
+    if (!slice_rows(r, my_begin, my_end, W, &s0, &s1)) continue;
+    FoldLayer F{};
+    if (scene->global[g].owner == me) {
+      F.base = layers->pool.as<float>() + layers->offs[g - scene->first_global] +
+               static_cast<uint64_t>(s0 - r.y0) * r.w * 5;
+    } else {
+      F.base = ctx->recv_buf.as<float>() + recv_slot[g];
+    }
+    F.x0 = r.x0;
+    F.w = r.w;
+    F.row0 = s0;
+    F.row1 = s1;
+    F.run = plan.run_of[g];
+    fold.push_back(F);
+  }
+  const int npix = my_end - my_begin;
+  CUDA_TRY(ctx, ctx->piece.reserve(std::max<size_t>(static_cast<size_t>(std::max(npix, 0)) * 20, 256)));
+  if (!fold.empty()) {
+    CUDA_TRY(ctx, ctx->fold_layers.reserve(fold.size() * sizeof(FoldLayer)));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->fold_layers.ptr, fold.data(), fold.size() * sizeof(FoldLayer),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+  }
+  LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
+                              my_begin, my_end, ctx->piece.as<float>(), ctx->stream,
+                              &ctx->launches));
+  if (region_begin) *region_begin = my_begin;
+  if (region_end) *region_end = my_end;
+  if (piece_out) *piece_out = ctx->piece.as<float>();
+  return AMRVR_OK;
+}
+
+}  // namespace
+
+extern "C" int amrvr_composite(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers* layers,
+                               const amrvr_camera* camera, const int* rank_order,
+                               int* region_begin, int* region_end, float** piece5_device) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, scene && layers && camera && rank_order, "NULL argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return composite_impl(ctx, scene, layers, camera, rank_order, region_begin, region_end,
+                        piece5_device, nullptr);
+}
+
+extern "C" int amrvr_composite_virtual(amrvr_ctx* ctx, const amrvr_scene* scene,
+                                       const amrvr_layers* layers, const amrvr_camera* camera,
+                                       int nvirtual, const int* box_owner, const int* rank_order,
+                                       float* full5_device, int* piece_owner_host) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, scene && layers && camera && box_owner && rank_order && full5_device,
+          "NULL argument");
+  REQUIRE(ctx, ctx->nranks == 1, "virtual composite needs a single-rank context");
+  REQUIRE(ctx, nvirtual >= 1, "nvirtual must be positive");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int n = static_cast<int>(scene->local.size());
+  REQUIRE(ctx, static_cast<int>(layers->rects.size()) == n, "layers do not belong to this scene");
+  const int W = layers->width, H = layers->height;
+  // the global table P ranks would have allgathered: owner-major, local order kept
+  amrvr_scene shadow;
+  std::vector<int> source;  // shadow index -> local layer
+  for (int r = 0; r < nvirtual; ++r) {
+    int local = 0;
+    for (int l = 0; l < n; ++l) {
+      REQUIRE(ctx, box_owner[l] >= 0 && box_owner[l] < nvirtual, "box_owner out of range");
+      if (box_owner[l] != r) continue;
+      amrvr_box_record rec = scene->global[scene->first_global + l];
+      rec.owner = r;
+      rec.local_index = local++;
+      shadow.global.push_back(rec);
+      source.push_back(l);
+    }
+  }
+  FramePlan plan;
+  make_frame_plan(shadow, *camera, W, H, nvirtual, rank_order, plan);
+  std::vector<FoldLayer> fold;
+  for (int pos = 0; pos < n; ++pos) {
+    const int g = plan.order[pos];
+    const Rect& r = plan.rects[g];
+    if (r.w <= 0 || r.h <= 0) continue;
+    FoldLayer F{};
+    F.base = layers->pool.as<float>() + layers->offs[source[g]];
+    F.x0 = r.x0;
+    F.w = r.w;
+    F.row0 = r.y0;
+    F.row1 = r.y0 + r.h;
+    F.run = plan.run_of[g];
+    fold.push_back(F);
+  }
+  if (!fold.empty()) {
+    CUDA_TRY(ctx, ctx->fold_layers.reserve(fold.size() * sizeof(FoldLayer)));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->fold_layers.ptr, fold.data(), fold.size() * sizeof(FoldLayer),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+  }
+  LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W, 0,
+                              W * H, full5_device, ctx->stream, &ctx->launches));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (piece_owner_host != nullptr)
+    for (int r = 0; r < nvirtual; ++r)
+      for (int p = plan.begin[r]; p < plan.end[r]; ++p) piece_owner_host[p] = r;
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_gather(amrvr_ctx* ctx, const float* piece5_device, int region_begin,
+                            int region_end, int num_pixels, int root, float* full5_device) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  const int P = ctx->nranks, me = ctx->rank;
+  REQUIRE(ctx, root >= 0 && root < P, "root out of range");
+  REQUIRE(ctx, region_begin >= 0 && region_end >= region_begin && region_end <= num_pixels,
+          "bad region");
+  REQUIRE(ctx, me != root || full5_device != nullptr, "root needs a destination");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const size_t mine = static_cast<size_t>(region_end - region_begin) * 5;
+  if (P == 1) {
+    if (mine > 0)
+      CUDA_TRY(ctx, cudaMemcpyAsync(full5_device + static_cast<size_t>(region_begin) * 5,
+                                    piece5_device, mine * sizeof(float), cudaMemcpyDeviceToDevice,
+                                    ctx->stream));
+    return AMRVR_OK;
+  }
+  // every rank learns every region (ImageColorOnly.hpp:220-270 gathers sizes first)
+  NcclApi& nc = nccl_api();
+  DeviceBuffer tmp;
+  CUDA_TRY(ctx, tmp.reserve(static_cast<size_t>(2 * (P + 1)) * sizeof(int)));
+  int* all_dev = tmp.as<int>();
+  const int span[2] = {region_begin, region_end};
+  CUDA_TRY(ctx, cudaMemcpyAsync(all_dev + 2 * P, span, sizeof(span), cudaMemcpyHostToDevice,
+                                ctx->stream));
+  NCCL_TRY(ctx, nc.AllGather(all_dev + 2 * P, all_dev, sizeof(span), ncclChar, ctx->comm,
+                             ctx->stream));
+  std::vector<int> spans(static_cast<size_t>(2 * P));
+  CUDA_TRY(ctx, cudaMemcpyAsync(spans.data(), all_dev, sizeof(int) * 2 * P, cudaMemcpyDeviceToHost,
+                                ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  tmp.release();
+  NCCL_TRY(ctx, nc.GroupStart());
+  if (me == root) {
+    for (int r = 0; r < P; ++r) {
+      const size_t len = static_cast<size_t>(spans[2 * r + 1] - spans[2 * r]) * 5;
+      if (r == me || len == 0) continue;
+      NCCL_TRY(ctx, nc.Recv(full5_device + static_cast<size_t>(spans[2 * r]) * 5, len, ncclFloat, r,
+                            ctx->comm, ctx->stream));
+    }
+  } else if (mine > 0) {
+    NCCL_TRY(ctx, nc.Send(piece5_device, mine, ncclFloat, root, ctx->comm, ctx->stream));
+  }
+  NCCL_TRY(ctx, nc.GroupEnd());
+  if (me == root && mine > 0)
+    CUDA_TRY(ctx, cudaMemcpyAsync(full5_device + static_cast<size_t>(region_begin) * 5,
+                                  piece5_device, mine * sizeof(float), cudaMemcpyDeviceToDevice,
+                                  ctx->stream));
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_downsample(amrvr_ctx* ctx, const float* full5_device, int width, int height,
+                                int sqrt_aa, float* out5_device) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, full5_device && out5_device && width > 0 && height > 0, "bad argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  LAUNCH_TRY(ctx, launch_downsample(full5_device, width, height, sqrt_aa, out5_device, ctx->stream,
+                                    &ctx->launches));
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_quantize_rgb8(amrvr_ctx* ctx, const float* full5_device, int width, int height,
+                                   uint8_t* rgb8_device) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, full5_device && rgb8_device && width > 0 && height > 0, "bad argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  LAUNCH_TRY(ctx, launch_quantize_rgb8(full5_device, width, height, rgb8_device, ctx->stream,
+                                       &ctx->launches));
+  return AMRVR_OK;
+}
+
+// ---------------------------------------------------------------------------
+// memory helpers
+// ---------------------------------------------------------------------------
+
+extern "C" int amrvr_device_alloc(amrvr_ctx* ctx, size_t bytes, void** out) {
+  if (ctx == nullptr || out == nullptr) return fail(ctx, AMRVR_ERR_INVALID, "NULL argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaMalloc(out, std::max<size_t>(bytes, 1)));
+  return AMRVR_OK;
+}
+extern "C" int amrvr_device_free(amrvr_ctx* ctx, void* ptr) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaFree(ptr));
+  return AMRVR_OK;
+}
+extern "C" int amrvr_copy_to_host(amrvr_ctx* ctx, void* dst_host, const void* src_device,
+                                  size_t bytes) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst_host, src_device, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return AMRVR_OK;
+}
+extern "C" int amrvr_copy_to_device(amrvr_ctx* ctx, void* dst_device, const void* src_host,
+                                    size_t bytes) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dst_device, src_host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return AMRVR_OK;
+}
+extern "C" int amrvr_host_alloc_pinned(size_t bytes, void** out) {
+  if (out == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "out is NULL");
+  CUDA_TRY(nullptr, cudaMallocHost(out, std::max<size_t>(bytes, 1)));
+  return AMRVR_OK;
+}
+extern "C" int amrvr_host_free_pinned(void* ptr) {
+  CUDA_TRY(nullptr, cudaFreeHost(ptr));
+  return AMRVR_OK;
+}
+extern "C" int amrvr_synchronize(amrvr_ctx* ctx) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return AMRVR_OK;
+}
+
+// ---------------------------------------------------------------------------
+// whole frame
+// ---------------------------------------------------------------------------
+
+extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
+                                  const amrvr_camera* camera, const amrvr_frame_params* params,
+                                  const amrvr_colormap_pt* pts, int npts, int root,
+                                  float* rgba5_host, uint8_t* rgb8_host, amrvr_frame_stats* stats) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, scene && camera && params, "NULL argument");
+  REQUIRE(ctx, params->width > 0 && params->height > 0, "width and height must be positive");
+  REQUIRE(ctx, root >= 0 && root < ctx->nranks, "root out of range");
+  const int sqrt_aa = static_cast<int>(std::lround(std::sqrt(static_cast<double>(params->antialiasing))));
+  REQUIRE(ctx, params->antialiasing >= 1 && sqrt_aa * sqrt_aa == params->antialiasing,
+          "antialiasing must be a positive perfect square");  // VolumeRenderer.cpp:425-437
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int W = params->width, H = params->height;
+  const int RW = W * sqrt_aa, RH = H * sqrt_aa;
+  const float aspect = static_cast<float>(W) / static_cast<float>(H);
+  const int n = static_cast<int>(scene->global.size());
+
+  // tight bounds of all boxes (VolumeRenderer.cpp:791-849), also the fallback
+  // bounds of the reference step
+  double tmin[3] = {0, 0, 0}, tmax[3] = {0, 0, 0};
+  for (int d = 0; d < 3 && n > 0; ++d) {
+    double lo = scene->global[0].min_corner[d], hi = scene->global[0].max_corner[d];
+    for (int g = 1; g < n; ++g) {
+      lo = std::min(lo, scene->global[g].min_corner[d]);
+      hi = std::max(hi, scene->global[g].max_corner[d]);
+    }
+    tmin[d] = static_cast<double>(static_cast<float>(lo));
+    tmax[d] = static_cast<double>(static_cast<float>(hi));
+  }
+  const float ref_step = reference_sample_distance(n, scene->global.data(), tmin, tmax);
+
+  cudaEvent_t* ev = ctx->ev;
+  CUDA_TRY(ctx, cudaEventRecord(ev[0], ctx->stream));
+  amrvr_layers* layers = nullptr;
+  int st = amrvr_raymarch(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
+                          params->count_samples, &layers);
+  if (st != AMRVR_OK) return st;
+  CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
+
+  std::vector<int> rank_order(static_cast<size_t>(ctx->nranks));
+  int graph_failed = 0;
+  st = amrvr_order_boxes(ctx, scene, camera, aspect, params->use_visibility_graph,
+                         rank_order.data(), &graph_failed);
+  if (st != AMRVR_OK) {
+    amrvr_layers_free(ctx, layers);
+    return st;
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ev[2], ctx->stream));
+
+  int begin = 0, end = 0;
+  float* piece = nullptr;
+  int64_t exchanged = 0;
+  st = composite_impl(ctx, scene, layers, camera, rank_order.data(), &begin, &end, &piece,
+                      &exchanged);
+  if (st != AMRVR_OK) {
+    amrvr_layers_free(ctx, layers);
+    return st;
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ev[3], ctx->stream));
+
+  const size_t render_floats = static_cast<size_t>(RW) * RH * 5;
+  const size_t out_floats = static_cast<size_t>(W) * H * 5;
+  if (ctx->rank == root) CUDA_TRY(ctx, ctx->full.reserve(render_floats * sizeof(float)));
+  st = amrvr_gather(ctx, piece, begin, end, RW * RH, root, ctx->full.as<float>());
+  if (st != AMRVR_OK) {
+    amrvr_layers_free(ctx, layers);
+    return st;
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ev[4], ctx->stream));
+
+  if (ctx->rank == root) {
+    float* image = ctx->full.as<float>();
+    if (sqrt_aa > 1) {
+      CUDA_TRY(ctx, ctx->small.reserve(out_floats * sizeof(float)));
+      LAUNCH_TRY(ctx, launch_downsample(ctx->full.as<float>(), W, H, sqrt_aa, ctx->small.as<float>(),
+                                        ctx->stream, &ctx->launches));
+      image = ctx->small.as<float>();
+    }
+    if (params->draw_bounding_box && n > 0) {
+      OverlayEdges edges;
+      make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
+      LAUNCH_TRY(ctx, launch_overlay(edges, 1, W, H, image, ctx->stream, &ctx->launches));
+    }
+    if (rgba5_host != nullptr)
+      CUDA_TRY(ctx, cudaMemcpyAsync(rgba5_host, image, out_floats * sizeof(float),
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+    if (rgb8_host != nullptr) {
+      CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
+      LAUNCH_TRY(ctx, launch_quantize_rgb8(image, W, H, ctx->rgb8.as<uint8_t>(), ctx->stream,
+                                           &ctx->launches));
+      CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->rgb8.ptr, static_cast<size_t>(W) * H * 3,
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+    }
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ev[5], ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (stats != nullptr) {
+    std::memset(stats, 0, sizeof(*stats));
+    amrvr_march_stats ms;
+    if (amrvr_layers_stats(layers, &ms) == AMRVR_OK) {
+      stats->samples = ms.samples;
+      stats->march_ms = ms.kernel_ms;
+    }
+    cudaEventElapsedTime(&stats->order_ms, ev[1], ev[2]);
+    cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[3]);
+    cudaEventElapsedTime(&stats->gather_ms, ev[3], ev[4]);
+    cudaEventElapsedTime(&stats->post_ms, ev[4], ev[5]);
+    stats->exchanged_bytes = exchanged;
+  }
+  amrvr_layers_free(ctx, layers);
+  return AMRVR_OK;
+}

@@ -1,0 +1,908 @@
+// host_logic.cpp -- the sequential, per-frame host side of the hot path: transfer
+// table, camera frame, per-box sampling constants, screen footprints, layer
+// order, visibility-graph driver.  Everything here is O(boxes) or O(256) work
+// the reference also does on the host; the per-pixel and per-cell work lives in
+// kernels.cu.  Compiled without FP contraction so float expressions round
+// exactly like the reference's default x86-64 build.
+#include "internal.hpp"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+#include <queue>
+
+namespace amrvr {
+
+namespace {
+
+constexpr float kPiF = 3.14159265358979323846f;
+
+inline float clampf(float v, float lo, float hi) {
+  return (v < lo) ? lo : ((hi < v) ? hi : v);
+}
+inline float fmax2(float a, float b) { return (a < b) ? b : a; }  // std::max
+inline float fmin2(float a, float b) { return (b < a) ? b : a; }  // std::min
+
+struct V3 {
+  double x, y, z;
+};
+inline V3 sub(const double* a, const double* b) {
+  return {a[0] - b[0], a[1] - b[1], a[2] - b[2]};
+}
+inline V3 cross(const V3& a, const V3& b) {
+  return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+inline double dot(const V3& a, const V3& b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// reference: Common/CameraUtils.hpp:16-22 (fallback is always (0,0,-1))
+inline V3 unit_or(const V3& v, const V3& fallback) {
+  const double len = std::sqrt(dot(v, v));
+  if (len > 0.0 && std::isfinite(len)) return {v.x / len, v.y / len, v.z / len};
+  return fallback;
+}
+
+struct Frame3 {
+  V3 f, r, u;
+};
+// forward / right / true-up, all in double (Common/VolumePainter.cpp:631-641,
+// Common/CameraUtils.hpp:27-39)
+Frame3 camera_frame(const amrvr_camera& cam) {
+  Frame3 fr;
+  fr.f = unit_or(sub(cam.look_at, cam.eye), V3{0.0, 0.0, -1.0});
+  const V3 up{cam.up[0], cam.up[1], cam.up[2]};
+  V3 r = cross(fr.f, up);
+  const double rl = std::sqrt(dot(r, r));
+  if (rl > 0.0 && std::isfinite(rl)) {
+    r.x /= rl;
+    r.y /= rl;
+    r.z /= rl;
+  } else {
+    r = V3{1.0, 0.0, 0.0};
+  }
+  fr.r = r;
+  fr.u = cross(fr.r, fr.f);
+  return fr;
+}
+
+}  // namespace
+
+void make_camera_basis(const amrvr_camera& cam, CameraBasis& out) {
+  const Frame3 fr = camera_frame(cam);
+  const double f[3] = {fr.f.x, fr.f.y, fr.f.z};
+  const double r[3] = {fr.r.x, fr.r.y, fr.r.z};
+  const double u[3] = {fr.u.x, fr.u.y, fr.u.z};
+  for (int d = 0; d < 3; ++d) {
+    out.fwd_d[d] = f[d];
+    out.right_d[d] = r[d];
+    out.up_d[d] = u[d];
+    out.fwd[d] = static_cast<float>(f[d]);
+    out.right[d] = static_cast<float>(r[d]);
+    out.up[d] = static_cast<float>(u[d]);
+    out.eye[d] = static_cast<float>(cam.eye[d]);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Transfer table.  Two piecewise functions over the scalar range: a colour
+// curve (RGB nodes; interpolated in RGB for the built-in map, in CIELAB for a
+// user map) and an opacity curve whose node alphas were already corrected for
+// the box's step length.  Reference: Common/VolumePainter.cpp:107-516.
+// ---------------------------------------------------------------------------
+namespace {
+
+struct ColorNode {
+  float v, r, g, b;
+};
+struct OpacityNode {
+  float v, a, mid, sharp;
+};
+
+struct TransferCurves {
+  bool lab = false;
+  std::vector<ColorNode> color;
+  std::vector<OpacityNode> opacity;
+
+  template <class Node>
+  static void put(std::vector<Node>& nodes, const Node& n) {
+    auto it = std::lower_bound(nodes.begin(), nodes.end(), n,
+                               [](const Node& a, const Node& b) { return a.v < b.v; });
+    if (it != nodes.end() && it->v == n.v) {
+      *it = n;  // same abscissa replaces (:127-151)
+    } else {
+      nodes.insert(it, n);
+    }
+  }
+
+  // :153-200 -- stretch all abscissae from their current span to [lo, hi]
+  void stretch_to(float lo, float hi) {
+    bool any = false;
+    float cur_lo = 0.0f, cur_hi = 0.0f;
+    auto see = [&](float v) {
+      if (!any) {
+        cur_lo = cur_hi = v;
+        any = true;
+      } else {
+        cur_lo = fmin2(cur_lo, v);
+        cur_hi = fmax2(cur_hi, v);
+      }
+    };
+    for (const auto& c : color) see(c.v);
+    for (const auto& o : opacity) see(o.v);
+    const float old_span = cur_hi - cur_lo;
+    const float new_span = hi - lo;
+    if (!(old_span > 0.0f) || !(new_span > 0.0f)) return;
+    for (auto& c : color) c.v = lo + new_span * ((c.v - cur_lo) / old_span);
+    for (auto& o : opacity) o.v = lo + new_span * ((o.v - cur_lo) / old_span);
+  }
+};
+
+// :107-125 -- opacity correction for the step length, in double
+float step_corrected_alpha(float base, float alpha_scale, float norm) {
+  const float s = clampf(base * alpha_scale, 0.0f, 1.0f);
+  if (norm <= 0.0f || s <= 0.0f) return 0.0f;
+  if (s >= 1.0f) return 1.0f;
+  const double remaining = std::pow(1.0 - static_cast<double>(s), static_cast<double>(norm));
+  float a = static_cast<float>(1.0 - remaining);
+  if (!std::isfinite(a)) a = s;
+  return clampf(a, 0.0f, 1.0f);
+}
+
+// sRGB <-> CIELAB (D65), float, with the reference's constants (:202-320)
+struct Lab {
+  float L, a, b;
+};
+inline float gamma_expand(float c) {
+  return (c > 0.04045f) ? std::pow((c + 0.055f) / 1.055f, 2.4f) : c / 12.92f;
+}
+inline float gamma_compress(float c) {
+  return (c > 0.0031308f) ? 1.055f * std::pow(c, 1.0f / 2.4f) - 0.055f : 12.92f * c;
+}
+inline float lab_curve(float t) {
+  return (t > 0.008856f) ? std::pow(t, 1.0f / 3.0f) : (7.787f * t) + 16.0f / 116.0f;
+}
+inline float lab_curve_inv(float t) {
+  const float cube = std::pow(t, 3.0f);
+  return (cube > 0.008856f) ? cube : (t - 16.0f / 116.0f) / 7.787f;
+}
+Lab to_lab(float r8, float g8, float b8) {
+  const float r = gamma_expand(r8), g = gamma_expand(g8), b = gamma_expand(b8);
+  const float X = r * 0.4124f + g * 0.3576f + b * 0.1805f;
+  const float Y = r * 0.2126f + g * 0.7152f + b * 0.0722f;
+  const float Z = r * 0.0193f + g * 0.1192f + b * 0.9505f;
+  const float fx = lab_curve(X / 0.9505f);
+  const float fy = lab_curve(Y / 1.0f);
+  const float fz = lab_curve(Z / 1.089f);
+  return {(116.0f * fy) - 16.0f, 500.0f * (fx - fy), 200.0f * (fy - fz)};
+}
+void from_lab(const Lab& c, float* rgb) {
+  float fy = (c.L + 16.0f) / 116.0f;
+  float fx = c.a / 500.0f + fy;
+  float fz = fy - c.b / 200.0f;
+  float X = lab_curve_inv(fx), Y = lab_curve_inv(fy), Z = lab_curve_inv(fz);
+  X *= 0.9505f;
+  Y *= 1.0f;
+  Z *= 1.089f;
+  float r = X * 3.2406f + Y * -1.5372f + Z * -0.4986f;
+  float g = X * -0.9689f + Y * 1.8758f + Z * 0.0415f;
+  float b = X * 0.0557f + Y * -0.2040f + Z * 1.0570f;
+  r = gamma_compress(r);
+  g = gamma_compress(g);
+  b = gamma_compress(b);
+  const float peak = fmax2(r, fmax2(g, b));
+  if (peak > 1.0f) {
+    r /= peak;
+    g /= peak;
+    b /= peak;
+  }
+  rgb[0] = fmax2(r, 0.0f);
+  rgb[1] = fmax2(g, 0.0f);
+  rgb[2] = fmax2(b, 0.0f);
+}
+
+// colour curve at `value`, clamping outside the node span (:331-379)
+void eval_color(const TransferCurves& tc, float value, float* rgb) {
+  if (!std::isfinite(value)) {
+    rgb[0] = tc.lab ? 1.0f : 0.25f;
+    rgb[1] = rgb[2] = 0.0f;
+    return;
+  }
+  if (tc.color.empty()) {
+    rgb[0] = rgb[1] = rgb[2] = 0.0f;
+    return;
+  }
+  const ColorNode& first = tc.color.front();
+  const ColorNode& last = tc.color.back();
+  const ColorNode* edge = nullptr;
+  if (value < first.v) {
+    edge = &first;
+  } else if (value > last.v) {
+    edge = &last;
+  } else if (value == first.v) {
+    edge = &first;
+  } else if (value == last.v) {
+    edge = &last;
+  }
+  if (edge == nullptr) {
+    for (size_t i = 1; i < tc.color.size(); ++i) {
+      const ColorNode& hi = tc.color[i];
+      if (!(hi.v >= value)) continue;
+      const ColorNode& lo = tc.color[i - 1];
+      const float span = hi.v - lo.v;
+      const float w = (span > 0.0f) ? (value - lo.v) / span : 0.0f;
+      if (tc.lab) {
+        const Lab a = to_lab(lo.r, lo.g, lo.b);
+        const Lab b = to_lab(hi.r, hi.g, hi.b);
+        const Lab m{a.L + (b.L - a.L) * w, a.a + (b.a - a.a) * w, a.b + (b.b - a.b) * w};
+        from_lab(m, rgb);
+      } else {
+        rgb[0] = lo.r + (hi.r - lo.r) * w;
+        rgb[1] = lo.g + (hi.g - lo.g) * w;
+        rgb[2] = lo.b + (hi.b - lo.b) * w;
+      }
+      return;
+    }
+    edge = &last;
+  }
+  rgb[0] = edge->r;
+  rgb[1] = edge->g;
+  rgb[2] = edge->b;
+}
+
+// opacity curve at `value` (:381-440): piecewise with midpoint / sharpness
+float eval_opacity(const TransferCurves& tc, float value) {
+  if (!std::isfinite(value) || tc.opacity.empty()) return 1.0f;
+  const OpacityNode& first = tc.opacity.front();
+  const OpacityNode& last = tc.opacity.back();
+  if (value <= first.v) return first.a;
+  if (value >= last.v) return last.a;
+  for (size_t i = 1; i < tc.opacity.size(); ++i) {
+    const OpacityNode& hi = tc.opacity[i];
+    if (!(hi.v >= value)) continue;
+    const OpacityNode& lo = tc.opacity[i - 1];
+    const float span = hi.v - lo.v;
+    float w = (span > 0.0f) ? (value - lo.v) / span : 0.0f;
+    if (w < lo.mid) {
+      w = 0.5f * w / lo.mid;
+    } else {
+      w = 0.5f + 0.5f * (w - lo.mid) / (1.0f - lo.mid);
+    }
+    if (lo.sharp == 1.0f) return (w < 0.5f) ? lo.a : hi.a;
+    if (lo.sharp == 0.0f) return lo.a + (hi.a - lo.a) * w;
+    if (w < 0.5f) {
+      w = 0.5f * std::pow(w * 2.0f, 1.0f + 10.0f * lo.sharp);
+    } else if (w > 0.5f) {
+      w = 1.0f - 0.5f * std::pow((1.0f - w) * 2.0f, 1.0f + 10.0f * lo.sharp);
+    }
+    const float w2 = w * w, w3 = w2 * w;
+    const float h00 = 2.0f * w3 - 3.0f * w2 + 1.0f;
+    const float h01 = -2.0f * w3 + 3.0f * w2;
+    const float h10 = w3 - 2.0f * w2 + w;
+    const float h11 = w3 - w2;
+    const float tangent = (1.0f - lo.sharp) * (hi.a - lo.a);
+    float a = h00 * lo.a + h01 * hi.a + h10 * tangent + h11 * tangent;
+    a = fmax2(a, fmin2(lo.a, hi.a));
+    a = fmin2(a, fmax2(lo.a, hi.a));
+    return a;
+  }
+  return last.a;
+}
+
+}  // namespace
+
+void build_color_table(float alpha_scale, float norm_factor, float range_min,
+                       float range_max, const amrvr_colormap_pt* pts, int npts,
+                       float* rgba256) {
+  TransferCurves tc;
+  const float span = range_max - range_min;
+  if (pts != nullptr && npts > 0) {  // user map (:449-466)
+    tc.lab = true;
+    for (int i = 0; i < npts; ++i) {
+      const amrvr_colormap_pt& p = pts[i];
+      TransferCurves::put(tc.color, ColorNode{p.value, clampf(p.red, 0.0f, 1.0f),
+                                              clampf(p.green, 0.0f, 1.0f),
+                                              clampf(p.blue, 0.0f, 1.0f)});
+      TransferCurves::put(
+          tc.opacity,
+          OpacityNode{p.value, step_corrected_alpha(p.alpha, alpha_scale, norm_factor),
+                      0.5f, 0.0f});
+    }
+  } else {  // built-in jet + opacity ramp (:467-500)
+    static const ColorNode kJet[] = {
+        {0.0f, 0.0f, 0.0f, 0.5625f},    {0.111111f, 0.0f, 0.0f, 1.0f},
+        {0.3650795f, 0.0f, 1.0f, 1.0f}, {0.4920635f, 0.5f, 1.0f, 0.5f},
+        {0.6190475f, 1.0f, 1.0f, 0.0f}, {0.873016f, 1.0f, 0.0f, 0.0f},
+        {1.0f, 0.5f, 0.0f, 0.0f}};
+    for (const ColorNode& n : kJet) TransferCurves::put(tc.color, n);
+    static const float kRampAt[] = {0.0f, 0.15f, 0.35f, 0.6f, 0.85f, 1.0f};
+    static const float kRampAlpha[] = {0.05f, 0.15f, 0.22f, 0.3f, 0.38f, 0.5f};
+    for (int i = 0; i < 6; ++i) {
+      TransferCurves::put(
+          tc.opacity,
+          OpacityNode{kRampAt[i] * span + range_min,
+                      step_corrected_alpha(kRampAlpha[i], alpha_scale, norm_factor),
+                      0.5f, 0.0f});
+    }
+    tc.stretch_to(range_min, range_max);
+  }
+  for (int i = 0; i < AMRVR_COLOR_TABLE_SIZE; ++i) {  // :507-514
+    const float t = static_cast<float>(i) / static_cast<float>(AMRVR_COLOR_TABLE_SIZE - 1);
+    const float value = range_min + span * t;
+    eval_color(tc, value, rgba256 + 4 * i);
+    rgba256[4 * i + 3] = eval_opacity(tc, value);
+  }
+}
+
+void box_sampling(const double* min_corner, const double* max_corner,
+                  const int32_t* dims, float reference_sample_distance,
+                  float* step_out, float* norm_out) {
+  float finest = FLT_MAX;
+  for (int d = 0; d < 3; ++d) {
+    double edge = 0.0;
+    if (dims[d] > 0) edge = (max_corner[d] - min_corner[d]) / static_cast<double>(dims[d]);
+    const float e = static_cast<float>(edge);
+    if (e > 0.0f && e < finest && std::isfinite(e)) finest = e;
+  }
+  if (!(finest > 0.0f && std::isfinite(finest))) {
+    // paint() is handed the box itself as `bounds` fallback (:593-598)
+    double shortest = max_corner[0] - min_corner[0];
+    for (int d = 1; d < 3; ++d) shortest = std::min(shortest, max_corner[d] - min_corner[d]);
+    finest = fmax2(1e-4f, static_cast<float>(shortest) * 0.01f);
+  }
+  const float step = fmax2(finest * 0.5f, 1e-5f);
+  float ref = reference_sample_distance;
+  if (!(ref > 0.0f && std::isfinite(ref))) ref = step;
+  float norm = step / ref;
+  if (!std::isfinite(norm)) norm = 1.0f;
+  *step_out = step;
+  *norm_out = fmax2(norm, 0.0f);
+}
+
+float box_depth_hint(const amrvr_box_record& rec, const amrvr_camera& cam) {
+  const V3 dir = unit_or(sub(cam.look_at, cam.eye), V3{0.0, 0.0, -1.0});
+  float nearest = INFINITY;
+  for (int c = 0; c < 8; ++c) {
+    const double p[3] = {(c & 1) ? rec.max_corner[0] : rec.min_corner[0],
+                         (c & 2) ? rec.max_corner[1] : rec.min_corner[1],
+                         (c & 4) ? rec.max_corner[2] : rec.min_corner[2]};
+    const float along = static_cast<float>(dot(sub(p, cam.eye), dir));
+    nearest = fmin2(nearest, along);
+  }
+  return nearest;
+}
+
+void layer_order(int nglobal, const amrvr_box_record* recs, const amrvr_camera& cam,
+                 float* hints, int* order) {
+  std::vector<float> depth(static_cast<size_t>(std::max(nglobal, 0)));
+  for (int i = 0; i < nglobal; ++i) {
+    depth[i] = box_depth_hint(recs[i], cam);
+    if (hints != nullptr) hints[i] = depth[i];
+    order[i] = i;
+  }
+  std::sort(order, order + std::max(nglobal, 0), [&](int a, int b) {
+    if (depth[a] == depth[b]) {
+      if (recs[a].owner == recs[b].owner) return recs[a].local_index < recs[b].local_index;
+      return recs[a].owner < recs[b].owner;
+    }
+    return depth[a] < depth[b];
+  });
+}
+
+void piece_range(int num_pixels, int piece, int num_pieces, int* begin, int* end) {
+  const int each = num_pixels / num_pieces;
+  *begin = each * piece;
+  *end = (piece < num_pieces - 1) ? (*begin + each) : num_pixels;
+}
+
+float reference_sample_distance(int nglobal, const amrvr_box_record* recs,
+                                const double* bounds_min, const double* bounds_max) {
+  float coarsest = 0.0f;
+  for (int i = 0; i < nglobal; ++i) {
+    float finest = FLT_MAX;
+    for (int d = 0; d < 3; ++d) {
+      double edge = 0.0;  // Real / float promotes to double (:1146-1154)
+      if (recs[i].dims[d] > 0)
+        edge = (recs[i].max_corner[d] - recs[i].min_corner[d]) /
+               static_cast<float>(recs[i].dims[d]);
+      if (edge > 0.0f && edge < finest && std::isfinite(edge)) finest = static_cast<float>(edge);
+    }
+    if (finest > 0.0f && std::isfinite(finest)) coarsest = fmax2(coarsest, finest);
+  }
+  if (!(coarsest > 0.0f && std::isfinite(coarsest))) {
+    float shortest = FLT_MAX;
+    for (int d = 0; d < 3; ++d) {
+      const float len = static_cast<float>(bounds_max[d] - bounds_min[d]);
+      if (len > 0.0f && std::isfinite(len)) shortest = fmin2(shortest, len);
+    }
+    if (!(shortest > 0.0f && std::isfinite(shortest))) shortest = 1.0f;
+    coarsest = fmax2(1e-4f, shortest * 0.01f);
+  }
+  return fmax2(coarsest * 0.5f, 1e-5f);
+}
+
+// ---------------------------------------------------------------------------
+// Screen footprint
+// ---------------------------------------------------------------------------
+Rect box_footprint(const double* min_corner, const double* max_corner,
+                   const int32_t* dims, const CameraBasis& basis,
+                   const amrvr_camera& cam, int width, int height) {
+  Rect full{0, 0, (width + 3) & ~3, height};
+  if (dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 || width <= 0 || height <= 0)
+    return Rect{0, 0, 0, 0};
+  const float aspect_f = static_cast<float>(width) / static_cast<float>(std::max(height, 1));
+  const double tan_half = std::tan(cam.fov_y_degrees * 0.5f * kPiF / 180.0f);
+  const double aspect = aspect_f;
+  // the march sees float-truncated corners and a float eye
+  double lo[3], hi[3], eye[3];
+  double diag2 = 0.0;
+  for (int d = 0; d < 3; ++d) {
+    lo[d] = static_cast<float>(min_corner[d]);
+    hi[d] = static_cast<float>(max_corner[d]);
+    eye[d] = basis.eye[d];
+    diag2 += (hi[d] - lo[d]) * (hi[d] - lo[d]);
+  }
+  const double guard = 1e-3 * std::sqrt(diag2) + 1e-6;
+  double px_lo = INFINITY, px_hi = -INFINITY, py_lo = INFINITY, py_hi = -INFINITY;
+  for (int c = 0; c < 8; ++c) {
+    const double p[3] = {(c & 1) ? hi[0] : lo[0], (c & 2) ? hi[1] : lo[1],
+                         (c & 4) ? hi[2] : lo[2]};
+    double depth = 0.0, xr = 0.0, yu = 0.0;
+    for (int d = 0; d < 3; ++d) {
+      const double rel = p[d] - eye[d];
+      depth += rel * basis.fwd[d];
+      xr += rel * basis.right[d];
+      yu += rel * basis.up[d];
+    }
+    if (!(depth > guard) || !std::isfinite(depth)) return full;  // corner at/behind the eye plane
+    const double ndc_x = xr / (depth * tan_half * aspect);
+    const double ndc_y = yu / (depth * tan_half);
+    if (!std::isfinite(ndc_x) || !std::isfinite(ndc_y)) return full;
+    const double px = (ndc_x + 1.0) * 0.5 * width - 0.5;
+    const double py = (ndc_y + 1.0) * 0.5 * height - 0.5;
+    px_lo = std::min(px_lo, px);
+    px_hi = std::max(px_hi, px);
+    py_lo = std::min(py_lo, py);
+    py_hi = std::max(py_hi, py);
+  }
+  // clamp in double before converting (far off-screen boxes)
+  const double big = 1e9;
+  px_lo = std::max(px_lo, -big);
+  py_lo = std::max(py_lo, -big);
+  px_hi = std::min(px_hi, big);
+  py_hi = std::min(py_hi, big);
+  long x_lo = static_cast<long>(std::floor(px_lo)) - 1;
+  long x_hi = static_cast<long>(std::ceil(px_hi)) + 1;
+  long y_lo = static_cast<long>(std::floor(py_lo)) - 1;
+  long y_hi = static_cast<long>(std::ceil(py_hi)) + 1;
+  x_lo = std::max<long>(x_lo, 0);
+  y_lo = std::max<long>(y_lo, 0);
+  x_hi = std::min<long>(x_hi, width - 1);
+  y_hi = std::min<long>(y_hi, height - 1);
+  if (x_lo > x_hi || y_lo > y_hi) return Rect{0, 0, 0, 0};
+  Rect r;
+  r.x0 = static_cast<int32_t>(x_lo) & ~3;
+  r.y0 = static_cast<int32_t>(y_lo);
+  r.w = (static_cast<int32_t>(x_hi) + 1 - r.x0 + 3) & ~3;
+  r.h = static_cast<int32_t>(y_hi - y_lo + 1);
+  return r;
+}
+
+// ---------------------------------------------------------------------------
+// Visibility ordering
+// ---------------------------------------------------------------------------
+void make_order_matrices(const amrvr_camera& cam, float aspect, OrderMatrices& m) {
+  const Frame3 fr = camera_frame(cam);
+  const V3 eye{cam.eye[0], cam.eye[1], cam.eye[2]};
+  float* v = m.view;
+  std::memset(v, 0, sizeof(m.view));
+  // Common/CameraUtils.hpp:41-60 writes basis vectors down the columns and the
+  // translation into the LAST ROW; reproduce the element positions, not the
+  // textbook matrix.
+  v[0 * 4 + 0] = static_cast<float>(fr.r.x);
+  v[1 * 4 + 0] = static_cast<float>(fr.r.y);
+  v[2 * 4 + 0] = static_cast<float>(fr.r.z);
+  v[3 * 4 + 0] = static_cast<float>(-dot(fr.r, eye));
+  v[0 * 4 + 1] = static_cast<float>(fr.u.x);
+  v[1 * 4 + 1] = static_cast<float>(fr.u.y);
+  v[2 * 4 + 1] = static_cast<float>(fr.u.z);
+  v[3 * 4 + 1] = static_cast<float>(-dot(fr.u, eye));
+  v[0 * 4 + 2] = static_cast<float>(-fr.f.x);
+  v[1 * 4 + 2] = static_cast<float>(-fr.f.y);
+  v[2 * 4 + 2] = static_cast<float>(-fr.f.z);
+  v[3 * 4 + 2] = static_cast<float>(dot(fr.f, eye));
+  v[3 * 4 + 3] = 1.0f;
+
+  float* p = m.proj;  // Common/VisibilityOrdering.cpp:34-59
+  std::memset(p, 0, sizeof(m.proj));
+  const float near_p = cam.near_plane, far_p = cam.far_plane;
+  const float half = near_p * std::tan(cam.fov_y_degrees * kPiF / 180.0f * 0.5f);
+  const float left = -half * aspect, right = half * aspect;
+  const float bottom = -half, top = half;
+  p[0 * 4 + 0] = 2.0f * near_p / (right - left);
+  p[1 * 4 + 1] = 2.0f * near_p / (top - bottom);
+  p[0 * 4 + 2] = (right + left) / (right - left);
+  p[1 * 4 + 2] = (top + bottom) / (top - bottom);
+  p[2 * 4 + 2] = -(far_p + near_p) / (far_p - near_p);
+  p[3 * 4 + 2] = -1.0f;
+  p[2 * 4 + 3] = -(2.0f * far_p * near_p) / (far_p - near_p);
+  p[3 * 4 + 3] = 0.0f;
+
+  m.dir[0] = static_cast<float>(fr.f.x);
+  m.dir[1] = static_cast<float>(fr.f.y);
+  m.dir[2] = static_cast<float>(fr.f.z);
+}
+
+namespace {
+inline void mul4(const float* a, const float* x, float* y) {
+  for (int r = 0; r < 4; ++r) {
+    float s = 0.0f;
+    for (int k = 0; k < 4; ++k) s += a[r * 4 + k] * x[k];
+    y[r] = s;
+  }
+}
+}  // namespace
+
+void order_box_depth_range(const OrderMatrices& m, OrderBox& b) {
+  float zmin = INFINITY, zmax = -INFINITY;
+  for (int c = 0; c < 8; ++c) {
+    const float h[4] = {(c & 1) ? b.hi[0] : b.lo[0], (c & 2) ? b.hi[1] : b.lo[1],
+                        (c & 4) ? b.hi[2] : b.lo[2], 1.0f};
+    float eye_space[4], clip[4];
+    mul4(m.view, h, eye_space);
+    mul4(m.proj, eye_space, clip);
+    if (clip[3] != 0.0f) {
+      const float z = clip[2] / clip[3];
+      zmin = fmin2(zmin, z);
+      zmax = fmax2(zmax, z);
+    }
+  }
+  if (!std::isfinite(zmin) || !std::isfinite(zmax)) zmin = zmax = INFINITY;
+  b.min_depth = zmin;
+  b.max_depth = zmax;
+}
+
+namespace {
+
+// Common/VisibilityOrdering.cpp:211-228
+inline bool touching(float a, float b) {
+  const float scale = fmax2(fmax2(1.0f, std::fabs(a)), std::fabs(b));
+  return std::fabs(a - b) <= 1e-5f * scale;
+}
+inline bool spans_overlap(float a0, float a1, float b0, float b1) {
+  const float lo = fmax2(a0, b0), hi = fmin2(a1, b1);
+  float scale = 1.0f;
+  for (float v : {a0, a1, b0, b1, lo, hi}) scale = fmax2(scale, std::fabs(v));
+  return (hi - lo) > 1e-5f * scale;
+}
+
+// total order of Common/VisibilityOrdering.cpp:238-257
+inline bool box_precedes(const std::vector<OrderBox>& boxes, int a, int b) {
+  const OrderBox& x = boxes[a];
+  const OrderBox& y = boxes[b];
+  const bool xf = std::isfinite(x.min_depth), yf = std::isfinite(y.min_depth);
+  if (xf != yf) return xf;
+  if (x.min_depth != y.min_depth) return x.min_depth < y.min_depth;
+  if (x.max_depth != y.max_depth) return x.max_depth < y.max_depth;
+  if (x.owner != y.owner) return x.owner < y.owner;
+  return a < b;
+}
+
+struct HostOrderBackend final : OrderBackend {
+  void rank_boxes(const std::vector<OrderBox>& boxes, std::vector<int32_t>& priority) override {
+    const int n = static_cast<int>(boxes.size());
+    std::vector<int> idx(n);
+    for (int i = 0; i < n; ++i) idx[i] = i;
+    std::sort(idx.begin(), idx.end(), [&](int a, int b) { return box_precedes(boxes, a, b); });
+    priority.assign(n, 0);
+    for (int p = 0; p < n; ++p) priority[idx[p]] = p;
+  }
+  void pair_edges(const std::vector<OrderBox>& boxes, const float* dir,
+                  std::vector<OrderEdge>& edges) override {
+    order_pair_edges_host(boxes, dir, edges);
+  }
+};
+
+}  // namespace
+
+OrderBackend* host_order_backend() {
+  static HostOrderBackend backend;
+  return &backend;
+}
+
+void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
+                           std::vector<OrderEdge>& edges) {
+  edges.clear();
+  const int n = static_cast<int>(boxes.size());
+  for (int i = 0; i < n; ++i) {
+    const OrderBox& a = boxes[i];
+    for (int j = i + 1; j < n; ++j) {
+      const OrderBox& b = boxes[j];
+      for (int axis = 0; axis < 3; ++axis) {
+        const int u = (axis + 1) % 3, v = (axis + 2) % 3;
+        if (!spans_overlap(a.lo[u], a.hi[u], b.lo[u], b.hi[u])) continue;
+        if (!spans_overlap(a.lo[v], a.hi[v], b.lo[v], b.hi[v])) continue;
+        const float along = dir[axis];
+        // a below b on this axis: looking up the axis (along > 0) puts a in front
+        int forward = -1;
+        if (touching(a.hi[axis], b.lo[axis])) {
+          if (along > 1e-6f) forward = 0;        // reference adds edge j -> i
+          else if (along < -1e-6f) forward = 1;  // edge i -> j
+        } else if (touching(b.hi[axis], a.lo[axis])) {
+          if (along > 1e-6f) forward = 1;
+          else if (along < -1e-6f) forward = 0;
+        }
+        if (forward >= 0) edges.push_back(OrderEdge{i, j, axis, forward});
+      }
+    }
+  }
+}
+
+namespace {
+
+struct Graph {
+  std::vector<std::vector<int>> out;
+  std::vector<int> indegree;
+};
+
+// adjacency lists in the reference's insertion order (:261-317): edges arrive
+// sorted by (i, j, axis); duplicates (same from->to) are dropped.
+void build_graph(int n, std::vector<OrderEdge>& edges, Graph& g) {
+  std::sort(edges.begin(), edges.end(), [](const OrderEdge& a, const OrderEdge& b) {
+    if (a.i != b.i) return a.i < b.i;
+    if (a.j != b.j) return a.j < b.j;
+    return a.axis < b.axis;
+  });
+  g.out.assign(n, {});
+  g.indegree.assign(n, 0);
+  for (const OrderEdge& e : edges) {
+    const int from = e.forward ? e.i : e.j;
+    const int to = e.forward ? e.j : e.i;
+    auto& list = g.out[from];
+    if (std::find(list.begin(), list.end(), to) != list.end()) continue;
+    list.push_back(to);
+    ++g.indegree[to];
+  }
+}
+
+// Kahn's algorithm taking, at each step, the ready box that comes first in the
+// compareBoxes order (:360-401 re-sorts the ready list and pops the front; a
+// min-heap on the precomputed priority picks the same box).
+bool topo_order(const Graph& g, const std::vector<int32_t>& priority, std::vector<int>& order,
+                std::vector<int>& residual) {
+  const int n = static_cast<int>(g.out.size());
+  residual = g.indegree;
+  using Item = std::pair<int32_t, int>;
+  std::priority_queue<Item, std::vector<Item>, std::greater<Item>> ready;
+  for (int i = 0; i < n; ++i)
+    if (residual[i] == 0) ready.push({priority[i], i});
+  order.clear();
+  order.reserve(n);
+  while (!ready.empty()) {
+    const int node = ready.top().second;
+    ready.pop();
+    order.push_back(node);
+    for (int next : g.out[node])
+      if (--residual[next] == 0) ready.push({priority[next], next});
+  }
+  return static_cast<int>(order.size()) == n;
+}
+
+// First cycle a depth-first walk meets, nodes in walk order (:403-443).
+// Iterative (the reference recurses); visiting order is identical.
+std::vector<int> first_cycle(const Graph& g, const std::vector<int>& residual) {
+  const int n = static_cast<int>(g.out.size());
+  std::vector<int> state(n, 0), parent(n, -1);
+  std::vector<size_t> cursor(n, 0);
+  std::vector<int> stack;
+  for (int root = 0; root < n; ++root) {
+    if (!(residual[root] > 0) || state[root] != 0) continue;
+    stack.assign(1, root);
+    state[root] = 1;
+    while (!stack.empty()) {
+      const int node = stack.back();
+      if (cursor[node] < g.out[node].size()) {
+        const int next = g.out[node][cursor[node]++];
+        if (state[next] == 0) {
+          parent[next] = node;
+          state[next] = 1;
+          stack.push_back(next);
+        } else if (state[next] == 1) {
+          std::vector<int> cycle{next};
+          for (int cur = node; cur != next && cur != -1; cur = parent[cur]) cycle.push_back(cur);
+          std::reverse(cycle.begin(), cycle.end());
+          return cycle;
+        }
+      } else {
+        state[node] = 2;
+        stack.pop_back();
+      }
+    }
+  }
+  return {};
+}
+
+// Cut the longest member of the cycle along the dominant view axis at another
+// member's face; the near half keeps the slot, the far half is appended
+// (:445-563).
+bool split_cycle_member(const std::vector<int>& cycle, std::vector<OrderBox>& boxes,
+                        const OrderMatrices& m) {
+  if (cycle.size() < 2) return false;
+  const float* dir = m.dir;
+  int axis = 0;
+  float strongest = std::fabs(dir[0]);
+  for (int a = 1; a < 3; ++a)
+    if (std::fabs(dir[a]) > strongest) {
+      strongest = std::fabs(dir[a]);
+      axis = a;
+    }
+  if (strongest <= 1e-6f) {
+    float widest = -1.0f;
+    for (int a = 0; a < 3; ++a)
+      for (int id : cycle) {
+        const float len = boxes[id].hi[a] - boxes[id].lo[a];
+        if (len > widest) {
+          widest = len;
+          axis = a;
+        }
+      }
+  }
+  const float along = dir[axis];
+  if (std::fabs(along) <= 1e-6f) return false;
+  int target = cycle.front();
+  float target_len = -1.0f;
+  for (int id : cycle) {
+    const float len = boxes[id].hi[axis] - boxes[id].lo[axis];
+    if (len > target_len && len > 1e-6f) {
+      target_len = len;
+      target = id;
+    }
+  }
+  if (target_len <= 1e-6f) return false;
+  const OrderBox whole = boxes[target];
+  const float lo = whole.lo[axis], hi = whole.hi[axis];
+  const float margin = fmax2(1e-5f * (hi - lo), 1e-6f);
+  bool any = false;
+  float cut_hi = 0.0f, cut_lo = 0.0f;
+  for (int id : cycle) {
+    if (id == target) continue;
+    for (float face : {boxes[id].lo[axis], boxes[id].hi[axis]}) {
+      if (!(face > lo + margin && face < hi - margin)) continue;
+      if (!any) {
+        cut_hi = cut_lo = face;
+        any = true;
+      } else {
+        if (cut_hi < face) cut_hi = face;
+        if (face < cut_lo) cut_lo = face;
+      }
+    }
+  }
+  float cut = 0.5f * (lo + hi);
+  if (any) cut = (along > 0.0f) ? cut_hi : cut_lo;
+  if (cut <= lo + margin) cut = lo + margin;
+  if (cut >= hi - margin) cut = hi - margin;
+  if (!(cut > lo && cut < hi)) return false;
+  OrderBox near_half = whole, far_half = whole;
+  if (along > 0.0f) {
+    near_half.hi[axis] = cut;
+    far_half.lo[axis] = cut;
+  } else {
+    near_half.lo[axis] = cut;
+    far_half.hi[axis] = cut;
+  }
+  order_box_depth_range(m, near_half);
+  order_box_depth_range(m, far_half);
+  boxes[target] = near_half;
+  boxes.push_back(far_half);
+  return true;
+}
+
+}  // namespace
+
+bool order_ranks(int nranks, int nglobal, const amrvr_box_record* recs,
+                 const amrvr_camera& cam, float aspect, bool use_graph,
+                 OrderBackend& backend, int* rank_order) {
+  for (int r = 0; r < nranks; ++r) rank_order[r] = r;
+  if (!use_graph || nglobal <= 0) return true;
+
+  OrderMatrices m;
+  make_order_matrices(cam, aspect, m);
+  std::vector<OrderBox> boxes(static_cast<size_t>(nglobal));
+  for (int i = 0; i < nglobal; ++i) {
+    for (int d = 0; d < 3; ++d) {
+      boxes[i].lo[d] = static_cast<float>(recs[i].min_corner[d]);
+      boxes[i].hi[d] = static_cast<float>(recs[i].max_corner[d]);
+    }
+    boxes[i].owner = recs[i].owner;
+    order_box_depth_range(m, boxes[i]);
+  }
+
+  const int max_rounds = std::max(nglobal, 1) * 8 + 32;  // :565-566
+  std::vector<OrderEdge> edges;
+  std::vector<int32_t> priority;
+  std::vector<int> order, residual;
+  Graph g;
+  for (int round = 0; round < max_rounds; ++round) {
+    const int n = static_cast<int>(boxes.size());
+    backend.pair_edges(boxes, m.dir, edges);
+    build_graph(n, edges, g);
+    backend.rank_boxes(boxes, priority);
+    if (topo_order(g, priority, order, residual)) {
+      std::vector<char> seen(static_cast<size_t>(nranks), 0);
+      int filled = 0;
+      for (int id : order) {  // :576-593 owners in first-appearance order
+        const int owner = boxes[id].owner;
+        if (owner >= 0 && owner < nranks && !seen[owner]) {
+          seen[owner] = 1;
+          rank_order[filled++] = owner;
+        }
+      }
+      for (int r = 0; r < nranks; ++r)
+        if (!seen[r]) rank_order[filled++] = r;
+      return true;
+    }
+    const std::vector<int> cycle = first_cycle(g, residual);
+    if (cycle.empty()) break;
+    if (!split_cycle_member(cycle, boxes, m)) break;
+  }
+  for (int r = 0; r < nranks; ++r) rank_order[r] = r;  // :615-623
+  return false;
+}
+
+// ---------------------------------------------------------------------------
+// Wireframe overlay geometry (VolumeRenderer.cpp:139-335, host part)
+// ---------------------------------------------------------------------------
+void make_overlay_edges(const double* tight_min, const double* tight_max,
+                        const amrvr_camera& cam, int sqrt_aa, int width, int height,
+                        OverlayEdges& out) {
+  std::memset(&out, 0, sizeof(out));
+  if (width <= 0 || height <= 0) return;
+  const Frame3 fr = camera_frame(cam);
+  const float aspect = static_cast<float>(width) / static_cast<float>(std::max(height, 1));
+  const float tan_half = std::tan(cam.fov_y_degrees * 0.5f * kPiF / 180.0f);
+  const float sx_scale = (width > 1) ? static_cast<float>(width - 1) : 0.0f;
+  const float sy_scale = (height > 1) ? static_cast<float>(height - 1) : 0.0f;
+  float sx[8], sy[8];
+  bool ok[8];
+  for (int c = 0; c < 8; ++c) {
+    const double p[3] = {(c & 1) ? tight_max[0] : tight_min[0],
+                         (c & 2) ? tight_max[1] : tight_min[1],
+                         (c & 4) ? tight_max[2] : tight_min[2]};
+    const V3 rel = sub(p, cam.eye);
+    ok[c] = false;
+    sx[c] = sy[c] = 0.0f;
+    const float depth = static_cast<float>(dot(rel, fr.f));
+    if (!(depth > 0.0f) || !std::isfinite(depth)) continue;
+    const float xc = static_cast<float>(dot(rel, fr.r));
+    const float yc = static_cast<float>(dot(rel, fr.u));
+    const float nx = xc / (depth * tan_half * aspect);
+    const float ny = yc / (depth * tan_half);
+    if (!std::isfinite(nx) || !std::isfinite(ny)) continue;
+    sx[c] = (nx * 0.5f + 0.5f) * sx_scale;
+    sy[c] = (ny * 0.5f + 0.5f) * sy_scale;
+    ok[c] = true;
+  }
+  static const int kEdge[12][2] = {{0, 1}, {1, 3}, {3, 2}, {2, 0}, {4, 5}, {5, 7},
+                                   {7, 6}, {6, 4}, {0, 4}, {1, 5}, {2, 6}, {3, 7}};
+  const float reach = 0.5f * static_cast<float>(std::max(sqrt_aa, 1)) + 0.5f;
+  for (int e = 0; e < 12; ++e) {
+    const int a = kEdge[e][0], b = kEdge[e][1];
+    if (!ok[a] || !ok[b]) continue;
+    const int k = out.count++;
+    out.ax[k] = sx[a];
+    out.ay[k] = sy[a];
+    out.bx[k] = sx[b];
+    out.by[k] = sy[b];
+    const float ex = sx[b] - sx[a], ey = sy[b] - sy[a];
+    out.degenerate[k] = !((ex * ex + ey * ey) > 0.0f);
+    if (out.degenerate[k]) {
+      out.x0[k] = out.x1[k] = static_cast<int32_t>(std::lround(sx[a]));
+      out.y0[k] = out.y1[k] = static_cast<int32_t>(std::lround(sy[a]));
+      continue;
+    }
+    out.x0[k] = std::max(0, static_cast<int>(std::floor(fmin2(sx[a], sx[b]) - reach)));
+    out.x1[k] = std::min(width - 1, static_cast<int>(std::ceil(fmax2(sx[a], sx[b]) + reach)));
+    out.y0[k] = std::max(0, static_cast<int>(std::floor(fmin2(sy[a], sy[b]) - reach)));
+    out.y1[k] = std::min(height - 1, static_cast<int>(std::ceil(fmax2(sy[a], sy[b]) + reach)));
+  }
+}
+
+}  // namespace amrvr

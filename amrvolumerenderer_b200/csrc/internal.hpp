@@ -1,0 +1,190 @@
+// internal.hpp -- declarations shared by the host logic, the CUDA kernels and the
+// C ABI of libamrvr_b200.so.  Not installed; include/amrvr.h is the public face.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/amrvr.h"
+
+namespace amrvr {
+
+// ----------------------------------------------------------------- host logic
+// (host_logic.cpp; pure CPU, callable without a GPU)
+
+struct CameraBasis {
+  // double-precision frame, then the float copies the march uses
+  // (reference: Common/VolumePainter.cpp:631-656).
+  double fwd_d[3], right_d[3], up_d[3];
+  float eye[3], fwd[3], right[3], up[3];
+};
+void make_camera_basis(const amrvr_camera& cam, CameraBasis& out);
+
+// Transfer-function table (reference: Common/VolumePainter.cpp:107-516).
+void build_color_table(float alpha_scale, float norm_factor, float range_min,
+                       float range_max, const amrvr_colormap_pt* pts, int npts,
+                       float* rgba256);
+
+// Step length and opacity-normalisation factor of one box
+// (reference: Common/VolumePainter.cpp:571-610).
+void box_sampling(const double* min_corner, const double* max_corner,
+                  const int32_t* dims, float reference_sample_distance,
+                  float* step, float* norm_factor);
+
+// reference: VolumeRenderer/VolumeRenderer.cpp:541-553
+float box_depth_hint(const amrvr_box_record& rec, const amrvr_camera& cam);
+// reference: DirectSend/Base/DirectSendBase.cpp:363-388
+void layer_order(int nglobal, const amrvr_box_record* recs,
+                 const amrvr_camera& cam, float* hints, int* order);
+// reference: DirectSend/Base/DirectSendBase.cpp:59-74
+void piece_range(int num_pixels, int piece, int num_pieces, int* begin, int* end);
+// reference: VolumeRenderer/VolumeRenderer.cpp:1138-1190
+float reference_sample_distance(int nglobal, const amrvr_box_record* recs,
+                                const double* bounds_min, const double* bounds_max);
+
+// Box as the visibility graph sees it: float-truncated corners, owner and NDC
+// depth interval (reference: Common/VisibilityOrdering.cpp:103-207).
+struct OrderBox {
+  float lo[3], hi[3];
+  int32_t owner;
+  float min_depth, max_depth;
+};
+struct OrderMatrices {
+  float view[16];  // row-major 4x4
+  float proj[16];
+  float dir[3];    // float view direction
+};
+void make_order_matrices(const amrvr_camera& cam, float aspect, OrderMatrices& m);
+void order_box_depth_range(const OrderMatrices& m, OrderBox& b);
+
+// One directed "in front of" relation found by the pair test, tagged with the
+// moment the reference would have inserted it (pair (i,j), i<j, axis).
+struct OrderEdge {
+  int32_t i, j;     // the pair, i < j
+  int32_t axis;     // 0..2
+  int32_t forward;  // 1: edge i->j, 0: edge j->i
+};
+// Host pair test (used when no GPU context is given and as the definition the
+// device kernel must match).  Appends edges in (i, j, axis) order.
+void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
+                           std::vector<OrderEdge>& edges);
+
+// Callbacks let the same sequential driver run with device or host back ends.
+struct OrderBackend {
+  virtual ~OrderBackend() = default;
+  // priority[i] = position of box i in the total order of
+  // VisibilityOrdering.cpp:238-257 (compareBoxes).
+  virtual void rank_boxes(const std::vector<OrderBox>& boxes,
+                          std::vector<int32_t>& priority) = 0;
+  virtual void pair_edges(const std::vector<OrderBox>& boxes, const float* dir,
+                          std::vector<OrderEdge>& edges) = 0;
+};
+OrderBackend* host_order_backend();
+// Full ordering (reference: Common/VisibilityOrdering.cpp:63-632).  Returns
+// true when the graph could be ordered; rank_order is identity otherwise.
+bool order_ranks(int nranks, int nglobal, const amrvr_box_record* recs,
+                 const amrvr_camera& cam, float aspect, bool use_graph,
+                 OrderBackend& backend, int* rank_order);
+
+// Screen-space footprint of a box: a conservative pixel rectangle that
+// contains every pixel whose centre ray can hit the box.  x0 and w are
+// multiples of 4 (w may overhang the frame on the right).  Empty boxes give
+// w = h = 0.
+struct Rect {
+  int32_t x0, y0, w, h;
+};
+Rect box_footprint(const double* min_corner, const double* max_corner,
+                   const int32_t* dims, const CameraBasis& basis,
+                   const amrvr_camera& cam, int width, int height);
+
+// Wireframe overlay geometry (reference: VolumeRenderer.cpp:139-335): projected
+// corners of the tight bounds; the per-pixel coverage runs in a kernel.
+struct OverlayEdges {
+  int32_t count;
+  float ax[12], ay[12], bx[12], by[12];
+  int32_t x0[12], x1[12], y0[12], y1[12];
+  int32_t degenerate[12];
+};
+void make_overlay_edges(const double* tight_min, const double* tight_max,
+                        const amrvr_camera& cam, int sqrt_aa, int width,
+                        int height, OverlayEdges& out);
+
+// ------------------------------------------------------------ device structs
+
+struct MarchBox {
+  float lo[3], hi[3];
+  float cell[3];       // dx, dy, dz (float, as the reference derives them)
+  int32_t n[3];
+  float step, eps;
+  int32_t table;       // index of the 256-entry table this box uses
+  int32_t rx0, ry0, rw, rh;
+  int32_t tile_base;   // first tile id of this box in the launch
+  int32_t tiles_x;
+  int32_t exact_recip; // 1: cell sizes are powers of two -> multiply by inverse is exact
+  float inv_cell[3];
+  uint64_t brick_off;  // byte offset into the brick pool
+  uint64_t layer_off;  // float offset into the layer pool
+};
+
+struct MarchFrame {
+  float eye[3], fwd[3], right[3], up[3];
+  float tan_half, aspect, inv_w, inv_h;
+  int32_t width, height;
+  int32_t nboxes, ntiles;
+};
+
+// One layer as the fold kernel sees it, already in global blend order.
+struct FoldLayer {
+  const float* base;   // row r of the available slice at base + r*w*5
+  int32_t x0, w;       // footprint rectangle origin (x) and padded width
+  int32_t row0, row1;  // rows [row0,row1) of the frame held at `base`
+  int32_t run;         // id of the same-owner run this layer belongs to
+  int32_t pad;
+};
+
+// A byte range to copy when packing slices for the exchange.
+struct CopyJob {
+  uint64_t src_off, dst_off;  // in floats
+  uint32_t count;             // floats, multiple of 4
+  uint32_t pad;
+};
+
+// ------------------------------------------------------------ kernel launchers
+// (kernels.cu; every launcher returns the cudaError_t of the launch as int and
+// bumps *launches by the number of kernels it started)
+
+int launch_brick_stats(const double* data, int64_t jstride, int64_t kstride,
+                       int nx, int ny, int nz, double* partials /*[4*blocks]*/,
+                       int blocks, void* stream, int64_t* launches);
+int launch_brick_stats_final(const double* partials, int nparts, double* out4,
+                             void* stream, int64_t* launches);
+int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride,
+                          int nx, int ny, int nz,
+                          const amrvr_scalar_transform& t, float range_min,
+                          float range_max, uint8_t* brick, void* stream,
+                          int64_t* launches);
+int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev,
+                    const uint8_t* bricks, const float* tables, float* layers,
+                    unsigned long long* sample_counter, bool count_samples,
+                    void* stream, int64_t* launches);
+int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
+                int pixel_begin, int pixel_end, float* piece5, void* stream,
+                int64_t* launches);
+int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst,
+                void* stream, int64_t* launches);
+int launch_downsample(const float* src5, int width, int height, int sqrt_aa,
+                      float* dst5, void* stream, int64_t* launches);
+int launch_overlay(const OverlayEdges& edges, int sqrt_aa, int width, int height,
+                   float* image5, void* stream, int64_t* launches);
+int launch_quantize_rgb8(const float* image5, int width, int height,
+                         uint8_t* rgb8, void* stream, int64_t* launches);
+int launch_order_rank(const OrderBox* boxes_dev, int n, void* scratch_a /*16 B per box*/,
+                      void* scratch_b, int owner_bits, int32_t* priority_dev,
+                      void* stream, int64_t* launches);
+int launch_order_pairs(const OrderBox* boxes_dev, int n, float dx, float dy,
+                       float dz, OrderEdge* edges_dev, int capacity,
+                       int32_t* count_dev, void* stream, int64_t* launches);
+
+}  // namespace amrvr

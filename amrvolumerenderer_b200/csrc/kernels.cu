@@ -1,0 +1,879 @@
+// kernels.cu -- sm_100a kernels of the hot path.  Compiled with -fmad=false: the
+// reference's default x86-64 build never contracts a*b+c, and position, cell
+// index and blend arithmetic must round the same way.
+// Division and sqrt stay IEEE (-prec-div/-prec-sqrt defaults, no fast-math).
+//
+//   brick_stats_kernel      K2  min / max / min-positive / finite count (HBM: 8 B/cell)
+//   brick_quantise_kernel   K5  FAB double -> colour-table index byte  (HBM: 9 B/cell)
+//   raymarch_bricks_kernel  K1  all (box, 16x16 pixel tile) pairs of a rank, one launch
+//   fold_layers_kernel      K6  per-pixel run-structured depth-swap 'over'
+//   pack_slices_kernel      C6  gather row slices into per-destination send buffers
+//   downsample_kernel       K8  box filter
+//   overlay_kernel               wireframe coverage
+//   quantize_rgb8_kernel         float -> byte, rows flipped
+//   order_rank_kernel       K7  single-CTA LSD radix sort of box depth keys
+//   order_pairs_kernel      K7  all-pairs face-adjacency test
+#include <cuda_runtime.h>
+
+#include <cfloat>
+#include <cmath>
+
+#include "internal.hpp"
+
+namespace amrvr {
+
+namespace {
+
+constexpr int kTile = 16;          // march tile edge in pixels
+constexpr int kMarchThreads = 256; // 8 warps, each an 8x4 pixel patch
+
+__device__ __forceinline__ float clamp01(float v) {
+  return (v < 0.0f) ? 0.0f : ((v > 1.0f) ? 1.0f : v);
+}
+
+// ------------------------------------------------------------------ K2 / K5
+
+struct ValuePath {  // frame constants of the per-cell value path
+  int log_scale, normalize;
+  double positive_floor, norm_min, inv_norm_span;
+  float range_min, inv_range, clip_start;
+  int apply_clip;
+};
+
+// reference: Common/VolumeTypes.hpp:33-67 + Common/VolumePainter.cpp:75-105, 870-883
+__device__ __forceinline__ unsigned char cell_to_index(double raw, const ValuePath& p) {
+  double v = isfinite(raw) ? raw : 0.0;
+  if (p.log_scale) {
+    if (!(v > 0.0) || v < p.positive_floor) v = p.positive_floor;
+    v = log(v);
+  }
+  if (p.normalize) {
+    v = (v - p.norm_min) * p.inv_norm_span;
+    v = (v < 0.0) ? 0.0 : ((v > 1.0) ? 1.0 : v);
+  }
+  float s = static_cast<float>(v);
+  if (p.apply_clip) {  // soft roll-off between clip_start and 1
+    const float end = (p.clip_start < 1.0f) ? 1.0f : p.clip_start;
+    float c = (s < 0.0f) ? 0.0f : ((s > end) ? end : s);
+    if ((end > p.clip_start + 1e-5f) && (c > p.clip_start)) {
+      if (!(c < end)) {
+        c = end;
+      } else {
+        const float n = (c - p.clip_start) / (end - p.clip_start);
+        const float smooth = n + n * n - n * n * n;
+        c = p.clip_start + (end - p.clip_start) * smooth;
+      }
+    }
+    s = c;
+  }
+  float t = (s - p.range_min) * p.inv_range;
+  t = (t < 0.0f) ? 0.0f : t;
+  t = (t > 1.0f) ? 1.0f : t;
+  int idx = static_cast<int>(t * 255.0f);
+  idx = (idx < 0) ? 0 : ((idx > 255) ? 255 : idx);
+  return static_cast<unsigned char>(idx);
+}
+
+__global__ void __launch_bounds__(256)
+brick_quantise_kernel(const double* __restrict__ data, long long jstride, long long kstride,
+                      int nx, int ny, int nz, ValuePath p, unsigned char* __restrict__ brick) {
+  // one thread per 4 consecutive cells of a row; rows are nx cells, i fastest
+  const int quads_per_row = (nx + 3) >> 2;
+  const long long nquads = static_cast<long long>(quads_per_row) * ny * nz;
+  for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < nquads;
+       q += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int qi = static_cast<int>(q % quads_per_row);
+    const long long row = q / quads_per_row;
+    const int j = static_cast<int>(row % ny);
+    const int k = static_cast<int>(row / ny);
+    const double* src = data + j * jstride + k * kstride + 4 * qi;
+    unsigned char* dst = brick + (static_cast<long long>(k) * ny + j) * nx + 4 * qi;
+    const int left = nx - 4 * qi;
+    if (left >= 4 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
+        ((reinterpret_cast<uintptr_t>(dst) & 3) == 0)) {
+      const double2 a = __ldcs(reinterpret_cast<const double2*>(src));
+      const double2 b = __ldcs(reinterpret_cast<const double2*>(src) + 1);
+      uchar4 o;
+      o.x = cell_to_index(a.x, p);
+      o.y = cell_to_index(a.y, p);
+      o.z = cell_to_index(b.x, p);
+      o.w = cell_to_index(b.y, p);
+      *reinterpret_cast<uchar4*>(dst) = o;
+    } else {
+      for (int c = 0; c < left && c < 4; ++c) dst[c] = cell_to_index(src[c], p);
+    }
+  }
+}
+
+struct Stats4 {
+  double lo, hi, lo_pos;
+  long long finite;
+};
+
+__device__ __forceinline__ void stats_merge(Stats4& a, const Stats4& b) {
+  a.lo = fmin(a.lo, b.lo);
+  a.hi = fmax(a.hi, b.hi);
+  a.lo_pos = fmin(a.lo_pos, b.lo_pos);
+  a.finite += b.finite;
+}
+
+__device__ __forceinline__ Stats4 stats_block_reduce(Stats4 s) {
+  __shared__ Stats4 part[32];
+  for (int off = 16; off > 0; off >>= 1) {
+    Stats4 o;
+    o.lo = __shfl_down_sync(0xffffffffu, s.lo, off);
+    o.hi = __shfl_down_sync(0xffffffffu, s.hi, off);
+    o.lo_pos = __shfl_down_sync(0xffffffffu, s.lo_pos, off);
+    o.finite = __shfl_down_sync(0xffffffffu, s.finite, off);
+    stats_merge(s, o);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) part[warp] = s;
+  __syncthreads();
+  if (warp == 0) {
+    const int nwarps = (blockDim.x + 31) >> 5;
+    Stats4 t = (lane < nwarps) ? part[lane] : Stats4{INFINITY, -INFINITY, INFINITY, 0};
+    for (int off = 16; off > 0; off >>= 1) {
+      Stats4 o;
+      o.lo = __shfl_down_sync(0xffffffffu, t.lo, off);
+      o.hi = __shfl_down_sync(0xffffffffu, t.hi, off);
+      o.lo_pos = __shfl_down_sync(0xffffffffu, t.lo_pos, off);
+      o.finite = __shfl_down_sync(0xffffffffu, t.finite, off);
+      stats_merge(t, o);
+    }
+    s = t;
+  }
+  return s;
+}
+
+// reference: VolumeRenderer/SceneBuilder.cpp:53-94 (non-finite cells are skipped)
+__global__ void __launch_bounds__(256)
+brick_stats_kernel(const double* __restrict__ data, long long jstride, long long kstride, int nx,
+                   int ny, int nz, double* __restrict__ partials) {
+  Stats4 s{INFINITY, -INFINITY, INFINITY, 0};
+  const long long ncells = static_cast<long long>(nx) * ny * nz;
+  for (long long c = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; c < ncells;
+       c += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int i = static_cast<int>(c % nx);
+    const long long row = c / nx;
+    const int j = static_cast<int>(row % ny);
+    const int k = static_cast<int>(row / ny);
+    const double v = __ldcs(data + i + j * jstride + k * kstride);
+    if (isfinite(v)) {
+      s.lo = fmin(s.lo, v);
+      s.hi = fmax(s.hi, v);
+      if (v > 0.0) s.lo_pos = fmin(s.lo_pos, v);
+      ++s.finite;
+    }
+  }
+  s = stats_block_reduce(s);
+  if (threadIdx.x == 0) {
+    double* o = partials + 4 * blockIdx.x;
+    o[0] = s.lo;
+    o[1] = s.hi;
+    o[2] = s.lo_pos;
+    o[3] = __longlong_as_double(s.finite);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+brick_stats_final_kernel(const double* __restrict__ partials, int nparts, double* __restrict__ out4) {
+  Stats4 s{INFINITY, -INFINITY, INFINITY, 0};
+  for (int p = threadIdx.x; p < nparts; p += blockDim.x) {
+    Stats4 o{partials[4 * p], partials[4 * p + 1], partials[4 * p + 2],
+             __double_as_longlong(partials[4 * p + 3])};
+    stats_merge(s, o);
+  }
+  s = stats_block_reduce(s);
+  if (threadIdx.x == 0) {
+    out4[0] = s.lo;
+    out4[1] = s.hi;
+    out4[2] = s.lo_pos;
+    out4[3] = __longlong_as_double(s.finite);
+  }
+}
+
+// ------------------------------------------------------------------------ K1
+
+// One CTA = one 16x16 pixel tile of one box's screen footprint; one thread = one
+// (ray, box) pair, marched with the reference's serial float recurrence
+// distance += step (Common/VolumePainter.cpp:735-922).  Cooperation is across
+// rays only: the transfer table is staged once per CTA in shared memory, warps
+// are 8x4 pixel patches so the bytes a warp gathers from the brick share L1
+// lines, and stores are whole 128 B row segments.
+template <bool kCount>
+__global__ void __launch_bounds__(kMarchThreads)
+raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __restrict__ boxes,
+                       const unsigned char* __restrict__ bricks,
+                       const float4* __restrict__ tables, float* __restrict__ layers,
+                       unsigned long long* __restrict__ sample_counter) {
+  __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE];
+  __shared__ MarchBox s_box;
+  __shared__ int s_which;
+
+  const int tile = blockIdx.x;
+  if (threadIdx.x == 0) {  // last box whose first tile is <= tile
+    int lo = 0, hi = f.nboxes - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (boxes[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+    }
+    s_which = lo;
+  }
+  __syncthreads();
+  {
+    const int words = sizeof(MarchBox) / 4;
+    const int* src = reinterpret_cast<const int*>(boxes + s_which);
+    if (threadIdx.x < words) reinterpret_cast<int*>(&s_box)[threadIdx.x] = src[threadIdx.x];
+  }
+  __syncthreads();
+  s_table[threadIdx.x] = tables[s_box.table * AMRVR_COLOR_TABLE_SIZE + threadIdx.x];
+  __syncthreads();
+
+  const int local_tile = tile - s_box.tile_base;
+  const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
+  const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
+  const int rw = s_box.rw;
+  const bool valid = x < rw && y < s_box.rh;
+  const int px = s_box.rx0 + x, py = s_box.ry0 + y;
+
+  const float lox = s_box.lo[0], loy = s_box.lo[1], loz = s_box.lo[2];
+  const float hix = s_box.hi[0], hiy = s_box.hi[1], hiz = s_box.hi[2];
+  const float ex = f.eye[0], ey = f.eye[1], ez = f.eye[2];
+
+  // ray through the pixel centre (:738-766)
+  const float ndc_x = (static_cast<float>(px) + 0.5f) * f.inv_w * 2.0f - 1.0f;
+  const float ndc_y = (static_cast<float>(py) + 0.5f) * f.inv_h * 2.0f - 1.0f;
+  const float plane_x = ndc_x * f.tan_half * f.aspect;
+  const float plane_y = ndc_y * f.tan_half;
+  float dx = f.fwd[0] + plane_x * f.right[0] + plane_y * f.up[0];
+  float dy = f.fwd[1] + plane_x * f.right[1] + plane_y * f.up[1];
+  float dz = f.fwd[2] + plane_x * f.right[2] + plane_y * f.up[2];
+  const float len_sq = dx * dx + dy * dy + dz * dz;
+  // host rsqrt of the reference is 1.0/sqrt(x) evaluated in double on a float
+  const float len = (len_sq > 0.0f)
+                        ? (1.0f / static_cast<float>(1.0 / static_cast<double>(sqrtf(len_sq))))
+                        : 0.0f;
+  if (len > 0.0f) {
+    const float inv = 1.0f / len;
+    dx *= inv;
+    dy *= inv;
+    dz *= inv;
+  }
+
+  // slab test (:768-809)
+  float tmin = -INFINITY, tmax = INFINITY;
+  {
+    const float o[3] = {ex, ey, ez}, d[3] = {dx, dy, dz};
+    const float lo3[3] = {lox, loy, loz}, hi3[3] = {hix, hiy, hiz};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      if (fabsf(d[a]) < 1e-8f) {
+        if (o[a] < lo3[a] || o[a] > hi3[a]) {
+          tmin = INFINITY;
+          tmax = -INFINITY;
+        }
+      } else {
+        const float inv = 1.0f / d[a];
+        float t1 = (lo3[a] - o[a]) * inv, t2 = (hi3[a] - o[a]) * inv;
+        if (t1 > t2) {
+          const float t = t1;
+          t1 = t2;
+          t2 = t;
+        }
+        tmin = (tmin > t1) ? tmin : t1;
+        tmax = (tmax < t2) ? tmax : t2;
+      }
+    }
+  }
+
+  float acc_r = 0.0f, acc_g = 0.0f, acc_b = 0.0f, acc_a = 0.0f;
+  float depth = INFINITY;
+  unsigned int nsamples = 0;
+  if (valid && tmax >= tmin) {
+    const float step = s_box.step;
+    float distance = tmin + s_box.eps;
+    if (distance < 0.0f) distance = s_box.eps;
+    float pxs = ex + dx * distance, pys = ey + dy * distance, pzs = ez + dz * distance;
+    auto outside = [&]() {
+      return pxs < lox || pxs > hix || pys < loy || pys > hiy || pzs < loz || pzs > hiz;
+    };
+    while (distance < tmax && outside()) {  // :827-835
+      distance += step;
+      pxs = ex + dx * distance;
+      pys = ey + dy * distance;
+      pzs = ez + dz * distance;
+    }
+    const int nx = s_box.n[0], ny = s_box.n[1], nz = s_box.n[2];
+    const unsigned char* __restrict__ brick = bricks + s_box.brick_off;
+    const bool recip = s_box.exact_recip != 0;
+    const float cx = recip ? s_box.inv_cell[0] : s_box.cell[0];
+    const float cy = recip ? s_box.inv_cell[1] : s_box.cell[1];
+    const float cz = recip ? s_box.inv_cell[2] : s_box.cell[2];
+    while (distance < tmax && acc_a < 1.0f) {  // :837-900
+      if (!outside()) {
+        // power-of-two cell sizes: multiplying by the inverse is the same
+        // rounding as the reference's division
+        const float fx = recip ? (pxs - lox) * cx : (pxs - lox) / cx;
+        const float fy = recip ? (pys - loy) * cy : (pys - loy) / cy;
+        const float fz = recip ? (pzs - loz) * cz : (pzs - loz) / cz;
+        int i = static_cast<int>(floorf(fx));
+        int j = static_cast<int>(floorf(fy));
+        int k = static_cast<int>(floorf(fz));
+        i = (i < 0) ? 0 : ((i >= nx) ? nx - 1 : i);
+        j = (j < 0) ? 0 : ((j >= ny) ? ny - 1 : j);
+        k = (k < 0) ? 0 : ((k >= nz) ? nz - 1 : k);
+        const unsigned int idx = __ldg(brick + (static_cast<size_t>(k) * ny + j) * nx + i);
+        const float4 e = s_table[idx];
+        const float a = e.w * (1.0f - acc_a);
+        acc_r += e.x * a;
+        acc_g += e.y * a;
+        acc_b += e.z * a;
+        acc_a += a;
+        if (kCount) ++nsamples;
+      }
+      distance += step;
+      pxs = ex + dx * distance;
+      pys = ey + dy * distance;
+      pzs = ez + dz * distance;
+    }
+    acc_r = (acc_r > 1.0f) ? 1.0f : acc_r;
+    acc_g = (acc_g > 1.0f) ? 1.0f : acc_g;
+    acc_b = (acc_b > 1.0f) ? 1.0f : acc_b;
+    acc_a = (acc_a > 1.0f) ? 1.0f : acc_a;
+    if (acc_a > 0.0f) {  // entry depth along the view axis (:912-921)
+      const float qx = ex + dx * tmin, qy = ey + dy * tmin, qz = ez + dz * tmin;
+      depth = (qx - ex) * f.fwd[0] + (qy - ey) * f.fwd[1] + (qz - ez) * f.fwd[2];
+    }
+  }
+  // host epilogue of the reference (:939-955)
+  float4 out = make_float4(clamp01(acc_r), clamp01(acc_g), clamp01(acc_b), clamp01(acc_a));
+  if (!isfinite(depth) || out.w <= 0.0f) depth = INFINITY;
+  if (valid) {
+    float* row = layers + s_box.layer_off + static_cast<size_t>(y) * rw * 5;
+    reinterpret_cast<float4*>(row)[x] = out;
+    row[4 * rw + x] = depth;
+  }
+  if (kCount) {
+    for (int off = 16; off > 0; off >>= 1) nsamples += __shfl_down_sync(0xffffffffu, nsamples, off);
+    if (lane == 0 && nsamples != 0)
+      atomicAdd(sample_counter, static_cast<unsigned long long>(nsamples));
+  }
+}
+
+// ------------------------------------------------------------------------ K6
+
+struct Px5 {
+  float r, g, b, a, d;
+};
+
+// reference: Common/ImageRGBAFloatColorDepthSort.hpp:13-27
+__device__ __forceinline__ Px5 blend_depth_swap(const Px5& top, const Px5& bottom) {
+  const bool top_front = top.d <= bottom.d;
+  const Px5& fr = top_front ? top : bottom;
+  const Px5& bk = top_front ? bottom : top;
+  const float t = 1.0f - fr.a;
+  Px5 o;
+  o.r = fr.r + bk.r * t;
+  o.g = fr.g + bk.g * t;
+  o.b = fr.b + bk.b * t;
+  o.a = fr.a + bk.a * t;
+  o.d = (bottom.d < top.d) ? bottom.d : top.d;
+  return o;
+}
+
+constexpr int kFoldThreads = 256;
+
+struct FoldEntry {  // FoldLayer narrowed for shared memory
+  const float* base;
+  int x0, w, row0, row1, run;
+};
+
+// One CTA = 256 consecutive pixels of this rank's piece.  The CTA filters the
+// globally ordered layer list down to the layers whose footprint touches its
+// pixel span (ordered compaction, 256 layers per round), then every thread
+// folds its pixel over that short list: consecutive layers of one run are
+// blended first, then the run result is blended into the accumulator --
+// DirectSendBase::composeLayered, per pixel (DirectSendBase.cpp:400-446).
+__global__ void __launch_bounds__(kFoldThreads)
+fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
+                   int width, int pixel_begin, int pixel_end, float* __restrict__ piece5) {
+  __shared__ FoldEntry s_list[kFoldThreads];
+  __shared__ int s_warp_count[kFoldThreads / 32];
+  __shared__ float s_out[kFoldThreads * 5];
+
+  const int first = pixel_begin + blockIdx.x * kFoldThreads;
+  const int last = min(first + kFoldThreads, pixel_end) - 1;  // inclusive
+  const int p = first + threadIdx.x;
+  const bool live = p <= last;
+  const int px = p % width, py = p / width;
+  const int y_first = first / width, y_last = last / width;
+  // x span of the CTA: one row -> exact, else whole rows
+  const int x_first = (y_first == y_last) ? (first % width) : 0;
+  const int x_last = (y_first == y_last) ? (last % width) : (width - 1);
+
+  Px5 acc{0.f, 0.f, 0.f, 0.f, INFINITY}, run{0.f, 0.f, 0.f, 0.f, INFINITY};
+  bool have_acc = false, have_run = false;
+  int cur_run = -1;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  for (int chunk = 0; chunk < nlayers; chunk += kFoldThreads) {
+    const int l = chunk + threadIdx.x;
+    bool keep = false;
+    FoldLayer L;
+    if (l < nlayers) {
+      L = layers[l];
+      keep = L.row0 <= y_last && L.row1 > y_first && L.x0 <= x_last && L.x0 + L.w > x_first;
+    }
+    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_warp_count[warp] = __popc(ballot);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kFoldThreads / 32; ++w) {
+      const int c = s_warp_count[w];
+      if (w < warp) before += c;
+      total += c;
+    }
+    if (keep) {
+      const int slot = before + __popc(ballot & ((1u << lane) - 1u));
+      s_list[slot] = FoldEntry{L.base, L.x0, L.w, L.row0, L.row1, L.run};
+    }
+    __syncthreads();
+    if (live) {
+      for (int e = 0; e < total; ++e) {
+        const FoldEntry& E = s_list[e];
+        if (E.run != cur_run) {
+          if (have_run) {
+            acc = have_acc ? blend_depth_swap(acc, run) : run;
+            have_acc = true;
+            have_run = false;
+          }
+          cur_run = E.run;
+        }
+        const int cx = px - E.x0;
+        if (py >= E.row0 && py < E.row1 && cx >= 0 && cx < E.w) {
+          const float* rowp = E.base + static_cast<size_t>(py - E.row0) * E.w * 5;
+          const float4 c = __ldg(reinterpret_cast<const float4*>(rowp) + cx);
+          const float d = __ldg(rowp + 4 * E.w + cx);
+          const Px5 frag{c.x, c.y, c.z, c.w, d};
+          run = have_run ? blend_depth_swap(run, frag) : frag;
+          have_run = true;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  if (have_run) {
+    acc = have_acc ? blend_depth_swap(acc, run) : run;
+    have_acc = true;
+  }
+  if (!have_acc) acc = Px5{0.f, 0.f, 0.f, 0.f, INFINITY};  // DirectSendBase.cpp:450-455
+  float* o = s_out + threadIdx.x * 5;
+  o[0] = acc.r;
+  o[1] = acc.g;
+  o[2] = acc.b;
+  o[3] = acc.a;
+  o[4] = acc.d;
+  __syncthreads();
+  const int nfloats = (last - first + 1) * 5;
+  float* dst = piece5 + static_cast<size_t>(first - pixel_begin) * 5;
+  for (int i = threadIdx.x; i < nfloats; i += kFoldThreads) dst[i] = s_out[i];
+}
+
+// ------------------------------------------------------------------------ C6
+
+__global__ void __launch_bounds__(256)
+pack_slices_kernel(const CopyJob* __restrict__ jobs, const float* __restrict__ src,
+                   float* __restrict__ dst) {
+  const CopyJob job = jobs[blockIdx.x];
+  const float4* s = reinterpret_cast<const float4*>(src + job.src_off);
+  float4* d = reinterpret_cast<float4*>(dst + job.dst_off);
+  const unsigned n4 = job.count >> 2;
+  for (unsigned i = threadIdx.x; i < n4; i += blockDim.x) d[i] = s[i];
+}
+
+// ------------------------------------------------------------------ K8, post
+
+// reference: VolumeRenderer/VolumeRenderer.cpp:479-528 (sum order dy-major, dx-minor)
+__global__ void __launch_bounds__(256)
+downsample_kernel(const float* __restrict__ src5, int width, int height, int block,
+                  float* __restrict__ dst5) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= width * height) return;
+  const int x = p % width, y = p / width;
+  const int src_w = width * block;
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+  for (int dy = 0; dy < block; ++dy)
+    for (int dx = 0; dx < block; ++dx) {
+      const float* s = src5 + 5 * (static_cast<size_t>(y * block + dy) * src_w + (x * block + dx));
+      s0 += s[0];
+      s1 += s[1];
+      s2 += s[2];
+      s3 += s[3];
+    }
+  const float inv = 1.0f / static_cast<float>(block * block);
+  float* d = dst5 + 5 * static_cast<size_t>(p);
+  d[0] = s0 * inv;
+  d[1] = s1 * inv;
+  d[2] = s2 * inv;
+  d[3] = s3 * inv;
+  d[4] = INFINITY;
+}
+
+// reference: VolumeRenderer/VolumeRenderer.cpp:228-333.  One thread per pixel walks
+// the 12 edges in order, so overlapping edges blend in the reference's order.
+__global__ void __launch_bounds__(256)
+overlay_kernel(const __grid_constant__ OverlayEdges edges, float pixel_radius, int width, int height,
+               float* __restrict__ image5) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= width * height) return;
+  const int px = p % width, py = p / width;
+  float* b = image5 + 5 * static_cast<size_t>(p);
+  float c0 = b[0], c1 = b[1], c2 = b[2], c3 = b[3], c4 = b[4];
+  bool touched = false;
+  for (int e = 0; e < edges.count; ++e) {
+    if (px < edges.x0[e] || px > edges.x1[e] || py < edges.y0[e] || py > edges.y1[e]) continue;
+    float coverage;
+    if (edges.degenerate[e]) {
+      coverage = 1.0f;
+    } else {
+      const float ax = edges.ax[e], ay = edges.ay[e], bx = edges.bx[e], by = edges.by[e];
+      const float ex = bx - ax, ey = by - ay;
+      const float len_sq = ex * ex + ey * ey;
+      const float cx = static_cast<float>(px) + 0.5f, cy = static_cast<float>(py) + 0.5f;
+      const float apx = cx - ax, apy = cy - ay;
+      float t = (apx * ex + apy * ey) / len_sq;
+      t = (t < 0.0f) ? 0.0f : ((1.0f < t) ? 1.0f : t);
+      const float qx = ax + (bx - ax) * t, qy = ay + (by - ay) * t;
+      const float ddx = cx - qx, ddy = cy - qy;
+      const float dist = sqrtf(ddx * ddx + ddy * ddy);
+      coverage = (pixel_radius + 0.5f - dist) * 0.6f;
+      coverage = (coverage < 0.0f) ? 0.0f : ((1.0f < coverage) ? 1.0f : coverage);
+      if (coverage <= 0.0f) continue;
+    }
+    const float a = coverage;  // already in [0,1]
+    const float s = 1.0f * a;  // white line
+    c0 = s + c0 * (1.0f - a);
+    c1 = s + c1 * (1.0f - a);
+    c2 = s + c2 * (1.0f - a);
+    c3 = a + c3 * (1.0f - a);
+    c4 = -FLT_MAX;
+    touched = true;
+  }
+  if (touched) {
+    b[0] = c0;
+    b[1] = c1;
+    b[2] = c2;
+    b[3] = c3;
+    b[4] = c4;
+  }
+}
+
+// reference: Common/Color.hpp:66-91 byte rule, Common/SavePPM.cpp:25-32 row order
+__global__ void __launch_bounds__(256)
+quantize_rgb8_kernel(const float* __restrict__ image5, int width, int height,
+                     unsigned char* __restrict__ rgb8) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= width * height) return;
+  const int x = p % width, out_row = p / width;
+  const float* s = image5 + 5 * (static_cast<size_t>(height - 1 - out_row) * width + x);
+  unsigned char* d = rgb8 + 3 * static_cast<size_t>(p);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const int v = static_cast<int>(s[c] * 256.f);
+    d[c] = static_cast<unsigned char>((v < 0) ? 0 : ((v > 255) ? 255 : v));
+  }
+}
+
+// ------------------------------------------------------------------------ K7
+
+__device__ __forceinline__ unsigned ordered_bits(float v) {
+  if (v == 0.0f) v = 0.0f;  // -0 and +0 compare equal in the reference comparator
+  const unsigned u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+constexpr int kSortThreads = 256;
+
+// Single-CTA least-significant-digit radix sort (4-bit digits) of the
+// (minDepth, maxDepth, owner) keys; the stable passes keep equal keys in index
+// order, which is the last tie-break of Common/VisibilityOrdering.cpp:238-257.
+// Non-finite depth intervals were already collapsed to (+inf,+inf) and so sort
+// last.  priority[i] = final position of box i.
+__global__ void __launch_bounds__(kSortThreads)
+order_rank_kernel(const OrderBox* __restrict__ boxes, int n, uint4* __restrict__ buf_a,
+                  uint4* __restrict__ buf_b, int owner_bits, int* __restrict__ priority) {
+  __shared__ unsigned s_hist[16 * kSortThreads];
+  __shared__ unsigned s_warp[kSortThreads / 32];
+  const int t = threadIdx.x;
+  const int per = (n + kSortThreads - 1) / kSortThreads;
+  const int begin = min(t * per, n), end = min(begin + per, n);
+
+  for (int i = t; i < n; i += kSortThreads) {
+    const OrderBox b = boxes[i];
+    buf_a[i] = make_uint4(static_cast<unsigned>(b.owner), ordered_bits(b.max_depth),
+                          ordered_bits(b.min_depth), static_cast<unsigned>(i));
+  }
+  __syncthreads();
+
+  uint4* in = buf_a;
+  uint4* out = buf_b;
+  const int owner_passes = (owner_bits + 3) / 4;
+  for (int pass = 0; pass < owner_passes + 16; ++pass) {
+    int word, shift;  // x = owner (least significant), y = max depth, z = min depth
+    if (pass < owner_passes) {
+      word = 0;
+      shift = 4 * pass;
+    } else {
+      const int q = pass - owner_passes;
+      word = 1 + (q >> 3);
+      shift = 4 * (q & 7);
+    }
+    unsigned local[16];
+#pragma unroll
+    for (int d = 0; d < 16; ++d) local[d] = 0;
+    for (int i = begin; i < end; ++i) {
+      const uint4 k = in[i];
+      const unsigned w = (word == 0) ? k.x : ((word == 1) ? k.y : k.z);
+      const unsigned digit = (w >> shift) & 15u;
+#pragma unroll
+      for (int d = 0; d < 16; ++d) local[d] += (digit == static_cast<unsigned>(d));
+    }
+#pragma unroll
+    for (int d = 0; d < 16; ++d) s_hist[d * kSortThreads + t] = local[d];
+    __syncthreads();
+    // exclusive scan of the 16*256 counters in (digit, thread) order
+    unsigned sum = 0;
+    unsigned vals[16];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      vals[e] = s_hist[t * 16 + e];
+      sum += vals[e];
+    }
+    unsigned incl = sum;
+    const int lane = t & 31, warp = t >> 5;
+    for (int off = 1; off < 32; off <<= 1) {
+      const unsigned o = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += o;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned base = incl - sum;
+    for (int w = 0; w < warp; ++w) base += s_warp[w];
+#pragma unroll
+    for (int e = 0; e < 16; ++e) {
+      s_hist[t * 16 + e] = base;
+      base += vals[e];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int d = 0; d < 16; ++d) local[d] = s_hist[d * kSortThreads + t];
+    for (int i = begin; i < end; ++i) {
+      const uint4 k = in[i];
+      const unsigned w = (word == 0) ? k.x : ((word == 1) ? k.y : k.z);
+      const unsigned digit = (w >> shift) & 15u;
+      unsigned pos = 0;
+#pragma unroll
+      for (int d = 0; d < 16; ++d)
+        if (digit == static_cast<unsigned>(d)) pos = local[d]++;
+      out[pos] = k;
+    }
+    __syncthreads();
+    uint4* tmp = in;
+    in = out;
+    out = tmp;
+  }
+  for (int i = t; i < n; i += kSortThreads) priority[in[i].w] = i;
+}
+
+__device__ __forceinline__ float fmax_std(float a, float b) { return (a < b) ? b : a; }
+__device__ __forceinline__ float fmin_std(float a, float b) { return (b < a) ? b : a; }
+
+__device__ __forceinline__ bool faces_touch(float a, float b) {
+  const float scale = fmax_std(fmax_std(1.0f, fabsf(a)), fabsf(b));
+  return fabsf(a - b) <= 1e-5f * scale;
+}
+__device__ __forceinline__ bool spans_overlap_dev(float a0, float a1, float b0, float b1) {
+  const float lo = fmax_std(a0, b0), hi = fmin_std(a1, b1);
+  float scale = 1.0f;
+  scale = fmax_std(scale, fabsf(a0));
+  scale = fmax_std(scale, fabsf(a1));
+  scale = fmax_std(scale, fabsf(b0));
+  scale = fmax_std(scale, fabsf(b1));
+  scale = fmax_std(scale, fabsf(lo));
+  scale = fmax_std(scale, fabsf(hi));
+  return (hi - lo) > 1e-5f * scale;
+}
+
+// All pairs i<j, three axes: face-adjacent boxes whose cross-sections overlap
+// get a front->back edge chosen by the sign of the view direction on that axis
+// (Common/VisibilityOrdering.cpp:261-317).  Edges are appended unordered; the
+// host sorts them back into the reference's insertion order.
+__global__ void __launch_bounds__(256)
+order_pairs_kernel(const OrderBox* __restrict__ boxes, int n, float dir0, float dir1, float dir2,
+                   OrderEdge* __restrict__ edges, int capacity, int* __restrict__ count) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (j >= n || j <= i) return;
+  const OrderBox a = boxes[i];
+  const OrderBox b = boxes[j];
+  const float dir[3] = {dir0, dir1, dir2};
+#pragma unroll
+  for (int axis = 0; axis < 3; ++axis) {
+    const int u = (axis + 1) % 3, v = (axis + 2) % 3;
+    if (!spans_overlap_dev(a.lo[u], a.hi[u], b.lo[u], b.hi[u])) continue;
+    if (!spans_overlap_dev(a.lo[v], a.hi[v], b.lo[v], b.hi[v])) continue;
+    const float along = dir[axis];
+    int forward = -1;
+    if (faces_touch(a.hi[axis], b.lo[axis])) {
+      if (along > 1e-6f) forward = 0;
+      else if (along < -1e-6f) forward = 1;
+    } else if (faces_touch(b.hi[axis], a.lo[axis])) {
+      if (along > 1e-6f) forward = 1;
+      else if (along < -1e-6f) forward = 0;
+    }
+    if (forward >= 0) {
+      const int slot = atomicAdd(count, 1);
+      if (slot < capacity) edges[slot] = OrderEdge{i, j, axis, forward};
+    }
+  }
+}
+
+inline cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
+
+ValuePath make_value_path(const amrvr_scalar_transform& t, float range_min, float range_max) {
+  ValuePath p;
+  p.log_scale = t.log_scale_input;
+  p.normalize = t.normalize_to_unit_range;
+  p.positive_floor = t.positive_floor;
+  p.norm_min = t.normalization_min;
+  p.inv_norm_span = t.inverse_normalization_span;
+  p.range_min = range_min;
+  p.inv_range = (range_max != range_min) ? 1.0f / (range_max - range_min) : 1.0f;  // :719-722
+  const float cs = (range_max < 0.0f) ? 0.0f : ((1.0f < range_max) ? 1.0f : range_max);
+  p.clip_start = cs;
+  p.apply_clip = 1.0f > cs + 1e-5f;
+  return p;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ launchers
+
+int launch_brick_stats(const double* data, int64_t jstride, int64_t kstride, int nx, int ny,
+                       int nz, double* partials, int blocks, void* stream, int64_t* launches) {
+  brick_stats_kernel<<<blocks, 256, 0, as_stream(stream)>>>(data, jstride, kstride, nx, ny, nz,
+                                                            partials);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_brick_stats_final(const double* partials, int nparts, double* out4, void* stream,
+                             int64_t* launches) {
+  brick_stats_final_kernel<<<1, 256, 0, as_stream(stream)>>>(partials, nparts, out4);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride, int nx, int ny,
+                          int nz, const amrvr_scalar_transform& t, float range_min,
+                          float range_max, uint8_t* brick, void* stream, int64_t* launches) {
+  const long long nquads = static_cast<long long>((nx + 3) / 4) * ny * nz;
+  if (nquads <= 0) return 0;
+  long long blocks = (nquads + 255) / 256;
+  if (blocks > 148LL * 32) blocks = 148LL * 32;
+  brick_quantise_kernel<<<static_cast<unsigned>(blocks), 256, 0, as_stream(stream)>>>(
+      data, jstride, kstride, nx, ny, nz, make_value_path(t, range_min, range_max), brick);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev, const uint8_t* bricks,
+                    const float* tables, float* layers, unsigned long long* sample_counter,
+                    bool count_samples, void* stream, int64_t* launches) {
+  if (frame.ntiles <= 0) return 0;
+  if (count_samples) {
+    raymarch_bricks_kernel<true><<<frame.ntiles, kMarchThreads, 0, as_stream(stream)>>>(
+        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter);
+  } else {
+    raymarch_bricks_kernel<false><<<frame.ntiles, kMarchThreads, 0, as_stream(stream)>>>(
+        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter);
+  }
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
+                int pixel_begin, int pixel_end, float* piece5, void* stream, int64_t* launches) {
+  const int npix = pixel_end - pixel_begin;
+  if (npix <= 0) return 0;
+  const int blocks = (npix + kFoldThreads - 1) / kFoldThreads;
+  fold_layers_kernel<<<blocks, kFoldThreads, 0, as_stream(stream)>>>(
+      layers_dev, nlayers, width, pixel_begin, pixel_end, piece5);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst, void* stream,
+                int64_t* launches) {
+  if (njobs <= 0) return 0;
+  pack_slices_kernel<<<njobs, 256, 0, as_stream(stream)>>>(jobs_dev, src, dst);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_downsample(const float* src5, int width, int height, int sqrt_aa, float* dst5,
+                      void* stream, int64_t* launches) {
+  const int n = width * height;
+  if (n <= 0) return 0;
+  downsample_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(src5, width, height,
+                                                                    sqrt_aa > 1 ? sqrt_aa : 1, dst5);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_overlay(const OverlayEdges& edges, int sqrt_aa, int width, int height, float* image5,
+                   void* stream, int64_t* launches) {
+  const int n = width * height;
+  if (n <= 0 || edges.count <= 0) return 0;
+  const float radius = 0.5f * static_cast<float>(sqrt_aa > 1 ? sqrt_aa : 1);
+  overlay_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(edges, radius, width, height,
+                                                                 image5);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_quantize_rgb8(const float* image5, int width, int height, uint8_t* rgb8, void* stream,
+                         int64_t* launches) {
+  const int n = width * height;
+  if (n <= 0) return 0;
+  quantize_rgb8_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(image5, width, height, rgb8);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_order_rank(const OrderBox* boxes_dev, int n, void* scratch_a, void* scratch_b,
+                      int owner_bits, int32_t* priority_dev, void* stream, int64_t* launches) {
+  if (n <= 0) return 0;
+  order_rank_kernel<<<1, kSortThreads, 0, as_stream(stream)>>>(
+      boxes_dev, n, static_cast<uint4*>(scratch_a), static_cast<uint4*>(scratch_b), owner_bits,
+      priority_dev);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_order_pairs(const OrderBox* boxes_dev, int n, float dx, float dy, float dz,
+                       OrderEdge* edges_dev, int capacity, int32_t* count_dev, void* stream,
+                       int64_t* launches) {
+  if (n <= 1) return 0;
+  dim3 grid((n + 255) / 256, n);
+  order_pairs_kernel<<<grid, 256, 0, as_stream(stream)>>>(boxes_dev, n, dx, dy, dz, edges_dev,
+                                                          capacity, count_dev);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+}  // namespace amrvr

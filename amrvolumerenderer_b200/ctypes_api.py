@@ -172,6 +172,10 @@ def _declare(lib):
         "amrvr_scene_global_boxes": (C.c_int, [vp, _P(i32), _P(_P(BoxRecord))]),
         "amrvr_scene_read_brick": (C.c_int, [vp, vp, i32, vp]),
         "amrvr_order_boxes": (C.c_int, [vp, vp, _P(Camera), f32, i32, _P(i32), _P(i32)]),
+        "amrvr_order_records": (C.c_int, [vp, i32, i32, _P(BoxRecord), _P(Camera), f32, i32,
+                                          _P(i32), _P(i32)]),
+        "amrvr_composite_virtual": (C.c_int, [vp, vp, vp, _P(Camera), i32, _P(i32), _P(i32), vp,
+                                              _P(i32)]),
         "amrvr_order_boxes_host": (C.c_int, [i32, i32, _P(BoxRecord), _P(Camera), f32, i32,
                                              _P(i32), _P(i32)]),
         "amrvr_layer_order_host": (C.c_int, [i32, _P(BoxRecord), _P(Camera), _P(f32), _P(i32)]),

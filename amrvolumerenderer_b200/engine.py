@@ -1,0 +1,263 @@
+"""Host-side handles over the C ABI (include/amrvr.h): one :class:`Context` per
+GPU, :class:`DeviceScene` for uploaded bricks, :class:`Layers` for a marched
+frame.  Every compute call goes to libamrvr_b200.so; nothing here computes
+pixels on the CPU and nothing here touches ``oracle/``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import ctypes_api as api
+
+_P = C.POINTER
+
+
+def _check(lib, ctx, status):
+    if status != api.AMRVR_OK:
+        raise api.AmrvrError(status, lib.amrvr_last_error(ctx).decode())
+
+
+def nccl_unique_id() -> bytes:
+    lib = api.load_library()
+    buf = C.create_string_buffer(api.NCCL_ID_BYTES)
+    _check(lib, None, lib.amrvr_nccl_unique_id(buf))
+    return buf.raw
+
+
+class Context:
+    """amrvr_ctx: one per GPU / rank."""
+
+    def __init__(self, device: int = 0, rank: int = 0, nranks: int = 1, nccl_id: bytes | None = None):
+        self.lib = api.load_library()
+        self.rank, self.nranks, self.device = rank, nranks, device
+        self._h = C.c_void_p()
+        idbuf = C.create_string_buffer(nccl_id, api.NCCL_ID_BYTES) if nccl_id else None
+        _check(self.lib, None, self.lib.amrvr_ctx_create(device, rank, nranks, idbuf, C.byref(self._h)))
+
+    def close(self):
+        if self._h:
+            self.lib.amrvr_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def check(self, status):
+        _check(self.lib, self._h, status)
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.amrvr_ctx_stream(self._h) or 0)
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self.lib.amrvr_ctx_kernel_launches(self._h))
+
+    def synchronize(self):
+        self.check(self.lib.amrvr_synchronize(self._h))
+
+    # ------------------------------------------------------------------ scene
+    def brick_stats(self, cboxes, n):
+        lo, hi, lp = C.c_double(), C.c_double(), C.c_double()
+        cnt = C.c_int64()
+        self.check(self.lib.amrvr_brick_stats(self._h, n, cboxes, C.byref(lo), C.byref(hi),
+                                              C.byref(lp), C.byref(cnt)))
+        return lo.value, hi.value, lp.value, cnt.value
+
+    def upload(self, cboxes, n, transform, scalar_range) -> "DeviceScene":
+        h = C.c_void_p()
+        self.check(self.lib.amrvr_scene_upload(self._h, n, cboxes, C.byref(transform),
+                                               float(scalar_range[0]), float(scalar_range[1]),
+                                               C.byref(h)))
+        return DeviceScene(self, h)
+
+    def upload_scene(self, scene) -> "DeviceScene":
+        """scene: amrvolumerenderer_b200.scenes.Scene; uploads this rank's boxes."""
+        cboxes, n, keep = scene.c_boxes(only_rank=self.rank if scene.nranks > 1 else None)
+        ds = self.upload(cboxes, n, scene.transform, scene.scalar_range)
+        ds._keep = keep
+        return ds
+
+    # ----------------------------------------------------------------- frames
+    def render_frame(self, dscene, camera, params, colormap=None, root=0, want_rgba=True,
+                     want_rgb8=True):
+        pts, npts = api.colormap_array(colormap)
+        is_root = self.rank == root
+        rgba = np.zeros((params.height, params.width, 5), np.float32) if (want_rgba and is_root) else None
+        rgb8 = np.zeros((params.height, params.width, 3), np.uint8) if (want_rgb8 and is_root) else None
+        stats = api.FrameStats()
+        self.check(self.lib.amrvr_render_frame(
+            self._h, dscene._h, C.byref(camera), C.byref(params), pts, npts, root,
+            rgba.ctypes.data_as(C.c_void_p) if rgba is not None else None,
+            rgb8.ctypes.data_as(C.c_void_p) if rgb8 is not None else None, C.byref(stats)))
+        return {"final5": rgba, "rgb8": rgb8, "stats": stats}
+
+    def raymarch(self, dscene, camera, width, height, box_transparency, ref_distance,
+                 colormap=None, count_samples=False) -> "Layers":
+        pts, npts = api.colormap_array(colormap)
+        h = C.c_void_p()
+        self.check(self.lib.amrvr_raymarch(self._h, dscene._h, C.byref(camera), width, height,
+                                           float(box_transparency), float(ref_distance), pts, npts,
+                                           int(count_samples), C.byref(h)))
+        return Layers(self, h, width, height)
+
+    def order_boxes(self, dscene, camera, aspect, use_graph=True):
+        out = np.zeros(self.nranks, np.int32)
+        failed = C.c_int(0)
+        self.check(self.lib.amrvr_order_boxes(self._h, dscene._h, C.byref(camera), float(aspect),
+                                              int(use_graph), out.ctypes.data_as(_P(C.c_int)),
+                                              C.byref(failed)))
+        return out, bool(failed.value)
+
+    def order_records(self, nranks, records, n, camera, aspect, use_graph=True):
+        out = np.zeros(nranks, np.int32)
+        failed = C.c_int(0)
+        self.check(self.lib.amrvr_order_records(self._h, nranks, n, records, C.byref(camera),
+                                                float(aspect), int(use_graph),
+                                                out.ctypes.data_as(_P(C.c_int)), C.byref(failed)))
+        return out, bool(failed.value)
+
+    def composite_virtual(self, dscene, layers, camera, nvirtual, box_owner, rank_order):
+        """Single-GPU emulation of an nvirtual-rank composite -> (full5, piece_owner)."""
+        own = np.ascontiguousarray(box_owner, np.int32)
+        ro = np.ascontiguousarray(rank_order, np.int32)
+        npix = layers.width * layers.height
+        dev = C.c_void_p()
+        self.check(self.lib.amrvr_device_alloc(self._h, npix * 20, C.byref(dev)))
+        piece_owner = np.full(npix, -1, np.int32)
+        try:
+            self.check(self.lib.amrvr_composite_virtual(
+                self._h, dscene._h, layers._h, C.byref(camera), nvirtual,
+                own.ctypes.data_as(_P(C.c_int)), ro.ctypes.data_as(_P(C.c_int)), dev,
+                piece_owner.ctypes.data_as(_P(C.c_int))))
+            full = np.zeros((layers.height, layers.width, 5), np.float32)
+            self.check(self.lib.amrvr_copy_to_host(self._h, full.ctypes.data_as(C.c_void_p), dev,
+                                                   npix * 20))
+        finally:
+            self.lib.amrvr_device_free(self._h, dev)
+        return full, piece_owner
+
+    def composite(self, dscene, layers, camera, rank_order):
+        ro = np.ascontiguousarray(rank_order, np.int32)
+        b, e = C.c_int(0), C.c_int(0)
+        piece = C.c_void_p()
+        self.check(self.lib.amrvr_composite(self._h, dscene._h, layers._h, C.byref(camera),
+                                            ro.ctypes.data_as(_P(C.c_int)), C.byref(b), C.byref(e),
+                                            C.byref(piece)))
+        return b.value, e.value, piece
+
+    def read_device(self, ptr, nbytes) -> bytes:
+        buf = np.zeros(nbytes, np.uint8)
+        self.check(self.lib.amrvr_copy_to_host(self._h, buf.ctypes.data_as(C.c_void_p), ptr, nbytes))
+        return buf
+
+    def gather(self, piece, begin, end, npix, root=0):
+        full = C.c_void_p()
+        if self.rank == root:
+            self.check(self.lib.amrvr_device_alloc(self._h, npix * 20, C.byref(full)))
+        self.check(self.lib.amrvr_gather(self._h, piece, begin, end, npix, root, full))
+        return full
+
+
+class DeviceScene:
+    def __init__(self, ctx: Context, handle):
+        self.ctx, self._h, self._keep = ctx, handle, None
+
+    def free(self):
+        if self._h:
+            self.ctx.lib.amrvr_scene_free(self.ctx._h, self._h)
+            self._h = C.c_void_p()
+
+    def global_boxes(self):
+        n = C.c_int(0)
+        recs = _P(api.BoxRecord)()
+        self.ctx.check(self.ctx.lib.amrvr_scene_global_boxes(self._h, C.byref(n), C.byref(recs)))
+        return recs, n.value
+
+    def read_brick(self, local_box: int, ncells: int) -> np.ndarray:
+        out = np.zeros(ncells, np.uint8)
+        self.ctx.check(self.ctx.lib.amrvr_scene_read_brick(self.ctx._h, self._h, local_box,
+                                                           out.ctypes.data_as(C.c_void_p)))
+        return out
+
+
+class Layers:
+    def __init__(self, ctx: Context, handle, width, height):
+        self.ctx, self._h, self.width, self.height = ctx, handle, width, height
+
+    def free(self):
+        if self._h:
+            self.ctx.lib.amrvr_layers_free(self.ctx._h, self._h)
+            self._h = C.c_void_p()
+
+    def __len__(self):
+        return int(self.ctx.lib.amrvr_layers_count(self._h))
+
+    def stats(self) -> api.MarchStats:
+        s = api.MarchStats()
+        self.ctx.check(self.ctx.lib.amrvr_layers_stats(self._h, C.byref(s)))
+        return s
+
+    def rect(self, layer: int):
+        v = [C.c_int(0) for _ in range(4)]
+        self.ctx.check(self.ctx.lib.amrvr_layers_rect(self._h, layer, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)
+
+    def read(self, layer: int) -> np.ndarray:
+        out = np.zeros((self.height, self.width, 5), np.float32)
+        self.ctx.check(self.ctx.lib.amrvr_layers_read(self.ctx._h, self._h, layer,
+                                                      out.ctypes.data_as(C.c_void_p)))
+        return out
+
+
+# ------------------------------------------------------------ host-only calls
+
+def color_table(alpha_scale, norm, rmin, rmax, colormap=None) -> np.ndarray:
+    lib = api.load_library()
+    out = np.zeros((256, 4), np.float32)
+    pts, n = api.colormap_array(colormap)
+    _check(lib, None, lib.amrvr_color_table(float(alpha_scale), float(norm), float(rmin),
+                                            float(rmax), pts, n,
+                                            out.ctypes.data_as(_P(C.c_float))))
+    return out
+
+
+def order_boxes_host(nranks, records, n, camera, aspect, use_graph=True):
+    lib = api.load_library()
+    out = np.zeros(nranks, np.int32)
+    failed = C.c_int(0)
+    _check(lib, None, lib.amrvr_order_boxes_host(nranks, n, records, C.byref(camera), float(aspect),
+                                                 int(use_graph), out.ctypes.data_as(_P(C.c_int)),
+                                                 C.byref(failed)))
+    return out, bool(failed.value)
+
+
+def layer_order_host(records, n, camera):
+    lib = api.load_library()
+    hints = np.zeros(max(n, 1), np.float32)
+    order = np.zeros(max(n, 1), np.int32)
+    _check(lib, None, lib.amrvr_layer_order_host(n, records, C.byref(camera),
+                                                 hints.ctypes.data_as(_P(C.c_float)),
+                                                 order.ctypes.data_as(_P(C.c_int))))
+    return hints[:n], order[:n]
+
+
+def piece_range(npix, piece, npieces):
+    lib = api.load_library()
+    b, e = C.c_int(0), C.c_int(0)
+    _check(lib, None, lib.amrvr_piece_range(npix, piece, npieces, C.byref(b), C.byref(e)))
+    return b.value, e.value
+
+
+def reference_sample_distance(records, n, bmin, bmax) -> float:
+    lib = api.load_library()
+    out = C.c_float(0)
+    lo = (C.c_double * 3)(*[float(x) for x in bmin])
+    hi = (C.c_double * 3)(*[float(x) for x in bmax])
+    _check(lib, None, lib.amrvr_reference_sample_distance(n, records, lo, hi, C.byref(out)))
+    return out.value

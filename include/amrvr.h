@@ -166,6 +166,13 @@ int amrvr_order_boxes(amrvr_ctx* ctx, const amrvr_scene* scene,
                       const amrvr_camera* camera, float aspect, int use_graph,
                       int* rank_order /*[nranks]*/, int* graph_failed);
 
+/* The same on an explicit global table (any nranks, independent of the ctx's
+ * own rank count): what amrvr_order_boxes runs after the allgather. */
+int amrvr_order_records(amrvr_ctx* ctx, int nranks, int nglobal,
+                        const amrvr_box_record* records,
+                        const amrvr_camera* camera, float aspect, int use_graph,
+                        int* rank_order, int* graph_failed);
+
 /* [host-only] Same computation on the host from an explicit global table;
  * used by the CPU tests and by amrvr_order_boxes for the sequential part. */
 int amrvr_order_boxes_host(int nranks, int nglobal,
@@ -233,6 +240,18 @@ int amrvr_composite(amrvr_ctx* ctx, const amrvr_scene* scene,
                     const amrvr_layers* layers, const amrvr_camera* camera,
                     const int* rank_order, int* region_begin, int* region_end,
                     float** piece5_device);
+/* Single-GPU emulation of the P-rank composite (no reference counterpart; for
+ * hosts with fewer GPUs than ranks and for parity tests): the layers of this
+ * ctx are treated as if box l were painted by virtual rank box_owner[l]
+ * (owner-local order = increasing l), blended with the run structure P ranks
+ * would produce, and the whole gathered frame (width*height*5 floats) is
+ * written to full5_device.  piece_owner_host (may be NULL, width*height ints)
+ * receives the virtual rank that would own each pixel. */
+int amrvr_composite_virtual(amrvr_ctx* ctx, const amrvr_scene* scene,
+                            const amrvr_layers* layers,
+                            const amrvr_camera* camera, int nvirtual,
+                            const int* box_owner, const int* rank_order,
+                            float* full5_device, int* piece_owner_host);
 /* a14.  Replaces ImageColorOnly::Gather (Common/ImageColorOnly.hpp:220-270).
  * full5_device (root only) receives width*height*5 floats. Collective. */
 int amrvr_gather(amrvr_ctx* ctx, const float* piece5_device, int region_begin,
