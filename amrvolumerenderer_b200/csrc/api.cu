@@ -142,6 +142,28 @@ bool is_pow2_float(float v) {
   return std::frexp(v, &e) == 0.5f;
 }
 
+// Distance by which the kernel shrinks a box before it trusts "this sample is
+// inside and its cell index is in range" without testing.  The float position
+// e + d*t carries at most 2^-24 * (|d*t| + |p|) of rounding error and the slab
+// bounds of the shrunk box a few ulps more; 64 * 2^-24 * (that magnitude) is a
+// 16-fold cover.  The floor() of (p - lo)/cell additionally needs the margin to
+// be a visible fraction of a cell.  Returns 0 (always test) when the two cannot
+// both hold.
+float inside_margin(const MarchBox& M, const float* eye) {
+  float coord = 0.0f, cell_min = INFINITY;
+  for (int d = 0; d < 3; ++d) {
+    coord = std::max(coord, std::max(std::fabs(M.lo[d]), std::fabs(M.hi[d])));
+    coord = std::max(coord, std::fabs(eye[d]));
+    if (!(M.cell[d] > 0.0f) || !std::isfinite(M.cell[d]) || M.n[d] < 1) return 0.0f;
+    cell_min = std::min(cell_min, M.cell[d]);
+  }
+  const float magnitude = 4.0f * coord;  // |e| + |d t| + |p| <= 2 (|e| + |p|)
+  const float rounding = 64.0f * 5.9604645e-8f * magnitude;
+  const float margin = std::max(rounding, cell_min * 0.0625f);
+  if (!std::isfinite(margin) || margin > 0.25f * cell_min) return 0.0f;
+  return margin;
+}
+
 struct DeviceOrderBackend final : OrderBackend {
   amrvr_ctx* ctx;
   int status = 0;
@@ -460,6 +482,9 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
   *out = nullptr;
   REQUIRE(ctx, nboxes >= 0 && (nboxes == 0 || boxes != nullptr), "bad box list");
   REQUIRE(ctx, transform != nullptr, "transform is NULL");
+  for (int b = 0; b < nboxes; ++b)
+    for (int d = 0; d < 3; ++d)
+      REQUIRE(ctx, boxes[b].dims[d] <= (1 << 20), "box dimension exceeds 2^20 cells");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   std::unique_ptr<amrvr_scene> scene(new amrvr_scene);
   scene->range_min = range_min;
@@ -739,8 +764,10 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
       M.hi[d] = static_cast<float>(B.max_corner[d]);
       M.n[d] = B.dims[d];
       M.cell[d] = (M.hi[d] - M.lo[d]) / static_cast<float>(B.dims[d]);  // VolumePainter.cpp:676-678
-      pow2 = pow2 && is_pow2_float(M.cell[d]);
-      M.inv_cell[d] = 1.0f / M.cell[d];
+      M.inv_cell_tiny[d] = std::ldexp(1.0f / M.cell[d], -149);
+      // 2^-149/cell must itself be a (subnormal) float: cell a power of two <= 1
+      pow2 = pow2 && is_pow2_float(M.cell[d]) && M.inv_cell_tiny[d] > 0.0f &&
+             std::ldexp(M.inv_cell_tiny[d], 149) == 1.0f / M.cell[d];
     }
     {  // :680-683 extent, float, x then y then z
       const float ex = M.hi[0] - M.lo[0], ey = M.hi[1] - M.lo[1], ez = M.hi[2] - M.lo[2];
@@ -748,6 +775,7 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
     }
     M.eps = std::sqrt(diag2) * 0.0001f;
     M.exact_recip = pow2 ? 1 : 0;
+    M.margin = inside_margin(M, basis.eye);
     const Rect r = box_footprint(B.min_corner, B.max_corner, B.dims, basis, *camera, width, height);
     L->rects[b] = r;
     M.rx0 = r.x0;

@@ -123,7 +123,8 @@ struct MarchBox {
   int32_t tile_base;   // first tile id of this box in the launch
   int32_t tiles_x;
   int32_t exact_recip; // 1: cell sizes are powers of two -> multiply by inverse is exact
-  float inv_cell[3];
+  float inv_cell_tiny[3];  // 2^-149 / cell (exact when cell is a power of two)
+  float margin;        // > 0: shrink distance of the provably-inside stretch; 0: always check
   uint64_t brick_off;  // byte offset into the brick pool
   uint64_t layer_off;  // float offset into the layer pool
 };

@@ -201,46 +201,48 @@ brick_stats_final_kernel(const double* __restrict__ partials, int nparts, double
 // rays only: the transfer table is staged once per CTA in shared memory, warps
 // are 8x4 pixel patches so the bytes a warp gathers from the brick share L1
 // lines, and stores are whole 128 B row segments.
-template <bool kCount>
-__global__ void __launch_bounds__(kMarchThreads)
-raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __restrict__ boxes,
-                       const unsigned char* __restrict__ bricks,
-                       const float4* __restrict__ tables, float* __restrict__ layers,
-                       unsigned long long* __restrict__ sample_counter) {
-  __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE];
-  __shared__ MarchBox s_box;
-  __shared__ int s_which;
+//
+// Every sample is evaluated with the reference's arithmetic (no FMA, true
+// division unless the cell size is a power of two).  What is removed is work
+// whose outcome is known in advance:
+//   * the table is stored kTableCopies times, entry e of copy c at float4 slot
+//     e*kTableCopies + c, and lane l reads copy l%8: the eight lanes of one
+//     LDS.128 phase then always hit eight different 16 B bank groups;
+//   * floor(v) for v >= 0 (the sample is inside the box) is a round-down
+//     multiply by 2^-149: the subnormal result's bit pattern IS the integer,
+//     exact for v < 2^23.  When the cell size is a power of two, (p - lo)/cell
+//     is itself exact, so one round-down multiply by 2^-149/cell gives the same
+//     integer.  This keeps the loop off the quarter-rate conversion pipe;
+//   * between t_safe0 and t_safe1 -- the slab interval of the box shrunk by
+//     MarchBox::margin, a bound on every rounding error of the position -- the
+//     sample is provably inside the box and its cell provably in range, so the
+//     six inside tests and the three index clamps are skipped there.  The few
+//     samples before and after that interval run the checked body.
 
-  const int tile = blockIdx.x;
-  if (threadIdx.x == 0) {  // last box whose first tile is <= tile
-    int lo = 0, hi = f.nboxes - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (boxes[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
-    }
-    s_which = lo;
-  }
-  __syncthreads();
-  {
-    const int words = sizeof(MarchBox) / 4;
-    const int* src = reinterpret_cast<const int*>(boxes + s_which);
-    if (threadIdx.x < words) reinterpret_cast<int*>(&s_box)[threadIdx.x] = src[threadIdx.x];
-  }
-  __syncthreads();
-  s_table[threadIdx.x] = tables[s_box.table * AMRVR_COLOR_TABLE_SIZE + threadIdx.x];
-  __syncthreads();
+constexpr int kTableCopies = 8;
+constexpr float kTinyOne = 1.401298464324817e-45f;  // 2^-149: bits(floor(v) * 2^-149) == floor(v)
 
-  const int local_tile = tile - s_box.tile_base;
-  const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
-  const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
-  const int rw = s_box.rw;
-  const bool valid = x < rw && y < s_box.rh;
-  const int px = s_box.rx0 + x, py = s_box.ry0 + y;
+__device__ __forceinline__ unsigned smem_u32(const void* p) {
+  return static_cast<unsigned>(__cvta_generic_to_shared(p));
+}
 
-  const float lox = s_box.lo[0], loy = s_box.lo[1], loz = s_box.lo[2];
-  const float hix = s_box.hi[0], hiy = s_box.hi[1], hiz = s_box.hi[2];
+__device__ __forceinline__ float4 lds_f4(unsigned addr) {
+  float4 v;
+  asm("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+
+struct RayOut {
+  float r, g, b, a, depth;
+  unsigned nsamples;
+};
+
+template <bool kCount, bool kRecip>
+__device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox& B,
+                                            const unsigned char* __restrict__ bricks,
+                                            unsigned table_addr, int px, int py, bool valid) {
+  const float lox = B.lo[0], loy = B.lo[1], loz = B.lo[2];
+  const float hix = B.hi[0], hiy = B.hi[1], hiz = B.hi[2];
   const float ex = f.eye[0], ey = f.eye[1], ez = f.eye[2];
 
   // ray through the pixel centre (:738-766)
@@ -263,93 +265,182 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __r
     dz *= inv;
   }
 
-  // slab test (:768-809)
+  // slab test (:768-809) and, with the same reciprocals, the slab interval of
+  // the box shrunk by B.margin on every face
   float tmin = -INFINITY, tmax = INFINITY;
-  {
-    const float o[3] = {ex, ey, ez}, d[3] = {dx, dy, dz};
-    const float lo3[3] = {lox, loy, loz}, hi3[3] = {hix, hiy, hiz};
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-      if (fabsf(d[a]) < 1e-8f) {
-        if (o[a] < lo3[a] || o[a] > hi3[a]) {
-          tmin = INFINITY;
-          tmax = -INFINITY;
-        }
-      } else {
-        const float inv = 1.0f / d[a];
-        float t1 = (lo3[a] - o[a]) * inv, t2 = (hi3[a] - o[a]) * inv;
-        if (t1 > t2) {
-          const float t = t1;
-          t1 = t2;
-          t2 = t;
-        }
-        tmin = (tmin > t1) ? tmin : t1;
-        tmax = (tmax < t2) ? tmax : t2;
-      }
-    }
+  float ts0 = -INFINITY, ts1 = INFINITY;
+  const float margin = B.margin;
+#define AMRVR_SLAB(o, d, lo, hi)                                        \
+  if (fabsf(d) < 1e-8f) {                                               \
+    if (o < lo || o > hi) {                                             \
+      tmin = INFINITY;                                                  \
+      tmax = -INFINITY;                                                 \
+    }                                                                   \
+    if (!(o >= lo + margin && o <= hi - margin)) {                      \
+      ts0 = INFINITY;                                                   \
+      ts1 = -INFINITY;                                                  \
+    }                                                                   \
+  } else {                                                              \
+    const float inv = 1.0f / d;                                         \
+    float t1 = (lo - o) * inv, t2 = (hi - o) * inv;                     \
+    if (t1 > t2) {                                                      \
+      const float t = t1;                                               \
+      t1 = t2;                                                          \
+      t2 = t;                                                           \
+    }                                                                   \
+    tmin = (tmin > t1) ? tmin : t1;                                     \
+    tmax = (tmax < t2) ? tmax : t2;                                     \
+    const float s_near = (((d > 0.0f) ? lo + margin : hi - margin) - o) * inv; \
+    const float s_far = (((d > 0.0f) ? hi - margin : lo + margin) - o) * inv;  \
+    ts0 = fmaxf(ts0, s_near);                                           \
+    ts1 = fminf(ts1, s_far);                                            \
+  }
+  AMRVR_SLAB(ex, dx, lox, hix)
+  AMRVR_SLAB(ey, dy, loy, hiy)
+  AMRVR_SLAB(ez, dz, loz, hiz)
+#undef AMRVR_SLAB
+  if (!(margin > 0.0f) || !(ts0 <= ts1)) {  // no provably-inside stretch on this ray
+    ts0 = INFINITY;
+    ts1 = -INFINITY;
   }
 
+  RayOut out{0.0f, 0.0f, 0.0f, 0.0f, INFINITY, 0u};
+  if (!(valid && tmax >= tmin)) return out;
+
   float acc_r = 0.0f, acc_g = 0.0f, acc_b = 0.0f, acc_a = 0.0f;
-  float depth = INFINITY;
-  unsigned int nsamples = 0;
-  if (valid && tmax >= tmin) {
-    const float step = s_box.step;
-    float distance = tmin + s_box.eps;
-    if (distance < 0.0f) distance = s_box.eps;
-    float pxs = ex + dx * distance, pys = ey + dy * distance, pzs = ez + dz * distance;
-    auto outside = [&]() {
-      return pxs < lox || pxs > hix || pys < loy || pys > hiy || pzs < loz || pzs > hiz;
-    };
-    while (distance < tmax && outside()) {  // :827-835
-      distance += step;
-      pxs = ex + dx * distance;
-      pys = ey + dy * distance;
-      pzs = ez + dz * distance;
+  unsigned nsamples = 0;
+  const float step = B.step;
+  float distance = tmin + B.eps;
+  if (distance < 0.0f) distance = B.eps;
+  float pxs = ex + dx * distance, pys = ey + dy * distance, pzs = ez + dz * distance;
+
+  const unsigned nx = static_cast<unsigned>(B.n[0]), ny = static_cast<unsigned>(B.n[1]);
+  const unsigned ix_max = nx - 1u, iy_max = ny - 1u, iz_max = static_cast<unsigned>(B.n[2]) - 1u;
+  const unsigned char* __restrict__ brick = bricks + B.brick_off;
+  const float cx = kRecip ? B.inv_cell_tiny[0] : B.cell[0];
+  const float cy = kRecip ? B.inv_cell_tiny[1] : B.cell[1];
+  const float cz = kRecip ? B.inv_cell_tiny[2] : B.cell[2];
+
+  auto advance = [&]() {
+    distance += step;
+    pxs = ex + dx * distance;
+    pys = ey + dy * distance;
+    pzs = ez + dz * distance;
+  };
+  auto shade = [&](unsigned jk, unsigned ib) {  // :884-894; jk = k*ny + j
+    unsigned cell, idx, slot;
+    // spelled out so that the byte arrives zero-extended and the table address
+    // is one multiply-add
+    cell = jk * nx + ib;
+    asm("ld.global.nc.u8 %0, [%1];" : "=r"(idx) : "l"(brick + cell));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(slot) : "r"(idx), "r"(16u * kTableCopies), "r"(table_addr));
+    const float4 e = lds_f4(slot);
+    const float a = e.w * (1.0f - acc_a);
+    acc_r += e.x * a;
+    acc_g += e.y * a;
+    acc_b += e.z * a;
+    acc_a += a;
+    if (kCount) ++nsamples;
+  };
+  auto cell_of = [&](float p, float lo, float c) {
+    // reference: floor((p - lo) / cell), :846-848
+    return __float_as_uint(kRecip ? __fmul_rd(p - lo, c) : __fmul_rd((p - lo) / c, kTinyOne));
+  };
+  auto checked = [&]() {
+    if (!(pxs < lox || pxs > hix || pys < loy || pys > hiy || pzs < loz || pzs > hiz)) {
+      // inside: (p - lo) >= 0, so floor() >= 0 and only the upper clamp can bind
+      const unsigned ib = min(cell_of(pxs, lox, cx), ix_max);
+      const unsigned jb = min(cell_of(pys, loy, cy), iy_max);
+      const unsigned kb = min(cell_of(pzs, loz, cz), iz_max);
+      shade(kb * ny + jb, ib);
     }
-    const int nx = s_box.n[0], ny = s_box.n[1], nz = s_box.n[2];
-    const unsigned char* __restrict__ brick = bricks + s_box.brick_off;
-    const bool recip = s_box.exact_recip != 0;
-    const float cx = recip ? s_box.inv_cell[0] : s_box.cell[0];
-    const float cy = recip ? s_box.inv_cell[1] : s_box.cell[1];
-    const float cz = recip ? s_box.inv_cell[2] : s_box.cell[2];
-    while (distance < tmax && acc_a < 1.0f) {  // :837-900
-      if (!outside()) {
-        // power-of-two cell sizes: multiplying by the inverse is the same
-        // rounding as the reference's division
-        const float fx = recip ? (pxs - lox) * cx : (pxs - lox) / cx;
-        const float fy = recip ? (pys - loy) * cy : (pys - loy) / cy;
-        const float fz = recip ? (pzs - loz) * cz : (pzs - loz) / cz;
-        int i = static_cast<int>(floorf(fx));
-        int j = static_cast<int>(floorf(fy));
-        int k = static_cast<int>(floorf(fz));
-        i = (i < 0) ? 0 : ((i >= nx) ? nx - 1 : i);
-        j = (j < 0) ? 0 : ((j >= ny) ? ny - 1 : j);
-        k = (k < 0) ? 0 : ((k >= nz) ? nz - 1 : k);
-        const unsigned int idx = __ldg(brick + (static_cast<size_t>(k) * ny + j) * nx + i);
-        const float4 e = s_table[idx];
-        const float a = e.w * (1.0f - acc_a);
-        acc_r += e.x * a;
-        acc_g += e.y * a;
-        acc_b += e.z * a;
-        acc_a += a;
-        if (kCount) ++nsamples;
-      }
-      distance += step;
-      pxs = ex + dx * distance;
-      pys = ey + dy * distance;
-      pzs = ez + dz * distance;
-    }
-    acc_r = (acc_r > 1.0f) ? 1.0f : acc_r;
-    acc_g = (acc_g > 1.0f) ? 1.0f : acc_g;
-    acc_b = (acc_b > 1.0f) ? 1.0f : acc_b;
-    acc_a = (acc_a > 1.0f) ? 1.0f : acc_a;
-    if (acc_a > 0.0f) {  // entry depth along the view axis (:912-921)
-      const float qx = ex + dx * tmin, qy = ey + dy * tmin, qz = ez + dz * tmin;
-      depth = (qx - ex) * f.fwd[0] + (qy - ey) * f.fwd[1] + (qz - ez) * f.fwd[2];
-    }
+    advance();
+  };
+
+  // The reference first steps forward until the sample is inside (:827-835) and
+  // then marches (:837-900); skipping outside samples inside one loop is the
+  // same sequence of samples.
+  const float t_head = fminf(ts0, tmax);
+  while (distance < t_head && acc_a < 1.0f) checked();
+  const float t_body = fminf(ts1, tmax);
+  while (distance < t_body && acc_a < 1.0f) {
+    const unsigned ib = cell_of(pxs, lox, cx);
+    const unsigned jb = cell_of(pys, loy, cy);
+    const unsigned kb = cell_of(pzs, loz, cz);
+    shade(kb * ny + jb, ib);
+    advance();
   }
+  while (distance < tmax && acc_a < 1.0f) checked();
+
+  acc_r = (acc_r > 1.0f) ? 1.0f : acc_r;
+  acc_g = (acc_g > 1.0f) ? 1.0f : acc_g;
+  acc_b = (acc_b > 1.0f) ? 1.0f : acc_b;
+  acc_a = (acc_a > 1.0f) ? 1.0f : acc_a;
+  float depth = INFINITY;
+  if (acc_a > 0.0f) {  // entry depth along the view axis (:912-921)
+    const float qx = ex + dx * tmin, qy = ey + dy * tmin, qz = ez + dz * tmin;
+    depth = (qx - ex) * f.fwd[0] + (qy - ey) * f.fwd[1] + (qz - ez) * f.fwd[2];
+  }
+  out.r = acc_r;
+  out.g = acc_g;
+  out.b = acc_b;
+  out.a = acc_a;
+  out.depth = depth;
+  out.nsamples = nsamples;
+  return out;
+}
+
+template <bool kCount>
+__global__ void __launch_bounds__(kMarchThreads)
+raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __restrict__ boxes,
+                       const unsigned char* __restrict__ bricks,
+                       const float4* __restrict__ tables, float* __restrict__ layers,
+                       unsigned long long* __restrict__ sample_counter) {
+  __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE * kTableCopies];
+  __shared__ MarchBox s_box;
+  __shared__ int s_which;
+
+  const int tile = blockIdx.x;
+  if (threadIdx.x == 0) {  // last box whose first tile is <= tile
+    int lo = 0, hi = f.nboxes - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (boxes[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+    }
+    s_which = lo;
+  }
+  __syncthreads();
+  {
+    const int words = sizeof(MarchBox) / 4;
+    const int* src = reinterpret_cast<const int*>(boxes + s_which);
+    if (threadIdx.x < words) reinterpret_cast<int*>(&s_box)[threadIdx.x] = src[threadIdx.x];
+  }
+  __syncthreads();
+  {
+    const float4 e = tables[s_box.table * AMRVR_COLOR_TABLE_SIZE + threadIdx.x];
+#pragma unroll
+    for (int c = 0; c < kTableCopies; ++c) s_table[threadIdx.x * kTableCopies + c] = e;
+  }
+  __syncthreads();
+
+  const int local_tile = tile - s_box.tile_base;
+  const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
+  const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
+  const int rw = s_box.rw;
+  const bool valid = x < rw && y < s_box.rh;
+  const unsigned table_addr = smem_u32(s_table) + static_cast<unsigned>(lane % kTableCopies) * 16u;
+
+  const RayOut r = s_box.exact_recip
+                       ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x,
+                                                 s_box.ry0 + y, valid)
+                       : march_ray<kCount, false>(f, s_box, bricks, table_addr, s_box.rx0 + x,
+                                                  s_box.ry0 + y, valid);
+
   // host epilogue of the reference (:939-955)
-  float4 out = make_float4(clamp01(acc_r), clamp01(acc_g), clamp01(acc_b), clamp01(acc_a));
+  float4 out = make_float4(clamp01(r.r), clamp01(r.g), clamp01(r.b), clamp01(r.a));
+  float depth = r.depth;
   if (!isfinite(depth) || out.w <= 0.0f) depth = INFINITY;
   if (valid) {
     float* row = layers + s_box.layer_off + static_cast<size_t>(y) * rw * 5;
@@ -357,6 +448,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __r
     row[4 * rw + x] = depth;
   }
   if (kCount) {
+    unsigned nsamples = r.nsamples;
     for (int off = 16; off > 0; off >>= 1) nsamples += __shfl_down_sync(0xffffffffu, nsamples, off);
     if (lane == 0 && nsamples != 0)
       atomicAdd(sample_counter, static_cast<unsigned long long>(nsamples));
