@@ -4,7 +4,10 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -50,6 +53,7 @@ struct DeviceBuffer {  // grow-only device allocation
 struct amrvr_ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
+  cudaStream_t aux = nullptr;  // visibility ordering: runs beside the march, never waits for it
   int64_t launches = 0;
   std::string error;
   ncclComm_t comm = nullptr;
@@ -99,6 +103,24 @@ struct amrvr_layers {
 namespace {
 
 thread_local std::string g_error = "";
+
+// AMRVR_TRACE=1: host wall-clock of every stage of amrvr_render_frame on stderr.
+struct Trace {
+  bool on;
+  std::chrono::steady_clock::time_point t0, last;
+  std::string line;
+  Trace() : on(std::getenv("AMRVR_TRACE") != nullptr) { t0 = last = std::chrono::steady_clock::now(); }
+  void mark(const char* what) {
+    if (!on) return;
+    const auto now = std::chrono::steady_clock::now();
+    line += std::string(what) + "=" +
+            std::to_string(std::chrono::duration<double, std::micro>(now - last).count()) + "us ";
+    last = now;
+  }
+  ~Trace() {
+    if (on) std::fprintf(stderr, "[amrvr trace] %s\n", line.c_str());
+  }
+};
 
 int fail(amrvr_ctx* ctx, int status, const std::string& msg) {
   if (ctx != nullptr) ctx->error = msg;
@@ -174,7 +196,7 @@ struct DeviceOrderBackend final : OrderBackend {
     const size_t n = boxes.size();
     if (ctx->order_boxes.reserve(n * sizeof(OrderBox)) != cudaSuccess) return AMRVR_ERR_CUDA;
     if (cudaMemcpyAsync(ctx->order_boxes.ptr, boxes.data(), n * sizeof(OrderBox),
-                        cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess)
+                        cudaMemcpyHostToDevice, ctx->aux) != cudaSuccess)
       return AMRVR_ERR_CUDA;
     return 0;
   }
@@ -195,10 +217,10 @@ struct DeviceOrderBackend final : OrderBackend {
     while ((1 << owner_bits) <= max_owner) ++owner_bits;
     if (launch_order_rank(ctx->order_boxes.as<OrderBox>(), n, ctx->order_scratch_a.ptr,
                           ctx->order_scratch_b.ptr, owner_bits, ctx->order_priority.as<int32_t>(),
-                          ctx->stream, &ctx->launches) != 0 ||
+                          ctx->aux, &ctx->launches) != 0 ||
         cudaMemcpyAsync(priority.data(), ctx->order_priority.ptr, static_cast<size_t>(n) * 4,
-                        cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
-        cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+                        cudaMemcpyDeviceToHost, ctx->aux) != cudaSuccess ||
+        cudaStreamSynchronize(ctx->aux) != cudaSuccess)
       status = AMRVR_ERR_CUDA;
   }
   void pair_edges(const std::vector<OrderBox>& boxes, const float* dir,
@@ -218,20 +240,21 @@ struct DeviceOrderBackend final : OrderBackend {
       int32_t* count_dev = ctx->order_edges.as<int32_t>();
       OrderEdge* edges_dev = reinterpret_cast<OrderEdge*>(ctx->order_edges.as<char>() + 16);
       int count = 0;
-      if (cudaMemsetAsync(count_dev, 0, 16, ctx->stream) != cudaSuccess ||
+      if (cudaMemsetAsync(count_dev, 0, 16, ctx->aux) != cudaSuccess ||
           launch_order_pairs(ctx->order_boxes.as<OrderBox>(), n, dir[0], dir[1], dir[2], edges_dev,
-                             capacity, count_dev, ctx->stream, &ctx->launches) != 0 ||
-          cudaMemcpyAsync(&count, count_dev, 4, cudaMemcpyDeviceToHost, ctx->stream) !=
+                             capacity, count_dev, ctx->aux, &ctx->launches) != 0 ||
+          cudaMemcpyAsync(&count, count_dev, 4, cudaMemcpyDeviceToHost, ctx->aux) !=
               cudaSuccess ||
-          cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+          cudaStreamSynchronize(ctx->aux) != cudaSuccess) {
         status = AMRVR_ERR_CUDA;
         return;
       }
       if (count <= capacity) {
         edges.resize(static_cast<size_t>(count));
         if (count > 0 &&
-            cudaMemcpy(edges.data(), edges_dev, static_cast<size_t>(count) * sizeof(OrderEdge),
-                       cudaMemcpyDeviceToHost) != cudaSuccess)
+            (cudaMemcpyAsync(edges.data(), edges_dev, static_cast<size_t>(count) * sizeof(OrderEdge),
+                             cudaMemcpyDeviceToHost, ctx->aux) != cudaSuccess ||
+             cudaStreamSynchronize(ctx->aux) != cudaSuccess))
           status = AMRVR_ERR_CUDA;
         return;
       }
@@ -335,6 +358,7 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
   ctx->rank = rank;
   ctx->nranks = nranks;
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
   for (auto& e : ctx->ev) CUDA_TRY(nullptr, cudaEventCreate(&e));
   CUDA_TRY(nullptr, ctx->counter.reserve(256));
   if (nranks > 1) {
@@ -363,6 +387,7 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (auto& e : ctx->ev)
     if (e != nullptr) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
+  cudaStreamDestroy(ctx->aux);
   delete ctx;
 }
 
@@ -635,6 +660,11 @@ extern "C" int amrvr_order_records(amrvr_ctx* ctx, int nranks, int nglobal,
                    camera != nullptr && rank_order != nullptr,
           "bad argument");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (nranks == 1) {  // one piece, one owner: the graph cannot change the answer
+    rank_order[0] = 0;
+    if (graph_failed) *graph_failed = 0;
+    return AMRVR_OK;
+  }
   DeviceOrderBackend backend(ctx);
   const bool ok = order_ranks(nranks, nglobal, records, *camera, aspect, use_graph != 0, backend,
                               rank_order);
@@ -1134,6 +1164,38 @@ extern "C" int amrvr_composite_virtual(amrvr_ctx* ctx, const amrvr_scene* scene,
   return AMRVR_OK;
 }
 
+namespace {
+
+// spans[2r], spans[2r+1] = pixel range of rank r's piece
+int gather_impl(amrvr_ctx* ctx, const float* piece5_device, const std::vector<int>& spans, int root,
+                float* full5_device) {
+  const int P = ctx->nranks, me = ctx->rank;
+  const int region_begin = spans[2 * me], region_end = spans[2 * me + 1];
+  const size_t mine = static_cast<size_t>(region_end - region_begin) * 5;
+  if (P > 1) {
+    NcclApi& nc = nccl_api();
+    NCCL_TRY(ctx, nc.GroupStart());
+    if (me == root) {
+      for (int r = 0; r < P; ++r) {
+        const size_t len = static_cast<size_t>(spans[2 * r + 1] - spans[2 * r]) * 5;
+        if (r == me || len == 0) continue;
+        NCCL_TRY(ctx, nc.Recv(full5_device + static_cast<size_t>(spans[2 * r]) * 5, len, ncclFloat, r,
+                              ctx->comm, ctx->stream));
+      }
+    } else if (mine > 0) {
+      NCCL_TRY(ctx, nc.Send(piece5_device, mine, ncclFloat, root, ctx->comm, ctx->stream));
+    }
+    NCCL_TRY(ctx, nc.GroupEnd());
+  }
+  if (me == root && mine > 0)
+    CUDA_TRY(ctx, cudaMemcpyAsync(full5_device + static_cast<size_t>(region_begin) * 5,
+                                  piece5_device, mine * sizeof(float), cudaMemcpyDeviceToDevice,
+                                  ctx->stream));
+  return AMRVR_OK;
+}
+
+}  // namespace
+
 extern "C" int amrvr_gather(amrvr_ctx* ctx, const float* piece5_device, int region_begin,
                             int region_end, int num_pixels, int root, float* full5_device) {
   if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
@@ -1143,46 +1205,26 @@ extern "C" int amrvr_gather(amrvr_ctx* ctx, const float* piece5_device, int regi
           "bad region");
   REQUIRE(ctx, me != root || full5_device != nullptr, "root needs a destination");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  const size_t mine = static_cast<size_t>(region_end - region_begin) * 5;
-  if (P == 1) {
-    if (mine > 0)
-      CUDA_TRY(ctx, cudaMemcpyAsync(full5_device + static_cast<size_t>(region_begin) * 5,
-                                    piece5_device, mine * sizeof(float), cudaMemcpyDeviceToDevice,
-                                    ctx->stream));
-    return AMRVR_OK;
-  }
-  // every rank learns every region (ImageColorOnly.hpp:220-270 gathers sizes first)
-  NcclApi& nc = nccl_api();
-  DeviceBuffer tmp;
-  CUDA_TRY(ctx, tmp.reserve(static_cast<size_t>(2 * (P + 1)) * sizeof(int)));
-  int* all_dev = tmp.as<int>();
-  const int span[2] = {region_begin, region_end};
-  CUDA_TRY(ctx, cudaMemcpyAsync(all_dev + 2 * P, span, sizeof(span), cudaMemcpyHostToDevice,
-                                ctx->stream));
-  NCCL_TRY(ctx, nc.AllGather(all_dev + 2 * P, all_dev, sizeof(span), ncclChar, ctx->comm,
-                             ctx->stream));
   std::vector<int> spans(static_cast<size_t>(2 * P));
-  CUDA_TRY(ctx, cudaMemcpyAsync(spans.data(), all_dev, sizeof(int) * 2 * P, cudaMemcpyDeviceToHost,
-                                ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  tmp.release();
-  NCCL_TRY(ctx, nc.GroupStart());
-  if (me == root) {
-    for (int r = 0; r < P; ++r) {
-      const size_t len = static_cast<size_t>(spans[2 * r + 1] - spans[2 * r]) * 5;
-      if (r == me || len == 0) continue;
-      NCCL_TRY(ctx, nc.Recv(full5_device + static_cast<size_t>(spans[2 * r]) * 5, len, ncclFloat, r,
-                            ctx->comm, ctx->stream));
-    }
-  } else if (mine > 0) {
-    NCCL_TRY(ctx, nc.Send(piece5_device, mine, ncclFloat, root, ctx->comm, ctx->stream));
-  }
-  NCCL_TRY(ctx, nc.GroupEnd());
-  if (me == root && mine > 0)
-    CUDA_TRY(ctx, cudaMemcpyAsync(full5_device + static_cast<size_t>(region_begin) * 5,
-                                  piece5_device, mine * sizeof(float), cudaMemcpyDeviceToDevice,
+  spans[2 * me] = region_begin;
+  spans[2 * me + 1] = region_end;
+  if (P > 1) {
+    // every rank learns every region (ImageColorOnly.hpp:220-270 gathers sizes first)
+    NcclApi& nc = nccl_api();
+    DeviceBuffer tmp;
+    CUDA_TRY(ctx, tmp.reserve(static_cast<size_t>(2 * (P + 1)) * sizeof(int)));
+    int* all_dev = tmp.as<int>();
+    const int span[2] = {region_begin, region_end};
+    CUDA_TRY(ctx, cudaMemcpyAsync(all_dev + 2 * P, span, sizeof(span), cudaMemcpyHostToDevice,
                                   ctx->stream));
-  return AMRVR_OK;
+    NCCL_TRY(ctx, nc.AllGather(all_dev + 2 * P, all_dev, sizeof(span), ncclChar, ctx->comm,
+                               ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(spans.data(), all_dev, sizeof(int) * 2 * P, cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    tmp.release();
+  }
+  return gather_impl(ctx, piece5_device, spans, root, full5_device);
 }
 
 extern "C" int amrvr_downsample(amrvr_ctx* ctx, const float* full5_device, int width, int height,
@@ -1289,23 +1331,30 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   }
   const float ref_step = reference_sample_distance(n, scene->global.data(), tmin, tmax);
 
+  Trace trace;
   cudaEvent_t* ev = ctx->ev;
   CUDA_TRY(ctx, cudaEventRecord(ev[0], ctx->stream));
+  trace.mark("setup");
   amrvr_layers* layers = nullptr;
   int st = amrvr_raymarch(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
                           params->count_samples, &layers);
   if (st != AMRVR_OK) return st;
   CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
+  trace.mark("march_enqueue");
 
   std::vector<int> rank_order(static_cast<size_t>(ctx->nranks));
   int graph_failed = 0;
+  const auto order_t0 = std::chrono::steady_clock::now();
   st = amrvr_order_boxes(ctx, scene, camera, aspect, params->use_visibility_graph,
                          rank_order.data(), &graph_failed);
   if (st != AMRVR_OK) {
     amrvr_layers_free(ctx, layers);
     return st;
   }
+  const float order_host_ms =
+      std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
   CUDA_TRY(ctx, cudaEventRecord(ev[2], ctx->stream));
+  trace.mark("order");
 
   int begin = 0, end = 0;
   float* piece = nullptr;
@@ -1317,11 +1366,17 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
     return st;
   }
   CUDA_TRY(ctx, cudaEventRecord(ev[3], ctx->stream));
+  trace.mark("composite_enqueue");
 
   const size_t render_floats = static_cast<size_t>(RW) * RH * 5;
   const size_t out_floats = static_cast<size_t>(W) * H * 5;
   if (ctx->rank == root) CUDA_TRY(ctx, ctx->full.reserve(render_floats * sizeof(float)));
-  st = amrvr_gather(ctx, piece, begin, end, RW * RH, root, ctx->full.as<float>());
+  {
+    std::vector<int> spans(static_cast<size_t>(2 * ctx->nranks));
+    for (int pc = 0; pc < ctx->nranks; ++pc)
+      piece_range(RW * RH, pc, ctx->nranks, &spans[2 * rank_order[pc]], &spans[2 * rank_order[pc] + 1]);
+    st = gather_impl(ctx, piece, spans, root, ctx->full.as<float>());
+  }
   if (st != AMRVR_OK) {
     amrvr_layers_free(ctx, layers);
     return st;
@@ -1353,7 +1408,9 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
     }
   }
   CUDA_TRY(ctx, cudaEventRecord(ev[5], ctx->stream));
+  trace.mark("post_enqueue");
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  trace.mark("final_sync");
   if (stats != nullptr) {
     std::memset(stats, 0, sizeof(*stats));
     amrvr_march_stats ms;
@@ -1361,7 +1418,7 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
       stats->samples = ms.samples;
       stats->march_ms = ms.kernel_ms;
     }
-    cudaEventElapsedTime(&stats->order_ms, ev[1], ev[2]);
+    stats->order_ms = order_host_ms;  // runs on the aux stream beside the march: host wall time
     cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[3]);
     cudaEventElapsedTime(&stats->gather_ms, ev[3], ev[4]);
     cudaEventElapsedTime(&stats->post_ms, ev[4], ev[5]);

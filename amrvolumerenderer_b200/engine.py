@@ -33,13 +33,29 @@ class Context:
         self.lib = api.load_library()
         self.rank, self.nranks, self.device = rank, nranks, device
         self._h = C.c_void_p()
+        self._pinned_pool = {}
         idbuf = C.create_string_buffer(nccl_id, api.NCCL_ID_BYTES) if nccl_id else None
         _check(self.lib, None, self.lib.amrvr_ctx_create(device, rank, nranks, idbuf, C.byref(self._h)))
 
     def close(self):
         if self._h:
+            for ptr, _arr in self._pinned_pool.values():
+                self.lib.amrvr_host_free_pinned(ptr)
+            self._pinned_pool.clear()
             self.lib.amrvr_ctx_destroy(self._h)
             self._h = C.c_void_p()
+
+    def _pinned(self, shape, dtype) -> np.ndarray:
+        key = (tuple(shape), np.dtype(dtype).str)
+        hit = self._pinned_pool.get(key)
+        if hit is None:
+            nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+            ptr = C.c_void_p()
+            _check(self.lib, None, self.lib.amrvr_host_alloc_pinned(max(nbytes, 1), C.byref(ptr)))
+            raw = (C.c_uint8 * max(nbytes, 1)).from_address(ptr.value)
+            arr = np.frombuffer(raw, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+            hit = self._pinned_pool[key] = (ptr, arr)
+        return hit[1]
 
     def __del__(self):
         try:
@@ -88,8 +104,11 @@ class Context:
                      want_rgb8=True):
         pts, npts = api.colormap_array(colormap)
         is_root = self.rank == root
-        rgba = np.zeros((params.height, params.width, 5), np.float32) if (want_rgba and is_root) else None
-        rgb8 = np.zeros((params.height, params.width, 3), np.uint8) if (want_rgb8 and is_root) else None
+        # results land in pinned host buffers owned by the context (a pageable
+        # destination makes the device->host copy synchronous and ~5x slower);
+        # they are overwritten by the next frame of the same size
+        rgba = self._pinned((params.height, params.width, 5), np.float32) if (want_rgba and is_root) else None
+        rgb8 = self._pinned((params.height, params.width, 3), np.uint8) if (want_rgb8 and is_root) else None
         stats = api.FrameStats()
         self.check(self.lib.amrvr_render_frame(
             self._h, dscene._h, C.byref(camera), C.byref(params), pts, npts, root,
