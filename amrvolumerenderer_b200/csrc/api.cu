@@ -55,6 +55,7 @@ struct amrvr_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t aux = nullptr;  // visibility ordering: runs beside the march, never waits for it
   int64_t launches = 0;
+  int order_device_min = 1024;  // global box count from which the ordering runs its device kernels
   std::string error;
   ncclComm_t comm = nullptr;
   cudaEvent_t ev[8] = {};
@@ -398,6 +399,14 @@ extern "C" void* amrvr_ctx_stream(amrvr_ctx* ctx) { return ctx ? ctx->stream : n
 extern "C" int64_t amrvr_ctx_kernel_launches(const amrvr_ctx* ctx) {
   return ctx ? ctx->launches : 0;
 }
+extern "C" const uint8_t* amrvr_ctx_frame_rgb8_device(const amrvr_ctx* ctx) {
+  return ctx ? ctx->rgb8.as<uint8_t>() : nullptr;
+}
+extern "C" int amrvr_ctx_set_order_device_min_boxes(amrvr_ctx* ctx, int min_boxes) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  ctx->order_device_min = min_boxes < 0 ? 0 : min_boxes;
+  return AMRVR_OK;
+}
 
 // ---------------------------------------------------------------------------
 // scene
@@ -663,6 +672,14 @@ extern "C" int amrvr_order_records(amrvr_ctx* ctx, int nranks, int nglobal,
   if (nranks == 1) {  // one piece, one owner: the graph cannot change the answer
     rank_order[0] = 0;
     if (graph_failed) *graph_failed = 0;
+    return AMRVR_OK;
+  }
+  if (nglobal < ctx->order_device_min) {
+    // a few hundred boxes: the pair test and the key sort take tens of
+    // microseconds on the host, less than one kernel launch + readback
+    const bool ok = order_ranks(nranks, nglobal, records, *camera, aspect, use_graph != 0,
+                                *host_order_backend(), rank_order);
+    if (graph_failed) *graph_failed = ok ? 0 : 1;
     return AMRVR_OK;
   }
   DeviceOrderBackend backend(ctx);
@@ -1399,12 +1416,13 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
     if (rgba5_host != nullptr)
       CUDA_TRY(ctx, cudaMemcpyAsync(rgba5_host, image, out_floats * sizeof(float),
                                     cudaMemcpyDeviceToHost, ctx->stream));
-    if (rgb8_host != nullptr) {
+    if (rgb8_host != nullptr || params->rgb8_on_device) {
       CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
       LAUNCH_TRY(ctx, launch_quantize_rgb8(image, W, H, ctx->rgb8.as<uint8_t>(), ctx->stream,
                                            &ctx->launches));
-      CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->rgb8.ptr, static_cast<size_t>(W) * H * 3,
-                                    cudaMemcpyDeviceToHost, ctx->stream));
+      if (rgb8_host != nullptr)
+        CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->rgb8.ptr, static_cast<size_t>(W) * H * 3,
+                                      cudaMemcpyDeviceToHost, ctx->stream));
     }
   }
   CUDA_TRY(ctx, cudaEventRecord(ev[5], ctx->stream));

@@ -548,7 +548,11 @@ void order_box_depth_range(const OrderMatrices& m, OrderBox& b) {
                         (c & 4) ? b.hi[2] : b.lo[2], 1.0f};
     float eye_space[4], clip[4];
     mul4(m.view, h, eye_space);
-    mul4(m.proj, eye_space, clip);
+    for (int r = 2; r < 4; ++r) {  // only z and w of the clip-space point are used
+      float s = 0.0f;
+      for (int k = 0; k < 4; ++k) s += m.proj[r * 4 + k] * eye_space[k];
+      clip[r] = s;
+    }
     if (clip[3] != 0.0f) {
       const float z = clip[2] / clip[3];
       zmin = fmin2(zmin, z);
@@ -612,10 +616,25 @@ void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
                            std::vector<OrderEdge>& edges) {
   edges.clear();
   const int n = static_cast<int>(boxes.size());
+  // Cheap exact reject.  An edge on any axis needs the faces to touch on that
+  // axis (|a - b| <= 1e-5 * scale, scale <= max(1, largest |coordinate|)) and
+  // the other two spans to overlap strictly, so the two boxes grown by `tol`
+  // must intersect on all three axes.  Valid when every box has lo <= hi.
+  float largest = 1.0f;
+  bool well_formed = true;
+  for (const OrderBox& b : boxes)
+    for (int d = 0; d < 3; ++d) {
+      largest = fmax2(largest, fmax2(std::fabs(b.lo[d]), std::fabs(b.hi[d])));
+      well_formed = well_formed && (b.lo[d] <= b.hi[d]);
+    }
+  const float tol = well_formed ? 2e-5f * largest : INFINITY;
   for (int i = 0; i < n; ++i) {
     const OrderBox& a = boxes[i];
     for (int j = i + 1; j < n; ++j) {
       const OrderBox& b = boxes[j];
+      if (b.lo[0] > a.hi[0] + tol || a.lo[0] > b.hi[0] + tol || b.lo[1] > a.hi[1] + tol ||
+          a.lo[1] > b.hi[1] + tol || b.lo[2] > a.hi[2] + tol || a.lo[2] > b.hi[2] + tol)
+        continue;
       for (int axis = 0; axis < 3; ++axis) {
         const int u = (axis + 1) % 3, v = (axis + 2) % 3;
         if (!spans_overlap(a.lo[u], a.hi[u], b.lo[u], b.hi[u])) continue;

@@ -114,7 +114,7 @@ class FrameParams(C.Structure):
         ("use_visibility_graph", C.c_int32),
         ("count_samples", C.c_int32),
         ("draw_bounding_box", C.c_int32),
-        ("reserved", C.c_int32),
+        ("rgb8_on_device", C.c_int32),
     ]
 
 
@@ -165,6 +165,8 @@ def _declare(lib):
         "amrvr_last_error": (C.c_char_p, [vp]),
         "amrvr_ctx_stream": (vp, [vp]),
         "amrvr_ctx_kernel_launches": (i64, [vp]),
+        "amrvr_ctx_set_order_device_min_boxes": (C.c_int, [vp, i32]),
+        "amrvr_ctx_frame_rgb8_device": (vp, [vp]),
         "amrvr_brick_stats": (C.c_int, [vp, i32, _P(Box), _P(C.c_double), _P(C.c_double),
                                         _P(C.c_double), _P(i64)]),
         "amrvr_scene_upload": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),

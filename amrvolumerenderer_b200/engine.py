@@ -74,6 +74,10 @@ class Context:
     def kernel_launches(self) -> int:
         return int(self.lib.amrvr_ctx_kernel_launches(self._h))
 
+    def set_order_device_min_boxes(self, n: int):
+        """Box count from which the visibility ordering uses its device kernels."""
+        self.check(self.lib.amrvr_ctx_set_order_device_min_boxes(self._h, int(n)))
+
     def synchronize(self):
         self.check(self.lib.amrvr_synchronize(self._h))
 

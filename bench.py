@@ -52,38 +52,73 @@ def _peaks():
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+    """SM clock and throttle reasons of one GPU while the timed region runs
+    (NVML in-process, every 5 ms; nvidia-smi as the fallback)."""
 
     QUERY = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index: int):
         super().__init__(daemon=True)
-        self.index, self.rows, self._halt = index, [], threading.Event()
+        self.index, self._halt = index, threading.Event()
+        self.sm, self.max_sm, self.reasons = [], [], set()
+        self.nvml = self.handle = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(visible.split(",")[index]) if visible and visible.split(",")[index].isdigit() else index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n, h = self.nvml, self.handle
+        self.sm.append(float(n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)))
+        self.max_sm.append(float(n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM)))
+        mask = n.nvmlDeviceGetCurrentClocksEventReasons(h)
+        for name, bit in (("hw_slowdown", n.nvmlClocksEventReasonHwSlowdown),
+                          ("hw_thermal_slowdown", n.nvmlClocksEventReasonHwThermalSlowdown),
+                          ("sw_thermal_slowdown", n.nvmlClocksEventReasonSwThermalSlowdown),
+                          ("sw_power_cap", n.nvmlClocksEventReasonSwPowerCap)):
+            if mask & bit:
+                self.reasons.add(name)
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                             timeout=5).stdout.strip()
+        r = [c.strip() for c in out.split(",")]
+        if len(r) >= 6:
+            self.sm.append(float(r[0]))
+            self.max_sm.append(float(r[1]))
+            for i in range(4):
+                if r[2 + i].lower().startswith("active"):
+                    self.reasons.add(self.NAMES[i])
 
     def run(self):
         while not self._halt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.QUERY}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if self.nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
-                pass
-            self._halt.wait(0.2)
+                if self.nvml is not None:
+                    self.nvml = None  # fall back to nvidia-smi
+            self._halt.wait(0.005 if self.nvml is not None else 0.2)
 
     def finish(self):
         self._halt.set()
         self.join(timeout=6)
-        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows for i in range(4)
-                          if len(r) >= 6 and r[2 + i].lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
+                "sm_max_mhz": max(self.max_sm) if self.max_sm else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def pin_scene(lib, scene, rank, nranks):
@@ -114,7 +149,7 @@ def reference_arm(args, workload):
     factory, W, H, aa, transp = WORKLOADS[workload]
     cores = len(os.sched_getaffinity(0))
     P = max(1, min(8, cores))
-    scene = factory(nranks=P)
+    scene = factory(nranks=P, rule="round_robin")
     camera = scenes.make_camera()
     sw, sh = 512, 512  # bounded sample: same boxes and camera, 1/16 of the rays
     params = api.FrameParams(width=sw // int(round(aa ** 0.5)), height=sh // int(round(aa ** 0.5)),
@@ -160,7 +195,7 @@ def cpu_baseline(workload):
     factory, W, H, aa, transp = WORKLOADS[workload]
     cores = len(os.sched_getaffinity(0))
     P = max(1, min(8, cores))
-    scene = factory(nranks=P)
+    scene = factory(nranks=P, rule="round_robin")
     sw = sh = 512
     root = int(round(aa ** 0.5))
     params = api.FrameParams(width=sw // root, height=sh // root, box_transparency=transp,
@@ -223,7 +258,10 @@ def main():
         torch.cuda.synchronize()
 
     factory, W, H, aa, transp = WORKLOADS[args.workload]
-    scene = factory(nranks=world)
+    # box -> rank: round-robin over the (level, k, j, i) order, so every rank holds
+    # the same number of boxes of every level (contiguous chunks would give rank 0
+    # all of level 0, i.e. 3/4 of the samples)
+    scene = factory(nranks=world, rule="round_robin")
     camera = scenes.make_camera()
     lib = api.load_library()
     pinned, fab_bytes = pin_scene(lib, scene, rank, world)
@@ -233,6 +271,10 @@ def main():
 
     params = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
                              use_visibility_graph=1, count_samples=0, draw_bounding_box=1)
+    # device-resident arm: the RGB8 frame is built on the root GPU and stays there
+    resident = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
+                               use_visibility_graph=1, count_samples=0, draw_bounding_box=1,
+                               rgb8_on_device=1)
     counting = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
                                use_visibility_graph=1, count_samples=1, draw_bounding_box=1)
 
@@ -244,7 +286,7 @@ def main():
     total_samples = int(samples.item())
 
     def one_frame():
-        return ctx.render_frame(dscene, camera, params, want_rgba=False)
+        return ctx.render_frame(dscene, camera, resident, want_rgba=False, want_rgb8=False)
 
     # ---- device-resident arm: K frames, L2 flushed between frames, events on the ctx stream
     for _ in range(args.warmup):
@@ -320,8 +362,10 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {len(scene.boxes)} boxes, {cells} cells, "
-                                   f"{W}x{H} AA{aa}, visibility graph on, boxes sharded over "
-                                   f"{world} rank(s)",
+                                   f"{W}x{H} AA{aa}, visibility graph on, boxes sharded "
+                                   f"round-robin over {world} rank(s)",
+                       "value_scope": "bricks resident in HBM, RGB8 frame left on the root GPU",
+                       "e2e_scope": "pinned host FABs -> upload+quantise -> frame -> RGB8 on the host",
                        "l2": "256 MiB buffer written between timed frames (L2 flush)",
                        "samples_per_frame": total_samples,
                        "frames_per_s": 1e3 / ms_per_step,

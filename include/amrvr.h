@@ -129,6 +129,14 @@ const char* amrvr_last_error(const amrvr_ctx* ctx);
 void* amrvr_ctx_stream(amrvr_ctx* ctx);
 /* Number of kernels this ctx has launched so far. */
 int64_t amrvr_ctx_kernel_launches(const amrvr_ctx* ctx);
+/* Device pointer of the RGB8 image (width*height*3, top row first) the last
+ * amrvr_render_frame built on this ctx (root only); valid until the next frame. */
+const uint8_t* amrvr_ctx_frame_rgb8_device(const amrvr_ctx* ctx);
+/* amrvr_order_boxes / amrvr_order_records run the device radix sort and the
+ * device pair test from this many global boxes upwards (default 1024); below
+ * it the same sequential driver uses its host back end, which is faster than a
+ * kernel launch plus readback for a few hundred boxes.  0 = always device. */
+int amrvr_ctx_set_order_device_min_boxes(amrvr_ctx* ctx, int min_boxes);
 
 /* ------------------------------------------------------------------- scene */
 
@@ -286,7 +294,8 @@ typedef struct amrvr_frame_params {
   int32_t use_visibility_graph;
   int32_t count_samples;
   int32_t draw_bounding_box;   /* renderBoundingBoxLayer, VolumeRenderer.cpp:1311-1314 */
-  int32_t reserved;
+  int32_t rgb8_on_device;      /* != 0: build the RGB8 image on the root's GPU even when
+                                  rgb8_host is NULL (read it with amrvr_ctx_frame_rgb8_device) */
 } amrvr_frame_params;
 
 typedef struct amrvr_frame_stats {

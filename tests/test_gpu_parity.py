@@ -230,6 +230,7 @@ def test_order_device_matches_oracle(ctx, oracle, nranks, rule):
     scene = scenes.scene_c4(box_cells=4, nranks=nranks, rule=rule)
     recs, n = scene.records()
     rng = np.random.default_rng(5)
+    ctx.set_order_device_min_boxes(0 if nranks != 4 else 1024)  # device kernels; host back end for P=4
     for trial in range(12):
         eye = rng.normal(size=3)
         eye = 0.5 + eye / np.linalg.norm(eye) * rng.uniform(1.2, 3.0)
@@ -243,6 +244,7 @@ def test_order_device_matches_oracle(ctx, oracle, nranks, rule):
 def test_order_device_random_boxes_with_cycles(ctx, oracle):
     """Random touching boxes (cycles get split) -- device path == oracle."""
     rng = np.random.default_rng(11)
+    ctx.set_order_device_min_boxes(0)
     for trial in range(20):
         n = int(rng.integers(2, 40))
         recs = (api.BoxRecord * n)()
@@ -262,6 +264,35 @@ def test_order_device_random_boxes_with_cycles(ctx, oracle):
         got, failed = ctx.order_records(4, recs, n, cam, 1.0)
         assert np.array_equal(got, want), (trial, got, want)
         assert failed == (not ok)
+
+
+def test_order_device_many_boxes(ctx, oracle):
+    """C5-sized table (16^3 = 4096 unit bricks, 8 owners): the default threshold
+    sends this to the device radix sort + pair kernel."""
+    n_axis = 16
+    n = n_axis ** 3
+    recs = (api.BoxRecord * n)()
+    local = {}
+    i = 0
+    for k in range(n_axis):
+        for j in range(n_axis):
+            for ii in range(n_axis):
+                r = recs[i]
+                for d, c in enumerate((ii, j, k)):
+                    r.min_corner[d], r.max_corner[d] = c / n_axis, (c + 1) / n_axis
+                    r.dims[d] = 4
+                r.owner = i % 8
+                r.local_index = local.get(r.owner, 0)
+                local[r.owner] = r.local_index + 1
+                i += 1
+    ctx.set_order_device_min_boxes(1024)
+    launches = ctx.kernel_launches
+    for eye in ((1.9, 1.3, 2.4), (-1.5, 0.2, 0.7)):
+        cam = scenes.make_camera(eye=eye)
+        want, ok = oracle.order(8, recs, n, cam, 1.0)
+        got, failed = ctx.order_records(8, recs, n, cam, 1.0)
+        assert np.array_equal(got, want) and failed == (not ok)
+    assert ctx.kernel_launches >= launches + 4  # pair kernel + sort kernel per call
 
 
 # --------------------------------------------- K6 fold with P-rank run structure
