@@ -320,6 +320,17 @@ bool slice_rows(const Rect& r, int begin, int end, int width, int* s0, int* s1) 
 
 extern "C" int amrvr_abi_version(void) { return AMRVR_ABI_VERSION; }
 
+extern "C" int amrvr_device_count(int* count) {
+  if (count == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "count is NULL");
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    (void)cudaGetLastError();
+    n = 0;
+  }
+  *count = n;
+  return AMRVR_OK;
+}
+
 extern "C" int amrvr_nccl_unique_id(void* id_out) {
   if (id_out == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "id_out is NULL");
   static_assert(sizeof(ncclUniqueId) == AMRVR_NCCL_ID_BYTES, "NCCL id size");
@@ -1121,6 +1132,187 @@ extern "C" int amrvr_composite(amrvr_ctx* ctx, const amrvr_scene* scene, const a
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   return composite_impl(ctx, scene, layers, camera, rank_order, region_begin, region_end,
                         piece5_device, nullptr);
+}
+
+extern "C" int amrvr_exchange_plan_host(int nranks, int rank, int nglobal,
+                                        const amrvr_box_record* records,
+                                        const amrvr_camera* camera, int width, int height,
+                                        const int* rank_order, int64_t* send_floats,
+                                        int64_t* recv_floats, int* region_begin, int* region_end) {
+  if (nranks < 1 || rank < 0 || rank >= nranks || nglobal < 0 ||
+      (nglobal > 0 && records == nullptr) || camera == nullptr || width <= 0 || height <= 0 ||
+      rank_order == nullptr || send_floats == nullptr || recv_floats == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "bad argument");
+  std::vector<char> seen(static_cast<size_t>(nranks), 0);
+  for (int i = 0; i < nranks; ++i) {
+    if (rank_order[i] < 0 || rank_order[i] >= nranks || seen[rank_order[i]])
+      return fail(nullptr, AMRVR_ERR_INVALID, "rank_order is not a permutation");
+    seen[rank_order[i]] = 1;
+  }
+  amrvr_scene shadow;
+  shadow.global.assign(records, records + nglobal);
+  FramePlan plan;
+  make_frame_plan(shadow, *camera, width, height, nranks, rank_order, plan);
+  for (int q = 0; q < nranks; ++q) send_floats[q] = recv_floats[q] = 0;
+  for (int g = 0; g < nglobal; ++g) {
+    const int owner = records[g].owner;
+    const Rect& r = plan.rects[g];
+    int s0, s1;
+    if (owner == rank) {
+      for (int q = 0; q < nranks; ++q)
+        if (q != rank && slice_rows(r, plan.begin[q], plan.end[q], width, &s0, &s1))
+          send_floats[q] += static_cast<int64_t>(s1 - s0) * r.w * 5;
+    } else if (owner >= 0 && owner < nranks &&
+               slice_rows(r, plan.begin[rank], plan.end[rank], width, &s0, &s1)) {
+      recv_floats[owner] += static_cast<int64_t>(s1 - s0) * r.w * 5;
+    }
+  }
+  if (region_begin) *region_begin = plan.begin[rank];
+  if (region_end) *region_end = plan.end[rank];
+  return AMRVR_OK;
+}
+
+// The reference's own calling convention for the composite: every layer is a
+// dense W*H*5-float host image (ImageRGBAFloatColorDepthSort) with a depth hint
+// (LayeredVolumeImage).  Used by the C++ adapter of DirectSendBase::compose;
+// the fast path (amrvr_composite) keeps layers on the device as footprints.
+extern "C" int amrvr_composite_dense(amrvr_ctx* ctx, int width, int height, int nlayers,
+                                     const float* const* layers5_host, const float* depth_hints,
+                                     const int* rank_order, int* region_begin, int* region_end,
+                                     float* piece5_host) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, width > 0 && height > 0 && nlayers >= 0, "bad image size or layer count");
+  REQUIRE(ctx, static_cast<int64_t>(width) * height < (1LL << 31), "frame too large");
+  REQUIRE(ctx, nlayers == 0 || (layers5_host != nullptr && depth_hints != nullptr), "NULL layers");
+  REQUIRE(ctx, rank_order != nullptr, "rank_order is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int P = ctx->nranks, me = ctx->rank;
+  const int npix = width * height;
+  std::vector<int> begin(P), end(P);
+  {
+    std::vector<char> seen(static_cast<size_t>(P), 0);
+    for (int piece = 0; piece < P; ++piece) {
+      const int r = rank_order[piece];
+      REQUIRE(ctx, r >= 0 && r < P && !seen[r], "rank_order is not a permutation");
+      seen[r] = 1;
+      piece_range(npix, piece, P, &begin[r], &end[r]);
+    }
+  }
+  // DirectSendBase.cpp:329-361: every rank learns every layer count and hint
+  std::vector<int> counts(P, 0);
+  std::vector<float> hints;  // rank-major
+  counts[me] = nlayers;
+  if (P == 1) {
+    hints.assign(depth_hints, depth_hints + nlayers);
+  } else {
+    NcclApi& nc = nccl_api();
+    DeviceBuffer tmp;
+    CUDA_TRY(ctx, tmp.reserve(static_cast<size_t>(P + 1) * sizeof(int)));
+    int* cd = tmp.as<int>();
+    CUDA_TRY(ctx, cudaMemcpyAsync(cd + P, &nlayers, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    NCCL_TRY(ctx, nc.AllGather(cd + P, cd, sizeof(int), ncclChar, ctx->comm, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(counts.data(), cd, sizeof(int) * P, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    const int most = std::max(1, *std::max_element(counts.begin(), counts.end()));
+    DeviceBuffer hb;
+    CUDA_TRY(ctx, hb.reserve(static_cast<size_t>(most) * (P + 1) * sizeof(float)));
+    float* hd = hb.as<float>();
+    if (nlayers > 0)
+      CUDA_TRY(ctx, cudaMemcpyAsync(hd + static_cast<size_t>(most) * P, depth_hints,
+                                    sizeof(float) * nlayers, cudaMemcpyHostToDevice, ctx->stream));
+    NCCL_TRY(ctx, nc.AllGather(hd + static_cast<size_t>(most) * P, hd, sizeof(float) * most, ncclChar,
+                               ctx->comm, ctx->stream));
+    std::vector<float> all(static_cast<size_t>(most) * P);
+    CUDA_TRY(ctx, cudaMemcpyAsync(all.data(), hd, all.size() * sizeof(float), cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int r = 0; r < P; ++r)
+      hints.insert(hints.end(), all.begin() + static_cast<size_t>(most) * r,
+                   all.begin() + static_cast<size_t>(most) * r + counts[r]);
+    tmp.release();
+    hb.release();
+  }
+  struct Entry {
+    float depth;
+    int owner, local;
+  };
+  std::vector<Entry> order;
+  for (int r = 0, k = 0; r < P; ++r)
+    for (int l = 0; l < counts[r]; ++l, ++k) order.push_back(Entry{hints[k], r, l});
+  std::sort(order.begin(), order.end(), [](const Entry& a, const Entry& b) {  // :378-388
+    if (a.depth == b.depth) {
+      if (a.owner == b.owner) return a.local < b.local;
+      return a.owner < b.owner;
+    }
+    return a.depth < b.depth;
+  });
+
+  // my layers go to the device whole (interleaved, as they are); each piece's
+  // pixel range is then a contiguous float range of every layer
+  const size_t layer_floats = static_cast<size_t>(npix) * 5;
+  CUDA_TRY(ctx, ctx->send_buf.reserve(std::max<size_t>(layer_floats * nlayers, 4) * sizeof(float)));
+  for (int l = 0; l < nlayers; ++l) {
+    REQUIRE(ctx, layers5_host[l] != nullptr, "NULL layer");
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->send_buf.as<float>() + layer_floats * l, layers5_host[l],
+                                  layer_floats * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+  }
+  const size_t mine = static_cast<size_t>(end[me] - begin[me]) * 5;
+  std::vector<size_t> recv_base(P + 1, 0);  // float offset of rank r's first layer slice
+  for (int r = 0; r < P; ++r) recv_base[r + 1] = recv_base[r] + (r == me ? 0 : mine * counts[r]);
+  CUDA_TRY(ctx, ctx->recv_buf.reserve(std::max<size_t>(recv_base[P], 4) * sizeof(float)));
+  if (P > 1) {
+    NcclApi& nc = nccl_api();
+    NCCL_TRY(ctx, nc.GroupStart());
+    for (int q = 0; q < P; ++q) {
+      if (q == me) continue;
+      const size_t theirs = static_cast<size_t>(end[q] - begin[q]) * 5;
+      for (int l = 0; l < nlayers && theirs > 0; ++l)
+        NCCL_TRY(ctx, nc.Send(ctx->send_buf.as<float>() + layer_floats * l + static_cast<size_t>(begin[q]) * 5,
+                              theirs, ncclFloat, q, ctx->comm, ctx->stream));
+      for (int l = 0; l < counts[q] && mine > 0; ++l)
+        NCCL_TRY(ctx, nc.Recv(ctx->recv_buf.as<float>() + recv_base[q] + mine * l, mine, ncclFloat, q,
+                              ctx->comm, ctx->stream));
+    }
+    NCCL_TRY(ctx, nc.GroupEnd());
+  }
+  std::vector<FoldLayer> fold;
+  int run = -1, prev_owner = -1;
+  const int row0 = begin[me] / width;
+  const int64_t lead = static_cast<int64_t>(begin[me]) - static_cast<int64_t>(row0) * width;  // pixels
+  for (size_t pos = 0; pos < order.size(); ++pos) {
+    const Entry& e = order[pos];
+    if (pos == 0 || e.owner != prev_owner) ++run;  // :400-407
+    prev_owner = e.owner;
+    if (mine == 0) continue;
+    FoldLayer F{};
+    const float* slice = (e.owner == me)
+                             ? ctx->send_buf.as<float>() + layer_floats * e.local +
+                                   static_cast<size_t>(begin[me]) * 5
+                             : ctx->recv_buf.as<float>() + recv_base[e.owner] + mine * e.local;
+    F.base = slice - lead * 5;  // pixel (0,row0) of a virtual full-width slice
+    F.x0 = 0;
+    F.w = width;
+    F.row0 = row0;
+    F.row1 = (end[me] - 1) / width + 1;
+    F.run = run;
+    F.interleaved = 1;
+    fold.push_back(F);
+  }
+  CUDA_TRY(ctx, ctx->piece.reserve(std::max<size_t>(mine * sizeof(float), 256)));
+  if (!fold.empty()) {
+    CUDA_TRY(ctx, ctx->fold_layers.reserve(fold.size() * sizeof(FoldLayer)));
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->fold_layers.ptr, fold.data(), fold.size() * sizeof(FoldLayer),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+  }
+  LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), width,
+                              begin[me], end[me], ctx->piece.as<float>(), ctx->stream, &ctx->launches));
+  if (piece5_host != nullptr && mine > 0)
+    CUDA_TRY(ctx, cudaMemcpyAsync(piece5_host, ctx->piece.ptr, mine * sizeof(float),
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if (region_begin) *region_begin = begin[me];
+  if (region_end) *region_end = end[me];
+  return AMRVR_OK;
 }
 
 extern "C" int amrvr_composite_virtual(amrvr_ctx* ctx, const amrvr_scene* scene,

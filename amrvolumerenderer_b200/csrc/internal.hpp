@@ -142,7 +142,8 @@ struct FoldLayer {
   int32_t x0, w;       // footprint rectangle origin (x) and padded width
   int32_t row0, row1;  // rows [row0,row1) of the frame held at `base`
   int32_t run;         // id of the same-owner run this layer belongs to
-  int32_t pad;
+  int32_t interleaved; // 1: pixel (x,y) at base + ((y-row0)*w + x-x0)*5 (the reference's layout);
+                       //    base may then point before the slice (only in-range pixels are read)
 };
 
 // A byte range to copy when packing slices for the exchange.

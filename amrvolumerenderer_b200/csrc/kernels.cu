@@ -480,7 +480,7 @@ constexpr int kFoldThreads = 256;
 
 struct FoldEntry {  // FoldLayer narrowed for shared memory
   const float* base;
-  int x0, w, row0, row1, run;
+  int x0, w, row0, row1, run, interleaved;
 };
 
 // One CTA = 256 consecutive pixels of this rank's piece.  The CTA filters the
@@ -531,7 +531,7 @@ fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
     }
     if (keep) {
       const int slot = before + __popc(ballot & ((1u << lane) - 1u));
-      s_list[slot] = FoldEntry{L.base, L.x0, L.w, L.row0, L.row1, L.run};
+      s_list[slot] = FoldEntry{L.base, L.x0, L.w, L.row0, L.row1, L.run, L.interleaved};
     }
     __syncthreads();
     if (live) {
@@ -547,10 +547,15 @@ fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
         }
         const int cx = px - E.x0;
         if (py >= E.row0 && py < E.row1 && cx >= 0 && cx < E.w) {
-          const float* rowp = E.base + static_cast<size_t>(py - E.row0) * E.w * 5;
-          const float4 c = __ldg(reinterpret_cast<const float4*>(rowp) + cx);
-          const float d = __ldg(rowp + 4 * E.w + cx);
-          const Px5 frag{c.x, c.y, c.z, c.w, d};
+          Px5 frag;
+          if (E.interleaved) {  // the reference's own layout: 5 floats per pixel
+            const float* q = E.base + (static_cast<long long>(py - E.row0) * E.w + cx) * 5;
+            frag = Px5{__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3), __ldg(q + 4)};
+          } else {
+            const float* rowp = E.base + static_cast<size_t>(py - E.row0) * E.w * 5;
+            const float4 c = __ldg(reinterpret_cast<const float4*>(rowp) + cx);
+            frag = Px5{c.x, c.y, c.z, c.w, __ldg(rowp + 4 * E.w + cx)};
+          }
           run = have_run ? blend_depth_swap(run, frag) : frag;
           have_run = true;
         }

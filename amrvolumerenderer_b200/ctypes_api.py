@@ -159,6 +159,7 @@ def _declare(lib):
     vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_int64, C.c_float
     protos = {
         "amrvr_abi_version": (C.c_int, []),
+        "amrvr_device_count": (C.c_int, [_P(i32)]),
         "amrvr_nccl_unique_id": (C.c_int, [vp]),
         "amrvr_ctx_create": (C.c_int, [i32, i32, i32, vp, _P(vp)]),
         "amrvr_ctx_destroy": (None, [vp]),
@@ -193,6 +194,10 @@ def _declare(lib):
         "amrvr_layers_rect": (C.c_int, [vp, i32, _P(i32), _P(i32), _P(i32), _P(i32)]),
         "amrvr_layers_read": (C.c_int, [vp, vp, i32, vp]),
         "amrvr_composite": (C.c_int, [vp, vp, vp, _P(Camera), _P(i32), _P(i32), _P(i32), _P(vp)]),
+        "amrvr_exchange_plan_host": (C.c_int, [i32, i32, i32, _P(BoxRecord), _P(Camera), i32, i32,
+                                               _P(i32), _P(i64), _P(i64), _P(i32), _P(i32)]),
+        "amrvr_composite_dense": (C.c_int, [vp, i32, i32, i32, _P(_P(f32)), _P(f32), _P(i32), _P(i32),
+                                            _P(i32), vp]),
         "amrvr_gather": (C.c_int, [vp, vp, i32, i32, i32, i32, vp]),
         "amrvr_downsample": (C.c_int, [vp, vp, i32, i32, i32, vp]),
         "amrvr_quantize_rgb8": (C.c_int, [vp, vp, i32, i32, vp]),

@@ -284,3 +284,17 @@ def reference_sample_distance(records, n, bmin, bmax) -> float:
     hi = (C.c_double * 3)(*[float(x) for x in bmax])
     _check(lib, None, lib.amrvr_reference_sample_distance(n, records, lo, hi, C.byref(out)))
     return out.value
+
+
+def exchange_plan_host(nranks, rank, records, n, camera, width, height, rank_order):
+    """(send_floats[P], recv_floats[P], (begin, end)) of amrvr_composite for `rank`."""
+    lib = api.load_library()
+    ro = np.ascontiguousarray(rank_order, np.int32)
+    send = np.zeros(nranks, np.int64)
+    recv = np.zeros(nranks, np.int64)
+    b, e = C.c_int(0), C.c_int(0)
+    _check(lib, None, lib.amrvr_exchange_plan_host(
+        nranks, rank, n, records, C.byref(camera), width, height, ro.ctypes.data_as(_P(C.c_int)),
+        send.ctypes.data_as(_P(C.c_int64)), recv.ctypes.data_as(_P(C.c_int64)), C.byref(b),
+        C.byref(e)))
+    return send, recv, (b.value, e.value)

@@ -111,6 +111,9 @@ typedef struct amrvr_march_stats {
 /* [host-only] Version of this ABI. */
 int amrvr_abi_version(void);
 
+/* Number of CUDA devices visible to this process (0 when there is none). */
+int amrvr_device_count(int* count);
+
 /* [host-only] Create an NCCL unique id (rank 0 calls it and ships the
  * AMRVR_NCCL_ID_BYTES to the other ranks with whatever the host already has:
  * MPI_Bcast in the reference's world, torch.distributed here). */
@@ -248,6 +251,28 @@ int amrvr_composite(amrvr_ctx* ctx, const amrvr_scene* scene,
                     const amrvr_layers* layers, const amrvr_camera* camera,
                     const int* rank_order, int* region_begin, int* region_end,
                     float** piece5_device);
+/* [host-only] The exchange amrvr_composite performs for `rank`, without doing
+ * it: floats this rank sends to / receives from every other rank (row slices
+ * of footprint layers that intersect the destination piece) and its own pixel
+ * range.  Every rank derives the same plan from the global table, so no count
+ * exchange is needed: send_floats[q] on rank r == recv_floats[r] on rank q. */
+int amrvr_exchange_plan_host(int nranks, int rank, int nglobal,
+                             const amrvr_box_record* records,
+                             const amrvr_camera* camera, int width, int height,
+                             const int* rank_order, int64_t* send_floats,
+                             int64_t* recv_floats, int* region_begin,
+                             int* region_end);
+/* The same composite in the reference's own calling convention, for the C++
+ * adapter of DirectSendBase::compose: layer l of this rank is a dense
+ * width*height*5-float HOST image (ImageRGBAFloatColorDepthSort buffer) with
+ * depth hint depth_hints[l] (LayeredVolumeImage, Common/LayeredVolumeImage.hpp:
+ * 18-57).  piece5_host (may be NULL) receives this rank's piece, pixels
+ * [*region_begin, *region_end).  Collective; blocking. */
+int amrvr_composite_dense(amrvr_ctx* ctx, int width, int height, int nlayers,
+                          const float* const* layers5_host,
+                          const float* depth_hints, const int* rank_order,
+                          int* region_begin, int* region_end,
+                          float* piece5_host);
 /* Single-GPU emulation of the P-rank composite (no reference counterpart; for
  * hosts with fewer GPUs than ranks and for parity tests): the layers of this
  * ctx are treated as if box l were painted by virtual rank box_owner[l]

@@ -20,6 +20,7 @@ from amrvolumerenderer_b200 import ctypes_api as api
 HERE = Path(__file__).resolve().parent
 RESTATE_LIB = HERE / "liboracle.so"
 REF_LIB = HERE / "_ref" / "libamrvr_ref.so"
+DROPIN_LIB = HERE / "_ref" / "libamrvr_dropin.so"
 REFERENCE_ROOT = Path("/root/reference")
 
 _P = C.POINTER
@@ -33,6 +34,10 @@ def build(ref: bool | None = None) -> None:
         ref = REFERENCE_ROOT.exists()
     if ref:
         subprocess.run(["make", "-s", "-j8", "-C", str(HERE), "ref"], check=True)
+        # the reference's driver with its three hot-path files swapped for the
+        # adapters over libamrvr_b200.so (needs that library built first)
+        if (HERE.parent / "amrvolumerenderer_b200" / "csrc" / "libamrvr_b200.so").exists():
+            subprocess.run(["make", "-s", "-j8", "-C", str(HERE), "dropin"], check=True)
 
 
 def _fptr(a: np.ndarray):
@@ -199,13 +204,17 @@ class RefUnavailable(RuntimeError):
 class Ref(_Base):
     """The reference's own code (oracle/_ref)."""
 
+    LIB = REF_LIB
+
     def __init__(self):
-        if not REF_LIB.exists():
+        if not self.LIB.exists():
             if REFERENCE_ROOT.exists():
                 build(ref=True)
             else:
-                raise RefUnavailable(f"{REF_LIB} not built and {REFERENCE_ROOT} is absent")
-        self.lib = C.CDLL(str(REF_LIB))
+                raise RefUnavailable(f"{self.LIB} not built and {REFERENCE_ROOT} is absent")
+        if not self.LIB.exists():
+            raise RefUnavailable(f"{self.LIB} could not be built")
+        self.lib = C.CDLL(str(self.LIB))
         self.lib.ref_last_error.restype = C.c_char_p
 
     def _check(self, status):
@@ -277,6 +286,15 @@ class Ref(_Base):
             if m:
                 out[key] = float(m.group(1))
         return out
+
+
+class DropIn(Ref):
+    """The reference's driver, scene builder and image classes with
+    VolumePainter / BuildVisibilityOrderedGroup / DirectSendBase replaced by the
+    adapters of amrvolumerenderer_b200/adapters (-> libamrvr_b200.so).  Same
+    entry points as Ref; needs a B200 to run anything."""
+
+    LIB = DROPIN_LIB
 
 
 def read_ppm(path) -> np.ndarray:

@@ -1,0 +1,137 @@
+"""CPU suite, part 2: the host logic of libamrvr_b200.so ([host-only] entry
+points of include/amrvr.h) against the oracle, and the shape of the ABI itself.
+No compute call is made -- there is no GPU here."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from amrvolumerenderer_b200 import ctypes_api as api, engine, scenes
+
+
+def test_library_exports_every_declared_symbol(lib):
+    names = api.declared_symbols()
+    assert len(names) >= 40
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, missing
+    assert lib.amrvr_abi_version() == 1
+
+
+def test_every_declared_symbol_has_a_ctypes_prototype(lib):
+    protos = api._declare(lib)
+    assert sorted(protos) == api.declared_symbols()
+
+
+def test_no_cpu_fallback(lib):
+    """Without a usable sm_100 device the context cannot be created."""
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(api.AmrvrError) as e:
+        engine.Context(device=0)
+    assert e.value.status == api.AMRVR_ERR_CUDA
+    assert "no CPU fallback" in e.value.message
+
+
+def test_product_package_never_imports_the_oracle():
+    import re
+    from pathlib import Path
+
+    pkg = Path(api.__file__).resolve().parent
+    for path in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cpp")) + list(pkg.rglob("*.cu")) + \
+            list(pkg.rglob("*.hpp")):
+        text = path.read_text()
+        assert not re.search(r"^\s*(from|import)\s+oracle", text, re.M), path
+        assert "liboracle" not in text and "oracle/restate" not in text, path
+
+
+def test_struct_sizes_match_the_header(lib):
+    # sizes the C compiler gives the PODs of include/amrvr.h (LP64)
+    assert C.sizeof(api.Box) == 120
+    assert C.sizeof(api.BoxRecord) == 72
+    assert C.sizeof(api.Camera) == 88
+    assert C.sizeof(api.ScalarTransform) == 64
+    assert C.sizeof(api.FrameParams) == 32
+
+
+@pytest.mark.parametrize("cmap", [None, [(0.0, 0.1, 0.1, 0.6, 0.0), (0.3, 0.2, 0.8, 0.3, 0.05),
+                                         (0.7, 0.9, 0.9, 0.1, 0.4), (1.0, 1.0, 0.2, 0.1, 0.9)]])
+def test_color_table_matches_oracle(oracle, cmap):
+    """buildColorTable (Common/VolumePainter.cpp:442-516), bit for bit."""
+    for alpha_scale, norm, rmin, rmax in ((1.0, 1.0, 0.0, 1.0), (0.85, 0.5, 0.0, 1.0),
+                                          (0.4, 0.25, 0.1, 0.9), (1.0, 2.0, 0.0, 0.5)):
+        got = engine.color_table(alpha_scale, norm, rmin, rmax, cmap)
+        want = oracle.color_table(alpha_scale, norm, rmin, rmax, cmap)
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("nranks,rule", [(1, "chunks"), (2, "chunks"), (3, "round_robin"), (8, "round_robin")])
+def test_host_order_matches_oracle(oracle, nranks, rule):
+    scene = scenes.scene_c4(box_cells=4, nranks=nranks, rule=rule)
+    recs, n = scene.records()
+    rng = np.random.default_rng(17)
+    for _ in range(12):
+        eye = rng.normal(size=3)
+        eye = 0.5 + eye / np.linalg.norm(eye) * rng.uniform(1.2, 3.0)
+        cam = scenes.make_camera(eye=eye)
+        for graph in (True, False):
+            want, ok = oracle.order(nranks, recs, n, cam, 1.25, graph)
+            got, failed = engine.order_boxes_host(nranks, recs, n, cam, 1.25, graph)
+            assert np.array_equal(got, want)
+            assert failed == (not ok)
+
+
+def test_host_order_random_boxes_with_cycles(oracle):
+    rng = np.random.default_rng(23)
+    for trial in range(40):
+        n = int(rng.integers(1, 48))
+        recs = (api.BoxRecord * n)()
+        local = {}
+        for i in range(n):
+            lo = rng.integers(0, 4, size=3) / 4.0
+            hi = lo + rng.integers(1, 3, size=3) / 4.0
+            for d in range(3):
+                recs[i].min_corner[d], recs[i].max_corner[d] = lo[d], hi[d]
+                recs[i].dims[d] = 4
+            recs[i].owner = int(i * 4 // n)
+            recs[i].local_index = local.get(recs[i].owner, 0)
+            local[recs[i].owner] = recs[i].local_index + 1
+        cam = scenes.make_camera(eye=tuple(rng.uniform(-2, 3, size=3)))
+        want, ok = oracle.order(4, recs, n, cam, 1.0)
+        got, failed = engine.order_boxes_host(4, recs, n, cam, 1.0)
+        assert np.array_equal(got, want), trial
+        assert failed == (not ok)
+
+
+def test_layer_order_and_hints_match_oracle(oracle):
+    """computeBoxDepthHint + the (depth, owner, local index) sort, bit-exact."""
+    for P, rule in ((1, "chunks"), (4, "round_robin"), (8, "chunks")):
+        scene = scenes.scene_c4(box_cells=4, nranks=P, rule=rule)
+        recs, n = scene.records()
+        for eye in ((1.9, 1.3, 2.4), (0.5, 0.5, 3.0), (-1.0, 0.2, 0.4)):
+            cam = scenes.make_camera(eye=eye)
+            hints, order = engine.layer_order_host(recs, n, cam)
+            want_hints, want_order = oracle.layer_order(recs, n, cam)
+            assert np.array_equal(hints, want_hints)
+            assert np.array_equal(order, want_order)
+
+
+def test_piece_range_matches_oracle(oracle):
+    for npix, P in ((10800, 8), (7, 3), (5, 8), (0, 2), (4096 * 4096, 7), (2048 * 2048, 8)):
+        for i in range(P):
+            assert engine.piece_range(npix, i, P) == oracle.piece_range(npix, i, P)
+    lib = api.load_library()
+    b, e = C.c_int(), C.c_int()
+    assert lib.amrvr_piece_range(10, 3, 3, C.byref(b), C.byref(e)) == api.AMRVR_ERR_INVALID
+
+
+def test_reference_sample_distance_matches_oracle(oracle):
+    for scene in (scenes.scene_c1(), scenes.scene_c2prime(box_cells=10), scenes.scene_c4(box_cells=4)):
+        recs, n = scene.records()
+        got = engine.reference_sample_distance(recs, n, scene.bounds_min, scene.bounds_max)
+        assert got == oracle.reference_sample_distance(recs, n, scene.bounds_min, scene.bounds_max)
+    # no boxes: falls back to 1 % of the shortest bounds edge
+    empty = (api.BoxRecord * 1)()
+    assert engine.reference_sample_distance(empty, 0, (0, 0, 0), (1, 2, 3)) == \
+        oracle.reference_sample_distance(empty, 0, (0, 0, 0), (1, 2, 3))
