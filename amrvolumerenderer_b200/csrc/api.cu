@@ -875,13 +875,14 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
   CUDA_TRY(ctx, cudaEventCreate(&L->t0));
   CUDA_TRY(ctx, cudaEventCreate(&L->t1));
   unsigned long long* counter = ctx->counter.as<unsigned long long>();
-  if (count_samples) CUDA_TRY(ctx, cudaMemsetAsync(counter, 0, 8, ctx->stream));
+  unsigned* tile_counter = reinterpret_cast<unsigned*>(counter + 1);
+  CUDA_TRY(ctx, cudaMemsetAsync(counter, 0, 16, ctx->stream));  // sample counter + tile counter
   CUDA_TRY(ctx, cudaEventRecord(L->t0, ctx->stream));
   if (n > 0)
     LAUNCH_TRY(ctx, launch_raymarch(frame, ctx->march_boxes.as<MarchBox>(),
                                     scene->bricks.as<uint8_t>(), ctx->tables.as<float>(),
-                                    L->pool.as<float>(), counter, count_samples != 0, ctx->stream,
-                                    &ctx->launches));
+                                    L->pool.as<float>(), counter, tile_counter, count_samples != 0,
+                                    ctx->stream, &ctx->launches));
   CUDA_TRY(ctx, cudaEventRecord(L->t1, ctx->stream));
   if (count_samples) {
     unsigned long long host = 0;

@@ -169,8 +169,8 @@ int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride,
                           int64_t* launches);
 int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev,
                     const uint8_t* bricks, const float* tables, float* layers,
-                    unsigned long long* sample_counter, bool count_samples,
-                    void* stream, int64_t* launches);
+                    unsigned long long* sample_counter, unsigned* tile_counter /*zeroed*/,
+                    bool count_samples, void* stream, int64_t* launches);
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int pixel_begin, int pixel_end, float* piece5, void* stream,
                 int64_t* launches);

@@ -15,6 +15,7 @@
 //   order_pairs_kernel      K7  all-pairs face-adjacency test
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cfloat>
 #include <cmath>
 
@@ -232,6 +233,15 @@ __device__ __forceinline__ float4 lds_f4(unsigned addr) {
   return v;
 }
 
+__device__ __forceinline__ float pin_reg(float v) {
+  asm volatile("mov.f32 %0, %1;" : "=f"(v) : "f"(v));
+  return v;
+}
+__device__ __forceinline__ const unsigned char* pin_ptr(const unsigned char* p) {
+  asm volatile("mov.b64 %0, %1;" : "=l"(p) : "l"(p));
+  return p;
+}
+
 struct RayOut {
   float r, g, b, a, depth;
   unsigned nsamples;
@@ -243,7 +253,8 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
                                             unsigned table_addr, int px, int py, bool valid) {
   const float lox = B.lo[0], loy = B.lo[1], loz = B.lo[2];
   const float hix = B.hi[0], hiy = B.hi[1], hiz = B.hi[2];
-  const float ex = f.eye[0], ey = f.eye[1], ez = f.eye[2];
+  // held in registers: re-reading the constant bank costs an issue slot per use
+  const float ex = pin_reg(f.eye[0]), ey = pin_reg(f.eye[1]), ez = pin_reg(f.eye[2]);
 
   // ray through the pixel centre (:738-766)
   const float ndc_x = (static_cast<float>(px) + 0.5f) * f.inv_w * 2.0f - 1.0f;
@@ -316,7 +327,7 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
 
   const unsigned nx = static_cast<unsigned>(B.n[0]), ny = static_cast<unsigned>(B.n[1]);
   const unsigned ix_max = nx - 1u, iy_max = ny - 1u, iz_max = static_cast<unsigned>(B.n[2]) - 1u;
-  const unsigned char* __restrict__ brick = bricks + B.brick_off;
+  const unsigned char* brick = pin_ptr(bricks + B.brick_off);
   const float cx = kRecip ? B.inv_cell_tiny[0] : B.cell[0];
   const float cy = kRecip ? B.inv_cell_tiny[1] : B.cell[1];
   const float cz = kRecip ? B.inv_cell_tiny[2] : B.cell[2];
@@ -327,14 +338,27 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
     pys = ey + dy * distance;
     pzs = ez + dz * distance;
   };
-  auto shade = [&](unsigned jk, unsigned ib) {  // :884-894; jk = k*ny + j
-    unsigned cell, idx, slot;
-    // spelled out so that the byte arrives zero-extended and the table address
-    // is one multiply-add
-    cell = jk * nx + ib;
-    asm("ld.global.nc.u8 %0, [%1];" : "=r"(idx) : "l"(brick + cell));
+  auto fetch = [&](unsigned cell) {
+    // spelled out so that the byte arrives zero-extended
+    unsigned idx;
+    asm volatile("ld.global.nc.u8 %0, [%1];" : "=r"(idx) : "l"(brick + cell));
+    return idx;
+  };
+  // predicated gather: no access when !wanted, and idx then keeps its previous
+  // (valid) value, so a table read through it stays in range
+  auto fetch_if = [&](unsigned& idx, unsigned cell, bool wanted) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %2, 0;\n\t"
+        "@p ld.global.nc.u8 %0, [%1];\n\t}"
+        : "+r"(idx)
+        : "l"(brick + cell), "r"(static_cast<int>(wanted)));
+  };
+  auto table_entry = [&](unsigned idx) {
+    unsigned slot;  // the table address is one multiply-add
     asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(slot) : "r"(idx), "r"(16u * kTableCopies), "r"(table_addr));
-    const float4 e = lds_f4(slot);
+    return lds_f4(slot);
+  };
+  auto blend = [&](const float4& e) {  // :884-894
     const float a = e.w * (1.0f - acc_a);
     acc_r += e.x * a;
     acc_g += e.y * a;
@@ -342,6 +366,7 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
     acc_a += a;
     if (kCount) ++nsamples;
   };
+  auto shade = [&](unsigned jk, unsigned ib) { blend(table_entry(fetch(jk * nx + ib))); };  // jk = k*ny + j
   auto cell_of = [&](float p, float lo, float c) {
     // reference: floor((p - lo) / cell), :846-848
     return __float_as_uint(kRecip ? __fmul_rd(p - lo, c) : __fmul_rd((p - lo) / c, kTinyOne));
@@ -362,13 +387,55 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
   // same sequence of samples.
   const float t_head = fminf(ts0, tmax);
   while (distance < t_head && acc_a < 1.0f) checked();
+  // Provably-inside stretch, software-pipelined two deep.  The position of a
+  // sample is a function of `distance` alone, never of the shading, so while
+  // sample A is blended the table entry of sample B is being read from shared
+  // memory and the brick byte of sample C is being gathered from L1/L2.  The
+  // sequence of samples and every operation on them are those of the plain
+  // loop; speculative requests are either predicated off or go to in-range
+  // addresses and their values are dropped when the ray saturates first.
   const float t_body = fminf(ts1, tmax);
-  while (distance < t_body && acc_a < 1.0f) {
-    const unsigned ib = cell_of(pxs, lox, cx);
-    const unsigned jb = cell_of(pys, loy, cy);
-    const unsigned kb = cell_of(pzs, loz, cz);
-    shade(kb * ny + jb, ib);
-    advance();
+  if (distance < t_body && acc_a < 1.0f) {
+    auto cell_at = [&](float d) {
+      const float qx = ex + dx * d, qy = ey + dy * d, qz = ez + dz * d;
+      return (cell_of(qz, loz, cz) * ny + cell_of(qy, loy, cy)) * nx + cell_of(qx, lox, cx);
+    };
+    unsigned idx_a = 0u, idx_b = 0u, idx_c = 0u;
+    fetch_if(idx_a, cell_at(distance), true);
+    float d_b = distance + step, d_c = 0.0f;
+    bool more_b = d_b < t_body, more_c = false;
+    fetch_if(idx_b, cell_at(d_b), more_b);
+    float4 e_a = table_entry(idx_a), e_b;
+    // One stage: request the byte two samples ahead, read the table entry one
+    // sample ahead, blend the current sample.  Returns true when the ray leaves
+    // the loop; d_next is then the plain loop's final `distance`.  The loop body
+    // is two stages with the roles of the register sets swapped, so nothing is
+    // moved between them.
+    auto stage = [&](const float4& e_cur, float4& e_next, unsigned idx_next, unsigned& idx_after,
+                     float d_next, float& d_after, bool more_next, bool& more_after) {
+      d_after = d_next + step;
+      more_after = more_next && (d_after < t_body);
+      fetch_if(idx_after, cell_at(d_after), more_after);
+      e_next = table_entry(idx_next);
+      blend(e_cur);
+      return !more_next || !(acc_a < 1.0f);
+    };
+    float d_exit;
+    for (;;) {
+      if (stage(e_a, e_b, idx_b, idx_c, d_b, d_c, more_b, more_c)) {
+        d_exit = d_b;
+        break;
+      }
+      if (stage(e_b, e_a, idx_c, idx_b, d_c, d_b, more_c, more_b)) {
+        d_exit = d_c;
+        break;
+      }
+    }
+    d_b = d_exit;
+    distance = d_b;  // the plain loop leaves the state one step past the last shaded sample
+    pxs = ex + dx * distance;
+    pys = ey + dy * distance;
+    pzs = ez + dz * distance;
   }
   while (distance < tmax && acc_a < 1.0f) checked();
 
@@ -390,65 +457,93 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
   return out;
 }
 
+// Persistent CTAs: the grid is (SM count x resident CTAs per SM) and every CTA
+// pulls 16x16 tiles from a global counter until none is left, heaviest launch
+// order preserved (tiles of one box are consecutive, so the box parameters and
+// the transfer table in shared memory are refilled only when they change --
+// three times per CTA on a three-level scene instead of once per tile).
+// Thread 0 claims tile i+1 and finds its box while the CTA marches tile i; the
+// claim lives in a two-slot mailbox indexed by iteration parity.
+#ifndef AMRVR_MARCH_MIN_BLOCKS
+#define AMRVR_MARCH_MIN_BLOCKS 4
+#endif
+
 template <bool kCount>
-__global__ void __launch_bounds__(kMarchThreads)
+__global__ void __launch_bounds__(kMarchThreads, AMRVR_MARCH_MIN_BLOCKS)
 raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __restrict__ boxes,
                        const unsigned char* __restrict__ bricks,
                        const float4* __restrict__ tables, float* __restrict__ layers,
-                       unsigned long long* __restrict__ sample_counter) {
+                       unsigned long long* __restrict__ sample_counter,
+                       unsigned* __restrict__ tile_counter) {
   __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE * kTableCopies];
   __shared__ MarchBox s_box;
-  __shared__ int s_which;
+  __shared__ int s_tile[2], s_which[2];
 
-  const int tile = blockIdx.x;
-  if (threadIdx.x == 0) {  // last box whose first tile is <= tile
-    int lo = 0, hi = f.nboxes - 1;
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if (boxes[mid].tile_base <= tile) lo = mid; else hi = mid - 1;
+  auto claim = [&](int slot) {  // thread 0 only
+    const int tile = static_cast<int>(atomicAdd(tile_counter, 1u));
+    int lo = 0;
+    if (tile < f.ntiles) {  // last box whose first tile is <= tile
+      int hi = f.nboxes - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(&boxes[mid].tile_base) <= tile) lo = mid; else hi = mid - 1;
+      }
     }
-    s_which = lo;
-  }
-  __syncthreads();
-  {
-    const int words = sizeof(MarchBox) / 4;
-    const int* src = reinterpret_cast<const int*>(boxes + s_which);
-    if (threadIdx.x < words) reinterpret_cast<int*>(&s_box)[threadIdx.x] = src[threadIdx.x];
-  }
-  __syncthreads();
-  {
-    const float4 e = tables[s_box.table * AMRVR_COLOR_TABLE_SIZE + threadIdx.x];
-#pragma unroll
-    for (int c = 0; c < kTableCopies; ++c) s_table[threadIdx.x * kTableCopies + c] = e;
-  }
-  __syncthreads();
+    s_tile[slot] = tile;
+    s_which[slot] = lo;
+  };
 
-  const int local_tile = tile - s_box.tile_base;
-  const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
-  const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
-  const int rw = s_box.rw;
-  const bool valid = x < rw && y < s_box.rh;
   const unsigned table_addr = smem_u32(s_table) + static_cast<unsigned>(lane % kTableCopies) * 16u;
+  int have_box = -1, have_table = -1;
+  unsigned nsamples = 0;
+  if (threadIdx.x == 0) claim(0);
+  for (int it = 0;; ++it) {
+    __syncthreads();  // mailbox slot it&1 is written; everyone is done with the previous tile
+    const int tile = s_tile[it & 1], which = s_which[it & 1];
+    if (tile >= f.ntiles) break;
+    if (which != have_box) {  // uniform across the CTA
+      const int words = sizeof(MarchBox) / 4;
+      const int* src = reinterpret_cast<const int*>(boxes + which);
+      if (threadIdx.x < words) reinterpret_cast<int*>(&s_box)[threadIdx.x] = __ldg(src + threadIdx.x);
+      const int table = __ldg(&boxes[which].table);
+      if (table != have_table) {
+        // consecutive threads write consecutive 16 B slots: conflict-free stores
+        const float4* src4 = tables + table * AMRVR_COLOR_TABLE_SIZE;
+        for (int slot = threadIdx.x; slot < AMRVR_COLOR_TABLE_SIZE * kTableCopies; slot += kMarchThreads)
+          s_table[slot] = __ldg(src4 + (slot / kTableCopies));
+        have_table = table;
+      }
+      have_box = which;
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) claim((it + 1) & 1);  // overlaps with the march below
 
-  const RayOut r = s_box.exact_recip
-                       ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x,
-                                                 s_box.ry0 + y, valid)
-                       : march_ray<kCount, false>(f, s_box, bricks, table_addr, s_box.rx0 + x,
-                                                  s_box.ry0 + y, valid);
+    const int local_tile = tile - s_box.tile_base;
+    const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
+    const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
+    const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
+    const int rw = s_box.rw;
+    const bool valid = x < rw && y < s_box.rh;
 
-  // host epilogue of the reference (:939-955)
-  float4 out = make_float4(clamp01(r.r), clamp01(r.g), clamp01(r.b), clamp01(r.a));
-  float depth = r.depth;
-  if (!isfinite(depth) || out.w <= 0.0f) depth = INFINITY;
-  if (valid) {
-    float* row = layers + s_box.layer_off + static_cast<size_t>(y) * rw * 5;
-    reinterpret_cast<float4*>(row)[x] = out;
-    row[4 * rw + x] = depth;
+    const RayOut r = s_box.exact_recip
+                         ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x,
+                                                   s_box.ry0 + y, valid)
+                         : march_ray<kCount, false>(f, s_box, bricks, table_addr, s_box.rx0 + x,
+                                                    s_box.ry0 + y, valid);
+
+    // host epilogue of the reference (:939-955)
+    float4 out = make_float4(clamp01(r.r), clamp01(r.g), clamp01(r.b), clamp01(r.a));
+    float depth = r.depth;
+    if (!isfinite(depth) || out.w <= 0.0f) depth = INFINITY;
+    if (valid) {
+      float* row = layers + s_box.layer_off + static_cast<size_t>(y) * rw * 5;
+      reinterpret_cast<float4*>(row)[x] = out;
+      row[4 * rw + x] = depth;
+    }
+    if (kCount) nsamples += r.nsamples;
   }
   if (kCount) {
-    unsigned nsamples = r.nsamples;
     for (int off = 16; off > 0; off >>= 1) nsamples += __shfl_down_sync(0xffffffffu, nsamples, off);
     if (lane == 0 && nsamples != 0)
       atomicAdd(sample_counter, static_cast<unsigned long long>(nsamples));
@@ -888,16 +983,37 @@ int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride, 
   return static_cast<int>(cudaGetLastError());
 }
 
+int march_grid_size(bool count_samples) {
+  static int cached[2] = {0, 0};
+  int& grid = cached[count_samples ? 1 : 0];
+  if (grid == 0) {
+    int device = 0, sms = 148, per_sm = 1;
+    cudaGetDevice(&device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (count_samples)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, raymarch_bricks_kernel<true>,
+                                                    kMarchThreads, 0);
+    else
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, raymarch_bricks_kernel<false>,
+                                                    kMarchThreads, 0);
+    grid = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  return grid;
+}
+
 int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev, const uint8_t* bricks,
                     const float* tables, float* layers, unsigned long long* sample_counter,
-                    bool count_samples, void* stream, int64_t* launches) {
+                    unsigned* tile_counter, bool count_samples, void* stream, int64_t* launches) {
   if (frame.ntiles <= 0) return 0;
+  const int grid = std::min(march_grid_size(count_samples), frame.ntiles);
   if (count_samples) {
-    raymarch_bricks_kernel<true><<<frame.ntiles, kMarchThreads, 0, as_stream(stream)>>>(
-        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter);
+    raymarch_bricks_kernel<true><<<grid, kMarchThreads, 0, as_stream(stream)>>>(
+        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter,
+        tile_counter);
   } else {
-    raymarch_bricks_kernel<false><<<frame.ntiles, kMarchThreads, 0, as_stream(stream)>>>(
-        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter);
+    raymarch_bricks_kernel<false><<<grid, kMarchThreads, 0, as_stream(stream)>>>(
+        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter,
+        tile_counter);
   }
   ++*launches;
   return static_cast<int>(cudaGetLastError());
