@@ -12,6 +12,7 @@
 #include <memory>
 #include <string>
 #include <type_traits>
+#include <unistd.h>
 #include <vector>
 
 #include "internal.hpp"
@@ -50,6 +51,15 @@ struct DeviceBuffer {  // grow-only device allocation
   }
 };
 
+// A buffer that exists with the same capacity on every rank of the box and is
+// mapped into every process: peer[q] is rank q's copy as seen from here.
+struct SymBuffer {
+  void* local = nullptr;
+  size_t cap = 0;
+  std::vector<void*> peer;   // [nranks]; peer[me] == local
+  std::vector<char> opened;  // peer[q] came from cudaIpcOpenMemHandle
+};
+
 struct amrvr_ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
@@ -72,6 +82,19 @@ struct amrvr_ctx {
   DeviceBuffer order_boxes, order_scratch_a, order_scratch_b, order_priority, order_edges;
   DeviceBuffer stats_partials;
   std::vector<DeviceBuffer> layer_pools;  // recycled layer pools
+  std::vector<cudaEvent_t> event_pool;    // recycled timing events
+  // peer-memory exchange (nranks > 1 on one NVLink box; off -> NCCL alltoallv)
+  bool peer_ok = false;
+  SymBuffer sym_flags, sym_pool, sym_piece, sym_rgb8;
+  uint32_t barrier_epoch = 0;
+  uint32_t* peer_error_host = nullptr;  // pinned copy of the barrier time-out flag
+  uint8_t* last_rgb8 = nullptr;         // RGB8 frame of the last amrvr_render_frame (root)
+  // transfer tables already built, keyed by every input of buildColorTable
+  struct TableEntry {
+    std::vector<unsigned char> key;
+    std::vector<float> rgba;
+  };
+  std::vector<TableEntry> table_cache;
 };
 
 struct LocalBox {
@@ -92,8 +115,10 @@ struct amrvr_layers {
   int width = 0, height = 0;
   amrvr_camera camera{};
   std::vector<Rect> rects;
+  std::vector<Rect> global_rects;  // footprints of ALL boxes of the scene (the composite's plan)
   std::vector<uint64_t> offs;  // float offsets into pool
   DeviceBuffer pool;
+  bool pool_shared = false;  // pool is the context's peer-mapped pool (not owned)
   uint64_t pool_floats = 0;
   bool counted = false;
   cudaEvent_t t0 = nullptr, t1 = nullptr;
@@ -275,7 +300,8 @@ struct FramePlan {
 };
 
 void make_frame_plan(const amrvr_scene& scene, const amrvr_camera& cam, int width, int height,
-                     int nranks, const int* rank_order, FramePlan& plan) {
+                     int nranks, const int* rank_order, FramePlan& plan,
+                     const std::vector<Rect>* known_rects = nullptr) {
   const int n = static_cast<int>(scene.global.size());
   plan.order.assign(n, 0);
   layer_order(n, scene.global.data(), cam, nullptr, plan.order.data());
@@ -289,10 +315,14 @@ void make_frame_plan(const amrvr_scene& scene, const amrvr_camera& cam, int widt
   }
   CameraBasis basis;
   make_camera_basis(cam, basis);
-  plan.rects.resize(n);
-  for (int g = 0; g < n; ++g)
-    plan.rects[g] = box_footprint(scene.global[g].min_corner, scene.global[g].max_corner,
-                                  scene.global[g].dims, basis, cam, width, height);
+  if (known_rects != nullptr && static_cast<int>(known_rects->size()) == n) {
+    plan.rects = *known_rects;  // computed by amrvr_raymarch for the same camera and size
+  } else {
+    plan.rects.resize(n);
+    for (int g = 0; g < n; ++g)
+      plan.rects[g] = box_footprint(scene.global[g].min_corner, scene.global[g].max_corner,
+                                    scene.global[g].dims, basis, cam, width, height);
+  }
   plan.piece_of_rank.assign(nranks, 0);
   plan.begin.assign(nranks, 0);
   plan.end.assign(nranks, 0);
@@ -310,6 +340,129 @@ bool slice_rows(const Rect& r, int begin, int end, int width, int* s0, int* s1) 
   *s0 = std::max(r.y0, yb);
   *s1 = std::min(r.y0 + r.h, ye + 1);
   return *s1 > *s0;
+}
+
+}  // namespace
+
+namespace {
+
+struct SymRecord {  // what every rank tells the others about its new allocation
+  cudaIpcMemHandle_t handle;
+  unsigned long long pointer;
+  long long pid;
+  int device;
+  int ok;
+};
+
+void sym_release(SymBuffer& b, int me) {
+  for (size_t q = 0; q < b.peer.size(); ++q)
+    if (static_cast<int>(q) != me && b.opened[q] && b.peer[q] != nullptr) cudaIpcCloseMemHandle(b.peer[q]);
+  if (b.local != nullptr) cudaFree(b.local);
+  b = SymBuffer{};
+}
+
+PeerPtrs peer_ptrs(const SymBuffer& b) {
+  PeerPtrs out{};
+  for (size_t q = 0; q < b.peer.size() && q < static_cast<size_t>(kMaxPeers); ++q) out.p[q] = b.peer[q];
+  return out;
+}
+
+// Collective: afterwards every rank holds >= bytes and has every peer's copy
+// mapped.  `bytes` must be the same on every rank (it is always derived from
+// the global box table or the frame size), so all ranks grow in the same call.
+// *all_ok reports whether EVERY rank could map every peer.
+int sym_reserve(amrvr_ctx* ctx, SymBuffer& buf, size_t bytes, bool* all_ok) {
+  if (all_ok) *all_ok = true;
+  if (bytes <= buf.cap && buf.local != nullptr) return AMRVR_OK;
+  const int P = ctx->nranks, me = ctx->rank;
+  NcclApi& nc = nccl_api();
+  const size_t want = ((bytes + bytes / 4) + (size_t(2) << 20) - 1) & ~((size_t(2) << 20) - 1);
+  SymBuffer fresh;
+  fresh.peer.assign(static_cast<size_t>(P), nullptr);
+  fresh.opened.assign(static_cast<size_t>(P), 0);
+  SymRecord mine{};
+  mine.ok = 1;
+  if (cudaMalloc(&fresh.local, want) != cudaSuccess) {
+    (void)cudaGetLastError();
+    fresh.local = nullptr;
+    mine.ok = 0;
+  } else {
+    cudaMemsetAsync(fresh.local, 0, want, ctx->stream);
+    if (cudaIpcGetMemHandle(&mine.handle, fresh.local) != cudaSuccess) {
+      (void)cudaGetLastError();
+      mine.ok = 0;
+    }
+  }
+  mine.pointer = reinterpret_cast<unsigned long long>(fresh.local);
+  mine.pid = static_cast<long long>(getpid());
+  mine.device = ctx->device;
+  // exchange the records (this allgather is also the barrier that makes it safe
+  // to drop the old buffers afterwards: every rank has finished using them)
+  DeviceBuffer tmp;
+  CUDA_TRY(ctx, tmp.reserve(sizeof(SymRecord) * static_cast<size_t>(P + 1)));
+  std::vector<SymRecord> all(static_cast<size_t>(P));
+  auto allgather = [&](SymRecord& rec) -> int {
+    CUDA_TRY(ctx, cudaMemcpyAsync(tmp.as<SymRecord>() + P, &rec, sizeof(SymRecord),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+    NCCL_TRY(ctx, nc.AllGather(tmp.as<SymRecord>() + P, tmp.ptr, sizeof(SymRecord), ncclChar,
+                               ctx->comm, ctx->stream));
+    CUDA_TRY(ctx, cudaMemcpyAsync(all.data(), tmp.ptr, sizeof(SymRecord) * P, cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return AMRVR_OK;
+  };
+  int st = allgather(mine);
+  if (st != AMRVR_OK) return st;
+  bool ok = true;
+  for (int q = 0; q < P; ++q) ok = ok && all[q].ok != 0;
+  if (ok) {
+    fresh.peer[me] = fresh.local;
+    for (int q = 0; q < P && ok; ++q) {
+      if (q == me) continue;
+      if (all[q].pid == mine.pid) {  // ranks are threads of one process: plain peer access
+        if (all[q].device != ctx->device) {
+          const cudaError_t e = cudaDeviceEnablePeerAccess(all[q].device, 0);
+          if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) ok = false;
+          (void)cudaGetLastError();
+        }
+        fresh.peer[q] = reinterpret_cast<void*>(all[q].pointer);
+      } else {
+        void* mapped = nullptr;
+        if (cudaIpcOpenMemHandle(&mapped, all[q].handle, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+          (void)cudaGetLastError();
+          ok = false;
+        } else {
+          fresh.peer[q] = mapped;
+          fresh.opened[q] = 1;
+        }
+      }
+    }
+  }
+  // second round: did everyone map everyone?
+  mine.ok = ok ? 1 : 0;
+  st = allgather(mine);
+  if (st != AMRVR_OK) return st;
+  for (int q = 0; q < P; ++q) ok = ok && all[q].ok != 0;
+  tmp.release();
+  if (!ok) {
+    sym_release(fresh, me);
+    if (all_ok) *all_ok = false;
+    return AMRVR_OK;  // not an error: the caller falls back to the NCCL exchange
+  }
+  sym_release(buf, me);
+  buf = fresh;
+  buf.cap = want;
+  return AMRVR_OK;
+}
+
+// Barrier kernel on the ctx stream (row `which` of the flag block).
+int peer_barrier(amrvr_ctx* ctx, int which) {
+  ++ctx->barrier_epoch;
+  uint32_t* error_flag = static_cast<uint32_t*>(ctx->sym_flags.local) + kFlagRows * kMaxPeers;
+  LAUNCH_TRY(ctx, launch_peer_barrier(peer_ptrs(ctx->sym_flags), ctx->rank, ctx->nranks, which,
+                                      ctx->barrier_epoch, 10ull * 1000 * 1000 * 1000, error_flag,
+                                      ctx->stream, &ctx->launches));
+  return AMRVR_OK;
 }
 
 }  // namespace
@@ -379,6 +532,22 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
     ncclUniqueId id;
     std::memcpy(&id, nccl_unique_id, sizeof(id));
     NCCL_TRY(nullptr, nccl_api().CommInitRank(&ctx->comm, nranks, id, rank));
+    // peer-memory exchange: every rank must be able to map every other rank's
+    // buffers (one NVLink box).  AMRVR_EXCHANGE=nccl keeps the NCCL alltoallv.
+    const char* mode = std::getenv("AMRVR_EXCHANGE");
+    const bool want_peer = nranks <= kMaxPeers && !(mode != nullptr && std::strcmp(mode, "nccl") == 0);
+    if (want_peer) {
+      bool ok = false;
+      amrvr_ctx* raw = ctx.get();
+      const int st = sym_reserve(raw, raw->sym_flags, (kFlagRows * kMaxPeers + 4) * sizeof(uint32_t), &ok);
+      if (st != AMRVR_OK) {
+        g_error = raw->error;
+        return st;
+      }
+      raw->peer_ok = ok;
+      if (ok) CUDA_TRY(nullptr, cudaMallocHost(reinterpret_cast<void**>(&raw->peer_error_host), 64));
+      if (ok) *raw->peer_error_host = 0;
+    }
   }
   *out = ctx.release();
   return AMRVR_OK;
@@ -388,6 +557,9 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   if (ctx == nullptr) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  for (SymBuffer* b : {&ctx->sym_flags, &ctx->sym_pool, &ctx->sym_piece, &ctx->sym_rgb8})
+    sym_release(*b, ctx->rank);
+  if (ctx->peer_error_host != nullptr) cudaFreeHost(ctx->peer_error_host);
   if (ctx->comm != nullptr) nccl_api().CommDestroy(ctx->comm);
   for (DeviceBuffer* b :
        {&ctx->stage, &ctx->march_boxes, &ctx->tables, &ctx->counter, &ctx->fold_layers,
@@ -398,6 +570,7 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (auto& p : ctx->layer_pools) p.release();
   for (auto& e : ctx->ev)
     if (e != nullptr) cudaEventDestroy(e);
+  for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
   cudaStreamDestroy(ctx->aux);
   delete ctx;
@@ -411,7 +584,7 @@ extern "C" int64_t amrvr_ctx_kernel_launches(const amrvr_ctx* ctx) {
   return ctx ? ctx->launches : 0;
 }
 extern "C" const uint8_t* amrvr_ctx_frame_rgb8_device(const amrvr_ctx* ctx) {
-  return ctx ? ctx->rgb8.as<uint8_t>() : nullptr;
+  return ctx ? ctx->last_rgb8 : nullptr;
 }
 extern "C" int amrvr_ctx_set_order_device_min_boxes(amrvr_ctx* ctx, int min_boxes) {
   if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
@@ -751,10 +924,66 @@ extern "C" int amrvr_color_table(float alpha_scale, float normalization_factor, 
 // ray-march
 // ---------------------------------------------------------------------------
 
+namespace {
+
+// buildColorTable is a pure function of (alpha scale, normalisation factor,
+// scalar range, control points); an animation re-uses the same few tables
+// every frame, so they are memoised per context (most recent first, <= 16).
+const float* cached_color_table(amrvr_ctx* ctx, float alpha_scale, float norm, float range_min,
+                                float range_max, const amrvr_colormap_pt* pts, int npts) {
+  std::vector<unsigned char> key(4 * sizeof(float) + static_cast<size_t>(npts) * sizeof(amrvr_colormap_pt));
+  const float head[4] = {alpha_scale, norm, range_min, range_max};
+  std::memcpy(key.data(), head, sizeof(head));
+  if (npts > 0) std::memcpy(key.data() + sizeof(head), pts, static_cast<size_t>(npts) * sizeof(amrvr_colormap_pt));
+  auto& cache = ctx->table_cache;
+  for (size_t i = 0; i < cache.size(); ++i)
+    if (cache[i].key == key) {
+      if (i != 0) std::rotate(cache.begin(), cache.begin() + static_cast<long>(i), cache.begin() + static_cast<long>(i) + 1);
+      return cache[0].rgba.data();
+    }
+  amrvr_ctx::TableEntry entry;
+  entry.key = std::move(key);
+  entry.rgba.resize(4 * AMRVR_COLOR_TABLE_SIZE);
+  build_color_table(alpha_scale, norm, range_min, range_max, pts, npts, entry.rgba.data());
+  cache.insert(cache.begin(), std::move(entry));
+  if (cache.size() > 16) cache.pop_back();
+  return cache[0].rgba.data();
+}
+
+cudaError_t take_event(amrvr_ctx* ctx, cudaEvent_t* out) {
+  if (!ctx->event_pool.empty()) {
+    *out = ctx->event_pool.back();
+    ctx->event_pool.pop_back();
+    return cudaSuccess;
+  }
+  return cudaEventCreate(out);
+}
+
+}  // namespace
+
+namespace {
+// shared_pool: the layers go into the context's peer-mapped pool so that other
+// GPUs can fold them straight over NVLink (collective: every rank must make
+// the same call; used by amrvr_render_frame only)
+int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
+                  int width, int height, float box_transparency,
+                  float reference_sample_distance_, const amrvr_colormap_pt* pts,
+                  int npts, int count_samples, bool shared_pool, amrvr_layers** out);
+}  // namespace
+
 extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
                               int width, int height, float box_transparency,
                               float reference_sample_distance_, const amrvr_colormap_pt* pts,
                               int npts, int count_samples, amrvr_layers** out) {
+  return raymarch_impl(ctx, scene, camera, width, height, box_transparency,
+                       reference_sample_distance_, pts, npts, count_samples, false, out);
+}
+
+namespace {
+int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
+                  int width, int height, float box_transparency,
+                  float reference_sample_distance_, const amrvr_colormap_pt* pts,
+                  int npts, int count_samples, bool shared_pool, amrvr_layers** out) {
   if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
   REQUIRE(ctx, out != nullptr, "out is NULL");
   *out = nullptr;
@@ -790,6 +1019,10 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
   frame.height = height;
   frame.nboxes = n;
 
+  L->global_rects.resize(scene->global.size());
+  for (size_t g = 0; g < scene->global.size(); ++g)
+    L->global_rects[g] = box_footprint(scene->global[g].min_corner, scene->global[g].max_corner,
+                                       scene->global[g].dims, basis, *camera, width, height);
   const float alpha_scale = std::min(std::max(1.0f - box_transparency, 0.0f), 1.0f);
   std::vector<MarchBox> mb(static_cast<size_t>(n));
   std::vector<float> table_norm;  // one table per distinct normalisation factor
@@ -810,8 +1043,10 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
       which = static_cast<int>(table_norm.size());
       table_norm.push_back(norm);
       tables.resize(tables.size() + 4 * AMRVR_COLOR_TABLE_SIZE);
-      build_color_table(alpha_scale, norm, scene->range_min, scene->range_max, pts, npts,
-                        tables.data() + static_cast<size_t>(which) * 4 * AMRVR_COLOR_TABLE_SIZE);
+      std::memcpy(tables.data() + static_cast<size_t>(which) * 4 * AMRVR_COLOR_TABLE_SIZE,
+                  cached_color_table(ctx, alpha_scale, norm, scene->range_min, scene->range_max, pts,
+                                     npts),
+                  4 * AMRVR_COLOR_TABLE_SIZE * sizeof(float));
     }
     M.table = which;
     M.step = step;
@@ -834,7 +1069,7 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
     M.eps = std::sqrt(diag2) * 0.0001f;
     M.exact_recip = pow2 ? 1 : 0;
     M.margin = inside_margin(M, basis.eye);
-    const Rect r = box_footprint(B.min_corner, B.max_corner, B.dims, basis, *camera, width, height);
+    const Rect r = L->global_rects[static_cast<size_t>(scene->first_global + b)];
     L->rects[b] = r;
     M.rx0 = r.x0;
     M.ry0 = r.y0;
@@ -854,9 +1089,26 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
   L->stats.rays = rays;
   L->stats.fragment_pixels = rays;
 
-  // layer pool: reuse a recycled one when it is large enough
+  // layer pool: the peer-mapped one, or a recycled one when it is large enough
   const size_t need = std::max<size_t>(floats * sizeof(float), 256);
-  for (size_t i = 0; i < ctx->layer_pools.size(); ++i)
+  if (shared_pool) {
+    // every rank sizes the pool for the largest rank (all of them know every footprint)
+    std::vector<uint64_t> per_rank(static_cast<size_t>(ctx->nranks), 0);
+    for (size_t g = 0; g < scene->global.size(); ++g) {
+      const int owner = scene->global[g].owner;
+      if (owner >= 0 && owner < ctx->nranks)
+        per_rank[owner] += static_cast<uint64_t>(L->global_rects[g].w) * L->global_rects[g].h * 5;
+    }
+    const uint64_t most = *std::max_element(per_rank.begin(), per_rank.end());
+    bool ok = true;
+    const int st = sym_reserve(ctx, ctx->sym_pool, std::max<size_t>(most * sizeof(float), 256), &ok);
+    if (st != AMRVR_OK) return st;
+    if (!ok) return fail(ctx, AMRVR_ERR_CUDA, "peer-mapped layer pool could not be grown on every rank");
+    L->pool.ptr = ctx->sym_pool.local;
+    L->pool.bytes = ctx->sym_pool.cap;
+    L->pool_shared = true;
+  }
+  for (size_t i = 0; L->pool.ptr == nullptr && i < ctx->layer_pools.size(); ++i)
     if (ctx->layer_pools[i].bytes >= need) {
       L->pool = ctx->layer_pools[i];
       ctx->layer_pools.erase(ctx->layer_pools.begin() + static_cast<long>(i));
@@ -864,23 +1116,26 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
     }
   if (L->pool.ptr == nullptr) CUDA_TRY(ctx, L->pool.reserve(need));
 
-  if (n > 0) {
-    CUDA_TRY(ctx, ctx->march_boxes.reserve(mb.size() * sizeof(MarchBox)));
-    CUDA_TRY(ctx, ctx->tables.reserve(tables.size() * sizeof(float)));
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->march_boxes.ptr, mb.data(), mb.size() * sizeof(MarchBox),
-                                  cudaMemcpyHostToDevice, ctx->stream));
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->tables.ptr, tables.data(), tables.size() * sizeof(float),
-                                  cudaMemcpyHostToDevice, ctx->stream));
-  }
-  CUDA_TRY(ctx, cudaEventCreate(&L->t0));
-  CUDA_TRY(ctx, cudaEventCreate(&L->t1));
-  unsigned long long* counter = ctx->counter.as<unsigned long long>();
+  // one parameter block, one host->device copy: [counters 16 B | tables | boxes]
+  const size_t tables_bytes = tables.size() * sizeof(float);
+  const size_t boxes_bytes = mb.size() * sizeof(MarchBox);
+  const size_t block_bytes = 16 + tables_bytes + boxes_bytes;
+  std::vector<unsigned char> block(block_bytes, 0);  // counters start at zero
+  if (tables_bytes) std::memcpy(block.data() + 16, tables.data(), tables_bytes);
+  if (boxes_bytes) std::memcpy(block.data() + 16 + tables_bytes, mb.data(), boxes_bytes);
+  CUDA_TRY(ctx, ctx->march_boxes.reserve(block_bytes));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->march_boxes.ptr, block.data(), block_bytes,
+                                cudaMemcpyHostToDevice, ctx->stream));
+  unsigned char* dev_block = ctx->march_boxes.as<unsigned char>();
+  unsigned long long* counter = reinterpret_cast<unsigned long long*>(dev_block);
   unsigned* tile_counter = reinterpret_cast<unsigned*>(counter + 1);
-  CUDA_TRY(ctx, cudaMemsetAsync(counter, 0, 16, ctx->stream));  // sample counter + tile counter
+  CUDA_TRY(ctx, take_event(ctx, &L->t0));
+  CUDA_TRY(ctx, take_event(ctx, &L->t1));
   CUDA_TRY(ctx, cudaEventRecord(L->t0, ctx->stream));
   if (n > 0)
-    LAUNCH_TRY(ctx, launch_raymarch(frame, ctx->march_boxes.as<MarchBox>(),
-                                    scene->bricks.as<uint8_t>(), ctx->tables.as<float>(),
+    LAUNCH_TRY(ctx, launch_raymarch(frame, reinterpret_cast<const MarchBox*>(dev_block + 16 + tables_bytes),
+                                    scene->bricks.as<uint8_t>(),
+                                    reinterpret_cast<const float*>(dev_block + 16),
                                     L->pool.as<float>(), counter, tile_counter, count_samples != 0,
                                     ctx->stream, &ctx->launches));
   CUDA_TRY(ctx, cudaEventRecord(L->t1, ctx->stream));
@@ -893,9 +1148,11 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
   *out = L.release();
   return AMRVR_OK;
 }
+}  // namespace
 
 extern "C" int amrvr_layers_free(amrvr_ctx* ctx, amrvr_layers* layers) {
   if (layers == nullptr) return AMRVR_OK;
+  if (layers->pool_shared) layers->pool = DeviceBuffer{};  // not owned
   if (ctx != nullptr) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
@@ -905,8 +1162,11 @@ extern "C" int amrvr_layers_free(amrvr_ctx* ctx, amrvr_layers* layers) {
     }
   }
   layers->pool.release();
-  if (layers->t0) cudaEventDestroy(layers->t0);
-  if (layers->t1) cudaEventDestroy(layers->t1);
+  for (cudaEvent_t e : {layers->t0, layers->t1}) {
+    if (e == nullptr) continue;
+    if (ctx != nullptr && ctx->event_pool.size() < 16) ctx->event_pool.push_back(e);
+    else cudaEventDestroy(e);
+  }
   delete layers;
   return AMRVR_OK;
 }
@@ -982,9 +1242,12 @@ extern "C" int amrvr_layers_read(amrvr_ctx* ctx, const amrvr_layers* layers, int
 // ---------------------------------------------------------------------------
 namespace {
 
+// piece_dst != nullptr: write the piece there instead of ctx->piece (single-rank
+// frames fold straight into the frame buffer)
 int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers* layers,
                    const amrvr_camera* camera, const int* rank_order, int* region_begin,
-                   int* region_end, float** piece_out, int64_t* exchanged_bytes) {
+                   int* region_end, float** piece_out, int64_t* exchanged_bytes,
+                   float* piece_dst = nullptr, bool peer = false) {
   const int P = ctx->nranks, me = ctx->rank;
   const int W = layers->width, H = layers->height;
   {
@@ -996,7 +1259,9 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
     }
   }
   FramePlan plan;
-  make_frame_plan(*scene, *camera, W, H, P, rank_order, plan);
+  const bool same_camera = std::memcmp(&layers->camera, camera, sizeof(amrvr_camera)) == 0;
+  make_frame_plan(*scene, *camera, W, H, P, rank_order, plan,
+                  same_camera ? &layers->global_rects : nullptr);
   const int n = static_cast<int>(scene->global.size());
   REQUIRE(ctx, static_cast<int>(layers->rects.size()) == static_cast<int>(scene->local.size()),
           "layers do not belong to this scene");
@@ -1013,7 +1278,25 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
   std::vector<uint64_t> send_off(P + 1, 0), recv_off(P + 1, 0);
   std::vector<CopyJob> jobs;
   std::vector<uint64_t> recv_slot(static_cast<size_t>(n), 0);  // float offset in recv_buf per global box
-  if (P > 1) {
+  // peer mode: no exchange step at all -- the fold kernel reads the other GPUs'
+  // fragments where they were marched, over NVLink.  pool_off[g] = float offset
+  // of box g's layer inside its owner's pool (owner-local prefix sum).
+  std::vector<uint64_t> pool_off;
+  if (peer) {
+    pool_off.assign(static_cast<size_t>(n), 0);
+    std::vector<uint64_t> cursor(static_cast<size_t>(P), 0);
+    uint64_t pulled = 0;
+    for (int g = 0; g < n; ++g) {
+      const int owner = scene->global[g].owner;
+      const Rect& r = plan.rects[g];
+      pool_off[g] = cursor[owner];
+      cursor[owner] += static_cast<uint64_t>(r.w) * r.h * 5;
+      int s0, s1;
+      if (owner != me && slice_rows(r, my_begin, my_end, W, &s0, &s1))
+        pulled += static_cast<uint64_t>(s1 - s0) * r.w * 5;
+    }
+    if (exchanged_bytes) *exchanged_bytes = static_cast<int64_t>(pulled * sizeof(float));
+  } else if (P > 1) {
     std::vector<uint64_t> send_len(P, 0), recv_len(P, 0);
     for (int g = 0; g < n; ++g) {
       const int owner = scene->global[g].owner;
@@ -1097,6 +1380,9 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
     if (scene->global[g].owner == me) {
       F.base = layers->pool.as<float>() + layers->offs[g - scene->first_global] +
                static_cast<uint64_t>(s0 - r.y0) * r.w * 5;
+    } else if (peer) {
+      F.base = static_cast<const float*>(ctx->sym_pool.peer[scene->global[g].owner]) + pool_off[g] +
+               static_cast<uint64_t>(s0 - r.y0) * r.w * 5;
     } else {
       F.base = ctx->recv_buf.as<float>() + recv_slot[g];
     }
@@ -1108,18 +1394,20 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
     fold.push_back(F);
   }
   const int npix = my_end - my_begin;
-  CUDA_TRY(ctx, ctx->piece.reserve(std::max<size_t>(static_cast<size_t>(std::max(npix, 0)) * 20, 256)));
+  if (piece_dst == nullptr) {
+    CUDA_TRY(ctx, ctx->piece.reserve(std::max<size_t>(static_cast<size_t>(std::max(npix, 0)) * 20, 256)));
+    piece_dst = ctx->piece.as<float>();
+  }
   if (!fold.empty()) {
     CUDA_TRY(ctx, ctx->fold_layers.reserve(fold.size() * sizeof(FoldLayer)));
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->fold_layers.ptr, fold.data(), fold.size() * sizeof(FoldLayer),
                                   cudaMemcpyHostToDevice, ctx->stream));
   }
   LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
-                              my_begin, my_end, ctx->piece.as<float>(), ctx->stream,
-                              &ctx->launches));
+                              my_begin, my_end, piece_dst, ctx->stream, &ctx->launches));
   if (region_begin) *region_begin = my_begin;
   if (region_end) *region_end = my_end;
-  if (piece_out) *piece_out = ctx->piece.as<float>();
+  if (piece_out) *piece_out = piece_dst;
   return AMRVR_OK;
 }
 
@@ -1546,8 +1834,21 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   CUDA_TRY(ctx, cudaEventRecord(ev[0], ctx->stream));
   trace.mark("setup");
   amrvr_layers* layers = nullptr;
-  int st = amrvr_raymarch(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
-                          params->count_samples, &layers);
+  // Peer mode (all ranks on one NVLink box): layers, pieces and the byte frame
+  // live in peer-mapped buffers; the only cross-GPU steps are two flag barriers.
+  const bool peer = ctx->peer_ok && ctx->nranks > 1;
+  int st = AMRVR_OK;
+  if (peer) {
+    const size_t npix_render = static_cast<size_t>(RW) * RH;
+    const size_t max_piece = npix_render / ctx->nranks + npix_render % ctx->nranks;
+    bool ok_a = true, ok_b = true;
+    st = sym_reserve(ctx, ctx->sym_piece, std::max<size_t>(max_piece * 20, 256), &ok_a);
+    if (st == AMRVR_OK) st = sym_reserve(ctx, ctx->sym_rgb8, static_cast<size_t>(W) * H * 3, &ok_b);
+    if (st != AMRVR_OK) return st;
+    if (!ok_a || !ok_b) return fail(ctx, AMRVR_ERR_CUDA, "peer-mapped frame buffers could not be grown");
+  }
+  st = raymarch_impl(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
+                     params->count_samples, peer, &layers);
   if (st != AMRVR_OK) return st;
   CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
   trace.mark("march_enqueue");
@@ -1569,8 +1870,17 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   int begin = 0, end = 0;
   float* piece = nullptr;
   int64_t exchanged = 0;
-  st = composite_impl(ctx, scene, layers, camera, rank_order.data(), &begin, &end, &piece,
-                      &exchanged);
+  const size_t render_floats = static_cast<size_t>(RW) * RH * 5;
+  const size_t out_floats = static_cast<size_t>(W) * H * 5;
+  if (ctx->rank == root) CUDA_TRY(ctx, ctx->full.reserve(render_floats * sizeof(float)));
+  const bool fold_into_frame = ctx->nranks == 1;  // the piece IS the frame: no gather copy
+  if (peer) st = peer_barrier(ctx, 0);  // every rank's layers are complete and visible
+  if (st == AMRVR_OK)
+    st = composite_impl(ctx, scene, layers, camera, rank_order.data(), &begin, &end, &piece,
+                        &exchanged,
+                        fold_into_frame ? ctx->full.as<float>()
+                                        : (peer ? static_cast<float*>(ctx->sym_piece.local) : nullptr),
+                        peer);
   if (st != AMRVR_OK) {
     amrvr_layers_free(ctx, layers);
     return st;
@@ -1578,10 +1888,36 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   CUDA_TRY(ctx, cudaEventRecord(ev[3], ctx->stream));
   trace.mark("composite_enqueue");
 
-  const size_t render_floats = static_cast<size_t>(RW) * RH * 5;
-  const size_t out_floats = static_cast<size_t>(W) * H * 5;
-  if (ctx->rank == root) CUDA_TRY(ctx, ctx->full.reserve(render_floats * sizeof(float)));
-  {
+  const bool bytes_by_pieces = peer && sqrt_aa == 1;  // every rank writes its bytes into the root's frame
+  if (peer) {
+    if (bytes_by_pieces) {
+      const OverlayEdges* edges_dev = nullptr;
+      if (params->draw_bounding_box && n > 0) {
+        OverlayEdges edges;
+        make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
+        CUDA_TRY(ctx, ctx->copy_jobs.reserve(sizeof(OverlayEdges)));
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, &edges, sizeof(edges), cudaMemcpyHostToDevice,
+                                      ctx->stream));
+        edges_dev = ctx->copy_jobs.as<OverlayEdges>();
+      }
+      LAUNCH_TRY(ctx, launch_post_piece(piece, begin, end, W, H, edges_dev,
+                                        static_cast<uint8_t*>(ctx->sym_rgb8.peer[root]), ctx->stream,
+                                        &ctx->launches));
+    }
+    st = peer_barrier(ctx, 1);  // pieces (and bytes) of every rank are in place
+    if (st == AMRVR_OK && ctx->rank == root && (!bytes_by_pieces || rgba5_host != nullptr)) {
+      // the root pulls the float pieces over NVLink (ImageColorOnly::Gather)
+      for (int pc = 0; pc < ctx->nranks && st == AMRVR_OK; ++pc) {
+        const int r = rank_order[pc];
+        int b0, e0;
+        piece_range(RW * RH, pc, ctx->nranks, &b0, &e0);
+        if (e0 > b0)
+          CUDA_TRY(ctx, cudaMemcpyAsync(ctx->full.as<float>() + static_cast<size_t>(b0) * 5,
+                                        ctx->sym_piece.peer[r], static_cast<size_t>(e0 - b0) * 20,
+                                        cudaMemcpyDeviceToDevice, ctx->stream));
+      }
+    }
+  } else if (!fold_into_frame) {
     std::vector<int> spans(static_cast<size_t>(2 * ctx->nranks));
     for (int pc = 0; pc < ctx->nranks; ++pc)
       piece_range(RW * RH, pc, ctx->nranks, &spans[2 * rank_order[pc]], &spans[2 * rank_order[pc] + 1]);
@@ -1593,7 +1929,24 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   }
   CUDA_TRY(ctx, cudaEventRecord(ev[4], ctx->stream));
 
-  if (ctx->rank == root) {
+  ctx->last_rgb8 = nullptr;
+  if (ctx->rank == root && bytes_by_pieces) {
+    // the byte frame is already complete in the peer-mapped buffer
+    ctx->last_rgb8 = static_cast<uint8_t*>(ctx->sym_rgb8.local);
+    if (rgba5_host != nullptr) {
+      float* image = ctx->full.as<float>();
+      if (params->draw_bounding_box && n > 0) {
+        OverlayEdges edges;
+        make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);
+        LAUNCH_TRY(ctx, launch_overlay(edges, 1, W, H, image, ctx->stream, &ctx->launches));
+      }
+      CUDA_TRY(ctx, cudaMemcpyAsync(rgba5_host, image, out_floats * sizeof(float),
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (rgb8_host != nullptr)
+      CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->sym_rgb8.local, static_cast<size_t>(W) * H * 3,
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+  } else if (ctx->rank == root) {
     float* image = ctx->full.as<float>();
     if (sqrt_aa > 1) {
       CUDA_TRY(ctx, ctx->small.reserve(out_floats * sizeof(float)));
@@ -1613,6 +1966,7 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
       CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
       LAUNCH_TRY(ctx, launch_quantize_rgb8(image, W, H, ctx->rgb8.as<uint8_t>(), ctx->stream,
                                            &ctx->launches));
+      ctx->last_rgb8 = ctx->rgb8.as<uint8_t>();
       if (rgb8_host != nullptr)
         CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->rgb8.ptr, static_cast<size_t>(W) * H * 3,
                                       cudaMemcpyDeviceToHost, ctx->stream));
@@ -1620,8 +1974,16 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   }
   CUDA_TRY(ctx, cudaEventRecord(ev[5], ctx->stream));
   trace.mark("post_enqueue");
+  if (peer)
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->peer_error_host,
+                                  static_cast<uint32_t*>(ctx->sym_flags.local) + kFlagRows * kMaxPeers,
+                                  sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   trace.mark("final_sync");
+  if (peer && *ctx->peer_error_host != 0) {
+    amrvr_layers_free(ctx, layers);
+    return fail(ctx, AMRVR_ERR_RUNTIME, "a peer GPU did not reach the frame barrier within 10 s");
+  }
   if (stats != nullptr) {
     std::memset(stats, 0, sizeof(*stats));
     amrvr_march_stats ms;

@@ -146,6 +146,15 @@ struct FoldLayer {
                        //    base may then point before the slice (only in-range pixels are read)
 };
 
+// Peer-memory exchange (one box, NVLink/NVSwitch): pointers to the same buffer on
+// every rank of the box, mapped into this process (CUDA IPC, or plain peer
+// access when the ranks are threads of one process).
+constexpr int kMaxPeers = 8;
+constexpr int kFlagRows = 4;  // flag block on every rank: [kFlagRows][kMaxPeers] u32 (+ error word)
+struct PeerPtrs {
+  void* p[kMaxPeers];
+};
+
 // A byte range to copy when packing slices for the exchange.
 struct CopyJob {
   uint64_t src_off, dst_off;  // in floats
@@ -176,6 +185,18 @@ int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int64_t* launches);
 int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst,
                 void* stream, int64_t* launches);
+// Cross-GPU barrier on the stream: store `epoch` into slot `me` of every peer's
+// flag row `which`, then wait until all nranks slots of the own row hold >= epoch.
+// Gives up after timeout_ns and raises *error_flag (own device memory) instead of
+// hanging the GPU.
+int launch_peer_barrier(const PeerPtrs& flags, int me, int nranks, int which, uint32_t epoch,
+                        unsigned long long timeout_ns, uint32_t* error_flag, void* stream,
+                        int64_t* launches);
+// Overlay + byte quantisation of one composited piece, written straight into the
+// root's RGB8 frame (a peer pointer when the root is another GPU).
+int launch_post_piece(const float* piece5, int pixel_begin, int pixel_end, int width, int height,
+                      const OverlayEdges* edges /*nullptr: no overlay*/, uint8_t* rgb8_root,
+                      void* stream, int64_t* launches);
 int launch_downsample(const float* src5, int width, int height, int sqrt_aa,
                       float* dst5, void* stream, int64_t* launches);
 int launch_overlay(const OverlayEdges& edges, int sqrt_aa, int width, int height,

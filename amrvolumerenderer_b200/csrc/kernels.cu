@@ -780,6 +780,94 @@ quantize_rgb8_kernel(const float* __restrict__ image5, int width, int height,
   }
 }
 
+// ------------------------------------------------------- peer-memory exchange
+
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__global__ void __launch_bounds__(32)
+peer_barrier_kernel(const __grid_constant__ PeerPtrs flags, int me, int nranks, int which,
+                    unsigned epoch, unsigned long long timeout_ns, unsigned* error_flag) {
+  const int q = threadIdx.x;
+  if (q >= nranks) return;
+  // everything this GPU wrote before (layers, pieces, bytes) is visible system-wide first
+  __threadfence_system();
+  volatile unsigned* theirs = static_cast<unsigned*>(flags.p[q]) + which * kMaxPeers + me;
+  *theirs = epoch;
+  volatile unsigned* mine = static_cast<unsigned*>(flags.p[me]) + which * kMaxPeers + q;
+  const unsigned long long t0 = global_timer_ns();
+  while (static_cast<int>(*mine - epoch) < 0) {
+    __nanosleep(64);
+    if (global_timer_ns() - t0 > timeout_ns) {
+      *error_flag = 1u;
+      break;
+    }
+  }
+  __threadfence_system();
+}
+
+// reference: VolumeRenderer/VolumeRenderer.cpp:228-333 (overlay, same arithmetic as
+// overlay_kernel) then Common/Color.hpp:66-91 + SavePPM row order, per pixel of a
+// piece; the three bytes go to the root's frame.
+__global__ void __launch_bounds__(256)
+post_piece_kernel(const float* __restrict__ piece5, int pixel_begin, int pixel_end, int width,
+                  int height, const OverlayEdges* __restrict__ edges_ptr, float pixel_radius,
+                  unsigned char* __restrict__ rgb8_root) {
+  __shared__ OverlayEdges s_edges;
+  const bool overlay = edges_ptr != nullptr;
+  if (overlay) {
+    const int words = sizeof(OverlayEdges) / 4;
+    for (int i = threadIdx.x; i < words; i += blockDim.x)
+      reinterpret_cast<int*>(&s_edges)[i] = reinterpret_cast<const int*>(edges_ptr)[i];
+    __syncthreads();
+  }
+  const int p = pixel_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= pixel_end) return;
+  const float* b = piece5 + 5 * static_cast<size_t>(p - pixel_begin);
+  float c0 = b[0], c1 = b[1], c2 = b[2];
+  const int px = p % width, py = p / width;
+  if (overlay) {
+    const OverlayEdges& edges = s_edges;
+    for (int e = 0; e < edges.count; ++e) {
+      if (px < edges.x0[e] || px > edges.x1[e] || py < edges.y0[e] || py > edges.y1[e]) continue;
+      float coverage;
+      if (edges.degenerate[e]) {
+        coverage = 1.0f;
+      } else {
+        const float ax = edges.ax[e], ay = edges.ay[e], bx = edges.bx[e], by = edges.by[e];
+        const float ex = bx - ax, ey = by - ay;
+        const float len_sq = ex * ex + ey * ey;
+        const float cx = static_cast<float>(px) + 0.5f, cy = static_cast<float>(py) + 0.5f;
+        const float apx = cx - ax, apy = cy - ay;
+        float t = (apx * ex + apy * ey) / len_sq;
+        t = (t < 0.0f) ? 0.0f : ((1.0f < t) ? 1.0f : t);
+        const float qx = ax + (bx - ax) * t, qy = ay + (by - ay) * t;
+        const float ddx = cx - qx, ddy = cy - qy;
+        const float dist = sqrtf(ddx * ddx + ddy * ddy);
+        coverage = (pixel_radius + 0.5f - dist) * 0.6f;
+        coverage = (coverage < 0.0f) ? 0.0f : ((1.0f < coverage) ? 1.0f : coverage);
+        if (coverage <= 0.0f) continue;
+      }
+      const float a = coverage;
+      const float s = 1.0f * a;
+      c0 = s + c0 * (1.0f - a);
+      c1 = s + c1 * (1.0f - a);
+      c2 = s + c2 * (1.0f - a);
+    }
+  }
+  unsigned char* d = rgb8_root + 3 * (static_cast<size_t>(height - 1 - py) * width + px);
+  const float c[3] = {c0, c1, c2};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int v = static_cast<int>(c[k] * 256.f);
+    d[k] = static_cast<unsigned char>((v < 0) ? 0 : ((v > 255) ? 255 : v));
+  }
+}
+
 // ------------------------------------------------------------------------ K7
 
 __device__ __forceinline__ unsigned ordered_bits(float v) {
@@ -1034,6 +1122,27 @@ int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst
                 int64_t* launches) {
   if (njobs <= 0) return 0;
   pack_slices_kernel<<<njobs, 256, 0, as_stream(stream)>>>(jobs_dev, src, dst);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_peer_barrier(const PeerPtrs& flags, int me, int nranks, int which, uint32_t epoch,
+                        unsigned long long timeout_ns, uint32_t* error_flag, void* stream,
+                        int64_t* launches) {
+  if (nranks > kMaxPeers || which < 0 || which >= kFlagRows) return static_cast<int>(cudaErrorInvalidValue);
+  peer_barrier_kernel<<<1, 32, 0, as_stream(stream)>>>(flags, me, nranks, which, epoch, timeout_ns,
+                                                       error_flag);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_post_piece(const float* piece5, int pixel_begin, int pixel_end, int width, int height,
+                      const OverlayEdges* edges, uint8_t* rgb8_root, void* stream,
+                      int64_t* launches) {
+  const int n = pixel_end - pixel_begin;
+  if (n <= 0) return 0;
+  post_piece_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(
+      piece5, pixel_begin, pixel_end, width, height, edges, 0.5f, rgb8_root);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }

@@ -123,7 +123,8 @@ def main():
         ctx.lib.amrvr_device_free(ctx._h, full)
         print(f"[mp_frame_worker] case={case} P={world} err={err:.3g} lsb={lsb} "
               f"samples={int(samples.item())} order={list(order)} "
-              f"exchanged_rank0={got['stats'].exchanged_bytes} {'OK' if ok else 'FAIL ' + '; '.join(msg)}",
+              f"exchanged_rank0={got['stats'].exchanged_bytes} exchange={os.environ.get('AMRVR_EXCHANGE', 'peer')} "
+              f"{'OK' if ok else 'FAIL ' + '; '.join(msg)}",
               flush=True)
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, src=0)

@@ -30,13 +30,15 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _run(nranks, case):
+def _run(nranks, case, exchange=None):
     if _gpu_count() < nranks:
         pytest.skip(f"needs {nranks} GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nranks}",
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            str(ROOT / "tests" / "mp_frame_worker.py"), case]
     env = dict(os.environ, OMP_NUM_THREADS="1")
+    if exchange is not None:
+        env["AMRVR_EXCHANGE"] = exchange  # "nccl": pack + alltoallv instead of peer-memory loads
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
     tail = (p.stdout + p.stderr)[-3000:]
     assert p.returncode == 0, tail
@@ -46,6 +48,12 @@ def _run(nranks, case):
 @pytest.mark.parametrize("case", ["c4", "c3_aa4", "c2prime", "c1_few_boxes"])
 def test_two_ranks(case):
     _run(2, case)
+
+
+@pytest.mark.parametrize("case", ["c4", "c3_aa4"])
+def test_two_ranks_nccl_exchange(case):
+    """The same frames with the peer-memory path switched off."""
+    _run(2, case, exchange="nccl")
 
 
 @pytest.mark.parametrize("case", ["c4", "c2prime"])
