@@ -75,6 +75,7 @@ struct amrvr_ctx {
   DeviceBuffer tables;       // float[ntables*1024]
   DeviceBuffer counter;      // sample counter + misc small results
   DeviceBuffer fold_layers;  // FoldLayer[]
+  DeviceBuffer fold_bins;    // per-band layer lists of the fold (fold_scratch_bytes)
   DeviceBuffer copy_jobs;    // CopyJob[]
   DeviceBuffer send_buf, recv_buf;
   DeviceBuffer piece;        // composited piece (5 floats / pixel)
@@ -562,7 +563,7 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   if (ctx->peer_error_host != nullptr) cudaFreeHost(ctx->peer_error_host);
   if (ctx->comm != nullptr) nccl_api().CommDestroy(ctx->comm);
   for (DeviceBuffer* b :
-       {&ctx->stage, &ctx->march_boxes, &ctx->tables, &ctx->counter, &ctx->fold_layers,
+       {&ctx->stage, &ctx->march_boxes, &ctx->tables, &ctx->counter, &ctx->fold_layers, &ctx->fold_bins,
         &ctx->copy_jobs, &ctx->send_buf, &ctx->recv_buf, &ctx->piece, &ctx->full, &ctx->small,
         &ctx->rgb8, &ctx->order_boxes, &ctx->order_scratch_a, &ctx->order_scratch_b,
         &ctx->order_priority, &ctx->order_edges, &ctx->stats_partials})
@@ -1403,8 +1404,12 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->fold_layers.ptr, fold.data(), fold.size() * sizeof(FoldLayer),
                                   cudaMemcpyHostToDevice, ctx->stream));
   }
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev[6], ctx->stream));
+  CUDA_TRY(ctx, ctx->fold_bins.reserve(std::max<size_t>(
+                    fold_scratch_bytes(static_cast<int>(fold.size()), W, my_begin, my_end), 256)));
   LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
-                              my_begin, my_end, piece_dst, ctx->stream, &ctx->launches));
+                              my_begin, my_end, piece_dst, ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev[7], ctx->stream));
   if (region_begin) *region_begin = my_begin;
   if (region_end) *region_end = my_end;
   if (piece_out) *piece_out = piece_dst;
@@ -1593,8 +1598,10 @@ extern "C" int amrvr_composite_dense(amrvr_ctx* ctx, int width, int height, int 
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->fold_layers.ptr, fold.data(), fold.size() * sizeof(FoldLayer),
                                   cudaMemcpyHostToDevice, ctx->stream));
   }
+  CUDA_TRY(ctx, ctx->fold_bins.reserve(std::max<size_t>(
+                    fold_scratch_bytes(static_cast<int>(fold.size()), width, begin[me], end[me]), 256)));
   LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), width,
-                              begin[me], end[me], ctx->piece.as<float>(), ctx->stream, &ctx->launches));
+                              begin[me], end[me], ctx->piece.as<float>(), ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
   if (piece5_host != nullptr && mine > 0)
     CUDA_TRY(ctx, cudaMemcpyAsync(piece5_host, ctx->piece.ptr, mine * sizeof(float),
                                   cudaMemcpyDeviceToHost, ctx->stream));
@@ -1653,8 +1660,10 @@ extern "C" int amrvr_composite_virtual(amrvr_ctx* ctx, const amrvr_scene* scene,
     CUDA_TRY(ctx, cudaMemcpyAsync(ctx->fold_layers.ptr, fold.data(), fold.size() * sizeof(FoldLayer),
                                   cudaMemcpyHostToDevice, ctx->stream));
   }
-  LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W, 0,
-                              W * H, full5_device, ctx->stream, &ctx->launches));
+  CUDA_TRY(ctx, ctx->fold_bins.reserve(std::max<size_t>(
+                    fold_scratch_bytes(static_cast<int>(fold.size()), W, 0, W * H), 256)));
+  LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
+                              0, W * H, full5_device, ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   if (piece_owner_host != nullptr)
     for (int r = 0; r < nvirtual; ++r)
@@ -1995,6 +2004,7 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
     cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[3]);
     cudaEventElapsedTime(&stats->gather_ms, ev[3], ev[4]);
     cudaEventElapsedTime(&stats->post_ms, ev[4], ev[5]);
+    cudaEventElapsedTime(&stats->fold_ms, ev[6], ev[7]);
     stats->exchanged_bytes = exchanged;
   }
   amrvr_layers_free(ctx, layers);

@@ -180,9 +180,11 @@ int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev,
                     const uint8_t* bricks, const float* tables, float* layers,
                     unsigned long long* sample_counter, unsigned* tile_counter /*zeroed*/,
                     bool count_samples, void* stream, int64_t* launches);
+// scratch: fold_scratch_bytes() of device memory (per-band layer lists)
+size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end);
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
-                int pixel_begin, int pixel_end, float* piece5, void* stream,
-                int64_t* launches);
+                int pixel_begin, int pixel_end, float* piece5, void* scratch,
+                void* stream, int64_t* launches);
 int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst,
                 void* stream, int64_t* launches);
 // Cross-GPU barrier on the stream: store `epoch` into slot `me` of every peer's

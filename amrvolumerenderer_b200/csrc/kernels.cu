@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <cfloat>
+#include <climits>
 #include <cmath>
 
 #include "internal.hpp"
@@ -572,47 +573,174 @@ __device__ __forceinline__ Px5 blend_depth_swap(const Px5& top, const Px5& botto
 }
 
 constexpr int kFoldThreads = 256;
+constexpr int kFoldTileW = 32;   // one warp = 32 consecutive pixels of one row
+constexpr int kFoldBandRows = 8; // one CTA = 32 x 8 pixels; one band = 8 frame rows
+constexpr int kFoldDepth = 4;    // fragments in flight per thread (HBM and NVLink latency)
 
 struct FoldEntry {  // FoldLayer narrowed for shared memory
   const float* base;
   int x0, w, row0, row1, run, interleaved;
 };
 
-// One CTA = 256 consecutive pixels of this rank's piece.  The CTA filters the
-// globally ordered layer list down to the layers whose footprint touches its
-// pixel span (ordered compaction, 256 layers per round), then every thread
-// folds its pixel over that short list: consecutive layers of one run are
-// blended first, then the run result is blended into the accumulator --
-// DirectSendBase::composeLayered, per pixel (DirectSendBase.cpp:400-446).
+struct FoldBatch {
+  Px5 frag[kFoldDepth];
+  bool hit[kFoldDepth];
+  int runid[kFoldDepth];  // -2: past the end of the list
+};
+
+// Issue the loads of list entries [e0, e0 + kFoldDepth) that cover pixel (px, py).
+__device__ __forceinline__ void fold_fetch(FoldBatch& b, const FoldEntry* s_list, int e0, int total,
+                                           int px, int py) {
+#pragma unroll
+  for (int k = 0; k < kFoldDepth; ++k) {
+    b.hit[k] = false;
+    b.runid[k] = -2;
+    if (e0 + k < total) {
+      const FoldEntry& E = s_list[e0 + k];
+      b.runid[k] = E.run;
+      const int cx = px - E.x0;
+      if (py >= E.row0 && py < E.row1 && cx >= 0 && cx < E.w) {
+        b.hit[k] = true;
+        if (E.interleaved) {  // the reference's own layout: 5 floats per pixel
+          const float* q = E.base + (static_cast<long long>(py - E.row0) * E.w + cx) * 5;
+          b.frag[k] = Px5{__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3), __ldg(q + 4)};
+        } else {
+          const float* rowp = E.base + static_cast<size_t>(py - E.row0) * E.w * 5;
+          const float4 c = __ldg(reinterpret_cast<const float4*>(rowp) + cx);
+          b.frag[k] = Px5{c.x, c.y, c.z, c.w, __ldg(rowp + 4 * E.w + cx)};
+        }
+      }
+    }
+  }
+}
+
+// Blend a fetched batch in list order with the run structure of
+// DirectSendBase::composeLayered (DirectSendBase.cpp:400-446).
+__device__ __forceinline__ void fold_consume(const FoldBatch& b, Px5& acc, Px5& run, bool& have_acc,
+                                             bool& have_run, int& cur_run) {
+#pragma unroll
+  for (int k = 0; k < kFoldDepth; ++k) {
+    if (b.runid[k] != -2) {
+      if (b.runid[k] != cur_run) {
+        if (have_run) {
+          acc = have_acc ? blend_depth_swap(acc, run) : run;
+          have_acc = true;
+          have_run = false;
+        }
+        cur_run = b.runid[k];
+      }
+      if (b.hit[k]) {
+        run = have_run ? blend_depth_swap(run, b.frag[k]) : b.frag[k];
+        have_run = true;
+      }
+    }
+  }
+}
+
+// Pass 1: one CTA per band of 8 frame rows filters the globally ordered layer
+// table down to the layers whose rows touch the band (ordered compaction, so
+// the list keeps the blend order).  band_lists[band * nlayers + i], band_counts[band].
 __global__ void __launch_bounds__(kFoldThreads)
+fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row,
+                int* __restrict__ band_lists, int* __restrict__ band_counts,
+                int2* __restrict__ band_xspan) {
+  __shared__ int s_warp_count[kFoldThreads / 32];
+  __shared__ int s_xmin, s_xmax;
+  if (threadIdx.x == 0) {
+    s_xmin = INT_MAX;
+    s_xmax = INT_MIN;
+  }
+  __syncthreads();
+  int xmin = INT_MAX, xmax = INT_MIN;  // union of the x ranges of the band's layers
+  const int band = blockIdx.x;
+  const int y0 = first_row + band * kFoldBandRows, y1 = y0 + kFoldBandRows;  // [y0, y1)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int* list = band_lists + static_cast<size_t>(band) * nlayers;
+  int written = 0;
+  for (int chunk = 0; chunk < nlayers; chunk += kFoldThreads) {
+    const int l = chunk + threadIdx.x;
+    bool keep = false;
+    if (l < nlayers) {
+      const int row0 = layers[l].row0, row1 = layers[l].row1;
+      keep = row0 < y1 && row1 > y0;
+      if (keep) {
+        xmin = min(xmin, layers[l].x0);
+        xmax = max(xmax, layers[l].x0 + layers[l].w);
+      }
+    }
+    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_warp_count[warp] = __popc(ballot);
+    __syncthreads();
+    int before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kFoldThreads / 32; ++w) {
+      const int c = s_warp_count[w];
+      if (w < warp) before += c;
+      total += c;
+    }
+    if (keep) list[written + before + __popc(ballot & ((1u << lane) - 1u))] = l;
+    written += total;
+    __syncthreads();
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    xmin = min(xmin, __shfl_xor_sync(0xffffffffu, xmin, o));
+    xmax = max(xmax, __shfl_xor_sync(0xffffffffu, xmax, o));
+  }
+  if (lane == 0 && xmin < xmax) {
+    atomicMin(&s_xmin, xmin);
+    atomicMax(&s_xmax, xmax);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    band_counts[band] = written;
+    band_xspan[band] = make_int2(s_xmin, s_xmax);  // empty band: (INT_MAX, INT_MIN)
+  }
+}
+
+// Pass 2: one CTA = a 32 x 8 pixel tile of this rank's piece (pixels outside
+// [pixel_begin, pixel_end) are masked: a piece may start and end inside a row).
+// The CTA narrows its band's list to the layers whose rectangle touches the
+// tile (ordered compaction, 256 candidates per round), then every thread folds
+// its pixel over that short list, kFoldDepth fragments in flight: consecutive
+// layers of one run are blended first, then the run result is blended into the
+// accumulator -- DirectSendBase::composeLayered, per pixel
+// (DirectSendBase.cpp:400-446).  Fragments of other GPUs are read where they
+// were marched (peer memory over NVLink): the fold IS the exchange.
+__global__ void __launch_bounds__(kFoldThreads, 4)
 fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
-                   int width, int pixel_begin, int pixel_end, float* __restrict__ piece5) {
+                   const int* __restrict__ band_lists, const int* __restrict__ band_counts,
+                   const int2* __restrict__ band_xspan,
+                   int first_row, int width, int pixel_begin, int pixel_end,
+                   float* __restrict__ piece5) {
   __shared__ FoldEntry s_list[kFoldThreads];
   __shared__ int s_warp_count[kFoldThreads / 32];
   __shared__ float s_out[kFoldThreads * 5];
 
-  const int first = pixel_begin + blockIdx.x * kFoldThreads;
-  const int last = min(first + kFoldThreads, pixel_end) - 1;  // inclusive
-  const int p = first + threadIdx.x;
-  const bool live = p <= last;
-  const int px = p % width, py = p / width;
-  const int y_first = first / width, y_last = last / width;
-  // x span of the CTA: one row -> exact, else whole rows
-  const int x_first = (y_first == y_last) ? (first % width) : 0;
-  const int x_last = (y_first == y_last) ? (last % width) : (width - 1);
+  const int band = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile_x0 = blockIdx.x * kFoldTileW;
+  const int tile_y0 = first_row + band * kFoldBandRows;
+  const int px = tile_x0 + lane, py = tile_y0 + warp;
+  const long long p_ll = static_cast<long long>(py) * width + px;
+  const bool live = px < width && p_ll >= pixel_begin && p_ll < pixel_end;
+  const int x_last = min(tile_x0 + kFoldTileW, width) - 1;
+  const int y_last = tile_y0 + kFoldBandRows - 1;
 
   Px5 acc{0.f, 0.f, 0.f, 0.f, INFINITY}, run{0.f, 0.f, 0.f, 0.f, INFINITY};
   bool have_acc = false, have_run = false;
   int cur_run = -1;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int* list = band_lists + static_cast<size_t>(band) * nlayers;
+  // no layer of this band reaches the tile's columns: nothing to scan, the tile is empty
+  const int2 xspan = band_xspan[band];
+  const int count = (xspan.x <= x_last && xspan.y > tile_x0) ? band_counts[band] : 0;
 
-  for (int chunk = 0; chunk < nlayers; chunk += kFoldThreads) {
-    const int l = chunk + threadIdx.x;
+  for (int chunk = 0; chunk < count; chunk += kFoldThreads) {
+    const int i = chunk + threadIdx.x;
     bool keep = false;
     FoldLayer L;
-    if (l < nlayers) {
-      L = layers[l];
-      keep = L.row0 <= y_last && L.row1 > y_first && L.x0 <= x_last && L.x0 + L.w > x_first;
+    if (i < count) {
+      L = layers[list[i]];
+      keep = L.row0 <= y_last && L.row1 > tile_y0 && L.x0 <= x_last && L.x0 + L.w > tile_x0;
     }
     const unsigned ballot = __ballot_sync(0xffffffffu, keep);
     if (lane == 0) s_warp_count[warp] = __popc(ballot);
@@ -630,30 +758,11 @@ fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
     }
     __syncthreads();
     if (live) {
-      for (int e = 0; e < total; ++e) {
-        const FoldEntry& E = s_list[e];
-        if (E.run != cur_run) {
-          if (have_run) {
-            acc = have_acc ? blend_depth_swap(acc, run) : run;
-            have_acc = true;
-            have_run = false;
-          }
-          cur_run = E.run;
-        }
-        const int cx = px - E.x0;
-        if (py >= E.row0 && py < E.row1 && cx >= 0 && cx < E.w) {
-          Px5 frag;
-          if (E.interleaved) {  // the reference's own layout: 5 floats per pixel
-            const float* q = E.base + (static_cast<long long>(py - E.row0) * E.w + cx) * 5;
-            frag = Px5{__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3), __ldg(q + 4)};
-          } else {
-            const float* rowp = E.base + static_cast<size_t>(py - E.row0) * E.w * 5;
-            const float4 c = __ldg(reinterpret_cast<const float4*>(rowp) + cx);
-            frag = Px5{c.x, c.y, c.z, c.w, __ldg(rowp + 4 * E.w + cx)};
-          }
-          run = have_run ? blend_depth_swap(run, frag) : frag;
-          have_run = true;
-        }
+      // kFoldDepth fragments in flight: all loads of a batch are issued before its first blend
+      for (int e0 = 0; e0 < total; e0 += kFoldDepth) {
+        FoldBatch A;
+        fold_fetch(A, s_list, e0, total, px, py);
+        fold_consume(A, acc, run, have_acc, have_run, cur_run);
       }
     }
     __syncthreads();
@@ -669,10 +778,19 @@ fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
   o[2] = acc.b;
   o[3] = acc.a;
   o[4] = acc.d;
-  __syncthreads();
-  const int nfloats = (last - first + 1) * 5;
-  float* dst = piece5 + static_cast<size_t>(first - pixel_begin) * 5;
-  for (int i = threadIdx.x; i < nfloats; i += kFoldThreads) dst[i] = s_out[i];
+  __syncwarp();
+  // each warp writes its own row segment: up to 32 pixels x 5 floats, contiguous
+  const int row_first = py * width + tile_x0;  // pixel index of lane 0 (frame < 2^31 pixels)
+  const int seg_lo = max(pixel_begin - row_first, 0);
+  const int seg_hi = min(min(pixel_end - row_first, width - tile_x0), kFoldTileW);
+  const float* src = s_out + warp * 32 * 5;
+  float* dst = piece5 + (static_cast<long long>(row_first) - pixel_begin) * 5;
+#pragma unroll
+  for (int j = 0; j < 5; ++j) {
+    const int f = lane + 32 * j;  // float within the row segment
+    const int pix = f / 5;        // pixel within the segment
+    if (pix >= seg_lo && pix < seg_hi) dst[f] = src[f];
+  }
 }
 
 // ------------------------------------------------------------------------ C6
@@ -1107,13 +1225,32 @@ int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev, const ui
   return static_cast<int>(cudaGetLastError());
 }
 
+size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end) {
+  if (pixel_end <= pixel_begin || width <= 0) return 0;
+  const int first_row = pixel_begin / width, last_row = (pixel_end - 1) / width;
+  const size_t bands = static_cast<size_t>((last_row - first_row) / kFoldBandRows + 1);
+  return bands * (static_cast<size_t>(std::max(nlayers, 1)) + 3) * sizeof(int);
+}
+
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
-                int pixel_begin, int pixel_end, float* piece5, void* stream, int64_t* launches) {
+                int pixel_begin, int pixel_end, float* piece5, void* scratch, void* stream,
+                int64_t* launches) {
   const int npix = pixel_end - pixel_begin;
   if (npix <= 0) return 0;
-  const int blocks = (npix + kFoldThreads - 1) / kFoldThreads;
-  fold_layers_kernel<<<blocks, kFoldThreads, 0, as_stream(stream)>>>(
-      layers_dev, nlayers, width, pixel_begin, pixel_end, piece5);
+  const int first_row = pixel_begin / width, last_row = (pixel_end - 1) / width;
+  const int bands = (last_row - first_row) / kFoldBandRows + 1;
+  int2* band_xspan = static_cast<int2*>(scratch);
+  int* band_counts = reinterpret_cast<int*>(band_xspan + bands);
+  int* band_lists = band_counts + bands;
+  fold_bin_kernel<<<bands, kFoldThreads, 0, as_stream(stream)>>>(layers_dev, nlayers, first_row,
+                                                                 band_lists, band_counts, band_xspan);
+  ++*launches;
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return static_cast<int>(e);
+  const dim3 grid((width + kFoldTileW - 1) / kFoldTileW, bands);
+  fold_layers_kernel<<<grid, kFoldThreads, 0, as_stream(stream)>>>(
+      layers_dev, nlayers, band_lists, band_counts, band_xspan, first_row, width, pixel_begin,
+      pixel_end, piece5);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }

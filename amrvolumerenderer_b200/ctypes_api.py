@@ -125,6 +125,7 @@ class FrameStats(C.Structure):
         ("composite_ms", C.c_float),
         ("gather_ms", C.c_float),
         ("post_ms", C.c_float),
+        ("fold_ms", C.c_float),
         ("samples", C.c_int64),
         ("exchanged_bytes", C.c_int64),
     ]

@@ -195,6 +195,10 @@ def _finish(name, raw_boxes, levels, extent_phys, field_kind, seed, nranks, rule
         if field_kind == "gauss":
             data = _gauss_field(ci[None, None, :], cj[None, :, None], ck[:, None, None],
                                 rng, (nz, ny, nx))
+        elif field_kind == "hash":
+            # C5: one constant per box, h = hash(box id) in [0.5, 1]
+            h = 0.5 + 0.5 * (((gi + 1) * 2654435761) % (1 << 32)) / float(1 << 32)
+            data = np.full((nz, ny, nx), h)
         else:
             raise ValueError(field_kind)
         data = np.ascontiguousarray(data, dtype=np.float64)
@@ -259,6 +263,18 @@ def scene_c4(box_cells=64, nranks=1, seed=1003, rule="chunks"):
     # L2: 4^3 boxes over [.375,.625]^3 -> origin at 0.375 * 4*n0 = 6*box_cells
     raw += _grid(2, (6 * box_cells,) * 3, 4, box_cells)
     return _finish("C4", raw, levels, (1.0, 1.0, 1.0), "gauss", seed, nranks, rule)
+
+
+def scene_c5(n=4, box_cells=2, nranks=1, seed=1005, rule="round_robin"):
+    """C5 (compositor sweep): n^3 bricks tiling the unit cube, n in {4, 8, 16} ->
+    64 / 512 / 4096 layers.  Each brick holds one constant h = hash(box id) in
+    [0.5, 1], so a layer is the brick's projected footprint filled with one
+    colour and its entry depth; the march is a few samples per ray and the frame
+    time is the composite's.  Boxes are dealt round-robin."""
+    cells = n * box_cells
+    levels = [((0.0,) * 3, (1.0 / cells,) * 3)]
+    return _finish(f"C5-{n}", _grid(0, (0, 0, 0), n, box_cells), levels, (1.0, 1.0, 1.0),
+                   "hash", seed, nranks, rule)
 
 
 def scene_c2prime(box_cells=50, nranks=1, seed=1011, rule="chunks"):

@@ -18,6 +18,7 @@ from __future__ import annotations
 
 import argparse
 import ctypes as C
+import functools
 import json
 import os
 import subprocess
@@ -40,7 +41,14 @@ WORKLOADS = {
     "C4": (scenes.scene_c4, 2048, 2048, 1, 0.0),
     "C3": (scenes.scene_c3, 1024, 1024, 4, 0.15),
     "C2": (scenes.scene_c2, 1024, 1024, 1, 0.0),
+    # C5, the compositor-only sweep (BASELINE.json configs[4]): 64 / 512 / 4096 layers at
+    # 4096^2; the bricks are 2^3 cells, so the frame time is the composite's.  Read the
+    # line's "composite" object, not `value`.
+    "C5-4": (functools.partial(scenes.scene_c5, n=4), 4096, 4096, 1, 0.0),
+    "C5-8": (functools.partial(scenes.scene_c5, n=8), 4096, 4096, 1, 0.0),
+    "C5-16": (functools.partial(scenes.scene_c5, n=16), 4096, 4096, 1, 0.0),
 }
+NVLINK_PEAK_GBPS = 900.0  # NVLink 5, per direction per GPU (B200_PROFILING.md); no measured link figure
 
 
 def _peaks():
@@ -49,6 +57,28 @@ def _peaks():
         d = json.loads(p.read_text())
         return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def _ncu_traffic(kernel_tag="march"):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch,
+    from the newest committed `ncu --set full` summary under profiles/ (a capture of
+    the same workload; ncu is never run inside the bench)."""
+    import re
+
+    best = None
+    for f in sorted((ROOT / "profiles").glob(f"r*_{kernel_tag}_v*_full.txt")):
+        best = f
+    if best is None:
+        return None, None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total = 0.0
+    seen = 0
+    for ln in best.read_text().splitlines():
+        m = re.match(r"\s*dram__bytes_(read|write)\.sum\s+([0-9.]+)\s+(\w+)", ln)
+        if m and seen < 2:
+            total += float(m.group(2)) * unit.get(m.group(3), 1.0)
+            seen += 1
+    return (total if seen == 2 else None), best.name
 
 
 class ClockSampler(threading.Thread):
@@ -293,7 +323,8 @@ def main():
         one_frame()
     sampler = ClockSampler(local)
     launches0 = ctx.kernel_launches
-    frame_ms, march_ms, stage = [], [], {"order": [], "composite": [], "gather": [], "post": []}
+    frame_ms, march_ms = [], []
+    stage = {"order": [], "composite": [], "fold": [], "gather": [], "post": []}
     barrier()
     sampler.start()
     for _ in range(args.steps):
@@ -309,17 +340,20 @@ def main():
         march_ms.append(res["stats"].march_ms)
         stage["order"].append(res["stats"].order_ms)
         stage["composite"].append(res["stats"].composite_ms)
+        stage["fold"].append(res["stats"].fold_ms)
         stage["gather"].append(res["stats"].gather_ms)
         stage["post"].append(res["stats"].post_ms)
     clocks = sampler.finish()
     launches = ctx.kernel_launches - launches0
     exchanged = res["stats"].exchanged_bytes
 
-    t = torch.tensor([float(np.mean(frame_ms)), float(np.mean(march_ms))], dtype=torch.float64,
+    t = torch.tensor([float(np.mean(frame_ms)), float(np.mean(march_ms)), float(np.mean(stage["fold"])),
+                      float(np.mean(stage["composite"])), float(exchanged)], dtype=torch.float64,
                      device=f"cuda:{local}")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_per_step, march_mean = float(t[0].item()), float(t[1].item())
+    fold_max_ms, composite_max_ms, pulled_max = float(t[2].item()), float(t[3].item()), float(t[4].item())
 
     # ---- end-to-end arm: pinned host FABs -> upload -> frame -> host RGB8
     e2e_ms = []
@@ -378,7 +412,10 @@ def main():
             "roofline": {
                 "kernel": "raymarch_bricks_kernel", "bound": "hbm",
                 "achieved": alg_bytes / march_s / 1e9, "peak": peak, "unit": "GB/s",
-                "frac": alg_bytes / march_s / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                "frac": alg_bytes / march_s / 1e9 / peak,
+                "traffic": _ncu_traffic()[0] if args.workload == "C4" and world == 1 else None,
+                "traffic_source": f"profiles/{_ncu_traffic()[1]} (ncu --set full, C4, 1 GPU, per launch)",
+                "peak_source": peak_src,
                 "algorithmic_bytes": alg_bytes,
                 "note": "PRIMARY accounting (8 B/cell + 20 B/fragment); the march is issue-bound, "
                         "see compute and sample_fetch",
@@ -390,6 +427,23 @@ def main():
                 "compute": {"samples_per_s_per_sm_clock": out["stats"].samples / march_s / (148 * sm_clock),
                             "note": "samples per SM per clock; 128 FP32 lanes/SM"},
             },
+        }
+        # the composite: in peer-memory mode the fold kernel reads the other GPUs'
+        # fragments over NVLink itself, so link bytes / fold time is the link rate
+        frag_bytes = 20 * frag_pixels
+        line["composite"] = {
+            "fold_ms_max_rank": fold_max_ms, "composite_ms_max_rank": composite_max_ms,
+            "layers": len(scene.boxes), "fragment_bytes_rank0": int(frag_bytes),
+            "link_bytes_max_rank": int(pulled_max),
+            "nvlink_GBps": (pulled_max / (fold_max_ms * 1e-3) / 1e9) if world > 1 and fold_max_ms > 0 else None,
+            "nvlink_peak_GBps": NVLINK_PEAK_GBPS,
+            "nvlink_frac": (pulled_max / (fold_max_ms * 1e-3) / 1e9 / NVLINK_PEAK_GBPS)
+            if world > 1 and fold_max_ms > 0 else None,
+            "fold_hbm_GBps": ((frag_bytes + 20 * W * H * aa) / (fold_max_ms * 1e-3) / 1e9)
+            if world == 1 and fold_max_ms > 0 else None,
+            "note": "fold_hbm_GBps (N=1): 20 B per stored fragment read + 20 B per pixel written; "
+                    "nvlink_GBps (N>1): bytes the busiest rank pulled from peers / its fold time; "
+                    "peak = NVLink 5 nominal per direction (no measured link figure on this pool)",
         }
         if world == 1 and not args.no_cpu_baseline:
             try:

@@ -325,8 +325,11 @@ typedef struct amrvr_frame_params {
 
 typedef struct amrvr_frame_stats {
   float march_ms, order_ms, composite_ms, gather_ms, post_ms;
+  float fold_ms;           /* the fold kernel alone (inside composite_ms); in peer-memory mode
+                              it is also the NVLink transfer: other GPUs' fragments are read
+                              by the fold itself */
   int64_t samples;
-  int64_t exchanged_bytes; /* bytes this rank sent to other ranks */
+  int64_t exchanged_bytes; /* bytes this rank sent to (NCCL) or pulled from (peer memory) other ranks */
 } amrvr_frame_stats;
 
 /* a1-a17 in one call = VolumeRenderer::renderSingleTrial

@@ -32,6 +32,8 @@ CASES = {
     "c3_aa4": (scenes.scene_c3, dict(box_cells=8), 96, 96, 4, 0.15, "round_robin"),
     "c2prime": (scenes.scene_c2prime, dict(box_cells=20), 101, 67, 1, 0.0, "round_robin"),
     "c1_few_boxes": (scenes.scene_c1, dict(), 64, 48, 1, 0.0, "chunks"),
+    # C5 compositor sweep at reduced size: 512 unit bricks, many layers per pixel
+    "c5": (scenes.scene_c5, dict(n=8), 192, 192, 1, 0.0, "round_robin"),
 }
 
 

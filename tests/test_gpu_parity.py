@@ -327,6 +327,70 @@ def test_composite_virtual_ranks(ctx, oracle, nranks, rule):
     ds.free()
 
 
+@pytest.mark.parametrize("n_axis,size", [(4, 512), (8, 256)])
+def test_composite_c5_sweep(ctx, oracle, n_axis, size):
+    """C5 (compositor sweep): n^3 unit bricks dealt round-robin to 8
+    ranks; parity at reduced frame size with the same boxes (the reference's dense
+    layers make 4096^2 infeasible for the oracle)."""
+    nranks = 8
+    scene_p = scenes.scene_c5(n_axis, nranks=nranks)
+    camera = scenes.make_camera()
+    w = h = size
+    recs, n = scene_p.records()
+    ref_d = oracle.reference_sample_distance(recs, n, scene_p.bounds_min, scene_p.bounds_max)
+    single = scenes.Scene(scene_p.name, scene_p.boxes, scene_p.transform, scene_p.scalar_range,
+                          scene_p.bounds_min, scene_p.bounds_max, 1, scene_p.levels)
+    ds = ctx.upload_scene(single)
+    layers = ctx.raymarch(ds, camera, w, h, 0.0, ref_d)
+    owners = scene_p.owners()
+    rank_order, _ = oracle.order(nranks, recs, n, camera, 1.0)
+    got, got_owner = ctx.composite_virtual(ds, layers, camera, nranks, owners, rank_order)
+    dense = [layers.read(b) for b in range(n)]
+    hints = [oracle.depth_hint(recs[i], camera) for i in range(n)]
+    want, want_owner = oracle.compose(nranks, w, h, dense, owners, hints, rank_order)
+    assert np.array_equal(got_owner, want_owner)
+    assert np.array_equal(got[..., :4], want[..., :4])
+    _assert_depth_equal(got[..., 4], want[..., 4])
+    layers.free()
+    ds.free()
+
+
+def test_full_size_c4_layers_of_sampled_boxes(ctx, oracle):
+    """BASELINE's full size (C4: 176 boxes of 64^3, 2048x2048): the layers of one
+    box per AMR level against the oracle's paint at full resolution, the exact
+    sample count of those boxes, and two size-independent properties of the
+    whole frame: rendering twice is bit-identical, and the frame equals the
+    1-virtual-rank composite of the stand-alone march."""
+    scene = scenes.scene_c4()
+    camera = scenes.make_camera()
+    w = h = 2048
+    recs, n = scene.records()
+    ref_d = oracle.reference_sample_distance(recs, n, scene.bounds_min, scene.bounds_max)
+    ds = ctx.upload_scene(scene)
+    layers = ctx.raymarch(ds, camera, w, h, 0.0, ref_d, count_samples=True)
+    cboxes, nb, _ = scene.c_boxes()
+    assert nb == 176
+    for b in (0, 60, 150):  # level 0, 1, 2
+        want, _s = oracle.paint(cboxes[b], scene.transform, *scene.scalar_range, 0.0, ref_d, w, h, camera,
+                                None)
+        got = layers.read(b)
+        assert np.abs(got[..., :4] - want[..., :4]).max() <= RGBA_TOL, f"box {b}"
+        _assert_depth_equal(got[..., 4], want[..., 4])
+    total = layers.stats().samples
+    full, owner = ctx.composite_virtual(ds, layers, camera, 1, np.zeros(n, np.int32), np.zeros(1, np.int32))
+    assert np.all(owner == 0)
+    params = _params(w, h)
+    params.draw_bounding_box = 0
+    a = ctx.render_frame(ds, camera, params)
+    first = a["final5"].copy()
+    assert a["stats"].samples == total
+    b2 = ctx.render_frame(ds, camera, params)
+    assert np.array_equal(first, b2["final5"])          # idempotent
+    assert np.array_equal(first[..., :4], full[..., :4])  # frame == fold of the marched layers
+    layers.free()
+    ds.free()
+
+
 def test_blend_known_answer(ctx, oracle):
     """ImageFullTest.cpp:253-255: over((.5,0,0,.5),(0,0,.5,.5)) = (.5,0,.25,.75)."""
     out = oracle.blend([0.5, 0, 0, 0.5, 1.0], [0, 0, 0.5, 0.5, 2.0])

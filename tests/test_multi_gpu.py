@@ -45,7 +45,7 @@ def _run(nranks, case, exchange=None):
     assert "OK" in p.stdout, tail
 
 
-@pytest.mark.parametrize("case", ["c4", "c3_aa4", "c2prime", "c1_few_boxes"])
+@pytest.mark.parametrize("case", ["c4", "c3_aa4", "c2prime", "c1_few_boxes", "c5"])
 def test_two_ranks(case):
     _run(2, case)
 
@@ -61,6 +61,6 @@ def test_four_ranks(case):
     _run(4, case)
 
 
-@pytest.mark.parametrize("case", ["c4", "c3_aa4", "c1_few_boxes"])
+@pytest.mark.parametrize("case", ["c4", "c3_aa4", "c1_few_boxes", "c5"])
 def test_eight_ranks(case):
     _run(8, case)
