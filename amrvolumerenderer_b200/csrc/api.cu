@@ -83,6 +83,8 @@ struct amrvr_ctx {
   DeviceBuffer order_boxes, order_scratch_a, order_scratch_b, order_priority, order_edges;
   DeviceBuffer stats_partials;
   std::vector<DeviceBuffer> layer_pools;  // recycled layer pools
+  std::vector<DeviceBuffer> brick_pools;  // recycled brick pools (amrvr_scene_free -> next upload)
+  DeviceBuffer gather_counts, gather_table;  // scratch of the box-record allgather
   std::vector<cudaEvent_t> event_pool;    // recycled timing events
   // peer-memory exchange (nranks > 1 on one NVLink box; off -> NCCL alltoallv)
   bool peer_ok = false;
@@ -566,9 +568,11 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
        {&ctx->stage, &ctx->march_boxes, &ctx->tables, &ctx->counter, &ctx->fold_layers, &ctx->fold_bins,
         &ctx->copy_jobs, &ctx->send_buf, &ctx->recv_buf, &ctx->piece, &ctx->full, &ctx->small,
         &ctx->rgb8, &ctx->order_boxes, &ctx->order_scratch_a, &ctx->order_scratch_b,
-        &ctx->order_priority, &ctx->order_edges, &ctx->stats_partials})
+        &ctx->order_priority, &ctx->order_edges, &ctx->stats_partials, &ctx->gather_counts,
+        &ctx->gather_table})
     b->release();
   for (auto& p : ctx->layer_pools) p.release();
+  for (auto& p : ctx->brick_pools) p.release();
   for (auto& e : ctx->ev)
     if (e != nullptr) cudaEventDestroy(e);
   for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
@@ -722,7 +726,16 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
                          std::max(L.dims[2], 0);
     brick_bytes += (cells + 255) & ~static_cast<size_t>(255);
   }
-  CUDA_TRY(ctx, scene->bricks.reserve(std::max<size_t>(brick_bytes, 256)));
+  {
+    const size_t need = std::max<size_t>(brick_bytes, 256);
+    for (size_t i = 0; i < ctx->brick_pools.size(); ++i)
+      if (ctx->brick_pools[i].bytes >= need && ctx->brick_pools[i].bytes <= 2 * need + (1u << 20)) {
+        scene->bricks = ctx->brick_pools[i];
+        ctx->brick_pools.erase(ctx->brick_pools.begin() + static_cast<long>(i));
+        break;
+      }
+    CUDA_TRY(ctx, scene->bricks.reserve(need));
+  }
   std::vector<StagedBox> staged;
   int st = stage_boxes(ctx, nboxes, boxes, staged);
   if (st != AMRVR_OK) {
@@ -759,7 +772,7 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
   } else {
     NcclApi& nc = nccl_api();
     const int P = ctx->nranks;
-    DeviceBuffer tmp;
+    DeviceBuffer& tmp = ctx->gather_counts;
     CUDA_TRY(ctx, tmp.reserve(static_cast<size_t>(P + 1) * sizeof(int)));
     int* counts_dev = tmp.as<int>();
     CUDA_TRY(ctx, cudaMemcpyAsync(counts_dev + P, &nboxes, sizeof(int), cudaMemcpyHostToDevice,
@@ -772,7 +785,7 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     const int most = *std::max_element(counts.begin(), counts.end());
     const size_t slot = static_cast<size_t>(std::max(most, 1)) * sizeof(amrvr_box_record);
-    DeviceBuffer table;
+    DeviceBuffer& table = ctx->gather_table;
     CUDA_TRY(ctx, table.reserve(slot * (P + 1)));
     char* send = table.as<char>() + slot * P;
     if (nboxes > 0)
@@ -788,8 +801,6 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
       const amrvr_box_record* recs = reinterpret_cast<const amrvr_box_record*>(all.data() + slot * r);
       scene->global.insert(scene->global.end(), recs, recs + counts[r]);
     }
-    tmp.release();
-    table.release();
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // host FABs may be reused on return
   *out = scene.release();
@@ -801,6 +812,10 @@ extern "C" int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene) {
   if (ctx != nullptr) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+  }
+  if (ctx != nullptr && scene->bricks.ptr != nullptr && ctx->brick_pools.size() < 2) {
+    ctx->brick_pools.push_back(scene->bricks);  // cudaMalloc/cudaFree cost more than the quantise
+    scene->bricks = DeviceBuffer{};
   }
   scene->bricks.release();
   delete scene;
@@ -1963,7 +1978,9 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
                                         ctx->stream, &ctx->launches));
       image = ctx->small.as<float>();
     }
-    if (params->draw_bounding_box && n > 0) {
+    const bool want_bytes = rgb8_host != nullptr || params->rgb8_on_device;
+    const bool fused_bytes = want_bytes && rgba5_host == nullptr;  // overlay + bytes in one pass
+    if (params->draw_bounding_box && n > 0 && !fused_bytes) {
       OverlayEdges edges;
       make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
       LAUNCH_TRY(ctx, launch_overlay(edges, 1, W, H, image, ctx->stream, &ctx->launches));
@@ -1971,10 +1988,25 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
     if (rgba5_host != nullptr)
       CUDA_TRY(ctx, cudaMemcpyAsync(rgba5_host, image, out_floats * sizeof(float),
                                     cudaMemcpyDeviceToHost, ctx->stream));
-    if (rgb8_host != nullptr || params->rgb8_on_device) {
+    if (want_bytes) {
       CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
-      LAUNCH_TRY(ctx, launch_quantize_rgb8(image, W, H, ctx->rgb8.as<uint8_t>(), ctx->stream,
-                                           &ctx->launches));
+      if (fused_bytes) {
+        // nobody reads the float frame: the overlay is applied on the way to the bytes
+        const OverlayEdges* edges_dev = nullptr;
+        if (params->draw_bounding_box && n > 0) {
+          OverlayEdges edges;
+          make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);
+          CUDA_TRY(ctx, ctx->copy_jobs.reserve(sizeof(OverlayEdges)));
+          CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, &edges, sizeof(edges),
+                                        cudaMemcpyHostToDevice, ctx->stream));
+          edges_dev = ctx->copy_jobs.as<OverlayEdges>();
+        }
+        LAUNCH_TRY(ctx, launch_post_piece(image, 0, W * H, W, H, edges_dev, ctx->rgb8.as<uint8_t>(),
+                                          ctx->stream, &ctx->launches));
+      } else {
+        LAUNCH_TRY(ctx, launch_quantize_rgb8(image, W, H, ctx->rgb8.as<uint8_t>(), ctx->stream,
+                                             &ctx->launches));
+      }
       ctx->last_rgb8 = ctx->rgb8.as<uint8_t>();
       if (rgb8_host != nullptr)
         CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->rgb8.ptr, static_cast<size_t>(W) * H * 3,

@@ -628,19 +628,40 @@ void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
       well_formed = well_formed && (b.lo[d] <= b.hi[d]);
     }
   const float tol = well_formed ? 2e-5f * largest : INFINITY;
+  // structure-of-arrays copy so the reject runs as straight-line SIMD compares
+  // over all j > i; the survivors (a few per box) take the exact test below
+  std::vector<float> soa(static_cast<size_t>(n) * 12);
+  float* lo0 = soa.data();
+  float* lo1 = lo0 + n;
+  float* lo2 = lo1 + n;
+  float* hi0 = lo2 + n;  // hi + tol
+  float* hi1 = hi0 + n;
+  float* hi2 = hi1 + n;
+  for (int i = 0; i < n; ++i) {
+    lo0[i] = boxes[i].lo[0];
+    lo1[i] = boxes[i].lo[1];
+    lo2[i] = boxes[i].lo[2];
+    hi0[i] = boxes[i].hi[0] + tol;
+    hi1[i] = boxes[i].hi[1] + tol;
+    hi2[i] = boxes[i].hi[2] + tol;
+  }
+  std::vector<unsigned char> pass(static_cast<size_t>(n));
   for (int i = 0; i < n; ++i) {
     const OrderBox& a = boxes[i];
+    const float al0 = lo0[i], al1 = lo1[i], al2 = lo2[i], ah0 = hi0[i], ah1 = hi1[i], ah2 = hi2[i];
+    unsigned char* m = pass.data();
+    for (int j = i + 1; j < n; ++j)
+      m[j] = static_cast<unsigned char>(!(lo0[j] > ah0) & !(al0 > hi0[j]) & !(lo1[j] > ah1) &
+                                        !(al1 > hi1[j]) & !(lo2[j] > ah2) & !(al2 > hi2[j]));
     for (int j = i + 1; j < n; ++j) {
+      if (!m[j]) continue;
       const OrderBox& b = boxes[j];
-      if (b.lo[0] > a.hi[0] + tol || a.lo[0] > b.hi[0] + tol || b.lo[1] > a.hi[1] + tol ||
-          a.lo[1] > b.hi[1] + tol || b.lo[2] > a.hi[2] + tol || a.lo[2] > b.hi[2] + tol)
-        continue;
       for (int axis = 0; axis < 3; ++axis) {
         const int u = (axis + 1) % 3, v = (axis + 2) % 3;
-        if (!spans_overlap(a.lo[u], a.hi[u], b.lo[u], b.hi[u])) continue;
-        if (!spans_overlap(a.lo[v], a.hi[v], b.lo[v], b.hi[v])) continue;
         const float along = dir[axis];
-        // a below b on this axis: looking up the axis (along > 0) puts a in front
+        // a below b on this axis: looking up the axis (along > 0) puts a in front.
+        // The (pure) face test runs first: it rejects most surviving pairs, and
+        // an edge needs it anyway.
         int forward = -1;
         if (touching(a.hi[axis], b.lo[axis])) {
           if (along > 1e-6f) forward = 0;        // reference adds edge j -> i
@@ -649,6 +670,9 @@ void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
           if (along > 1e-6f) forward = 1;
           else if (along < -1e-6f) forward = 0;
         }
+        if (forward < 0) continue;
+        if (!spans_overlap(a.lo[u], a.hi[u], b.lo[u], b.hi[u])) continue;
+        if (!spans_overlap(a.lo[v], a.hi[v], b.lo[v], b.hi[v])) continue;
         if (forward >= 0) edges.push_back(OrderEdge{i, j, axis, forward});
       }
     }

@@ -936,6 +936,7 @@ post_piece_kernel(const float* __restrict__ piece5, int pixel_begin, int pixel_e
                   int height, const OverlayEdges* __restrict__ edges_ptr, float pixel_radius,
                   unsigned char* __restrict__ rgb8_root) {
   __shared__ OverlayEdges s_edges;
+  __shared__ __align__(16) unsigned char s_bytes[256 * 3];
   const bool overlay = edges_ptr != nullptr;
   if (overlay) {
     const int words = sizeof(OverlayEdges) / 4;
@@ -943,46 +944,74 @@ post_piece_kernel(const float* __restrict__ piece5, int pixel_begin, int pixel_e
       reinterpret_cast<int*>(&s_edges)[i] = reinterpret_cast<const int*>(edges_ptr)[i];
     __syncthreads();
   }
-  const int p = pixel_begin + blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= pixel_end) return;
-  const float* b = piece5 + 5 * static_cast<size_t>(p - pixel_begin);
-  float c0 = b[0], c1 = b[1], c2 = b[2];
-  const int px = p % width, py = p / width;
-  if (overlay) {
-    const OverlayEdges& edges = s_edges;
-    for (int e = 0; e < edges.count; ++e) {
-      if (px < edges.x0[e] || px > edges.x1[e] || py < edges.y0[e] || py > edges.y1[e]) continue;
-      float coverage;
-      if (edges.degenerate[e]) {
-        coverage = 1.0f;
-      } else {
-        const float ax = edges.ax[e], ay = edges.ay[e], bx = edges.bx[e], by = edges.by[e];
-        const float ex = bx - ax, ey = by - ay;
-        const float len_sq = ex * ex + ey * ey;
-        const float cx = static_cast<float>(px) + 0.5f, cy = static_cast<float>(py) + 0.5f;
-        const float apx = cx - ax, apy = cy - ay;
-        float t = (apx * ex + apy * ey) / len_sq;
-        t = (t < 0.0f) ? 0.0f : ((1.0f < t) ? 1.0f : t);
-        const float qx = ax + (bx - ax) * t, qy = ay + (by - ay) * t;
-        const float ddx = cx - qx, ddy = cy - qy;
-        const float dist = sqrtf(ddx * ddx + ddy * ddy);
-        coverage = (pixel_radius + 0.5f - dist) * 0.6f;
-        coverage = (coverage < 0.0f) ? 0.0f : ((1.0f < coverage) ? 1.0f : coverage);
-        if (coverage <= 0.0f) continue;
+  // the CTA's 256 pixels start at a multiple of 4, so that (width % 4 == 0) every
+  // group of 4 pixels = 12 bytes = 3 aligned words lies in one row of the frame
+  const int p0 = (pixel_begin & ~3) + blockIdx.x * 256;
+  const int p = p0 + threadIdx.x;
+  const bool live = p >= pixel_begin && p < pixel_end;
+  if (live) {
+    const float* b = piece5 + 5 * static_cast<size_t>(p - pixel_begin);
+    float c0 = b[0], c1 = b[1], c2 = b[2];
+    const int px = p % width, py = p / width;
+    if (overlay) {
+      const OverlayEdges& edges = s_edges;
+      for (int e = 0; e < edges.count; ++e) {
+        if (px < edges.x0[e] || px > edges.x1[e] || py < edges.y0[e] || py > edges.y1[e]) continue;
+        float coverage;
+        if (edges.degenerate[e]) {
+          coverage = 1.0f;
+        } else {
+          const float ax = edges.ax[e], ay = edges.ay[e], bx = edges.bx[e], by = edges.by[e];
+          const float ex = bx - ax, ey = by - ay;
+          const float len_sq = ex * ex + ey * ey;
+          const float cx = static_cast<float>(px) + 0.5f, cy = static_cast<float>(py) + 0.5f;
+          const float apx = cx - ax, apy = cy - ay;
+          float t = (apx * ex + apy * ey) / len_sq;
+          t = (t < 0.0f) ? 0.0f : ((1.0f < t) ? 1.0f : t);
+          const float qx = ax + (bx - ax) * t, qy = ay + (by - ay) * t;
+          const float ddx = cx - qx, ddy = cy - qy;
+          const float dist = sqrtf(ddx * ddx + ddy * ddy);
+          coverage = (pixel_radius + 0.5f - dist) * 0.6f;
+          coverage = (coverage < 0.0f) ? 0.0f : ((1.0f < coverage) ? 1.0f : coverage);
+          if (coverage <= 0.0f) continue;
+        }
+        const float a = coverage;
+        const float s = 1.0f * a;
+        c0 = s + c0 * (1.0f - a);
+        c1 = s + c1 * (1.0f - a);
+        c2 = s + c2 * (1.0f - a);
       }
-      const float a = coverage;
-      const float s = 1.0f * a;
-      c0 = s + c0 * (1.0f - a);
-      c1 = s + c1 * (1.0f - a);
-      c2 = s + c2 * (1.0f - a);
+    }
+    const float c[3] = {c0, c1, c2};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int v = static_cast<int>(c[k] * 256.f);
+      s_bytes[threadIdx.x * 3 + k] = static_cast<unsigned char>((v < 0) ? 0 : ((v > 255) ? 255 : v));
     }
   }
-  unsigned char* d = rgb8_root + 3 * (static_cast<size_t>(height - 1 - py) * width + px);
-  const float c[3] = {c0, c1, c2};
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    const int v = static_cast<int>(c[k] * 256.f);
-    d[k] = static_cast<unsigned char>((v < 0) ? 0 : ((v > 255) ? 255 : v));
+  __syncthreads();
+  if ((width & 3) == 0) {
+    // 192 words; word w belongs to the 4-pixel group w / 3 (one row, bottom-up row order)
+    if (threadIdx.x < 192) {
+      const int w = threadIdx.x, g = w / 3;
+      const int pg = p0 + 4 * g;
+      if (pg < pixel_end && pg + 3 >= pixel_begin) {
+        const int px = pg % width, py = pg / width;
+        unsigned char* row = rgb8_root + 3 * (static_cast<size_t>(height - 1 - py) * width + px);
+        if (pg >= pixel_begin && pg + 3 < pixel_end) {
+          reinterpret_cast<unsigned*>(row)[w - 3 * g] = reinterpret_cast<const unsigned*>(s_bytes)[w];
+        } else {  // a piece boundary cuts the group: bytes of the live pixels only
+          for (int k = 0; k < 4; ++k) {
+            const int byte = 4 * (w - 3 * g) + k, q = pg + byte / 3;
+            if (q >= pixel_begin && q < pixel_end) row[byte] = s_bytes[12 * g + byte];
+          }
+        }
+      }
+    }
+  } else if (live) {
+    const int px = p % width, py = p / width;
+    unsigned char* d = rgb8_root + 3 * (static_cast<size_t>(height - 1 - py) * width + px);
+    for (int k = 0; k < 3; ++k) d[k] = s_bytes[threadIdx.x * 3 + k];
   }
 }
 
@@ -1278,7 +1307,8 @@ int launch_post_piece(const float* piece5, int pixel_begin, int pixel_end, int w
                       int64_t* launches) {
   const int n = pixel_end - pixel_begin;
   if (n <= 0) return 0;
-  post_piece_kernel<<<(n + 255) / 256, 256, 0, as_stream(stream)>>>(
+  const int first = pixel_begin & ~3;
+  post_piece_kernel<<<(pixel_end - first + 255) / 256, 256, 0, as_stream(stream)>>>(
       piece5, pixel_begin, pixel_end, width, height, edges, 0.5f, rgb8_root);
   ++*launches;
   return static_cast<int>(cudaGetLastError());

@@ -48,6 +48,7 @@ WORKLOADS = {
     "C5-8": (functools.partial(scenes.scene_c5, n=8), 4096, 4096, 1, 0.0),
     "C5-16": (functools.partial(scenes.scene_c5, n=16), 4096, 4096, 1, 0.0),
 }
+DEAL = "skewed"  # box i -> rank (i + i div P) mod P over the (level, k, j, i) order
 NVLINK_PEAK_GBPS = 900.0  # NVLink 5, per direction per GPU (B200_PROFILING.md); no measured link figure
 
 
@@ -179,7 +180,7 @@ def reference_arm(args, workload):
     factory, W, H, aa, transp = WORKLOADS[workload]
     cores = len(os.sched_getaffinity(0))
     P = max(1, min(8, cores))
-    scene = factory(nranks=P, rule="round_robin")
+    scene = factory(nranks=P, rule=DEAL)
     camera = scenes.make_camera()
     sw, sh = 512, 512  # bounded sample: same boxes and camera, 1/16 of the rays
     params = api.FrameParams(width=sw // int(round(aa ** 0.5)), height=sh // int(round(aa ** 0.5)),
@@ -225,7 +226,7 @@ def cpu_baseline(workload):
     factory, W, H, aa, transp = WORKLOADS[workload]
     cores = len(os.sched_getaffinity(0))
     P = max(1, min(8, cores))
-    scene = factory(nranks=P, rule="round_robin")
+    scene = factory(nranks=P, rule=DEAL)
     sw = sh = 512
     root = int(round(aa ** 0.5))
     params = api.FrameParams(width=sw // root, height=sh // root, box_transparency=transp,
@@ -288,10 +289,10 @@ def main():
         torch.cuda.synchronize()
 
     factory, W, H, aa, transp = WORKLOADS[args.workload]
-    # box -> rank: round-robin over the (level, k, j, i) order, so every rank holds
-    # the same number of boxes of every level (contiguous chunks would give rank 0
-    # all of level 0, i.e. 3/4 of the samples)
-    scene = factory(nranks=world, rule="round_robin")
+    # box -> rank: skewed round-robin over the (level, k, j, i) order, so every rank
+    # holds the same number of boxes of every level and of every grid column
+    # (contiguous chunks would give rank 0 all of level 0, i.e. 3/4 of the samples)
+    scene = factory(nranks=world, rule=DEAL)
     camera = scenes.make_camera()
     lib = api.load_library()
     pinned, fab_bytes = pin_scene(lib, scene, rank, world)
@@ -396,8 +397,8 @@ def main():
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {len(scene.boxes)} boxes, {cells} cells, "
-                                   f"{W}x{H} AA{aa}, visibility graph on, boxes sharded "
-                                   f"round-robin over {world} rank(s)",
+                                   f"{W}x{H} AA{aa}, visibility graph on, boxes dealt "
+                                   f"{DEAL} round-robin to {world} rank(s)",
                        "value_scope": "bricks resident in HBM, RGB8 frame left on the root GPU",
                        "e2e_scope": "pinned host FABs -> upload+quantise -> frame -> RGB8 on the host",
                        "l2": "256 MiB buffer written between timed frames (L2 flush)",

@@ -203,6 +203,25 @@ def test_frame_ragged_width(ctx, oracle):
     _check_frame(ctx, oracle, scenes.scene_c2(box_cells=8), scenes.make_camera(), _params(101, 67))
 
 
+@pytest.mark.parametrize("w,h", [(128, 96), (101, 67)])
+def test_frame_bytes_only_path(ctx, oracle, w, h):
+    """rgb8 without the float frame takes the fused overlay+quantise kernel (word
+    stores when width % 4 == 0, byte stores otherwise): same bytes as the float path
+    and as the oracle."""
+    scene = scenes.scene_c2(box_cells=8)
+    camera = scenes.make_camera()
+    params = _params(w, h)
+    ds = ctx.upload_scene(scene)
+    both = ctx.render_frame(ds, camera, params)
+    want_bytes = both["rgb8"].copy()
+    only = ctx.render_frame(ds, camera, params, want_rgba=False)
+    assert only["final5"] is None
+    assert np.array_equal(only["rgb8"], want_bytes)
+    ref = oracle.render_frame(scene, camera, params)
+    assert int(np.abs(only["rgb8"].astype(int) - ref["rgb8"].astype(int)).max()) <= 1
+    ds.free()
+
+
 def test_frame_empty_scene(ctx):
     t = scenes.identity_transform()
     ds = ctx.upload((api.Box * 1)(), 0, t, (0.0, 1.0))
