@@ -5,6 +5,8 @@
 
 #include <algorithm>
 #include <chrono>
+#include <future>
+#include <limits>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -804,6 +806,231 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // host FABs may be reused on return
   *out = scene.release();
+  return AMRVR_OK;
+}
+
+// ---------------------------------------------------------------------------
+// scene construction (f1) and histogram (f4)
+// ---------------------------------------------------------------------------
+namespace {
+
+// min over ranks of `mins` and sum over ranks of `sums` (two NCCL allreduces on
+// the ctx stream, one readback).  Maxima travel negated.
+int allreduce_min_sum(amrvr_ctx* ctx, double* mins, int nmin, int64_t* sums, int nsum) {
+  if (ctx->nranks == 1) return AMRVR_OK;
+  NcclApi& nc = nccl_api();
+  const size_t bytes = static_cast<size_t>(nmin) * sizeof(double) + static_cast<size_t>(nsum) * sizeof(int64_t);
+  CUDA_TRY(ctx, ctx->gather_counts.reserve(std::max<size_t>(bytes, 256)));
+  double* dmin = ctx->gather_counts.as<double>();
+  int64_t* dsum = reinterpret_cast<int64_t*>(dmin + nmin);
+  CUDA_TRY(ctx, cudaMemcpyAsync(dmin, mins, nmin * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(dsum, sums, nsum * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+  NCCL_TRY(ctx, nc.AllReduce(dmin, dmin, static_cast<size_t>(nmin), ncclDouble, ncclMin, ctx->comm, ctx->stream));
+  NCCL_TRY(ctx, nc.AllReduce(dsum, dsum, static_cast<size_t>(nsum), ncclInt64, ncclSum, ctx->comm, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(mins, dmin, nmin * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(sums, dsum, nsum * sizeof(int64_t), cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return AMRVR_OK;
+}
+
+}  // namespace
+
+extern "C" int amrvr_scene_build(amrvr_ctx* ctx, int nlevels, const amrvr_level* levels,
+                                 int min_level, int max_level, int component, int log_scale_input,
+                                 int normalize_to_data_range, amrvr_box* boxes_out, int capacity,
+                                 amrvr_scene_summary* summary) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, nlevels >= 0 && (nlevels == 0 || levels != nullptr) && summary != nullptr &&
+                   capacity >= 0 && (capacity == 0 || boxes_out != nullptr) && component >= 0,
+          "bad argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  std::memset(summary, 0, sizeof(*summary));
+  const double big = std::numeric_limits<double>::max();
+  const double inf = std::numeric_limits<double>::infinity();
+
+  // SceneBuilder.cpp:134-196: boxes of the requested levels, corners from the level geometry
+  std::vector<amrvr_box> local;
+  double lmin[3] = {big, big, big}, lmax[3] = {-big, -big, -big};
+  for (int level = min_level; level <= max_level; ++level) {
+    if (level < 0 || level >= nlevels) continue;
+    const amrvr_level& L = levels[level];
+    REQUIRE(ctx, L.nfabs >= 0 && (L.nfabs == 0 || L.fabs != nullptr), "bad level");
+    for (int f = 0; f < L.nfabs; ++f) {
+      const amrvr_fab& F = L.fabs[f];
+      const int nx = F.hi[0] - F.lo[0] + 1, ny = F.hi[1] - F.lo[1] + 1, nz = F.hi[2] - F.lo[2] + 1;
+      if (nx <= 0 || ny <= 0 || nz <= 0) continue;
+      amrvr_box B;
+      std::memset(&B, 0, sizeof(B));
+      for (int d = 0; d < 3; ++d) {
+        B.min_corner[d] = L.prob_lo[d] + static_cast<double>(F.lo[d]) * L.cell_size[d];
+        B.max_corner[d] = L.prob_lo[d] + static_cast<double>(F.hi[d] + 1) * L.cell_size[d];
+        B.lo[d] = F.lo[d];
+        B.begin[d] = F.begin[d];
+        lmin[d] = std::min(lmin[d], B.min_corner[d]);
+        lmax[d] = std::max(lmax[d], B.max_corner[d]);
+      }
+      B.dims[0] = nx;
+      B.dims[1] = ny;
+      B.dims[2] = nz;
+      B.data = F.data;
+      B.jstride = F.jstride;
+      B.kstride = F.kstride;
+      B.nstride = F.nstride;
+      B.component = component;
+      local.push_back(B);
+    }
+  }
+  REQUIRE(ctx, static_cast<int>(local.size()) <= capacity, "boxes_out is too small");
+
+  // scalar statistics of the local cells on the GPU (K2; reduceLocalScalarStats :53-94)
+  double smin = inf, smax = -inf, spos = inf;
+  int64_t finite = 0;
+  if (!local.empty()) {
+    const int st = amrvr_brick_stats(ctx, static_cast<int>(local.size()), local.data(), &smin, &smax,
+                                     &spos, &finite);
+    if (st != AMRVR_OK) return st;
+  }
+  const double send_min = (finite > 0) ? smin : inf;   // :312-319
+  const double send_max = (finite > 0) ? smax : -inf;
+  const double send_pos = (spos > 0.0 && std::isfinite(spos)) ? spos : inf;  // :361-366
+
+  // one min-allreduce (maxima negated) + one sum-allreduce replace :210-221,
+  // :281-292, :324-341, :367-385
+  double mins[11] = {lmin[0], lmin[1], lmin[2], -lmax[0], -lmax[1], -lmax[2], send_min, -send_max,
+                     send_pos, 0.0, 0.0};
+  int64_t sums[2] = {finite, (send_pos < inf) ? 1 : 0};
+  {
+    const int st = allreduce_min_sum(ctx, mins, 9, sums, 2);
+    if (st != AMRVR_OK) return st;
+  }
+  double gmin[3] = {mins[0], mins[1], mins[2]}, gmax[3] = {-mins[3], -mins[4], -mins[5]};
+  const double global_scalar_min = mins[6], global_scalar_max = -mins[7], global_pos_min = mins[8];
+  const int64_t global_finite = sums[0], global_pos_count = sums[1];
+
+  // :230-257 global rescale to a unit shortest side
+  double min_extent = big;
+  for (int d = 0; d < 3; ++d) {
+    const double len = std::fabs(gmax[d] - gmin[d]);
+    if (len > 0.0 && std::isfinite(len)) min_extent = std::min(min_extent, len);
+  }
+  double scale = 1.0;
+  if (min_extent > 0.0 && std::isfinite(min_extent)) scale = 1.0 / min_extent;
+  if (!std::isfinite(scale) || !(scale > 0.0)) scale = 1.0;
+  if (scale != 1.0) {
+    for (amrvr_box& B : local)
+      for (int d = 0; d < 3; ++d) {
+        B.min_corner[d] *= scale;
+        B.max_corner[d] *= scale;
+      }
+    // min/max commute with the (monotone, identical) multiplication, so the second
+    // pair of allreduces of the reference (:281-292) gives exactly these values
+    for (int d = 0; d < 3; ++d) {
+      gmin[d] *= scale;
+      gmax[d] *= scale;
+    }
+  }
+  if (gmin[0] > gmax[0] || gmin[1] > gmax[1] || gmin[2] > gmax[2])
+    return fail(ctx, AMRVR_ERR_RUNTIME, "no data");  // options.noDataError
+  const double ext[3] = {gmax[0] - gmin[0], gmax[1] - gmin[1], gmax[2] - gmin[2]};
+  const double max_extent = std::max(ext[0], std::max(ext[1], ext[2]));
+  const double pad = (max_extent > 0.0) ? max_extent * 0.05 : 1.0;
+  for (int d = 0; d < 3; ++d) {
+    summary->bounds_min[d] = gmin[d] - pad;
+    summary->bounds_max[d] = gmax[d] + pad;
+  }
+  summary->global_scale = scale;
+
+  auto make_range = [](double lo, double hi, float* out) {  // makeScalarRange :103-109
+    if (lo == hi) hi = lo + 1.0;
+    out[0] = static_cast<float>(lo);
+    out[1] = static_cast<float>(hi);
+  };
+  if (global_finite > 0 && std::isfinite(global_scalar_min) && std::isfinite(global_scalar_max)) {
+    make_range(global_scalar_min, global_scalar_max, summary->original_range);
+    summary->has_original_range = 1;
+  }
+  double pmin = global_scalar_min, pmax = global_scalar_max;
+  amrvr_scalar_transform& T = summary->transform;
+  T.log_scale_input = log_scale_input ? 1 : 0;
+  T.normalize_to_unit_range = 0;
+  T.positive_floor = 0.0;
+  T.inverse_normalization_span = 1.0;
+  T.inverse_processed_span = 1.0;
+  T.processed_max = 1.0;
+  T.normalization_max = 1.0;
+  if (log_scale_input) {
+    if (global_pos_count <= 0 || !std::isfinite(global_pos_min) || !(global_pos_min > 0.0))
+      return fail(ctx, AMRVR_ERR_RUNTIME,
+                  "Log scaling requested but no positive scalar values were found.");
+    T.positive_floor = global_pos_min;
+    pmin = std::log(global_pos_min);
+    pmax = std::log(std::max(global_scalar_max, global_pos_min));
+  }
+  if (!std::isfinite(pmin) || !std::isfinite(pmax))
+    return fail(ctx, AMRVR_ERR_RUNTIME, "invalid scalar range");  // options.invalidScalarError
+  if (pmin == pmax) pmax = pmin + 1.0;
+  make_range(pmin, pmax, summary->processed_range);
+  T.processed_min = pmin;
+  T.processed_max = pmax;
+  T.inverse_processed_span = 1.0 / (pmax - pmin);
+  T.normalization_min = pmin;
+  T.normalization_max = pmax;
+  T.inverse_normalization_span = T.inverse_processed_span;
+  summary->scalar_range[0] = summary->processed_range[0];
+  summary->scalar_range[1] = summary->processed_range[1];
+  if (normalize_to_data_range) {  // SetSceneNormalizationRange :427-443
+    const double span = pmax - pmin;
+    if (!(span > 0.0) || !std::isfinite(span))
+      return fail(ctx, AMRVR_ERR_RUNTIME,
+                  "Failed to establish a finite scalar range for color mapping.");
+    T.normalize_to_unit_range = 1;
+    T.normalization_min = pmin;
+    T.normalization_max = pmax;
+    T.inverse_normalization_span = 1.0 / span;
+    summary->scalar_range[0] = 0.0f;
+    summary->scalar_range[1] = 1.0f;
+  }
+  for (size_t b = 0; b < local.size(); ++b) boxes_out[b] = local[b];
+  summary->nboxes = static_cast<int32_t>(local.size());
+  return AMRVR_OK;
+}
+
+extern "C" int amrvr_scene_histogram(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                                     const amrvr_scalar_transform* transform, float range_min,
+                                     float range_max, int bin_count, uint64_t* counts_host,
+                                     uint64_t* sample_count) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, bin_count > 0, "binCount must be positive");  // :448-450
+  REQUIRE(ctx, nboxes >= 0 && (nboxes == 0 || boxes != nullptr) && transform != nullptr &&
+                   counts_host != nullptr,
+          "bad argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  for (int b = 0; b < bin_count; ++b) counts_host[b] = 0;
+  if (sample_count) *sample_count = 0;
+  const float width = range_max - range_min;
+  if (!(width > 0.0f) || !std::isfinite(width)) return AMRVR_OK;  // :469-471
+  std::vector<StagedBox> staged;
+  const int st = stage_boxes(ctx, nboxes, boxes, staged);
+  if (st != AMRVR_OK) return st;
+  const size_t bytes = static_cast<size_t>(bin_count) * sizeof(unsigned long long);
+  CUDA_TRY(ctx, ctx->counter.reserve(std::max<size_t>(bytes, 256)));
+  unsigned long long* counts = ctx->counter.as<unsigned long long>();
+  CUDA_TRY(ctx, cudaMemsetAsync(counts, 0, bytes, ctx->stream));
+  for (int b = 0; b < nboxes; ++b) {
+    if (staged[b].dev == nullptr) continue;
+    LAUNCH_TRY(ctx, launch_brick_histogram(staged[b].dev, staged[b].jstride, staged[b].kstride,
+                                           boxes[b].dims[0], boxes[b].dims[1], boxes[b].dims[2],
+                                           *transform, range_min, range_max, bin_count, counts,
+                                           ctx->stream, &ctx->launches));
+  }
+  if (ctx->nranks > 1)  // the two MPI_Allreduce of :557-570 (the total is the sum of the bins)
+    NCCL_TRY(ctx, nccl_api().AllReduce(counts, counts, static_cast<size_t>(bin_count), ncclUint64,
+                                       ncclSum, ctx->comm, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(counts_host, counts, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  uint64_t total = 0;
+  for (int b = 0; b < bin_count; ++b) total += counts_host[b];
+  if (sample_count) *sample_count = total;
   return AMRVR_OK;
 }
 
@@ -1871,23 +2098,49 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
     if (st != AMRVR_OK) return st;
     if (!ok_a || !ok_b) return fail(ctx, AMRVR_ERR_CUDA, "peer-mapped frame buffers could not be grown");
   }
-  st = raymarch_impl(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
-                     params->count_samples, peer, &layers);
-  if (st != AMRVR_OK) return st;
-  CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
-  trace.mark("march_enqueue");
-
+  // The visibility ordering of a few hundred boxes is pure host work on the global
+  // table (no ctx state): it runs on a helper thread while this thread sets up and
+  // enqueues the march, so the composite is enqueued as soon as both are done.
   std::vector<int> rank_order(static_cast<size_t>(ctx->nranks));
   int graph_failed = 0;
   const auto order_t0 = std::chrono::steady_clock::now();
-  st = amrvr_order_boxes(ctx, scene, camera, aspect, params->use_visibility_graph,
-                         rank_order.data(), &graph_failed);
+  const bool order_on_thread = ctx->nranks > 1 && n < ctx->order_device_min;
+  std::future<float> order_job;
+  if (order_on_thread) {
+    const int P = ctx->nranks;
+    const bool use_graph = params->use_visibility_graph != 0;
+    int* out = rank_order.data();
+    int* failed = &graph_failed;
+    const amrvr_box_record* recs = scene->global.data();
+    const amrvr_camera cam_copy = *camera;
+    order_job = std::async(std::launch::async, [=]() {
+      const bool ok = order_ranks(P, n, recs, cam_copy, aspect, use_graph, *host_order_backend(), out);
+      *failed = ok ? 0 : 1;
+      return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
+    });
+  }
+  st = raymarch_impl(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
+                     params->count_samples, peer, &layers);
   if (st != AMRVR_OK) {
-    amrvr_layers_free(ctx, layers);
+    if (order_on_thread) order_job.wait();
     return st;
   }
-  const float order_host_ms =
-      std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
+  CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
+  trace.mark("march_enqueue");
+
+  float order_host_ms = 0.0f;
+  if (order_on_thread) {
+    order_host_ms = order_job.get();
+  } else {
+    st = amrvr_order_boxes(ctx, scene, camera, aspect, params->use_visibility_graph,
+                           rank_order.data(), &graph_failed);
+    if (st != AMRVR_OK) {
+      amrvr_layers_free(ctx, layers);
+      return st;
+    }
+    order_host_ms =
+        std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
+  }
   CUDA_TRY(ctx, cudaEventRecord(ev[2], ctx->stream));
   trace.mark("order");
 

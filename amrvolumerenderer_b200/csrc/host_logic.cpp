@@ -646,6 +646,7 @@ void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
     hi2[i] = boxes[i].hi[2] + tol;
   }
   std::vector<unsigned char> pass(static_cast<size_t>(n));
+  std::vector<int> cand(static_cast<size_t>(n) + 1);
   for (int i = 0; i < n; ++i) {
     const OrderBox& a = boxes[i];
     const float al0 = lo0[i], al1 = lo1[i], al2 = lo2[i], ah0 = hi0[i], ah1 = hi1[i], ah2 = hi2[i];
@@ -653,8 +654,14 @@ void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
     for (int j = i + 1; j < n; ++j)
       m[j] = static_cast<unsigned char>(!(lo0[j] > ah0) & !(al0 > hi0[j]) & !(lo1[j] > ah1) &
                                         !(al1 > hi1[j]) & !(lo2[j] > ah2) & !(al2 > hi2[j]));
+    // branch-free compaction of the survivors, then the exact test on those only
+    int ncand = 0;
     for (int j = i + 1; j < n; ++j) {
-      if (!m[j]) continue;
+      cand[ncand] = j;
+      ncand += m[j];
+    }
+    for (int c = 0; c < ncand; ++c) {
+      const int j = cand[c];
       const OrderBox& b = boxes[j];
       for (int axis = 0; axis < 3; ++axis) {
         const int u = (axis + 1) % 3, v = (axis + 2) % 3;

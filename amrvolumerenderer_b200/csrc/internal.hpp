@@ -171,6 +171,10 @@ int launch_brick_stats(const double* data, int64_t jstride, int64_t kstride,
                        int blocks, void* stream, int64_t* launches);
 int launch_brick_stats_final(const double* partials, int nparts, double* out4,
                              void* stream, int64_t* launches);
+int launch_brick_histogram(const double* data, int64_t jstride, int64_t kstride,
+                           int nx, int ny, int nz, const amrvr_scalar_transform& t,
+                           float range_min, float range_max, int bin_count,
+                           unsigned long long* counts_dev, void* stream, int64_t* launches);
 int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride,
                           int nx, int ny, int nz,
                           const amrvr_scalar_transform& t, float range_min,

@@ -195,6 +195,64 @@ brick_stats_final_kernel(const double* __restrict__ partials, int nparts, double
   }
 }
 
+// f4.  reference: VolumeRenderer/SceneBuilder.cpp:445-577 (per-cell body :503-539).
+// Per-CTA histogram in shared memory (bins <= kHistSmemBins), flushed with one
+// 64-bit atomic per non-empty bin; larger bin counts go straight to global atomics.
+constexpr int kHistSmemBins = 8192;
+
+__device__ __forceinline__ int histogram_bin(double raw, const ValuePath& p, float range_min,
+                                             float range_max, float inverse_width, int bin_count) {
+  double v = isfinite(raw) ? raw : 0.0;  // applyScalarTransform, VolumeTypes.hpp:33-67
+  if (p.log_scale) {
+    if (!(v > 0.0) || v < p.positive_floor) v = p.positive_floor;
+    v = log(v);
+  }
+  if (p.normalize) {
+    v = (v - p.norm_min) * p.inv_norm_span;
+    v = (v < 0.0) ? 0.0 : ((v > 1.0) ? 1.0 : v);
+  }
+  float value = static_cast<float>(v);
+  if (value < range_min) value = range_min;
+  else if (value > range_max) value = range_max;
+  float normalized = (value - range_min) * inverse_width;
+  if (normalized < 0.0f) normalized = 0.0f;
+  else if (normalized > 1.0f) normalized = 1.0f;
+  int index = static_cast<int>(normalized * static_cast<float>(bin_count));
+  if (index >= bin_count) index = bin_count - 1;
+  else if (index < 0) index = 0;
+  return index;
+}
+
+__global__ void __launch_bounds__(256)
+brick_histogram_kernel(const double* __restrict__ data, long long jstride, long long kstride, int nx,
+                       int ny, int nz, const __grid_constant__ ValuePath p, float range_min,
+                       float range_max, float inverse_width, int bin_count,
+                       unsigned long long* __restrict__ counts) {
+  extern __shared__ unsigned s_bins[];
+  const bool in_smem = bin_count <= kHistSmemBins;
+  if (in_smem) {
+    for (int b = threadIdx.x; b < bin_count; b += blockDim.x) s_bins[b] = 0u;
+    __syncthreads();
+  }
+  const long long ncells = static_cast<long long>(nx) * ny * nz;
+  for (long long c = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; c < ncells;
+       c += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int i = static_cast<int>(c % nx);
+    const long long row = c / nx;
+    const int j = static_cast<int>(row % ny);
+    const int k = static_cast<int>(row / ny);
+    const double v = __ldcs(data + i + j * jstride + k * kstride);
+    const int bin = histogram_bin(v, p, range_min, range_max, inverse_width, bin_count);
+    if (in_smem) atomicAdd(&s_bins[bin], 1u);  // < 2^32 cells per CTA by the grid-stride bound
+    else atomicAdd(&counts[bin], 1ULL);
+  }
+  if (in_smem) {
+    __syncthreads();
+    for (int b = threadIdx.x; b < bin_count; b += blockDim.x)
+      if (s_bins[b] != 0u) atomicAdd(&counts[b], static_cast<unsigned long long>(s_bins[b]));
+  }
+}
+
 // ------------------------------------------------------------------------ K1
 
 // One CTA = one 16x16 pixel tile of one box's screen footprint; one thread = one
@@ -1194,6 +1252,27 @@ int launch_brick_stats(const double* data, int64_t jstride, int64_t kstride, int
                        int nz, double* partials, int blocks, void* stream, int64_t* launches) {
   brick_stats_kernel<<<blocks, 256, 0, as_stream(stream)>>>(data, jstride, kstride, nx, ny, nz,
                                                             partials);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_brick_histogram(const double* data, int64_t jstride, int64_t kstride, int nx, int ny,
+                           int nz, const amrvr_scalar_transform& t, float range_min,
+                           float range_max, int bin_count, unsigned long long* counts_dev,
+                           void* stream, int64_t* launches) {
+  const long long ncells = static_cast<long long>(nx) * ny * nz;
+  if (ncells <= 0) return 0;
+  ValuePath p{};
+  p.log_scale = t.log_scale_input;
+  p.normalize = t.normalize_to_unit_range;
+  p.positive_floor = t.positive_floor;
+  p.norm_min = t.normalization_min;
+  p.inv_norm_span = t.inverse_normalization_span;
+  const float width = range_max - range_min;
+  const int blocks = static_cast<int>(std::min<long long>(148 * 8, (ncells + 255) / 256));
+  const size_t smem = bin_count <= kHistSmemBins ? static_cast<size_t>(bin_count) * sizeof(unsigned) : 0;
+  brick_histogram_kernel<<<blocks, 256, smem, as_stream(stream)>>>(
+      data, jstride, kstride, nx, ny, nz, p, range_min, range_max, 1.0f / width, bin_count, counts_dev);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }

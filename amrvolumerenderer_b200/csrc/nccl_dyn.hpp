@@ -20,6 +20,8 @@ struct NcclApi {
   ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t) = nullptr;
   ncclResult_t (*GroupStart)() = nullptr;
   ncclResult_t (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
@@ -43,6 +45,7 @@ struct NcclApi {
     const bool ok = bind(GetUniqueId, "ncclGetUniqueId") && bind(CommInitRank, "ncclCommInitRank") &&
                     bind(CommDestroy, "ncclCommDestroy") && bind(Send, "ncclSend") &&
                     bind(Recv, "ncclRecv") && bind(AllGather, "ncclAllGather") &&
+                    bind(AllReduce, "ncclAllReduce") &&
                     bind(GroupStart, "ncclGroupStart") && bind(GroupEnd, "ncclGroupEnd") &&
                     bind(GetErrorString, "ncclGetErrorString");
     if (!ok) {

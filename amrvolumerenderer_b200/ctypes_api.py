@@ -131,6 +131,49 @@ class FrameStats(C.Structure):
     ]
 
 
+class Fab(C.Structure):
+    """amrvr_fab: one FAB as MFIter hands it out (valid box + Array4 view)."""
+
+    _fields_ = [
+        ("lo", C.c_int32 * 3),
+        ("hi", C.c_int32 * 3),
+        ("data", C.c_void_p),
+        ("jstride", C.c_int64),
+        ("kstride", C.c_int64),
+        ("nstride", C.c_int64),
+        ("begin", C.c_int32 * 3),
+        ("reserved", C.c_int32),
+    ]
+
+
+class Level(C.Structure):
+    """amrvr_level: one AMR level of api::AmrData (this rank's FABs + geometry)."""
+
+    _fields_ = [
+        ("prob_lo", C.c_double * 3),
+        ("cell_size", C.c_double * 3),
+        ("nfabs", C.c_int32),
+        ("reserved", C.c_int32),
+        ("fabs", C.POINTER(Fab)),
+    ]
+
+
+class SceneSummary(C.Structure):
+    """amrvr_scene_summary: SceneGeometry minus the boxes (VolumeRenderer.hpp:46-62)."""
+
+    _fields_ = [
+        ("transform", ScalarTransform),
+        ("scalar_range", C.c_float * 2),
+        ("processed_range", C.c_float * 2),
+        ("original_range", C.c_float * 2),
+        ("has_original_range", C.c_int32),
+        ("nboxes", C.c_int32),
+        ("bounds_min", C.c_double * 3),
+        ("bounds_max", C.c_double * 3),
+        ("global_scale", C.c_double),
+    ]
+
+
 class LibraryMissingError(RuntimeError):
     """libamrvr_b200.so has not been built (run __graft_entry__.build())."""
 
@@ -173,6 +216,10 @@ def _declare(lib):
                                         _P(C.c_double), _P(i64)]),
         "amrvr_scene_upload": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),
         "amrvr_scene_free": (C.c_int, [vp, vp]),
+        "amrvr_scene_build": (C.c_int, [vp, i32, _P(Level), i32, i32, i32, i32, i32, _P(Box), i32,
+                                        _P(SceneSummary)]),
+        "amrvr_scene_histogram": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, i32,
+                                            _P(C.c_uint64), _P(C.c_uint64)]),
         "amrvr_scene_global_boxes": (C.c_int, [vp, _P(i32), _P(_P(BoxRecord))]),
         "amrvr_scene_read_brick": (C.c_int, [vp, vp, i32, vp]),
         "amrvr_order_boxes": (C.c_int, [vp, vp, _P(Camera), f32, i32, _P(i32), _P(i32)]),

@@ -89,6 +89,31 @@ class Context:
                                               C.byref(lp), C.byref(cnt)))
         return lo.value, hi.value, lp.value, cnt.value
 
+    def scene_build(self, levels, nlevels, min_level=0, max_level=None, component=0,
+                    log_scale=False, normalize_to_data_range=True, capacity=None):
+        """amrvr_scene_build (= detail::BuildSceneGeometry) -> (Box array, SceneSummary)."""
+        if max_level is None:
+            max_level = nlevels - 1
+        if capacity is None:
+            capacity = sum(int(levels[i].nfabs) for i in range(nlevels))
+        boxes = (api.Box * max(capacity, 1))()
+        summary = api.SceneSummary()
+        self.check(self.lib.amrvr_scene_build(self._h, nlevels, levels, int(min_level), int(max_level),
+                                              int(component), int(bool(log_scale)),
+                                              int(bool(normalize_to_data_range)), boxes, int(capacity),
+                                              C.byref(summary)))
+        return boxes, summary
+
+    def scene_histogram(self, cboxes, n, transform, scalar_range, bin_count):
+        """amrvr_scene_histogram (= detail::ComputeSceneHistogram) -> (counts, total)."""
+        counts = np.zeros(max(int(bin_count), 1), np.uint64)
+        total = C.c_uint64(0)
+        self.check(self.lib.amrvr_scene_histogram(self._h, n, cboxes, C.byref(transform),
+                                                  float(scalar_range[0]), float(scalar_range[1]),
+                                                  int(bin_count), counts.ctypes.data_as(_P(C.c_uint64)),
+                                                  C.byref(total)))
+        return counts, int(total.value)
+
     def upload(self, cboxes, n, transform, scalar_range) -> "DeviceScene":
         h = C.c_void_p()
         self.check(self.lib.amrvr_scene_upload(self._h, n, cboxes, C.byref(transform),

@@ -124,6 +124,51 @@ class Scene:
                      self.bounds_max, nranks, self.levels)
 
 
+def c_levels(scene: "Scene", only_rank: int | None = None, ghost: int = 0, ncomp: int = 1,
+             component: int = 0):
+    """The scene as api::AmrData would hand it over: one amrvr_level per AMR level
+    with the FABs of `only_rank` (or of all ranks) in generation order.  ghost > 0
+    pads every FAB with that many ghost cells (filled with 1e30, never part of
+    the valid box) so the Array4 strides differ from the valid extents; ncomp > 1
+    stores the field in `component` and junk in the others.
+    Returns (Level array, nlevels, keepalive)."""
+    nlevels = len(scene.levels)
+    per = [[] for _ in range(nlevels)]
+    for b in sorted(scene.boxes, key=lambda b: b.gen_index):
+        if only_rank is None or b.owner == only_rank:
+            per[b.level].append(b)
+    levels = (api.Level * max(nlevels, 1))()
+    keep = []
+    for li in range(nlevels):
+        prob_lo, cs = scene.levels[li]
+        fabs = (api.Fab * max(len(per[li]), 1))()
+        for fi, b in enumerate(per[li]):
+            nx, ny, nz = b.dims
+            gx, gy, gz = nx + 2 * ghost, ny + 2 * ghost, nz + 2 * ghost
+            if ghost == 0 and ncomp == 1:
+                arr = b.data
+            else:
+                arr = np.full((ncomp, gz, gy, gx), 1e30, dtype=np.float64)
+                arr[component, ghost:ghost + nz, ghost:ghost + ny, ghost:ghost + nx] = b.data
+            keep.append(arr)
+            f = fabs[fi]
+            for d in range(3):
+                f.lo[d] = int(b.lo[d])
+                f.hi[d] = int(b.lo[d] + b.dims[d] - 1)
+                f.begin[d] = int(b.lo[d]) - ghost
+            f.data = arr.ctypes.data
+            f.jstride = gx
+            f.kstride = gx * gy
+            f.nstride = gx * gy * gz
+        keep.append(fabs)
+        for d in range(3):
+            levels[li].prob_lo[d] = float(prob_lo[d])
+            levels[li].cell_size[d] = float(cs[d])
+        levels[li].nfabs = len(per[li])
+        levels[li].fabs = fabs
+    return levels, nlevels, keep
+
+
 def make_camera(eye=DEFAULT_EYE, look_at=DEFAULT_LOOK_AT, up=DEFAULT_UP, fov_y=45.0,
                 near=0.1, far=10.0) -> api.Camera:
     cam = api.Camera()

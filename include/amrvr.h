@@ -166,6 +166,70 @@ int amrvr_scene_global_boxes(const amrvr_scene* scene, int* nglobal,
 int amrvr_scene_read_brick(amrvr_ctx* ctx, const amrvr_scene* scene,
                            int local_box, uint8_t* dst);
 
+/* ------------------------------------------------------ scene construction */
+
+/* One FAB of a MultiFab as MFIter hands it out (VolumeRenderer/SceneBuilder.cpp:
+ * 148-187): valid box + the amrex::Array4<Real const> view.  `data` may be a
+ * host or a device pointer (same addressing rule as amrvr_box). */
+typedef struct amrvr_fab {
+  int32_t lo[3];    /* validbox().smallEnd() */
+  int32_t hi[3];    /* validbox().bigEnd()   */
+  const double* data;
+  int64_t jstride, kstride, nstride;
+  int32_t begin[3]; /* Array4::begin (valid box grown by the ghost cells) */
+  int32_t reserved;
+} amrvr_fab;
+
+/* One AMR level of api::AmrData (VolumeRenderer/VolumeRendererApi.hpp:22-26):
+ * this rank's FABs in MFIter order + LevelGridGeometry (SceneBuilder.hpp). */
+typedef struct amrvr_level {
+  double prob_lo[3];
+  double cell_size[3];
+  int32_t nfabs;
+  int32_t reserved;
+  const amrvr_fab* fabs;
+} amrvr_level;
+
+/* What BuildSceneGeometry leaves in VolumeRenderer::SceneGeometry besides the
+ * boxes (VolumeRenderer/VolumeRenderer.hpp:46-62). */
+typedef struct amrvr_scene_summary {
+  amrvr_scalar_transform transform;
+  float scalar_range[2];
+  float processed_range[2];
+  float original_range[2];
+  int32_t has_original_range;
+  int32_t nboxes;          /* boxes written to boxes_out */
+  double bounds_min[3];    /* explicitBounds (padded by 5 % of the longest side) */
+  double bounds_max[3];
+  double global_scale;     /* 1 / shortest side of the global extent */
+} amrvr_scene_summary;
+
+/* f1.  Replaces detail::BuildSceneGeometry (VolumeRenderer/SceneBuilder.cpp:
+ * 113-425) for already-convex levels: box corners from the level geometry,
+ * global rescale to a unit shortest side, scalar statistics on the GPU (K2),
+ * the ScalarTransform and the three scalar ranges.  Levels outside
+ * [min_level, max_level] are skipped as in the reference.  Collective when
+ * nranks > 1 (one min- and one sum-allreduce instead of the reference's eleven
+ * MPI_Allreduce calls).  boxes_out (capacity entries) receives this rank's
+ * boxes in (level, MFIter) order, ready for amrvr_scene_upload.
+ * Errors: AMRVR_ERR_RUNTIME with the reference's messages ("no data", "invalid
+ * scalar range", "Log scaling requested but no positive scalar values were
+ * found."); AMRVR_ERR_INVALID when capacity is too small. */
+int amrvr_scene_build(amrvr_ctx* ctx, int nlevels, const amrvr_level* levels,
+                      int min_level, int max_level, int component,
+                      int log_scale_input, int normalize_to_data_range,
+                      amrvr_box* boxes_out, int capacity,
+                      amrvr_scene_summary* summary);
+
+/* f4.  Replaces detail::ComputeSceneHistogram (SceneBuilder.cpp:445-577):
+ * bin_count bins over [range_min, range_max] of the transformed scalar of
+ * every cell of the given boxes, summed over all ranks (collective when
+ * nranks > 1).  counts_host[bin_count]; *sample_count = total cells. */
+int amrvr_scene_histogram(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                          const amrvr_scalar_transform* transform,
+                          float range_min, float range_max, int bin_count,
+                          uint64_t* counts_host, uint64_t* sample_count);
+
 /* ---------------------------------------------------------------- ordering */
 
 /* a10.  Replaces BuildVisibilityOrderedGroup (Common/VisibilityOrdering.hpp:

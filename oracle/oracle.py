@@ -165,6 +165,29 @@ class Oracle(_Base):
                                  _d3(up) if up is not None else None, C.byref(cam))
         return cam
 
+    def scene_build(self, levels, nlevels, min_level=0, max_level=None, component=0,
+                    log_scale=False, normalize_to_data_range=True):
+        """orc_scene_build over levels holding the FABs of all ranks ->
+        (Box array, SceneSummary, status)."""
+        if max_level is None:
+            max_level = nlevels - 1
+        cap = max(sum(int(levels[i].nfabs) for i in range(nlevels)), 1)
+        boxes = (api.Box * cap)()
+        summary = api.SceneSummary()
+        self.lib.orc_scene_build.restype = C.c_int
+        st = self.lib.orc_scene_build(nlevels, levels, int(min_level), int(max_level), int(component),
+                                      int(bool(log_scale)), int(bool(normalize_to_data_range)), boxes,
+                                      cap, C.byref(summary))
+        return boxes, summary, st
+
+    def scene_histogram(self, cboxes, n, transform, scalar_range, bin_count):
+        counts = np.zeros(max(int(bin_count), 1), np.uint64)
+        total = C.c_uint64(0)
+        self.lib.orc_scene_histogram(n, cboxes, C.byref(transform), C.c_float(scalar_range[0]),
+                                     C.c_float(scalar_range[1]), int(bin_count),
+                                     counts.ctypes.data_as(_P(C.c_uint64)), C.byref(total))
+        return counts, int(total.value)
+
     def render_frame(self, scene, camera, params, colormap=None):
         """scene: amrvolumerenderer_b200.scenes.Scene.  Returns dict."""
         cboxes, n, _keep = scene.c_boxes()
@@ -272,6 +295,74 @@ class Ref(_Base):
             str(out_path).encode(), int(pin_cores), C.byref(samples), C.byref(wall), log,
             len(log)))
         return {"samples": samples.value, "wall_s": wall.value, "log": log.value.decode()}
+
+    def build_scene(self, scene, min_level=0, max_level=None, component=0, log_scale=False,
+                    normalize_to_data_range=True, ncomp=1):
+        """The real detail::BuildSceneGeometry on scene.nranks thread-ranks from the
+        scene's levels -> dict (boxes, owners, transform, ranges, bounds, handle)."""
+        nlevels = len(scene.levels)
+        if max_level is None:
+            max_level = nlevels - 1
+        per = [[] for _ in range(nlevels)]
+        for b in sorted(scene.boxes, key=lambda b: b.gen_index):
+            per[b.level].append(b)
+        levels = (RefLevel * max(nlevels, 1))()
+        keep = []
+        for li in range(nlevels):
+            n = len(per[li])
+            lo = (C.c_int32 * max(3 * n, 1))()
+            hi = (C.c_int32 * max(3 * n, 1))()
+            owner = (C.c_int32 * max(n, 1))()
+            data = (C.c_void_p * max(n, 1))()
+            for i, b in enumerate(per[li]):
+                for d in range(3):
+                    lo[3 * i + d] = int(b.lo[d])
+                    hi[3 * i + d] = int(b.lo[d] + b.dims[d] - 1)
+                owner[i] = int(b.owner)
+                if ncomp == 1:
+                    arr = b.data
+                else:
+                    arr = np.full((ncomp,) + b.data.shape, 1e30, np.float64)
+                    arr[component] = b.data
+                keep.append(arr)
+                data[i] = arr.ctypes.data
+            prob_lo, cs = scene.levels[li]
+            for d in range(3):
+                levels[li].prob_lo[d] = float(prob_lo[d])
+                levels[li].cell_size[d] = float(cs[d])
+            levels[li].nboxes, levels[li].ncomp = n, ncomp
+            levels[li].lo, levels[li].hi, levels[li].owner = lo, hi, owner
+            levels[li].data = data
+            keep += [lo, hi, owner, data]
+        handle = C.c_void_p()
+        self._check(self.lib.ref_build_scene(scene.nranks, nlevels, levels, int(min_level),
+                                             int(max_level), int(component), int(bool(log_scale)),
+                                             int(bool(normalize_to_data_range)), C.byref(handle)))
+        nb = C.c_int(0)
+        boxes = _P(api.Box)()
+        owners = _P(C.c_int32)()
+        t = api.ScalarTransform()
+        rmin, rmax = C.c_float(0), C.c_float(0)
+        bmin, bmax = (C.c_double * 3)(), (C.c_double * 3)()
+        proc, orig = (C.c_float * 2)(), (C.c_float * 2)()
+        self.lib.ref_scene_info(handle, C.byref(nb), C.byref(boxes), C.byref(owners), C.byref(t),
+                                C.byref(rmin), C.byref(rmax), bmin, bmax, proc, orig)
+        return {"handle": handle, "keep": keep, "nboxes": nb.value, "boxes": boxes,
+                "owners": [owners[i] for i in range(nb.value)], "transform": t,
+                "scalar_range": (rmin.value, rmax.value), "bounds_min": list(bmin),
+                "bounds_max": list(bmax), "processed_range": tuple(proc), "original_range": tuple(orig)}
+
+    def scene_histogram(self, built, bin_count):
+        """The real detail::ComputeSceneHistogram on the scene build_scene returned."""
+        counts = np.zeros(max(int(bin_count), 1), np.uint64)
+        total = C.c_uint64(0)
+        self._check(self.lib.ref_scene_histogram(built["handle"], int(bin_count),
+                                                 counts.ctypes.data_as(_P(C.c_uint64)), C.byref(total)))
+        return counts, int(total.value)
+
+    def free_scene(self, built):
+        self.lib.ref_scene_free(built["handle"])
+        built["handle"] = None
 
     @staticmethod
     def stage_seconds(log: str) -> dict:

@@ -349,6 +349,24 @@ int ref_scene_info(const ref_scene* scene, int* nboxes,
   return 0;
 }
 
+// The real ComputeSceneHistogram (SceneBuilder.cpp:445-577), collectively on the
+// scene's thread-ranks; counts as rank 0 sees them (all ranks hold the same sums).
+int ref_scene_histogram(const ref_scene* scene, int binCount, uint64_t* counts,
+                        uint64_t* sampleCount) {
+  return guarded([&] {
+    Capture quiet;
+    std::vector<VolumeRenderer::ScalarHistogram> results(scene->nranks);
+    fake_mpi_run(scene->nranks, [&](int rank) {
+      results[rank] = amrVolumeRenderer::detail::ComputeSceneHistogram(
+          scene->perRank[rank], binCount);
+    });
+    const VolumeRenderer::ScalarHistogram& h = results[0];
+    for (int b = 0; b < binCount; ++b)
+      counts[b] = h.binCounts[static_cast<std::size_t>(b)];
+    if (sampleCount) *sampleCount = h.sampleCount;
+  });
+}
+
 // The real api::Render for ONE level (config 1, Examples/RenderFromMultiFab.cpp)
 // on `nranks` thread-ranks.  Optional arguments follow api::RenderOptions.
 int ref_api_render(int nranks, const ref_level* level,

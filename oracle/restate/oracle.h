@@ -114,6 +114,21 @@ void orc_auto_camera(const double* bounds_min, const double* bounds_max,
                      float azimuth, float altitude, const double* up_or_null,
                      amrvr_camera* out);
 
+/* VolumeRenderer/SceneBuilder.cpp:113-425 BuildSceneGeometry for already-convex
+ * levels holding the FABs of ALL ranks (orc_scene.c).  Returns 0, or 1 "no
+ * data", 2 "invalid scalar range", 3 no positive value for the log scale,
+ * 4 normalisation span not finite, 5 boxes_out too small. */
+int orc_scene_build(int nlevels, const amrvr_level* levels, int min_level,
+                    int max_level, int component, int log_scale_input,
+                    int normalize_to_data_range, amrvr_box* boxes_out,
+                    int capacity, amrvr_scene_summary* summary);
+
+/* VolumeRenderer/SceneBuilder.cpp:445-577 ComputeSceneHistogram. */
+void orc_scene_histogram(int nboxes, const amrvr_box* boxes,
+                         const amrvr_scalar_transform* t, float range_min,
+                         float range_max, int bin_count, uint64_t* counts,
+                         uint64_t* sample_count);
+
 #ifdef __cplusplus
 }
 #endif
