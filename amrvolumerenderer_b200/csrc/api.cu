@@ -159,6 +159,10 @@ int fail(amrvr_ctx* ctx, int status, const std::string& msg) {
   return status;
 }
 
+}  // namespace
+int amrvr::report_error(int status, const std::string& msg) { return fail(nullptr, status, msg); }
+namespace {
+
 #define CUDA_TRY(ctx, expr)                                                              \
   do {                                                                                   \
     const cudaError_t err__ = (expr);                                                    \

@@ -956,3 +956,76 @@ void make_overlay_edges(const double* tight_min, const double* tight_max,
 }
 
 }  // namespace amrvr
+
+// ------------------------------------------------------------ automatic camera
+// reference: VolumeRenderer/VolumeRenderer.cpp:975-1030 (renderScene without an
+// explicit camera).  The two angles come from std::mt19937(seed) through
+// std::uniform_real_distribution<float> -- the same libstdc++ templates the
+// reference instantiates -- azimuth first, then altitude.
+#include <random>
+
+namespace {
+
+struct D3 {
+  double v[3];
+};
+
+double length3(const D3& a) { return std::sqrt(a.v[0] * a.v[0] + a.v[1] * a.v[1] + a.v[2] * a.v[2]); }
+
+D3 cross3(const D3& a, const D3& b) {
+  return D3{{a.v[1] * b.v[2] - a.v[2] * b.v[1], a.v[2] * b.v[0] - a.v[0] * b.v[2],
+             a.v[0] * b.v[1] - a.v[1] * b.v[0]}};
+}
+
+// safeNormalize of the reference: (0, 0, -1) when the length is unusable
+D3 unit_or_minus_z(const D3& a) {
+  const double len = length3(a);
+  if (!(len > 0.0) || !std::isfinite(len)) return D3{{0.0, 0.0, -1.0}};
+  return D3{{a.v[0] / len, a.v[1] / len, a.v[2] / len}};
+}
+
+}  // namespace
+
+extern "C" int amrvr_auto_camera(const double* bounds_min, const double* bounds_max, unsigned seed,
+                                 const double* custom_up, amrvr_camera* out) {
+  if (bounds_min == nullptr || bounds_max == nullptr || out == nullptr)
+    return amrvr::report_error(AMRVR_ERR_INVALID, "bad argument");
+  constexpr float pi = 3.14159265358979323846f;
+  D3 center, half_extent;
+  for (int d = 0; d < 3; ++d) {
+    center.v[d] = 0.5f * (bounds_min[d] + bounds_max[d]);
+    half_extent.v[d] = 0.5f * (bounds_max[d] - bounds_min[d]);
+  }
+  float radius = static_cast<float>(length3(half_extent));
+  if (radius <= 0.0f) radius = 1.0f;
+
+  const float fov = pi * 0.25f, max_altitude = pi * 0.25f, half_fov = fov * 0.5f;
+  const float fit = (half_fov > 0.0f) ? radius / static_cast<float>(std::tan(half_fov)) : radius;
+  const float distance = fit + std::max(0.25f * radius, 0.5f);
+
+  std::mt19937 rng(seed);
+  std::uniform_real_distribution<float> pick_azimuth(0.0f, 2.0f * pi);
+  std::uniform_real_distribution<float> pick_altitude(-max_altitude, max_altitude);
+  const float azimuth = pick_azimuth(rng);
+  const float altitude = pick_altitude(rng);
+  const float cos_alt = std::cos(altitude);
+
+  const D3 eye{{center.v[0] + distance * cos_alt * std::sin(azimuth),
+                center.v[1] + distance * std::sin(altitude),
+                center.v[2] + distance * cos_alt * std::cos(azimuth)}};
+  const D3 view = unit_or_minus_z(D3{{center.v[0] - eye.v[0], center.v[1] - eye.v[1], center.v[2] - eye.v[2]}});
+  D3 up = (custom_up != nullptr) ? D3{{custom_up[0], custom_up[1], custom_up[2]}} : D3{{0.0, 1.0, 0.0}};
+  const D3 spare[2] = {D3{{0.0, 0.0, 1.0}}, D3{{1.0, 0.0, 0.0}}};
+  for (int k = 0; k < 2 && length3(cross3(view, up)) <= 1e-4f; ++k) up = spare[k];
+  up = unit_or_minus_z(up);
+
+  for (int d = 0; d < 3; ++d) {
+    out->eye[d] = eye.v[d];
+    out->look_at[d] = center.v[d];
+    out->up[d] = up.v[d];
+  }
+  out->fov_y_degrees = fov * 180.0f / pi;
+  out->near_plane = 0.1f;
+  out->far_plane = distance * 4.0f;
+  return AMRVR_OK;
+}

@@ -216,4 +216,8 @@ int launch_order_pairs(const OrderBox* boxes_dev, int n, float dx, float dy,
                        float dz, OrderEdge* edges_dev, int capacity,
                        int32_t* count_dev, void* stream, int64_t* launches);
 
+// Records msg as the calling thread's last error (amrvr_last_error(NULL)) and
+// returns status; for the host-only entry points that have no ctx (amr_io.cpp).
+int report_error(int status, const std::string& msg);
+
 }  // namespace amrvr

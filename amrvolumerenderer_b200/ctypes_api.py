@@ -174,6 +174,33 @@ class SceneSummary(C.Structure):
     ]
 
 
+class PlotfileInfo(C.Structure):
+    """amrvr_plotfile_info: what PlotFileData reports about the whole file."""
+
+    _fields_ = [
+        ("space_dim", C.c_int32),
+        ("ncomp", C.c_int32),
+        ("finest_level", C.c_int32),
+        ("reserved", C.c_int32),
+        ("time", C.c_double),
+        ("prob_lo", C.c_double * 3),
+        ("prob_hi", C.c_double * 3),
+    ]
+
+
+class PlotfileLevel(C.Structure):
+    """amrvr_plotfile_level: per-level geometry + BoxArray size."""
+
+    _fields_ = [
+        ("cell_size", C.c_double * 3),
+        ("ref_ratio", C.c_int32 * 3),
+        ("domain_lo", C.c_int32 * 3),
+        ("domain_hi", C.c_int32 * 3),
+        ("nboxes", C.c_int32),
+        ("real_bytes", C.c_int32),
+    ]
+
+
 class LibraryMissingError(RuntimeError):
     """libamrvr_b200.so has not been built (run __graft_entry__.build())."""
 
@@ -222,6 +249,22 @@ def _declare(lib):
                                             _P(C.c_uint64), _P(C.c_uint64)]),
         "amrvr_scene_global_boxes": (C.c_int, [vp, _P(i32), _P(_P(BoxRecord))]),
         "amrvr_scene_read_brick": (C.c_int, [vp, vp, i32, vp]),
+        "amrvr_plotfile_open": (C.c_int, [C.c_char_p, _P(vp)]),
+        "amrvr_plotfile_close": (None, [vp]),
+        "amrvr_plotfile_get_info": (C.c_int, [vp, _P(PlotfileInfo)]),
+        "amrvr_plotfile_var_name": (C.c_char_p, [vp, i32]),
+        "amrvr_plotfile_var_index": (C.c_int, [vp, C.c_char_p]),
+        "amrvr_plotfile_get_level": (C.c_int, [vp, i32, _P(PlotfileLevel)]),
+        "amrvr_plotfile_level_boxes": (C.c_int, [vp, i32, _P(C.c_int32), i32]),
+        "amrvr_plotfile_read_fab": (C.c_int, [vp, i32, i32, i32, vp, i64]),
+        "amrvr_plotfile_read_level": (C.c_int, [vp, i32, i32, i32, i32, i32, i32, vp, i64,
+                                                _P(C.c_int32), _P(i64), i32, _P(C.c_int32)]),
+        "amrvr_convexify_boxes": (C.c_int, [i32, _P(C.c_int32), i32, _P(C.c_int32), _P(C.c_int32),
+                                            _P(C.c_int32), _P(C.c_int32), i32, _P(C.c_int32)]),
+        "amrvr_convexify_levels": (C.c_int, [i32, _P(Level), _P(_P(C.c_int32)), _P(C.c_int32),
+                                             _P(C.c_int32 * 3), _P(Fab), i32, _P(C.c_int32)]),
+        "amrvr_auto_camera": (C.c_int, [_P(C.c_double), _P(C.c_double), C.c_uint, _P(C.c_double),
+                                        _P(Camera)]),
         "amrvr_order_boxes": (C.c_int, [vp, vp, _P(Camera), f32, i32, _P(i32), _P(i32)]),
         "amrvr_order_records": (C.c_int, [vp, i32, i32, _P(BoxRecord), _P(Camera), f32, i32,
                                           _P(i32), _P(i32)]),

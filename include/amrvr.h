@@ -230,6 +230,95 @@ int amrvr_scene_histogram(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                           float range_min, float range_max, int bin_count,
                           uint64_t* counts_host, uint64_t* sample_count);
 
+/* -------------------------------------------- plotfiles and convexify (f2, f3) */
+
+/* f3.  Replaces the use the reference makes of amrex::PlotFileData
+ * (VolumeRenderer/VolumeRenderer.cpp:599-679; AMReX 26.04, un-vendored): the
+ * plotfile's `Header`, every level's `Level_n/Cell_H` (VisMF header: BoxArray +
+ * FabOnDisk table) and the FAB records in `Cell_D_*` (text descriptor, then
+ * the reals, component-major, Fortran order; 8- or 4-byte IEEE, either byte
+ * order -- values are widened to double as amrex::Real = double does).
+ * [host-only]; errors go to amrvr_last_error(NULL). */
+typedef struct amrvr_plotfile amrvr_plotfile;
+
+typedef struct amrvr_plotfile_info {
+  int32_t space_dim;    /* PlotFileData::spaceDim()    */
+  int32_t ncomp;        /* varNames().size()           */
+  int32_t finest_level; /* finestLevel()               */
+  int32_t reserved;
+  double time;
+  double prob_lo[3];    /* probLo()                    */
+  double prob_hi[3];
+} amrvr_plotfile_info;
+
+typedef struct amrvr_plotfile_level {
+  double cell_size[3];   /* cellSize(level)                               */
+  int32_t ref_ratio[3];  /* refRatio(level) towards level+1; 0 on the finest */
+  int32_t domain_lo[3];  /* probDomain(level)                             */
+  int32_t domain_hi[3];
+  int32_t nboxes;        /* boxArray(level).size()                        */
+  int32_t real_bytes;    /* 8 or 4: precision of the FABs on disk         */
+} amrvr_plotfile_level;
+
+int amrvr_plotfile_open(const char* path, amrvr_plotfile** out);
+void amrvr_plotfile_close(amrvr_plotfile* pf);
+int amrvr_plotfile_get_info(const amrvr_plotfile* pf, amrvr_plotfile_info* info);
+/* varNames()[component]; NULL when out of range.  Owned by pf. */
+const char* amrvr_plotfile_var_name(const amrvr_plotfile* pf, int component);
+/* Index of a variable name, -1 when absent (VolumeRenderer.cpp:614-624). */
+int amrvr_plotfile_var_index(const amrvr_plotfile* pf, const char* name);
+int amrvr_plotfile_get_level(const amrvr_plotfile* pf, int level,
+                             amrvr_plotfile_level* out);
+/* boxArray(level): lo_hi[6*b .. 6*b+5] = lo[3], hi[3] of box b. */
+int amrvr_plotfile_level_boxes(const amrvr_plotfile* pf, int level,
+                               int32_t* lo_hi, int capacity);
+/* One component of one FAB into dst[nx*ny*nz] (i fastest), = what
+ * PlotFileData::get(level, name) leaves in that FAB.  Thread-safe per call
+ * (pread), so a caller may read several FABs concurrently. */
+int amrvr_plotfile_read_fab(const amrvr_plotfile* pf, int level, int box,
+                            int component, double* dst, int64_t capacity);
+/* All FABs of `level` dealt to `rank` (box b belongs to rank b % nranks when
+ * rule = 0, to contiguous chunks of ceil(n/nranks) when rule = 1) read with
+ * `threads` reader threads into dst (dense, one after another in box order).
+ * box_index_out[k] / offset_out[k] (may be NULL) name box k of the rank and
+ * its first element in dst.  Returns the count through nread. */
+int amrvr_plotfile_read_level(const amrvr_plotfile* pf, int level, int component,
+                              int rank, int nranks, int rule, int threads,
+                              double* dst, int64_t capacity,
+                              int32_t* box_index_out, int64_t* offset_out,
+                              int box_capacity, int32_t* nread);
+
+/* f2.  Replaces amrex::convexify (AMReX 26.04 MultiFabUtil, un-vendored; call
+ * sites VolumeRenderer.cpp:669-670, VolumeRendererApi.cpp:97-98) for one level
+ * transition: every coarse box minus the union of the fine boxes coarsened by
+ * `ratio` (floor division, as amrex::coarsen), cut into disjoint boxes with
+ * AMReX's BoxList boxDiff order (highest dimension first, low side before high
+ * side).  Piece k = out_lo_hi[6k..6k+5], lying wholly inside coarse box
+ * out_source[k]; pieces come in coarse-box order.  No cell data moves: the
+ * caller re-points an amrvr_fab at the source FAB with the piece as valid box
+ * (amrvr_convexify_levels does that), and amrvr_scene_upload's strided
+ * quantise pass is the masked copy.  [host-only]
+ * Returns AMRVR_ERR_INVALID when capacity is too small (*npieces = needed). */
+int amrvr_convexify_boxes(int ncoarse, const int32_t* coarse_lo_hi, int nfine,
+                          const int32_t* fine_lo_hi, const int32_t ratio[3],
+                          int32_t* out_lo_hi, int32_t* out_source, int capacity,
+                          int32_t* npieces);
+
+/* Whole hierarchy: levels[l] holds this rank's FABs; fine_boxes[l] /
+ * nfine_boxes[l] the GLOBAL BoxArray of level l (what MultiFab::boxArray()
+ * returns on every rank; NULL = this rank's FABs are the whole level, i.e. one
+ * rank); ref_ratio[l] the ratio between level l and l+1.  fabs_out receives,
+ * level after level, views into the callers' FABs restricted to the cells no
+ * finer level covers (finest level unchanged); nfabs_out[l] counts them.
+ * Pieces stay on the rank that owns the source FAB -- the reference lets AMReX
+ * build a fresh DistributionMapping and ParallelCopy; here nothing is
+ * exchanged.  [host-only] */
+int amrvr_convexify_levels(int nlevels, const amrvr_level* levels,
+                           const int32_t* const* fine_boxes,
+                           const int32_t* nfine_boxes,
+                           const int32_t (*ref_ratio)[3], amrvr_fab* fabs_out,
+                           int capacity, int32_t* nfabs_out);
+
 /* ---------------------------------------------------------------- ordering */
 
 /* a10.  Replaces BuildVisibilityOrderedGroup (Common/VisibilityOrdering.hpp:
@@ -373,6 +462,14 @@ int amrvr_copy_to_device(amrvr_ctx* ctx, void* dst_device, const void* src_host,
 int amrvr_host_alloc_pinned(size_t bytes, void** out);
 int amrvr_host_free_pinned(void* ptr);
 int amrvr_synchronize(amrvr_ctx* ctx);
+
+/* The camera VolumeRenderer::renderScene builds when none is given
+ * (VolumeRenderer/VolumeRenderer.cpp:975-1030): orbit at a random azimuth and
+ * altitude (std::mt19937(seed), RenderParameters::cameraSeed = 91021 by
+ * default) around the centre of the scene bounds, far enough to see all of it
+ * at 45 degrees.  custom_up = RenderParameters::cameraUp or NULL.  [host-only] */
+int amrvr_auto_camera(const double* bounds_min, const double* bounds_max,
+                      unsigned seed, const double* custom_up, amrvr_camera* out);
 
 /* ------------------------------------------------------------ whole frame */
 
