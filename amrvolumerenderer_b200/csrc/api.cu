@@ -5,7 +5,10 @@
 
 #include <algorithm>
 #include <chrono>
-#include <future>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
 #include <limits>
 #include <cmath>
 #include <cstdio>
@@ -62,17 +65,73 @@ struct SymBuffer {
   std::vector<char> opened;  // peer[q] came from cudaIpcOpenMemHandle
 };
 
+// One helper thread per context, started on first use and parked on a condition
+// variable between frames: the visibility ordering of a few hundred boxes is
+// pure host work, so it runs here while the calling thread enqueues the march.
+// (A thread created per frame costs about as much as the ordering itself.)
+class HostWorker {
+ public:
+  ~HostWorker() {
+    {
+      std::lock_guard<std::mutex> lock(m_);
+      quit_ = true;
+    }
+    cv_.notify_all();
+    if (thread_.joinable()) thread_.join();
+  }
+  void submit(std::function<void()> job) {
+    if (!thread_.joinable()) thread_ = std::thread([this] { loop(); });
+    {
+      std::lock_guard<std::mutex> lock(m_);
+      job_ = std::move(job);
+      pending_ = true;
+      done_ = false;
+    }
+    cv_.notify_all();
+  }
+  void wait() {
+    std::unique_lock<std::mutex> lock(m_);
+    cv_.wait(lock, [this] { return done_; });
+  }
+
+ private:
+  void loop() {
+    std::unique_lock<std::mutex> lock(m_);
+    for (;;) {
+      cv_.wait(lock, [this] { return pending_ || quit_; });
+      if (quit_) return;
+      pending_ = false;
+      std::function<void()> job = std::move(job_);
+      lock.unlock();
+      job();
+      lock.lock();
+      done_ = true;
+      cv_.notify_all();
+    }
+  }
+  std::thread thread_;
+  std::mutex m_;
+  std::condition_variable cv_;
+  std::function<void()> job_;
+  bool pending_ = false, done_ = true, quit_ = false;
+};
+
 struct amrvr_ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
   cudaStream_t aux = nullptr;  // visibility ordering: runs beside the march, never waits for it
+  cudaStream_t copy = nullptr;  // host->device FAB copies of amrvr_scene_upload, ahead of the quantise
+  cudaEvent_t copy_ev[4] = {};  // copy-group fences (round-robin)
+  cudaEvent_t copy_start = nullptr;
   int64_t launches = 0;
   int order_device_min = 1024;  // global box count from which the ordering runs its device kernels
   std::string error;
+  HostWorker worker;
   ncclComm_t comm = nullptr;
   cudaEvent_t ev[8] = {};
   // per-frame parameter blocks and scratch
   DeviceBuffer stage;        // FAB doubles waiting for quantisation
+  DeviceBuffer quant_jobs;   // QuantJob[] of the upload in flight
   DeviceBuffer march_boxes;  // MarchBox[]
   DeviceBuffer tables;       // float[ntables*1024]
   DeviceBuffer counter;      // sample counter + misc small results
@@ -533,6 +592,9 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
   ctx->nranks = nranks;
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
+  CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->copy, cudaStreamNonBlocking));
+  for (auto& e : ctx->copy_ev) CUDA_TRY(nullptr, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  CUDA_TRY(nullptr, cudaEventCreateWithFlags(&ctx->copy_start, cudaEventDisableTiming));
   for (auto& e : ctx->ev) CUDA_TRY(nullptr, cudaEventCreate(&e));
   CUDA_TRY(nullptr, ctx->counter.reserve(256));
   if (nranks > 1) {
@@ -584,6 +646,11 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
   cudaStreamDestroy(ctx->aux);
+  cudaStreamDestroy(ctx->copy);
+  for (auto& e : ctx->copy_ev)
+    if (e != nullptr) cudaEventDestroy(e);
+  if (ctx->copy_start != nullptr) cudaEventDestroy(ctx->copy_start);
+  ctx->quant_jobs.release();
   delete ctx;
 }
 
@@ -665,6 +732,126 @@ int stage_boxes(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes, std::vector<
   return AMRVR_OK;
 }
 
+// Host FABs -> bytes, pipelined: the copy stream moves FAB doubles into the
+// staging buffer group by group (about 16 MB, a third of a millisecond of PCIe
+// Gen5) while the main stream quantises the group before it with ONE batched
+// launch, so the quantise and its launches hide behind the H2D copies and the
+// upload costs the copy time plus one small kernel.  Device-resident FABs
+// (in-situ) are quantised in place with a single launch.
+int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                  const amrvr_scalar_transform& transform, float range_min, float range_max,
+                  amrvr_scene& scene) {
+  struct Item {
+    int box;
+    bool on_device;
+    size_t cells, stage_off;
+  };
+  std::vector<Item> items;
+  size_t need = 0;
+  for (int b = 0; b < nboxes; ++b) {
+    const amrvr_box& B = boxes[b];
+    const size_t cells = static_cast<size_t>(std::max(B.dims[0], 0)) * std::max(B.dims[1], 0) *
+                         std::max(B.dims[2], 0);
+    if (cells == 0) continue;
+    REQUIRE(ctx, B.data != nullptr, "box data pointer is NULL");
+    cudaPointerAttributes attr;
+    const cudaError_t e = cudaPointerGetAttributes(&attr, B.data);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+    const bool dev =
+        (e == cudaSuccess && (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged));
+    items.push_back(Item{b, dev, cells, need});
+    if (!dev) need += (cells * sizeof(double) + 255) & ~static_cast<size_t>(255);
+  }
+  if (items.empty()) return AMRVR_OK;
+  CUDA_TRY(ctx, ctx->stage.reserve(need));
+  CUDA_TRY(ctx, ctx->quant_jobs.reserve(items.size() * sizeof(QuantJob)));
+
+  std::vector<QuantJob> jobs(items.size());
+  for (size_t i = 0; i < items.size(); ++i) {
+    const amrvr_box& B = boxes[items[i].box];
+    const int nx = B.dims[0], ny = B.dims[1];
+    QuantJob& J = jobs[i];
+    if (items[i].on_device) {
+      J.src = B.data + (B.lo[0] - B.begin[0]) + (B.lo[1] - B.begin[1]) * B.jstride +
+              (B.lo[2] - B.begin[2]) * B.kstride + B.component * B.nstride;
+      J.jstride = B.jstride;
+      J.kstride = B.kstride;
+    } else {
+      J.src = reinterpret_cast<const double*>(ctx->stage.as<char>() + items[i].stage_off);
+      J.jstride = nx;
+      J.kstride = static_cast<int64_t>(nx) * ny;
+    }
+    J.dst = scene.bricks.as<uint8_t>() + scene.local[items[i].box].brick_off;
+    J.nx = nx;
+    J.ny = ny;
+    J.nz = B.dims[2];
+    J.pad = 0;
+  }
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->quant_jobs.ptr, jobs.data(), jobs.size() * sizeof(QuantJob),
+                                cudaMemcpyHostToDevice, ctx->stream));
+  // the staging buffer may still be read by work queued on the main stream
+  CUDA_TRY(ctx, cudaEventRecord(ctx->copy_start, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy, ctx->copy_start, 0));
+
+  const size_t group_bytes = 16u << 20;
+  size_t first = 0, in_group = 0, max_cells = 0;
+  int fence = 0;
+  auto flush = [&](size_t end, bool copied) -> int {
+    if (end == first) return AMRVR_OK;
+    if (copied) {
+      cudaEvent_t ev = ctx->copy_ev[fence++ & 3];
+      CUDA_TRY(ctx, cudaEventRecord(ev, ctx->copy));
+      CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ev, 0));
+    }
+    LAUNCH_TRY(ctx, launch_brick_quantise_batch(ctx->quant_jobs.as<QuantJob>() + first,
+                                                static_cast<int>(end - first),
+                                                static_cast<long long>(max_cells), transform, range_min,
+                                                range_max, ctx->stream, &ctx->launches));
+    first = end;
+    in_group = 0;
+    max_cells = 0;
+    return AMRVR_OK;
+  };
+  bool group_copied = false;
+  for (size_t i = 0; i < items.size(); ++i) {
+    const Item& it = items[i];
+    const amrvr_box& B = boxes[it.box];
+    if (!it.on_device) {
+      const int nx = B.dims[0], ny = B.dims[1], nz = B.dims[2];
+      const double* src = B.data + (B.lo[0] - B.begin[0]) + (B.lo[1] - B.begin[1]) * B.jstride +
+                          (B.lo[2] - B.begin[2]) * B.kstride + B.component * B.nstride;
+      double* dst = reinterpret_cast<double*>(ctx->stage.as<char>() + it.stage_off);
+      if (B.jstride == nx && B.kstride == static_cast<int64_t>(nx) * ny) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, it.cells * sizeof(double), cudaMemcpyHostToDevice,
+                                      ctx->copy));
+      } else if (B.kstride % B.jstride == 0 && B.kstride / B.jstride >= ny) {
+        // ghost cells or a sub-view: one 3-D pitched copy
+        cudaMemcpy3DParms p{};
+        p.srcPtr = make_cudaPitchedPtr(const_cast<double*>(src), B.jstride * sizeof(double),
+                                       static_cast<size_t>(B.jstride), static_cast<size_t>(B.kstride / B.jstride));
+        p.dstPtr = make_cudaPitchedPtr(dst, nx * sizeof(double), static_cast<size_t>(nx), static_cast<size_t>(ny));
+        p.extent = make_cudaExtent(nx * sizeof(double), static_cast<size_t>(ny), static_cast<size_t>(nz));
+        p.kind = cudaMemcpyHostToDevice;
+        CUDA_TRY(ctx, cudaMemcpy3DAsync(&p, ctx->copy));
+      } else {
+        for (int k = 0; k < nz; ++k)  // irregular strides: one pitched copy per k-slab
+          CUDA_TRY(ctx, cudaMemcpy2DAsync(dst + static_cast<size_t>(k) * nx * ny, nx * sizeof(double),
+                                          src + k * B.kstride, B.jstride * sizeof(double),
+                                          nx * sizeof(double), ny, cudaMemcpyHostToDevice, ctx->copy));
+      }
+      group_copied = true;
+      in_group += it.cells * sizeof(double);
+    }
+    max_cells = std::max(max_cells, it.cells);
+    if (in_group >= group_bytes) {
+      const int st = flush(i + 1, group_copied);
+      if (st != AMRVR_OK) return st;
+      group_copied = false;
+    }
+  }
+  return flush(items.size(), group_copied);
+}
+
 }  // namespace
 
 extern "C" int amrvr_brick_stats(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
@@ -742,24 +929,17 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
       }
     CUDA_TRY(ctx, scene->bricks.reserve(need));
   }
-  std::vector<StagedBox> staged;
-  int st = stage_boxes(ctx, nboxes, boxes, staged);
-  if (st != AMRVR_OK) {
-    scene->bricks.release();
-    return st;
-  }
-  for (int b = 0; b < nboxes; ++b) {
-    if (staged[b].dev == nullptr) continue;
-    const int err = launch_brick_quantise(
-        staged[b].dev, staged[b].jstride, staged[b].kstride, boxes[b].dims[0], boxes[b].dims[1],
-        boxes[b].dims[2], *transform, range_min, range_max,
-        scene->bricks.as<uint8_t>() + scene->local[b].brick_off, ctx->stream, &ctx->launches);
-    if (err != 0) {
+  Trace tr;
+  tr.mark("upload_setup");
+  {
+    const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene);
+    if (st != AMRVR_OK) {
       scene->bricks.release();
-      return fail(ctx, AMRVR_ERR_CUDA, cudaGetErrorString(static_cast<cudaError_t>(err)));
+      return st;
     }
   }
 
+  tr.mark("upload_enqueue");
   // global table: every rank's records, owner-major (VisibilityOrdering.cpp:85-152)
   std::vector<amrvr_box_record> mine(static_cast<size_t>(nboxes));
   for (int b = 0; b < nboxes; ++b) {
@@ -808,7 +988,9 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
       scene->global.insert(scene->global.end(), recs, recs + counts[r]);
     }
   }
+  tr.mark("upload_table");
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // host FABs may be reused on return
+  tr.mark("upload_sync");
   *out = scene.release();
   return AMRVR_OK;
 }
@@ -2109,7 +2291,7 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   int graph_failed = 0;
   const auto order_t0 = std::chrono::steady_clock::now();
   const bool order_on_thread = ctx->nranks > 1 && n < ctx->order_device_min;
-  std::future<float> order_job;
+  float order_thread_ms = 0.0f;
   if (order_on_thread) {
     const int P = ctx->nranks;
     const bool use_graph = params->use_visibility_graph != 0;
@@ -2117,16 +2299,17 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
     int* failed = &graph_failed;
     const amrvr_box_record* recs = scene->global.data();
     const amrvr_camera cam_copy = *camera;
-    order_job = std::async(std::launch::async, [=]() {
+    float* took = &order_thread_ms;
+    ctx->worker.submit([=]() {
       const bool ok = order_ranks(P, n, recs, cam_copy, aspect, use_graph, *host_order_backend(), out);
       *failed = ok ? 0 : 1;
-      return std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
+      *took = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
     });
   }
   st = raymarch_impl(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
                      params->count_samples, peer, &layers);
   if (st != AMRVR_OK) {
-    if (order_on_thread) order_job.wait();
+    if (order_on_thread) ctx->worker.wait();
     return st;
   }
   CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
@@ -2134,7 +2317,8 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
 
   float order_host_ms = 0.0f;
   if (order_on_thread) {
-    order_host_ms = order_job.get();
+    ctx->worker.wait();
+    order_host_ms = order_thread_ms;
   } else {
     st = amrvr_order_boxes(ctx, scene, camera, aspect, params->use_visibility_graph,
                            rank_order.data(), &graph_failed);

@@ -10,7 +10,12 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <cstdio>
+#include <cstdlib>
 #include <queue>
+#if defined(__x86_64__) && defined(__GNUC__)
+#include <immintrin.h>
+#endif
 
 namespace amrvr {
 
@@ -612,126 +617,295 @@ OrderBackend* host_order_backend() {
   return &backend;
 }
 
+namespace {
+
+// Exact test of one pair (i < j), all three axes: VisibilityOrdering.cpp:261-317.
+inline void pair_edges_exact(const std::vector<OrderBox>& boxes, const float* dir, int i, int j,
+                             unsigned axes, std::vector<OrderEdge>& edges) {
+  const OrderBox& a = boxes[i];
+  const OrderBox& b = boxes[j];
+  for (int axis = 0; axis < 3; ++axis) {
+    if (((axes >> axis) & 1u) == 0u) continue;  // the filter proved this axis carries no edge
+    const int u = (axis + 1) % 3, v = (axis + 2) % 3;
+    const float along = dir[axis];
+    // a below b on this axis: looking up the axis (along > 0) puts a in front.
+    int forward = -1;
+    if (touching(a.hi[axis], b.lo[axis])) {
+      if (along > 1e-6f) forward = 0;        // reference adds edge j -> i
+      else if (along < -1e-6f) forward = 1;  // edge i -> j
+    } else if (touching(b.hi[axis], a.lo[axis])) {
+      if (along > 1e-6f) forward = 1;
+      else if (along < -1e-6f) forward = 0;
+    }
+    if (forward < 0) continue;
+    if (!spans_overlap(a.lo[u], a.hi[u], b.lo[u], b.hi[u])) continue;
+    if (!spans_overlap(a.lo[v], a.hi[v], b.lo[v], b.hi[v])) continue;
+    edges.push_back(OrderEdge{i, j, axis, forward});
+  }
+}
+
+// Conservative filter for "pair (i, j) may carry an edge", eight (AVX2), four
+// (SSE2) or one pair at a time.  An edge on axis A needs the faces to touch on A
+// (|a.hi - b.lo| or |b.hi - a.lo| <= 1e-5 * scale, and scale <= `largest`, so
+// <= tol) and the spans on the other two axes to overlap by MORE than
+// 1e-5 * scale > 0; the filter keeps every pair for which that can hold and the
+// exact test above decides.  soa = lo0 lo1 lo2 hi0 hi1 hi2, `stride` floats each
+// (n boxes, then 8 columns of padding placed far away from everything).
+// cand[k] = j | (axes << 28): bit a of axes set when axis a may carry the edge (n < 2^28).
+typedef void (*PairFilterFn)(const float* soa, int stride, int n, int i, float tol, int* cand, int* ncand);
+
+inline unsigned pair_may_touch(const float* soa, int stride, int i, int j, float tol) {
+  bool ov[3], touch[3];
+  for (int d = 0; d < 3; ++d) {
+    const float alo = soa[d * stride + i], ahi = soa[(3 + d) * stride + i];
+    const float blo = soa[d * stride + j], bhi = soa[(3 + d) * stride + j];
+    ov[d] = (fmin2(ahi, bhi) - fmax2(alo, blo)) > 0.0f;
+    touch[d] = std::fabs(ahi - blo) <= tol || std::fabs(bhi - alo) <= tol;
+  }
+  return (touch[0] && ov[1] && ov[2] ? 1u : 0u) | (touch[1] && ov[2] && ov[0] ? 2u : 0u) |
+         (touch[2] && ov[0] && ov[1] ? 4u : 0u);
+}
+
+[[maybe_unused]] void pair_filter_scalar(const float* soa, int stride, int n, int i, float tol,
+                                         int* cand, int* ncand) {
+  int k = 0;
+  for (int j = i + 1; j < n; ++j) {
+    const unsigned axes = pair_may_touch(soa, stride, i, j, tol);
+    if (axes != 0u) cand[k++] = j | static_cast<int>(axes << 28);
+  }
+  *ncand = k;
+}
+
+#if defined(__x86_64__) && defined(__GNUC__)
+__attribute__((target("avx2"))) void pair_filter_avx2(const float* soa, int stride, int n, int i,
+                                                      float tol, int* cand, int* ncand) {
+  const __m256 absmask = _mm256_castsi256_ps(_mm256_set1_epi32(0x7fffffff));
+  const __m256 vtol = _mm256_set1_ps(tol), zero = _mm256_setzero_ps();
+  __m256 alo[3], ahi[3];
+  for (int d = 0; d < 3; ++d) {
+    alo[d] = _mm256_set1_ps(soa[d * stride + i]);
+    ahi[d] = _mm256_set1_ps(soa[(3 + d) * stride + i]);
+  }
+  int k = 0, j = i + 1;
+  for (; j < n; j += 8) {  // columns n .. n+7 are padding that never matches
+    __m256 ov[3], touch[3];
+    for (int d = 0; d < 3; ++d) {
+      const __m256 blo = _mm256_loadu_ps(soa + d * stride + j), bhi = _mm256_loadu_ps(soa + (3 + d) * stride + j);
+      ov[d] = _mm256_cmp_ps(_mm256_sub_ps(_mm256_min_ps(ahi[d], bhi), _mm256_max_ps(alo[d], blo)), zero,
+                            _CMP_GT_OQ);
+      const __m256 g0 = _mm256_and_ps(_mm256_sub_ps(ahi[d], blo), absmask);
+      const __m256 g1 = _mm256_and_ps(_mm256_sub_ps(bhi, alo[d]), absmask);
+      touch[d] = _mm256_cmp_ps(_mm256_min_ps(g0, g1), vtol, _CMP_LE_OQ);
+    }
+    const unsigned m0 = static_cast<unsigned>(
+        _mm256_movemask_ps(_mm256_and_ps(touch[0], _mm256_and_ps(ov[1], ov[2]))));
+    const unsigned m1 = static_cast<unsigned>(
+        _mm256_movemask_ps(_mm256_and_ps(touch[1], _mm256_and_ps(ov[2], ov[0]))));
+    const unsigned m2 = static_cast<unsigned>(
+        _mm256_movemask_ps(_mm256_and_ps(touch[2], _mm256_and_ps(ov[0], ov[1]))));
+    unsigned bits = m0 | m1 | m2;
+    while (bits != 0u) {
+      const int b = __builtin_ctz(bits);
+      const unsigned axes = ((m0 >> b) & 1u) | (((m1 >> b) & 1u) << 1) | (((m2 >> b) & 1u) << 2);
+      cand[k++] = (j + b) | static_cast<int>(axes << 28);
+      bits &= bits - 1u;
+    }
+  }
+  *ncand = k;
+}
+
+void pair_filter_sse2(const float* soa, int stride, int n, int i, float tol, int* cand, int* ncand) {
+  const __m128 absmask = _mm_castsi128_ps(_mm_set1_epi32(0x7fffffff));
+  const __m128 vtol = _mm_set1_ps(tol), zero = _mm_setzero_ps();
+  __m128 alo[3], ahi[3];
+  for (int d = 0; d < 3; ++d) {
+    alo[d] = _mm_set1_ps(soa[d * stride + i]);
+    ahi[d] = _mm_set1_ps(soa[(3 + d) * stride + i]);
+  }
+  int k = 0, j = i + 1;
+  for (; j < n; j += 4) {  // columns n .. n+7 are padding that never matches
+    __m128 ov[3], touch[3];
+    for (int d = 0; d < 3; ++d) {
+      const __m128 blo = _mm_loadu_ps(soa + d * stride + j), bhi = _mm_loadu_ps(soa + (3 + d) * stride + j);
+      ov[d] = _mm_cmpgt_ps(_mm_sub_ps(_mm_min_ps(ahi[d], bhi), _mm_max_ps(alo[d], blo)), zero);
+      const __m128 g0 = _mm_and_ps(_mm_sub_ps(ahi[d], blo), absmask);
+      const __m128 g1 = _mm_and_ps(_mm_sub_ps(bhi, alo[d]), absmask);
+      touch[d] = _mm_cmple_ps(_mm_min_ps(g0, g1), vtol);
+    }
+    const unsigned m0 =
+        static_cast<unsigned>(_mm_movemask_ps(_mm_and_ps(touch[0], _mm_and_ps(ov[1], ov[2]))));
+    const unsigned m1 =
+        static_cast<unsigned>(_mm_movemask_ps(_mm_and_ps(touch[1], _mm_and_ps(ov[2], ov[0]))));
+    const unsigned m2 =
+        static_cast<unsigned>(_mm_movemask_ps(_mm_and_ps(touch[2], _mm_and_ps(ov[0], ov[1]))));
+    unsigned bits = m0 | m1 | m2;
+    while (bits != 0u) {
+      const int b = __builtin_ctz(bits);
+      const unsigned axes = ((m0 >> b) & 1u) | (((m1 >> b) & 1u) << 1) | (((m2 >> b) & 1u) << 2);
+      cand[k++] = (j + b) | static_cast<int>(axes << 28);
+      bits &= bits - 1u;
+    }
+  }
+  *ncand = k;
+}
+
+PairFilterFn pick_pair_filter() {
+  __builtin_cpu_init();
+  return __builtin_cpu_supports("avx2") ? pair_filter_avx2 : pair_filter_sse2;
+}
+#else
+PairFilterFn pick_pair_filter() { return pair_filter_scalar; }
+#endif
+
+}  // namespace
+
 void order_pair_edges_host(const std::vector<OrderBox>& boxes, const float* dir,
                            std::vector<OrderEdge>& edges) {
   edges.clear();
   const int n = static_cast<int>(boxes.size());
-  // Cheap exact reject.  An edge on any axis needs the faces to touch on that
-  // axis (|a - b| <= 1e-5 * scale, scale <= max(1, largest |coordinate|)) and
-  // the other two spans to overlap strictly, so the two boxes grown by `tol`
-  // must intersect on all three axes.  Valid when every box has lo <= hi.
+  static const PairFilterFn filter = pick_pair_filter();
+  // The filter is valid when every coordinate is finite and lo <= hi (NaNs and
+  // inverted boxes make min/max/compare behave differently from the scalar
+  // reference test); anything else takes the exact test on every pair.
   float largest = 1.0f;
   bool well_formed = true;
   for (const OrderBox& b : boxes)
     for (int d = 0; d < 3; ++d) {
       largest = fmax2(largest, fmax2(std::fabs(b.lo[d]), std::fabs(b.hi[d])));
-      well_formed = well_formed && (b.lo[d] <= b.hi[d]);
+      well_formed = well_formed && (b.lo[d] <= b.hi[d]) && std::isfinite(b.lo[d]) && std::isfinite(b.hi[d]);
     }
-  const float tol = well_formed ? 2e-5f * largest : INFINITY;
-  // structure-of-arrays copy so the reject runs as straight-line SIMD compares
-  // over all j > i; the survivors (a few per box) take the exact test below
-  std::vector<float> soa(static_cast<size_t>(n) * 12);
-  float* lo0 = soa.data();
-  float* lo1 = lo0 + n;
-  float* lo2 = lo1 + n;
-  float* hi0 = lo2 + n;  // hi + tol
-  float* hi1 = hi0 + n;
-  float* hi2 = hi1 + n;
-  for (int i = 0; i < n; ++i) {
-    lo0[i] = boxes[i].lo[0];
-    lo1[i] = boxes[i].lo[1];
-    lo2[i] = boxes[i].lo[2];
-    hi0[i] = boxes[i].hi[0] + tol;
-    hi1[i] = boxes[i].hi[1] + tol;
-    hi2[i] = boxes[i].hi[2] + tol;
+  if (!well_formed || !std::isfinite(largest) || n >= (1 << 28)) {
+    for (int i = 0; i < n; ++i)
+      for (int j = i + 1; j < n; ++j) pair_edges_exact(boxes, dir, i, j, 7u, edges);
+    return;
   }
-  std::vector<unsigned char> pass(static_cast<size_t>(n));
-  std::vector<int> cand(static_cast<size_t>(n) + 1);
+  const float tol = 1.001e-5f * largest;
+  thread_local std::vector<float> soa;
+  thread_local std::vector<int> cand;
+  const int stride = n + 8;
+  soa.assign(static_cast<size_t>(stride) * 6, 3.0e38f);  // padding: touches and overlaps nothing
+  cand.resize(static_cast<size_t>(n) + 8);
+  for (int i = 0; i < n; ++i)
+    for (int d = 0; d < 3; ++d) {
+      soa[static_cast<size_t>(d) * stride + i] = boxes[i].lo[d];
+      soa[static_cast<size_t>(3 + d) * stride + i] = boxes[i].hi[d];
+    }
   for (int i = 0; i < n; ++i) {
-    const OrderBox& a = boxes[i];
-    const float al0 = lo0[i], al1 = lo1[i], al2 = lo2[i], ah0 = hi0[i], ah1 = hi1[i], ah2 = hi2[i];
-    unsigned char* m = pass.data();
-    for (int j = i + 1; j < n; ++j)
-      m[j] = static_cast<unsigned char>(!(lo0[j] > ah0) & !(al0 > hi0[j]) & !(lo1[j] > ah1) &
-                                        !(al1 > hi1[j]) & !(lo2[j] > ah2) & !(al2 > hi2[j]));
-    // branch-free compaction of the survivors, then the exact test on those only
     int ncand = 0;
-    for (int j = i + 1; j < n; ++j) {
-      cand[ncand] = j;
-      ncand += m[j];
-    }
-    for (int c = 0; c < ncand; ++c) {
-      const int j = cand[c];
-      const OrderBox& b = boxes[j];
-      for (int axis = 0; axis < 3; ++axis) {
-        const int u = (axis + 1) % 3, v = (axis + 2) % 3;
-        const float along = dir[axis];
-        // a below b on this axis: looking up the axis (along > 0) puts a in front.
-        // The (pure) face test runs first: it rejects most surviving pairs, and
-        // an edge needs it anyway.
-        int forward = -1;
-        if (touching(a.hi[axis], b.lo[axis])) {
-          if (along > 1e-6f) forward = 0;        // reference adds edge j -> i
-          else if (along < -1e-6f) forward = 1;  // edge i -> j
-        } else if (touching(b.hi[axis], a.lo[axis])) {
-          if (along > 1e-6f) forward = 1;
-          else if (along < -1e-6f) forward = 0;
-        }
-        if (forward < 0) continue;
-        if (!spans_overlap(a.lo[u], a.hi[u], b.lo[u], b.hi[u])) continue;
-        if (!spans_overlap(a.lo[v], a.hi[v], b.lo[v], b.hi[v])) continue;
-        if (forward >= 0) edges.push_back(OrderEdge{i, j, axis, forward});
-      }
-    }
+    filter(soa.data(), stride, n, i, tol, cand.data(), &ncand);
+    for (int c = 0; c < ncand; ++c)
+      pair_edges_exact(boxes, dir, i, cand[c] & 0x0fffffff, static_cast<unsigned>(cand[c]) >> 28, edges);
   }
 }
 
 namespace {
 
+// Adjacency in compressed rows: the targets of node v are adj[start[v] ..
+// start[v + 1]) in the reference's insertion order.
 struct Graph {
-  std::vector<std::vector<int>> out;
-  std::vector<int> indegree;
+  int n = 0;
+  std::vector<int> start, adj, indegree;
+  int degree(int v) const { return start[v + 1] - start[v]; }
+  int target(int v, int k) const { return adj[start[v] + k]; }
 };
 
 // adjacency lists in the reference's insertion order (:261-317): edges arrive
-// sorted by (i, j, axis); duplicates (same from->to) are dropped.
+// sorted by (i, j, axis); duplicates (same from->to) are dropped.  Two edges
+// with the same endpoints always belong to the same pair (i, j), so after the
+// sort a duplicate is one of the at most two edges just before it.
 void build_graph(int n, std::vector<OrderEdge>& edges, Graph& g) {
-  std::sort(edges.begin(), edges.end(), [](const OrderEdge& a, const OrderEdge& b) {
+  auto by_pair = [](const OrderEdge& a, const OrderEdge& b) {
     if (a.i != b.i) return a.i < b.i;
     if (a.j != b.j) return a.j < b.j;
     return a.axis < b.axis;
-  });
-  g.out.assign(n, {});
-  g.indegree.assign(n, 0);
-  for (const OrderEdge& e : edges) {
-    const int from = e.forward ? e.i : e.j;
-    const int to = e.forward ? e.j : e.i;
-    auto& list = g.out[from];
-    if (std::find(list.begin(), list.end(), to) != list.end()) continue;
-    list.push_back(to);
+  };
+  if (!std::is_sorted(edges.begin(), edges.end(), by_pair)) {
+    // the host pair test emits edges in order; the device kernel appends them as
+    // its threads find them.  Bucket by i (counting sort), then order each
+    // bucket -- a box has a handful of neighbours -- by (j, axis).
+    thread_local std::vector<int> head;
+    thread_local std::vector<OrderEdge> sorted;
+    bool in_range = true;
+    for (const OrderEdge& e : edges) in_range = in_range && e.i >= 0 && e.i < n;
+    if (in_range) {
+      head.assign(static_cast<size_t>(n) + 1, 0);
+      for (const OrderEdge& e : edges) ++head[static_cast<size_t>(e.i) + 1];
+      for (int v = 0; v < n; ++v) head[v + 1] += head[v];
+      sorted.resize(edges.size());
+      {
+        std::vector<int> at(head.begin(), head.end() - 1);
+        for (const OrderEdge& e : edges) sorted[at[e.i]++] = e;
+      }
+      for (int v = 0; v < n; ++v) std::sort(sorted.begin() + head[v], sorted.begin() + head[v + 1], by_pair);
+      edges.swap(sorted);
+    } else {
+      std::sort(edges.begin(), edges.end(), by_pair);
+    }
+  }
+  const size_t m = edges.size();
+  thread_local std::vector<unsigned char> keep;
+  keep.assign(m, 1);
+  g.n = n;
+  g.start.assign(static_cast<size_t>(n) + 1, 0);
+  g.indegree.assign(static_cast<size_t>(n), 0);
+  for (size_t e = 0; e < m; ++e) {
+    const OrderEdge& E = edges[e];
+    for (size_t back = 1; back <= 2 && back <= e; ++back) {
+      const OrderEdge& F = edges[e - back];
+      if (F.i != E.i || F.j != E.j) break;
+      if (keep[e - back] && F.forward == E.forward) keep[e] = 0;
+    }
+    if (!keep[e]) continue;
+    const int from = E.forward ? E.i : E.j, to = E.forward ? E.j : E.i;
+    ++g.start[static_cast<size_t>(from) + 1];
     ++g.indegree[to];
+  }
+  for (int v = 0; v < n; ++v) g.start[v + 1] += g.start[v];
+  g.adj.resize(static_cast<size_t>(g.start[n]));
+  thread_local std::vector<int> fill;
+  fill.assign(g.start.begin(), g.start.end() - 1);
+  for (size_t e = 0; e < m; ++e) {
+    if (!keep[e]) continue;
+    const OrderEdge& E = edges[e];
+    const int from = E.forward ? E.i : E.j, to = E.forward ? E.j : E.i;
+    g.adj[fill[from]++] = to;
   }
 }
 
 // Kahn's algorithm taking, at each step, the ready box that comes first in the
-// compareBoxes order (:360-401 re-sorts the ready list and pops the front; a
-// min-heap on the precomputed priority picks the same box).
+// compareBoxes order (:360-401 re-sorts the ready list and pops the front).
+// priority is a permutation of 0..n-1, so the ready set is a bitmap indexed by
+// priority and "the front" is its lowest set bit.
 bool topo_order(const Graph& g, const std::vector<int32_t>& priority, std::vector<int>& order,
                 std::vector<int>& residual) {
-  const int n = static_cast<int>(g.out.size());
+  const int n = g.n;
   residual = g.indegree;
-  using Item = std::pair<int32_t, int>;
-  std::priority_queue<Item, std::vector<Item>, std::greater<Item>> ready;
+  const int words = (n + 63) / 64;
+  thread_local std::vector<uint64_t> ready;
+  thread_local std::vector<int> node_at;
+  ready.assign(static_cast<size_t>(words), 0);
+  node_at.resize(static_cast<size_t>(n));
+  for (int i = 0; i < n; ++i) node_at[priority[i]] = i;
   for (int i = 0; i < n; ++i)
-    if (residual[i] == 0) ready.push({priority[i], i});
+    if (residual[i] == 0) ready[priority[i] >> 6] |= 1ull << (priority[i] & 63);
   order.clear();
   order.reserve(n);
-  while (!ready.empty()) {
-    const int node = ready.top().second;
-    ready.pop();
+  int low = 0;  // no bit is set below word `low`... unless a push lowers it again
+  for (;;) {
+    while (low < words && ready[low] == 0) ++low;
+    if (low == words) break;
+    const int bit = __builtin_ctzll(ready[low]);
+    ready[low] &= ready[low] - 1;
+    const int node = node_at[low * 64 + bit];
     order.push_back(node);
-    for (int next : g.out[node])
-      if (--residual[next] == 0) ready.push({priority[next], next});
+    for (int k = g.start[node]; k < g.start[node + 1]; ++k) {
+      const int next = g.adj[k];
+      if (--residual[next] == 0) {
+        const int p = priority[next];
+        ready[p >> 6] |= 1ull << (p & 63);
+        if ((p >> 6) < low) low = p >> 6;
+      }
+    }
   }
   return static_cast<int>(order.size()) == n;
 }
@@ -739,7 +913,7 @@ bool topo_order(const Graph& g, const std::vector<int32_t>& priority, std::vecto
 // First cycle a depth-first walk meets, nodes in walk order (:403-443).
 // Iterative (the reference recurses); visiting order is identical.
 std::vector<int> first_cycle(const Graph& g, const std::vector<int>& residual) {
-  const int n = static_cast<int>(g.out.size());
+  const int n = g.n;
   std::vector<int> state(n, 0), parent(n, -1);
   std::vector<size_t> cursor(n, 0);
   std::vector<int> stack;
@@ -749,8 +923,8 @@ std::vector<int> first_cycle(const Graph& g, const std::vector<int>& residual) {
     state[root] = 1;
     while (!stack.empty()) {
       const int node = stack.back();
-      if (cursor[node] < g.out[node].size()) {
-        const int next = g.out[node][cursor[node]++];
+      if (cursor[node] < static_cast<size_t>(g.degree(node))) {
+        const int next = g.target(node, static_cast<int>(cursor[node]++));
         if (state[next] == 0) {
           parent[next] = node;
           state[next] = 1;

@@ -113,6 +113,13 @@ void make_overlay_edges(const double* tight_min, const double* tight_max,
 
 // ------------------------------------------------------------ device structs
 
+struct QuantJob {  // one brick of a batched quantise launch
+  const double* src;
+  int64_t jstride, kstride;
+  uint8_t* dst;
+  int32_t nx, ny, nz, pad;
+};
+
 struct MarchBox {
   float lo[3], hi[3];
   float cell[3];       // dx, dy, dz (float, as the reference derives them)
@@ -175,6 +182,9 @@ int launch_brick_histogram(const double* data, int64_t jstride, int64_t kstride,
                            int nx, int ny, int nz, const amrvr_scalar_transform& t,
                            float range_min, float range_max, int bin_count,
                            unsigned long long* counts_dev, void* stream, int64_t* launches);
+int launch_brick_quantise_batch(const QuantJob* jobs_dev, int njobs, long long max_cells,
+                                const amrvr_scalar_transform& t, float range_min, float range_max,
+                                void* stream, int64_t* launches);
 int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride,
                           int nx, int ny, int nz,
                           const amrvr_scalar_transform& t, float range_min,

@@ -107,6 +107,40 @@ brick_quantise_kernel(const double* __restrict__ data, long long jstride, long l
   }
 }
 
+// Same cells, several bricks per launch: blockIdx.y picks the job.  A 64^3 brick
+// is 2 MB -- alone it cannot fill the machine for longer than a launch takes, so
+// the upload path quantises a whole group of freshly copied FABs at once.
+__global__ void __launch_bounds__(256)
+brick_quantise_batch_kernel(const QuantJob* __restrict__ jobs, ValuePath p) {
+  const QuantJob J = jobs[blockIdx.y];
+  const int nx = J.nx, ny = J.ny;
+  const int quads_per_row = (nx + 3) >> 2;
+  const long long nquads = static_cast<long long>(quads_per_row) * ny * J.nz;
+  for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < nquads;
+       q += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int qi = static_cast<int>(q % quads_per_row);
+    const long long row = q / quads_per_row;
+    const int j = static_cast<int>(row % ny);
+    const int k = static_cast<int>(row / ny);
+    const double* src = J.src + j * J.jstride + k * J.kstride + 4 * qi;
+    unsigned char* dst = J.dst + (static_cast<long long>(k) * ny + j) * nx + 4 * qi;
+    const int left = nx - 4 * qi;
+    if (left >= 4 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
+        ((reinterpret_cast<uintptr_t>(dst) & 3) == 0)) {
+      const double2 a = __ldcs(reinterpret_cast<const double2*>(src));
+      const double2 b = __ldcs(reinterpret_cast<const double2*>(src) + 1);
+      uchar4 o;
+      o.x = cell_to_index(a.x, p);
+      o.y = cell_to_index(a.y, p);
+      o.z = cell_to_index(b.x, p);
+      o.w = cell_to_index(b.y, p);
+      *reinterpret_cast<uchar4*>(dst) = o;
+    } else {
+      for (int c = 0; c < left && c < 4; ++c) dst[c] = cell_to_index(src[c], p);
+    }
+  }
+}
+
 struct Stats4 {
   double lo, hi, lo_pos;
   long long finite;
@@ -1294,6 +1328,25 @@ int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride, 
   brick_quantise_kernel<<<static_cast<unsigned>(blocks), 256, 0, as_stream(stream)>>>(
       data, jstride, kstride, nx, ny, nz, make_value_path(t, range_min, range_max), brick);
   ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_brick_quantise_batch(const QuantJob* jobs_dev, int njobs, long long max_cells,
+                                const amrvr_scalar_transform& t, float range_min, float range_max,
+                                void* stream, int64_t* launches) {
+  if (njobs <= 0 || max_cells <= 0) return 0;
+  // a quarter cell-quad per thread, grid-stride; x sized so the whole launch is about
+  // 148 SMs x 8 resident CTAs x a few waves
+  long long bx = (max_cells / 4 + 255) / 256;
+  const long long cap = std::max<long long>(1, (148LL * 32) / njobs);
+  if (bx > cap) bx = cap;
+  for (int first = 0; first < njobs; first += 65535) {
+    const int n = std::min(65535, njobs - first);
+    brick_quantise_batch_kernel<<<dim3(static_cast<unsigned>(bx), static_cast<unsigned>(n)), 256, 0,
+                                  as_stream(stream)>>>(jobs_dev + first,
+                                                       make_value_path(t, range_min, range_max));
+    ++*launches;
+  }
   return static_cast<int>(cudaGetLastError());
 }
 
