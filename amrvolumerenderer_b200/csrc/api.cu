@@ -152,6 +152,9 @@ struct amrvr_ctx {
   SymBuffer sym_flags, sym_pool, sym_piece, sym_rgb8;
   uint32_t barrier_epoch = 0;
   uint32_t* peer_error_host = nullptr;  // pinned copy of the barrier time-out flag
+  unsigned char* param_host = nullptr;  // pinned staging of the per-frame march parameter block
+  size_t param_host_bytes = 0;
+  cudaEvent_t param_copied = nullptr;   // the last copy out of param_host has completed
   uint8_t* last_rgb8 = nullptr;         // RGB8 frame of the last amrvr_render_frame (root)
   // transfer tables already built, keyed by every input of buildColorTable
   struct TableEntry {
@@ -173,6 +176,9 @@ struct amrvr_scene {
   int first_global = 0;  // global index of local box 0
   DeviceBuffer bricks;
   float range_min = 0.f, range_max = 1.f;
+  // MarchBox fields that depend on the box alone (corners, cell sizes, exactness
+  // of the reciprocal, epsilon, brick offset): built once, on the first frame
+  std::vector<MarchBox> march_const;
 };
 
 struct amrvr_layers {
@@ -631,6 +637,8 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (SymBuffer* b : {&ctx->sym_flags, &ctx->sym_pool, &ctx->sym_piece, &ctx->sym_rgb8})
     sym_release(*b, ctx->rank);
   if (ctx->peer_error_host != nullptr) cudaFreeHost(ctx->peer_error_host);
+  if (ctx->param_host != nullptr) cudaFreeHost(ctx->param_host);
+  if (ctx->param_copied != nullptr) cudaEventDestroy(ctx->param_copied);
   if (ctx->comm != nullptr) nccl_api().CommDestroy(ctx->comm);
   for (DeviceBuffer* b :
        {&ctx->stage, &ctx->march_boxes, &ctx->tables, &ctx->counter, &ctx->fold_layers, &ctx->fold_bins,
@@ -1453,7 +1461,31 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
     L->global_rects[g] = box_footprint(scene->global[g].min_corner, scene->global[g].max_corner,
                                        scene->global[g].dims, basis, *camera, width, height);
   const float alpha_scale = std::min(std::max(1.0f - box_transparency, 0.0f), 1.0f);
-  std::vector<MarchBox> mb(static_cast<size_t>(n));
+  if (scene->march_const.size() != static_cast<size_t>(n)) {
+    std::vector<MarchBox>& mc = const_cast<amrvr_scene*>(scene)->march_const;
+    mc.assign(static_cast<size_t>(n), MarchBox{});
+    for (int b = 0; b < n; ++b) {
+      const LocalBox& B = scene->local[b];
+      MarchBox& M = mc[b];
+      bool pow2 = true;
+      for (int d = 0; d < 3; ++d) {
+        M.lo[d] = static_cast<float>(B.min_corner[d]);
+        M.hi[d] = static_cast<float>(B.max_corner[d]);
+        M.n[d] = B.dims[d];
+        M.cell[d] = (M.hi[d] - M.lo[d]) / static_cast<float>(B.dims[d]);  // VolumePainter.cpp:676-678
+        M.inv_cell_tiny[d] = std::ldexp(1.0f / M.cell[d], -149);
+        // 2^-149/cell must itself be a (subnormal) float: cell a power of two <= 1
+        pow2 = pow2 && is_pow2_float(M.cell[d]) && M.inv_cell_tiny[d] > 0.0f &&
+               std::ldexp(M.inv_cell_tiny[d], 149) == 1.0f / M.cell[d];
+      }
+      // :680-683 extent, float, x then y then z
+      const float ex = M.hi[0] - M.lo[0], ey = M.hi[1] - M.lo[1], ez = M.hi[2] - M.lo[2];
+      M.eps = std::sqrt(ex * ex + ey * ey + ez * ez) * 0.0001f;
+      M.exact_recip = pow2 ? 1 : 0;
+      M.brick_off = B.brick_off;
+    }
+  }
+  std::vector<MarchBox> mb(scene->march_const);
   std::vector<float> table_norm;  // one table per distinct normalisation factor
   std::vector<float> tables;
   uint64_t floats = 0;
@@ -1462,7 +1494,6 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
   for (int b = 0; b < n; ++b) {
     const LocalBox& B = scene->local[b];
     MarchBox& M = mb[b];
-    std::memset(&M, 0, sizeof(M));
     float step, norm;
     box_sampling(B.min_corner, B.max_corner, B.dims, reference_sample_distance_, &step, &norm);
     int which = -1;
@@ -1479,24 +1510,6 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
     }
     M.table = which;
     M.step = step;
-    float diag2 = 0.0f;
-    bool pow2 = true;
-    for (int d = 0; d < 3; ++d) {
-      M.lo[d] = static_cast<float>(B.min_corner[d]);
-      M.hi[d] = static_cast<float>(B.max_corner[d]);
-      M.n[d] = B.dims[d];
-      M.cell[d] = (M.hi[d] - M.lo[d]) / static_cast<float>(B.dims[d]);  // VolumePainter.cpp:676-678
-      M.inv_cell_tiny[d] = std::ldexp(1.0f / M.cell[d], -149);
-      // 2^-149/cell must itself be a (subnormal) float: cell a power of two <= 1
-      pow2 = pow2 && is_pow2_float(M.cell[d]) && M.inv_cell_tiny[d] > 0.0f &&
-             std::ldexp(M.inv_cell_tiny[d], 149) == 1.0f / M.cell[d];
-    }
-    {  // :680-683 extent, float, x then y then z
-      const float ex = M.hi[0] - M.lo[0], ey = M.hi[1] - M.lo[1], ez = M.hi[2] - M.lo[2];
-      diag2 = ex * ex + ey * ey + ez * ez;
-    }
-    M.eps = std::sqrt(diag2) * 0.0001f;
-    M.exact_recip = pow2 ? 1 : 0;
     M.margin = inside_margin(M, basis.eye);
     const Rect r = L->global_rects[static_cast<size_t>(scene->first_global + b)];
     L->rects[b] = r;
@@ -1507,7 +1520,6 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
     M.tiles_x = (r.w + 15) / 16;
     M.tile_base = tiles;
     tiles += M.tiles_x * ((r.h + 15) / 16);
-    M.brick_off = B.brick_off;
     M.layer_off = floats;
     L->offs[b] = floats;
     floats += static_cast<uint64_t>(r.w) * r.h * 5;
@@ -1549,12 +1561,28 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
   const size_t tables_bytes = tables.size() * sizeof(float);
   const size_t boxes_bytes = mb.size() * sizeof(MarchBox);
   const size_t block_bytes = 16 + tables_bytes + boxes_bytes;
-  std::vector<unsigned char> block(block_bytes, 0);  // counters start at zero
-  if (tables_bytes) std::memcpy(block.data() + 16, tables.data(), tables_bytes);
-  if (boxes_bytes) std::memcpy(block.data() + 16 + tables_bytes, mb.data(), boxes_bytes);
+  // staged in pinned memory so the copy is a plain enqueue; the previous copy out
+  // of the staging block must have completed before it is rewritten
+  if (ctx->param_copied == nullptr)
+    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->param_copied, cudaEventDisableTiming));
+  else
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->param_copied));
+  if (ctx->param_host_bytes < block_bytes) {
+    if (ctx->param_host != nullptr) CUDA_TRY(ctx, cudaFreeHost(ctx->param_host));
+    ctx->param_host = nullptr;
+    ctx->param_host_bytes = 0;
+    const size_t want = (block_bytes + 65535) & ~static_cast<size_t>(65535);
+    CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->param_host), want));
+    ctx->param_host_bytes = want;
+  }
+  unsigned char* block = ctx->param_host;
+  std::memset(block, 0, 16);  // counters start at zero
+  if (tables_bytes) std::memcpy(block + 16, tables.data(), tables_bytes);
+  if (boxes_bytes) std::memcpy(block + 16 + tables_bytes, mb.data(), boxes_bytes);
   CUDA_TRY(ctx, ctx->march_boxes.reserve(block_bytes));
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->march_boxes.ptr, block.data(), block_bytes,
-                                cudaMemcpyHostToDevice, ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->march_boxes.ptr, block, block_bytes, cudaMemcpyHostToDevice,
+                                ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->param_copied, ctx->stream));
   unsigned char* dev_block = ctx->march_boxes.as<unsigned char>();
   unsigned long long* counter = reinterpret_cast<unsigned long long*>(dev_block);
   unsigned* tile_counter = reinterpret_cast<unsigned*>(counter + 1);
@@ -1676,7 +1704,7 @@ namespace {
 int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers* layers,
                    const amrvr_camera* camera, const int* rank_order, int* region_begin,
                    int* region_end, float** piece_out, int64_t* exchanged_bytes,
-                   float* piece_dst = nullptr, bool peer = false) {
+                   float* piece_dst = nullptr, bool peer = false, const FoldBytes* bytes = nullptr) {
   const int P = ctx->nranks, me = ctx->rank;
   const int W = layers->width, H = layers->height;
   {
@@ -1836,7 +1864,8 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
   CUDA_TRY(ctx, ctx->fold_bins.reserve(std::max<size_t>(
                     fold_scratch_bytes(static_cast<int>(fold.size()), W, my_begin, my_end), 256)));
   LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
-                              my_begin, my_end, piece_dst, ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
+                              my_begin, my_end, piece_dst, ctx->fold_bins.ptr, ctx->stream, &ctx->launches,
+                              bytes));
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev[7], ctx->stream));
   if (region_begin) *region_begin = my_begin;
   if (region_end) *region_end = my_end;
@@ -2339,13 +2368,31 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   const size_t out_floats = static_cast<size_t>(W) * H * 5;
   if (ctx->rank == root) CUDA_TRY(ctx, ctx->full.reserve(render_floats * sizeof(float)));
   const bool fold_into_frame = ctx->nranks == 1;  // the piece IS the frame: no gather copy
+  // One rank, no antialiasing, nobody asks for the float frame: the fold's epilogue
+  // applies the overlay and writes the bytes itself (no 84 MB float frame at 2048^2
+  // written and read back).
+  const bool want_bytes_early = rgb8_host != nullptr || params->rgb8_on_device;
+  const bool fold_bytes = fold_into_frame && sqrt_aa == 1 && want_bytes_early && rgba5_host == nullptr;
+  FoldBytes fold_bytes_args{nullptr, H, nullptr};
+  if (fold_bytes) {
+    CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
+    fold_bytes_args.rgb8 = ctx->rgb8.as<uint8_t>();
+    if (params->draw_bounding_box && n > 0) {
+      OverlayEdges edges;
+      make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
+      CUDA_TRY(ctx, ctx->copy_jobs.reserve(sizeof(OverlayEdges)));
+      CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, &edges, sizeof(edges), cudaMemcpyHostToDevice,
+                                    ctx->stream));
+      fold_bytes_args.edges = ctx->copy_jobs.as<OverlayEdges>();
+    }
+  }
   if (peer) st = peer_barrier(ctx, 0);  // every rank's layers are complete and visible
   if (st == AMRVR_OK)
     st = composite_impl(ctx, scene, layers, camera, rank_order.data(), &begin, &end, &piece,
                         &exchanged,
                         fold_into_frame ? ctx->full.as<float>()
                                         : (peer ? static_cast<float*>(ctx->sym_piece.local) : nullptr),
-                        peer);
+                        peer, fold_bytes ? &fold_bytes_args : nullptr);
   if (st != AMRVR_OK) {
     amrvr_layers_free(ctx, layers);
     return st;
@@ -2431,7 +2478,9 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
                                     cudaMemcpyDeviceToHost, ctx->stream));
     if (want_bytes) {
       CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
-      if (fused_bytes) {
+      if (fold_bytes) {
+        // the fold already wrote overlay + bytes
+      } else if (fused_bytes) {
         // nobody reads the float frame: the overlay is applied on the way to the bytes
         const OverlayEdges* edges_dev = nullptr;
         if (params->draw_bounding_box && n > 0) {

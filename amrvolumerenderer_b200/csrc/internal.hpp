@@ -196,9 +196,17 @@ int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev,
                     bool count_samples, void* stream, int64_t* launches);
 // scratch: fold_scratch_bytes() of device memory (per-band layer lists)
 size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end);
+// Byte epilogue of the fold (one rank, bytes-only frame): overlay edges in device
+// memory (nullptr: no overlay), frame height, RGB8 frame (top row first).
+struct FoldBytes {
+  const OverlayEdges* edges;
+  int height;
+  uint8_t* rgb8;
+};
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int pixel_begin, int pixel_end, float* piece5, void* scratch,
-                void* stream, int64_t* launches);
+                void* stream, int64_t* launches,
+                const FoldBytes* bytes = nullptr);
 int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst,
                 void* stream, int64_t* launches);
 // Cross-GPU barrier on the stream: store `epoch` into slot `me` of every peer's

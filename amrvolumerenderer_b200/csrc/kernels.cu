@@ -664,6 +664,47 @@ __device__ __forceinline__ Px5 blend_depth_swap(const Px5& top, const Px5& botto
   return o;
 }
 
+// Wireframe overlay of one pixel (VolumeRenderer/VolumeRenderer.cpp:228-333, same
+// arithmetic as overlay_kernel) followed by the byte rule of Common/Color.hpp:66-91.
+__device__ __forceinline__ void overlay_and_quantise(int px, int py, float c0, float c1, float c2,
+                                                     const OverlayEdges* edges, float pixel_radius,
+                                                     unsigned char* out3) {
+  if (edges != nullptr) {
+    for (int e = 0; e < edges->count; ++e) {
+      if (px < edges->x0[e] || px > edges->x1[e] || py < edges->y0[e] || py > edges->y1[e]) continue;
+      float coverage;
+      if (edges->degenerate[e]) {
+        coverage = 1.0f;
+      } else {
+        const float ax = edges->ax[e], ay = edges->ay[e], bx = edges->bx[e], by = edges->by[e];
+        const float ex = bx - ax, ey = by - ay;
+        const float len_sq = ex * ex + ey * ey;
+        const float cx = static_cast<float>(px) + 0.5f, cy = static_cast<float>(py) + 0.5f;
+        const float apx = cx - ax, apy = cy - ay;
+        float t = (apx * ex + apy * ey) / len_sq;
+        t = (t < 0.0f) ? 0.0f : ((1.0f < t) ? 1.0f : t);
+        const float qx = ax + (bx - ax) * t, qy = ay + (by - ay) * t;
+        const float ddx = cx - qx, ddy = cy - qy;
+        const float dist = sqrtf(ddx * ddx + ddy * ddy);
+        coverage = (pixel_radius + 0.5f - dist) * 0.6f;
+        coverage = (coverage < 0.0f) ? 0.0f : ((1.0f < coverage) ? 1.0f : coverage);
+        if (coverage <= 0.0f) continue;
+      }
+      const float a = coverage;
+      const float s = 1.0f * a;
+      c0 = s + c0 * (1.0f - a);
+      c1 = s + c1 * (1.0f - a);
+      c2 = s + c2 * (1.0f - a);
+    }
+  }
+  const float c[3] = {c0, c1, c2};
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int v = static_cast<int>(c[k] * 256.f);
+    out3[k] = static_cast<unsigned char>((v < 0) ? 0 : ((v > 255) ? 255 : v));
+  }
+}
+
 constexpr int kFoldThreads = 256;
 constexpr int kFoldTileW = 32;   // one warp = 32 consecutive pixels of one row
 constexpr int kFoldBandRows = 8; // one CTA = 32 x 8 pixels; one band = 8 frame rows
@@ -798,15 +839,28 @@ fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row
 // accumulator -- DirectSendBase::composeLayered, per pixel
 // (DirectSendBase.cpp:400-446).  Fragments of other GPUs are read where they
 // were marched (peer memory over NVLink): the fold IS the exchange.
+// kBytes: the piece is the whole frame and nobody reads it as floats (one rank,
+// bytes-only frame), so the epilogue applies the overlay and the byte rule and
+// writes RGB8 rows (top row = y_max, SavePPM order) instead of 20 B per pixel
+// that a second kernel would read back.
+template <bool kBytes>
 __global__ void __launch_bounds__(kFoldThreads, 4)
 fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
                    const int* __restrict__ band_lists, const int* __restrict__ band_counts,
                    const int2* __restrict__ band_xspan,
                    int first_row, int width, int pixel_begin, int pixel_end,
-                   float* __restrict__ piece5) {
+                   float* __restrict__ piece5, const OverlayEdges* __restrict__ edges_ptr,
+                   int height, unsigned char* __restrict__ rgb8) {
   __shared__ FoldEntry s_list[kFoldThreads];
   __shared__ int s_warp_count[kFoldThreads / 32];
-  __shared__ float s_out[kFoldThreads * 5];
+  __shared__ __align__(16) float s_out[kFoldThreads * 5];
+  __shared__ OverlayEdges s_edges;
+  if (kBytes && edges_ptr != nullptr) {
+    const int words = sizeof(OverlayEdges) / 4;
+    for (int i = threadIdx.x; i < words; i += kFoldThreads)
+      reinterpret_cast<int*>(&s_edges)[i] = reinterpret_cast<const int*>(edges_ptr)[i];
+    __syncthreads();
+  }
 
   const int band = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -864,6 +918,24 @@ fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
     have_acc = true;
   }
   if (!have_acc) acc = Px5{0.f, 0.f, 0.f, 0.f, INFINITY};  // DirectSendBase.cpp:450-455
+  if (kBytes) {
+    unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_out);  // 96 B per warp
+    overlay_and_quantise(px, py, acc.r, acc.g, acc.b, edges_ptr != nullptr ? &s_edges : nullptr, 0.5f,
+                         s_bytes + threadIdx.x * 3);
+    __syncwarp();
+    if (py < height) {
+      unsigned char* row = rgb8 + 3 * (static_cast<size_t>(height - 1 - py) * width + tile_x0);
+      const int npx = min(width - tile_x0, kFoldTileW);  // pixels of this row segment
+      if ((width & 3) == 0) {
+        // tile_x0 is a multiple of 32 and the width of 4: whole aligned words
+        if (lane < (npx * 3) / 4)
+          reinterpret_cast<unsigned*>(row)[lane] = reinterpret_cast<const unsigned*>(s_bytes + warp * 96)[lane];
+      } else if (lane < npx) {
+        for (int k = 0; k < 3; ++k) row[lane * 3 + k] = s_bytes[threadIdx.x * 3 + k];
+      }
+    }
+    return;
+  }
   float* o = s_out + threadIdx.x * 5;
   o[0] = acc.r;
   o[1] = acc.g;
@@ -1043,43 +1115,9 @@ post_piece_kernel(const float* __restrict__ piece5, int pixel_begin, int pixel_e
   const bool live = p >= pixel_begin && p < pixel_end;
   if (live) {
     const float* b = piece5 + 5 * static_cast<size_t>(p - pixel_begin);
-    float c0 = b[0], c1 = b[1], c2 = b[2];
     const int px = p % width, py = p / width;
-    if (overlay) {
-      const OverlayEdges& edges = s_edges;
-      for (int e = 0; e < edges.count; ++e) {
-        if (px < edges.x0[e] || px > edges.x1[e] || py < edges.y0[e] || py > edges.y1[e]) continue;
-        float coverage;
-        if (edges.degenerate[e]) {
-          coverage = 1.0f;
-        } else {
-          const float ax = edges.ax[e], ay = edges.ay[e], bx = edges.bx[e], by = edges.by[e];
-          const float ex = bx - ax, ey = by - ay;
-          const float len_sq = ex * ex + ey * ey;
-          const float cx = static_cast<float>(px) + 0.5f, cy = static_cast<float>(py) + 0.5f;
-          const float apx = cx - ax, apy = cy - ay;
-          float t = (apx * ex + apy * ey) / len_sq;
-          t = (t < 0.0f) ? 0.0f : ((1.0f < t) ? 1.0f : t);
-          const float qx = ax + (bx - ax) * t, qy = ay + (by - ay) * t;
-          const float ddx = cx - qx, ddy = cy - qy;
-          const float dist = sqrtf(ddx * ddx + ddy * ddy);
-          coverage = (pixel_radius + 0.5f - dist) * 0.6f;
-          coverage = (coverage < 0.0f) ? 0.0f : ((1.0f < coverage) ? 1.0f : coverage);
-          if (coverage <= 0.0f) continue;
-        }
-        const float a = coverage;
-        const float s = 1.0f * a;
-        c0 = s + c0 * (1.0f - a);
-        c1 = s + c1 * (1.0f - a);
-        c2 = s + c2 * (1.0f - a);
-      }
-    }
-    const float c[3] = {c0, c1, c2};
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      const int v = static_cast<int>(c[k] * 256.f);
-      s_bytes[threadIdx.x * 3 + k] = static_cast<unsigned char>((v < 0) ? 0 : ((v > 255) ? 255 : v));
-    }
+    overlay_and_quantise(px, py, b[0], b[1], b[2], overlay ? &s_edges : nullptr, pixel_radius,
+                         s_bytes + threadIdx.x * 3);
   }
   __syncthreads();
   if ((width & 3) == 0) {
@@ -1395,7 +1433,7 @@ size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end
 
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int pixel_begin, int pixel_end, float* piece5, void* scratch, void* stream,
-                int64_t* launches) {
+                int64_t* launches, const FoldBytes* bytes) {
   const int npix = pixel_end - pixel_begin;
   if (npix <= 0) return 0;
   const int first_row = pixel_begin / width, last_row = (pixel_end - 1) / width;
@@ -1409,9 +1447,16 @@ int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return static_cast<int>(e);
   const dim3 grid((width + kFoldTileW - 1) / kFoldTileW, bands);
-  fold_layers_kernel<<<grid, kFoldThreads, 0, as_stream(stream)>>>(
-      layers_dev, nlayers, band_lists, band_counts, band_xspan, first_row, width, pixel_begin,
-      pixel_end, piece5);
+  if (bytes != nullptr && bytes->rgb8 != nullptr) {
+    if (pixel_begin != 0 || pixel_end != width * bytes->height) return static_cast<int>(cudaErrorInvalidValue);
+    fold_layers_kernel<true><<<grid, kFoldThreads, 0, as_stream(stream)>>>(
+        layers_dev, nlayers, band_lists, band_counts, band_xspan, first_row, width, pixel_begin,
+        pixel_end, nullptr, bytes->edges, bytes->height, bytes->rgb8);
+  } else {
+    fold_layers_kernel<false><<<grid, kFoldThreads, 0, as_stream(stream)>>>(
+        layers_dev, nlayers, band_lists, band_counts, band_xspan, first_row, width, pixel_begin,
+        pixel_end, piece5, nullptr, 0, nullptr);
+  }
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }

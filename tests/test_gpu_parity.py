@@ -203,11 +203,12 @@ def test_frame_ragged_width(ctx, oracle):
     _check_frame(ctx, oracle, scenes.scene_c2(box_cells=8), scenes.make_camera(), _params(101, 67))
 
 
-@pytest.mark.parametrize("w,h", [(128, 96), (101, 67)])
+@pytest.mark.parametrize("w,h", [(128, 96), (101, 67), (100, 50)])
 def test_frame_bytes_only_path(ctx, oracle, w, h):
-    """rgb8 without the float frame takes the fused overlay+quantise kernel (word
-    stores when width % 4 == 0, byte stores otherwise): same bytes as the float path
-    and as the oracle."""
+    """rgb8 without the float frame: on one rank the fold's own epilogue applies the
+    overlay and writes the bytes (word stores when width % 4 == 0, byte stores
+    otherwise; 100x50 ends in a 4-pixel tile and a 2-row band): same bytes as the
+    float path and as the oracle."""
     scene = scenes.scene_c2(box_cells=8)
     camera = scenes.make_camera()
     params = _params(w, h)
@@ -220,6 +221,22 @@ def test_frame_bytes_only_path(ctx, oracle, w, h):
     ref = oracle.render_frame(scene, camera, params)
     assert int(np.abs(only["rgb8"].astype(int) - ref["rgb8"].astype(int)).max()) <= 1
     ds.free()
+
+
+def test_frame_bytes_only_antialiased_and_empty(ctx, oracle):
+    """AA > 1 keeps the downsample -> fused overlay+bytes pass; an empty scene gives a black frame."""
+    scene = scenes.scene_c2(box_cells=8)
+    camera = scenes.make_camera()
+    params = _params(64, 48, aa=4)
+    ds = ctx.upload_scene(scene)
+    only = ctx.render_frame(ds, camera, params, want_rgba=False)
+    ref = oracle.render_frame(scene, camera, params)
+    assert int(np.abs(only["rgb8"].astype(int) - ref["rgb8"].astype(int)).max()) <= 1
+    ds.free()
+    empty = ctx.upload((api.Box * 1)(), 0, scenes.identity_transform(), (0.0, 1.0))
+    out = ctx.render_frame(empty, camera, _params(36, 20), want_rgba=False)
+    assert out["final5"] is None and np.all(out["rgb8"] == 0)
+    empty.free()
 
 
 def test_frame_empty_scene(ctx):
