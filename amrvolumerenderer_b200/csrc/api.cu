@@ -821,6 +821,15 @@ int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
     return AMRVR_OK;
   };
   bool group_copied = false;
+  const char* run_src = nullptr;  // pending run of adjacent dense copies
+  char* run_dst = nullptr;
+  size_t run_bytes = 0;
+  auto flush_run = [&]() -> int {
+    if (run_bytes > 0)
+      CUDA_TRY(ctx, cudaMemcpyAsync(run_dst, run_src, run_bytes, cudaMemcpyHostToDevice, ctx->copy));
+    run_bytes = 0;
+    return AMRVR_OK;
+  };
   for (size_t i = 0; i < items.size(); ++i) {
     const Item& it = items[i];
     const amrvr_box& B = boxes[it.box];
@@ -830,8 +839,19 @@ int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                           (B.lo[2] - B.begin[2]) * B.kstride + B.component * B.nstride;
       double* dst = reinterpret_cast<double*>(ctx->stage.as<char>() + it.stage_off);
       if (B.jstride == nx && B.kstride == static_cast<int64_t>(nx) * ny) {
-        CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, it.cells * sizeof(double), cudaMemcpyHostToDevice,
-                                      ctx->copy));
+        // dense FAB: merged with the copy before it when both ends are adjacent
+        // (FABs carved from one arena block travel as one DMA transfer)
+        const size_t bytes = it.cells * sizeof(double);
+        if (run_bytes > 0 && reinterpret_cast<const char*>(src) == run_src + run_bytes &&
+            reinterpret_cast<char*>(dst) == run_dst + run_bytes) {
+          run_bytes += bytes;
+        } else {
+          const int st = flush_run();
+          if (st != AMRVR_OK) return st;
+          run_src = reinterpret_cast<const char*>(src);
+          run_dst = reinterpret_cast<char*>(dst);
+          run_bytes = bytes;
+        }
       } else if (B.kstride % B.jstride == 0 && B.kstride / B.jstride >= ny) {
         // ghost cells or a sub-view: one 3-D pitched copy
         cudaMemcpy3DParms p{};
@@ -852,10 +872,15 @@ int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
     }
     max_cells = std::max(max_cells, it.cells);
     if (in_group >= group_bytes) {
-      const int st = flush(i + 1, group_copied);
+      int st = flush_run();
+      if (st == AMRVR_OK) st = flush(i + 1, group_copied);
       if (st != AMRVR_OK) return st;
       group_copied = false;
     }
+  }
+  {
+    const int st = flush_run();
+    if (st != AMRVR_OK) return st;
   }
   return flush(items.size(), group_copied);
 }

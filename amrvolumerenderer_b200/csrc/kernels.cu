@@ -666,11 +666,15 @@ __device__ __forceinline__ Px5 blend_depth_swap(const Px5& top, const Px5& botto
 
 // Wireframe overlay of one pixel (VolumeRenderer/VolumeRenderer.cpp:228-333, same
 // arithmetic as overlay_kernel) followed by the byte rule of Common/Color.hpp:66-91.
+// `candidates`: bit e set when edge e can reach this pixel (callers that know
+// nothing pass all ones); edges are visited in index order either way.
 __device__ __forceinline__ void overlay_and_quantise(int px, int py, float c0, float c1, float c2,
                                                      const OverlayEdges* edges, float pixel_radius,
-                                                     unsigned char* out3) {
+                                                     unsigned char* out3, unsigned candidates = ~0u) {
   if (edges != nullptr) {
-    for (int e = 0; e < edges->count; ++e) {
+    if (edges->count < 32) candidates &= (1u << edges->count) - 1u;
+    for (unsigned m = candidates; m != 0u; m &= m - 1u) {
+      const int e = __ffs(m) - 1;
       if (px < edges->x0[e] || px > edges->x1[e] || py < edges->y0[e] || py > edges->y1[e]) continue;
       float coverage;
       if (edges->degenerate[e]) {
@@ -920,8 +924,21 @@ fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
   if (!have_acc) acc = Px5{0.f, 0.f, 0.f, 0.f, INFINITY};  // DirectSendBase.cpp:450-455
   if (kBytes) {
     unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_out);  // 96 B per warp
+    // which of the (at most 12) wireframe edges can reach this 32x8 tile at all:
+    // most tiles see none, and the per-pixel loop then has nothing to visit
+    __shared__ unsigned s_edge_mask;
+    if (edges_ptr != nullptr) {
+      if (warp == 0) {
+        const bool reach = lane < s_edges.count && lane < 12 && !(x_last < s_edges.x0[lane] ||
+                           tile_x0 > s_edges.x1[lane] || y_last < s_edges.y0[lane] ||
+                           tile_y0 > s_edges.y1[lane]);
+        const unsigned mask = __ballot_sync(0xffffffffu, reach);
+        if (lane == 0) s_edge_mask = mask;
+      }
+      __syncthreads();
+    }
     overlay_and_quantise(px, py, acc.r, acc.g, acc.b, edges_ptr != nullptr ? &s_edges : nullptr, 0.5f,
-                         s_bytes + threadIdx.x * 3);
+                         s_bytes + threadIdx.x * 3, edges_ptr != nullptr ? s_edge_mask : 0u);
     __syncwarp();
     if (py < height) {
       unsigned char* row = rgb8 + 3 * (static_cast<size_t>(height - 1 - py) * width + tile_x0);

@@ -7,4 +7,4 @@ import json
 d=json.loads(open('gpurun_out/g_C4_n1.json').read().strip().splitlines()[-1])
 print('value',d['value'],'ms',d['ms_per_step'],'e2e',d['e2e'],'stage',d['config']['stage_ms'])
 PY
-AMRVR_TRACE=1 timeout 300 python bench.py --steps 3 --no-cpu-baseline 2>&1 >/dev/null | grep 'upload' | tail -4
+AMRVR_TRACE=1 timeout 300 python bench.py --steps 3 --no-cpu-baseline 2>&1 >/dev/null | grep 'amrvr trace' | tail -8 | cut -c1-260
