@@ -69,6 +69,8 @@ def _ncu_traffic(kernel_tag="march"):
     best = None
     for f in sorted((ROOT / "profiles").glob(f"r*_{kernel_tag}_v*_full.txt")):
         best = f
+    for f in sorted((ROOT / "profiles").glob(f"r*_{kernel_tag}_fold_current_full.txt")):
+        best = f  # the capture of the code as committed; its first block is the march
     if best is None:
         return None, None
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
