@@ -21,6 +21,76 @@ from amrvolumerenderer_b200 import engine, scenes  # noqa: E402
 from oracle.oracle import Oracle  # noqa: E402
 
 
+def check_input_side(rank, world):
+    """Plotfile boxes are dealt to ranks without loss or overlap, every rank reads
+    exactly its FABs, and convexify on each rank's share against the GLOBAL fine
+    BoxArray yields, over all ranks, the same uncovered cells as one rank does."""
+    import ctypes as C
+    import tempfile
+
+    from amrvolumerenderer_b200 import ctypes_api as api
+    from amrvolumerenderer_b200.plotfile import PlotFile, synthetic_hierarchy, write_plotfile
+    from oracle import amr_io_oracle as aio
+
+    lib = api.load_library()
+    levels, plo, phi = synthetic_hierarchy(base_cells=16, box_cells=4, nlevels=3, seed=5)
+    box = [None]
+    if rank == 0:
+        box[0] = str(write_plotfile(Path(tempfile.mkdtemp()) / "plt", levels, ("rho",), plo, phi,
+                                    fabs_per_file=7))
+    dist.broadcast_object_list(box, src=0)
+    P32 = C.POINTER(C.c_int32)
+    with PlotFile(box[0]) as pf:
+        nlev = pf.finest_level + 1
+        clev = (api.Level * nlev)()
+        keep, gboxes = [], []
+        for l in range(nlev):
+            allb = np.ascontiguousarray(pf.boxes(l))
+            gboxes.append(allb)
+            idx, off = pf.level_share(l, rank, world, rule=l % 2)
+            dst = np.empty(int(off[-1]))
+            pf.read_level(l, 0, dst, rank, world, rule=l % 2, threads=2)
+            shares = [None] * world
+            dist.all_gather_object(shares, idx.tolist())
+            assert sorted(b for sh in shares for b in sh) == list(range(len(allb)))
+            fabs = (api.Fab * max(len(idx), 1))()
+            for k, b in enumerate(idx):
+                want = levels[l].boxes[b][1][0]
+                assert np.array_equal(dst[off[k]:off[k + 1]].reshape(want.shape), want)
+                nx, ny, nz = (int(allb[b, 3 + d] - allb[b, d] + 1) for d in range(3))
+                f = fabs[k]
+                for d in range(3):
+                    f.lo[d], f.hi[d], f.begin[d] = int(allb[b, d]), int(allb[b, 3 + d]), int(allb[b, d])
+                f.data = dst.ctypes.data + int(off[k]) * 8
+                f.jstride, f.kstride, f.nstride = nx, nx * ny, nx * ny * nz
+            keep += [dst, fabs]
+            clev[l].nfabs, clev[l].fabs = len(idx), fabs
+        ratios = (C.c_int32 * 3 * (nlev - 1))()
+        for l in range(nlev - 1):
+            for d in range(3):
+                ratios[l][d] = 2
+        ptrs = (P32 * nlev)(*[g.ctypes.data_as(P32) for g in gboxes])
+        counts_in = (C.c_int32 * nlev)(*[len(g) for g in gboxes])
+        out = (api.Fab * 4096)()
+        counts = (C.c_int32 * nlev)()
+        assert lib.amrvr_convexify_levels(nlev, clev, ptrs, counts_in, ratios, out, 4096, counts) == 0
+        mine, base = [], 0
+        for l in range(nlev):
+            mine.append([[out[base + k].lo[d] for d in range(3)] + [out[base + k].hi[d] for d in range(3)]
+                         for k in range(counts[l])])
+            base += counts[l]
+        everyone = [None] * world
+        dist.all_gather_object(everyone, mine)
+        for l in range(nlev):
+            meta = pf.level(l)
+            domain = tuple(meta.domain_lo) + tuple(meta.domain_hi)
+            pieces = [p for r in everyone for p in r[l]]
+            got, most = aio.pieces_mask(domain, pieces)
+            fine = [tuple(b) for b in gboxes[l + 1]] if l + 1 < nlev else []
+            want = aio.uncovered_mask(domain, [tuple(b) for b in gboxes[l]], fine, (2, 2, 2))
+            assert most <= 1 and np.array_equal(got, want), (rank, l)
+
+
 def main():
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
@@ -64,6 +134,7 @@ def main():
         covered = sorted(spans)
         assert covered[0][0] == 0 and covered[-1][1] == w * h
         assert all(a[1] == c[0] for a, c in zip(covered, covered[1:]))
+    check_input_side(rank, world)
     dist.barrier()
     if rank == 0:
         print("mp_cpu_worker OK", flush=True)
