@@ -569,6 +569,59 @@ void order_box_depth_range(const OrderMatrices& m, OrderBox& b) {
   b.max_depth = zmax;
 }
 
+// All boxes of the table.  On x86 the eight corners of a box go through the two
+// matrices four at a time (SSE2): every lane performs the scalar code's
+// operations in the scalar code's order (no contraction, zeros included), so
+// each corner's z is bit-identical; only the min/max reduction is re-associated,
+// which cannot change a finite or infinite result.
+void order_box_depth_ranges(const OrderMatrices& m, OrderBox* boxes, int n) {
+#if defined(__x86_64__) && defined(__GNUC__)
+  const __m128 zero = _mm_setzero_ps(), one = _mm_set1_ps(1.0f);
+  const __m128 inf = _mm_set1_ps(INFINITY), ninf = _mm_set1_ps(-INFINITY);
+  for (int i = 0; i < n; ++i) {
+    OrderBox& b = boxes[i];
+    const __m128 X = _mm_setr_ps(b.lo[0], b.hi[0], b.lo[0], b.hi[0]);  // corners c = 0..3 (and 4..7)
+    const __m128 Y = _mm_setr_ps(b.lo[1], b.lo[1], b.hi[1], b.hi[1]);
+    const __m128 Z[2] = {_mm_set1_ps(b.lo[2]), _mm_set1_ps(b.hi[2])};
+    __m128 txy[4];
+    for (int r = 0; r < 4; ++r)
+      txy[r] = _mm_add_ps(_mm_add_ps(zero, _mm_mul_ps(_mm_set1_ps(m.view[r * 4 + 0]), X)),
+                          _mm_mul_ps(_mm_set1_ps(m.view[r * 4 + 1]), Y));
+    __m128 lo_acc = inf, hi_acc = ninf;
+    for (int half = 0; half < 2; ++half) {
+      __m128 e[4];
+      for (int r = 0; r < 4; ++r)
+        e[r] = _mm_add_ps(_mm_add_ps(txy[r], _mm_mul_ps(_mm_set1_ps(m.view[r * 4 + 2]), Z[half])),
+                          _mm_mul_ps(_mm_set1_ps(m.view[r * 4 + 3]), one));
+      __m128 clip[2];
+      for (int r = 2; r < 4; ++r) {
+        __m128 sum = zero;
+        for (int k = 0; k < 4; ++k) sum = _mm_add_ps(sum, _mm_mul_ps(_mm_set1_ps(m.proj[r * 4 + k]), e[k]));
+        clip[r - 2] = sum;
+      }
+      const __m128 z = _mm_div_ps(clip[0], clip[1]);
+      const __m128 use = _mm_cmpneq_ps(clip[1], zero);  // clip.w != 0 (true for NaN, as in C++)
+      const __m128 lo_new = _mm_min_ps(z, lo_acc), hi_new = _mm_max_ps(z, hi_acc);
+      lo_acc = _mm_or_ps(_mm_and_ps(use, lo_new), _mm_andnot_ps(use, lo_acc));
+      hi_acc = _mm_or_ps(_mm_and_ps(use, hi_new), _mm_andnot_ps(use, hi_acc));
+    }
+    float lo4[4], hi4[4];
+    _mm_storeu_ps(lo4, lo_acc);
+    _mm_storeu_ps(hi4, hi_acc);
+    float zmin = INFINITY, zmax = -INFINITY;
+    for (int k = 0; k < 4; ++k) {
+      zmin = fmin2(zmin, lo4[k]);
+      zmax = fmax2(zmax, hi4[k]);
+    }
+    if (!std::isfinite(zmin) || !std::isfinite(zmax)) zmin = zmax = INFINITY;
+    b.min_depth = zmin;
+    b.max_depth = zmax;
+  }
+#else
+  for (int i = 0; i < n; ++i) order_box_depth_range(m, boxes[i]);
+#endif
+}
+
 namespace {
 
 // Common/VisibilityOrdering.cpp:211-228
@@ -822,8 +875,9 @@ void build_graph(int n, std::vector<OrderEdge>& edges, Graph& g) {
   if (!std::is_sorted(edges.begin(), edges.end(), by_pair)) {
     // the host pair test emits edges in order; the device kernel appends them as
     // its threads find them.  Bucket by i (counting sort), then order each
-    // bucket -- a box has a handful of neighbours -- by (j, axis).
-    thread_local std::vector<int> head;
+    // bucket -- a box has a handful of neighbours -- by (j, axis) with an
+    // insertion sort.
+    thread_local std::vector<int> head, at;
     thread_local std::vector<OrderEdge> sorted;
     bool in_range = true;
     for (const OrderEdge& e : edges) in_range = in_range && e.i >= 0 && e.i < n;
@@ -831,12 +885,18 @@ void build_graph(int n, std::vector<OrderEdge>& edges, Graph& g) {
       head.assign(static_cast<size_t>(n) + 1, 0);
       for (const OrderEdge& e : edges) ++head[static_cast<size_t>(e.i) + 1];
       for (int v = 0; v < n; ++v) head[v + 1] += head[v];
+      at.assign(head.begin(), head.end() - 1);
       sorted.resize(edges.size());
-      {
-        std::vector<int> at(head.begin(), head.end() - 1);
-        for (const OrderEdge& e : edges) sorted[at[e.i]++] = e;
+      for (const OrderEdge& e : edges) {
+        // insert into the filled part of bucket e.i, keeping it ordered
+        const int first = head[e.i];
+        int pos = at[e.i]++;
+        while (pos > first && by_pair(e, sorted[pos - 1])) {
+          sorted[pos] = sorted[pos - 1];
+          --pos;
+        }
+        sorted[pos] = e;
       }
-      for (int v = 0; v < n; ++v) std::sort(sorted.begin() + head[v], sorted.begin() + head[v + 1], by_pair);
       edges.swap(sorted);
     } else {
       std::sort(edges.begin(), edges.end(), by_pair);
@@ -1036,8 +1096,8 @@ bool order_ranks(int nranks, int nglobal, const amrvr_box_record* recs,
       boxes[i].hi[d] = static_cast<float>(recs[i].max_corner[d]);
     }
     boxes[i].owner = recs[i].owner;
-    order_box_depth_range(m, boxes[i]);
   }
+  order_box_depth_ranges(m, boxes.data(), nglobal);
 
   const int max_rounds = std::max(nglobal, 1) * 8 + 32;  // :565-566
   std::vector<OrderEdge> edges;

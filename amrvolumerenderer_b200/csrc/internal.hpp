@@ -58,6 +58,7 @@ struct OrderMatrices {
 };
 void make_order_matrices(const amrvr_camera& cam, float aspect, OrderMatrices& m);
 void order_box_depth_range(const OrderMatrices& m, OrderBox& b);
+void order_box_depth_ranges(const OrderMatrices& m, OrderBox* boxes, int n);  // same values, whole table
 
 // One directed "in front of" relation found by the pair test, tagged with the
 // moment the reference would have inserted it (pair (i,j), i<j, axis).
