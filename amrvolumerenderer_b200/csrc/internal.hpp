@@ -186,11 +186,6 @@ int launch_brick_histogram(const double* data, int64_t jstride, int64_t kstride,
 int launch_brick_quantise_batch(const QuantJob* jobs_dev, int njobs, long long max_cells,
                                 const amrvr_scalar_transform& t, float range_min, float range_max,
                                 void* stream, int64_t* launches);
-int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride,
-                          int nx, int ny, int nz,
-                          const amrvr_scalar_transform& t, float range_min,
-                          float range_max, uint8_t* brick, void* stream,
-                          int64_t* launches);
 int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev,
                     const uint8_t* bricks, const float* tables, float* layers,
                     unsigned long long* sample_counter, unsigned* tile_counter /*zeroed*/,

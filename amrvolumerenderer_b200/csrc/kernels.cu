@@ -4,7 +4,7 @@
 // Division and sqrt stay IEEE (-prec-div/-prec-sqrt defaults, no fast-math).
 //
 //   brick_stats_kernel      K2  min / max / min-positive / finite count (HBM: 8 B/cell)
-//   brick_quantise_kernel   K5  FAB double -> colour-table index byte  (HBM: 9 B/cell)
+//   brick_quantise_batch_kernel K5  FAB doubles -> colour-table index bytes (HBM: 9 B/cell)
 //   raymarch_bricks_kernel  K1  all (box, 16x16 pixel tile) pairs of a rank, one launch
 //   fold_layers_kernel      K6  per-pixel run-structured depth-swap 'over'
 //   pack_slices_kernel      C6  gather row slices into per-destination send buffers
@@ -76,40 +76,10 @@ __device__ __forceinline__ unsigned char cell_to_index(double raw, const ValuePa
   return static_cast<unsigned char>(idx);
 }
 
-__global__ void __launch_bounds__(256)
-brick_quantise_kernel(const double* __restrict__ data, long long jstride, long long kstride,
-                      int nx, int ny, int nz, ValuePath p, unsigned char* __restrict__ brick) {
-  // one thread per 4 consecutive cells of a row; rows are nx cells, i fastest
-  const int quads_per_row = (nx + 3) >> 2;
-  const long long nquads = static_cast<long long>(quads_per_row) * ny * nz;
-  for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < nquads;
-       q += static_cast<long long>(gridDim.x) * blockDim.x) {
-    const int qi = static_cast<int>(q % quads_per_row);
-    const long long row = q / quads_per_row;
-    const int j = static_cast<int>(row % ny);
-    const int k = static_cast<int>(row / ny);
-    const double* src = data + j * jstride + k * kstride + 4 * qi;
-    unsigned char* dst = brick + (static_cast<long long>(k) * ny + j) * nx + 4 * qi;
-    const int left = nx - 4 * qi;
-    if (left >= 4 && ((reinterpret_cast<uintptr_t>(src) & 15) == 0) &&
-        ((reinterpret_cast<uintptr_t>(dst) & 3) == 0)) {
-      const double2 a = __ldcs(reinterpret_cast<const double2*>(src));
-      const double2 b = __ldcs(reinterpret_cast<const double2*>(src) + 1);
-      uchar4 o;
-      o.x = cell_to_index(a.x, p);
-      o.y = cell_to_index(a.y, p);
-      o.z = cell_to_index(b.x, p);
-      o.w = cell_to_index(b.y, p);
-      *reinterpret_cast<uchar4*>(dst) = o;
-    } else {
-      for (int c = 0; c < left && c < 4; ++c) dst[c] = cell_to_index(src[c], p);
-    }
-  }
-}
-
-// Same cells, several bricks per launch: blockIdx.y picks the job.  A 64^3 brick
-// is 2 MB -- alone it cannot fill the machine for longer than a launch takes, so
-// the upload path quantises a whole group of freshly copied FABs at once.
+// One thread per 4 consecutive cells of a row (rows are nx cells, i fastest);
+// blockIdx.y picks the brick.  A 64^3 brick is 2 MB -- alone it cannot fill the
+// machine for longer than a launch takes, so the upload path quantises a whole
+// group of freshly copied FABs with one launch.
 __global__ void __launch_bounds__(256)
 brick_quantise_batch_kernel(const QuantJob* __restrict__ jobs, ValuePath p) {
   const QuantJob J = jobs[blockIdx.y];
@@ -1369,19 +1339,6 @@ int launch_brick_histogram(const double* data, int64_t jstride, int64_t kstride,
 int launch_brick_stats_final(const double* partials, int nparts, double* out4, void* stream,
                              int64_t* launches) {
   brick_stats_final_kernel<<<1, 256, 0, as_stream(stream)>>>(partials, nparts, out4);
-  ++*launches;
-  return static_cast<int>(cudaGetLastError());
-}
-
-int launch_brick_quantise(const double* data, int64_t jstride, int64_t kstride, int nx, int ny,
-                          int nz, const amrvr_scalar_transform& t, float range_min,
-                          float range_max, uint8_t* brick, void* stream, int64_t* launches) {
-  const long long nquads = static_cast<long long>((nx + 3) / 4) * ny * nz;
-  if (nquads <= 0) return 0;
-  long long blocks = (nquads + 255) / 256;
-  if (blocks > 148LL * 32) blocks = 148LL * 32;
-  brick_quantise_kernel<<<static_cast<unsigned>(blocks), 256, 0, as_stream(stream)>>>(
-      data, jstride, kstride, nx, ny, nz, make_value_path(t, range_min, range_max), brick);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }
