@@ -253,3 +253,54 @@ def test_render_argument_errors(tmp_path):
             render(p, **kwargs)
     with pytest.raises(RuntimeError, match="plotfile path is required"):
         render("")
+
+
+def test_image_writers_round_trip(tmp_path, capsys):
+    """PPM as Common/SavePPM.cpp lays it out, PNG readable by a plain zlib decoder,
+    unknown extensions fall back to PPM with the reference's warning (VolumeRenderer.cpp:1316-1328)."""
+    import struct
+    import zlib
+
+    from amrvolumerenderer_b200.render import save_image
+    from oracle.oracle import read_ppm
+
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, (37, 53, 3), dtype=np.uint8)
+    save_image(tmp_path / "a.ppm", img)
+    assert np.array_equal(read_ppm(tmp_path / "a.ppm"), img)
+    save_image(tmp_path / "b.PNG", img)
+    raw = (tmp_path / "b.PNG").read_bytes()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat = 8, b""
+    while pos < len(raw):
+        n, tag = struct.unpack(">I4s", raw[pos:pos + 8])
+        body = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(tag + body)
+        if tag == b"IHDR":
+            assert struct.unpack(">IIBBBBB", body) == (53, 37, 8, 2, 0, 0, 0)
+        if tag == b"IDAT":
+            idat += body
+        pos += 12 + n
+    rows = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(37, 1 + 3 * 53)
+    assert not rows[:, 0].any() and np.array_equal(rows[:, 1:].reshape(37, 53, 3), img)
+    save_image(tmp_path / "c.jpeg", img)
+    assert "unrecognized image extension '.jpeg'" in capsys.readouterr().err
+    assert np.array_equal(read_ppm(tmp_path / "c.jpeg"), img)
+
+
+def test_convexify_three_levels_is_a_partition_of_the_domain(lib):
+    """After convexify every point of the coarsest domain is covered by exactly one level's pieces."""
+    levels, plo, phi = synthetic_hierarchy(base_cells=16, box_cells=4, nlevels=3, seed=2)
+    boxes = [[tuple(lo) + tuple(lo[d] + 3 for d in range(3)) for lo, _ in L.boxes] for L in levels]
+    fine_domain = (0, 0, 0, 63, 63, 63)
+    covered = np.zeros((64, 64, 64), np.int32)
+    for l in range(3):
+        if l < 2:
+            pieces, _src = _convexify(lib, boxes[l], boxes[l + 1], (2, 2, 2))
+        else:
+            pieces = np.array(boxes[l], np.int32)
+        scale = 4 >> l  # level-l cell = scale^3 finest cells
+        for p in pieces:
+            covered[p[2] * scale:(p[5] + 1) * scale, p[1] * scale:(p[4] + 1) * scale,
+                    p[0] * scale:(p[3] + 1) * scale] += 1
+    assert covered.min() == 1 and covered.max() == 1, fine_domain
