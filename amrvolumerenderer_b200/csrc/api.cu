@@ -1482,9 +1482,8 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
   frame.nboxes = n;
 
   L->global_rects.resize(scene->global.size());
-  for (size_t g = 0; g < scene->global.size(); ++g)
-    L->global_rects[g] = box_footprint(scene->global[g].min_corner, scene->global[g].max_corner,
-                                       scene->global[g].dims, basis, *camera, width, height);
+  box_footprints(static_cast<int>(scene->global.size()), scene->global.data(), basis, *camera, width,
+                 height, L->global_rects.data());
   const float alpha_scale = std::min(std::max(1.0f - box_transparency, 0.0f), 1.0f);
   if (scene->march_const.size() != static_cast<size_t>(n)) {
     std::vector<MarchBox>& mc = const_cast<amrvr_scene*>(scene)->march_const;

@@ -427,15 +427,35 @@ float reference_sample_distance(int nglobal, const amrvr_box_record* recs,
 // ---------------------------------------------------------------------------
 // Screen footprint
 // ---------------------------------------------------------------------------
+namespace {
+Rect footprint_core(const double* min_corner, const double* max_corner, const int32_t* dims,
+                    const CameraBasis& basis, double tan_half, double aspect, int width, int height);
+}  // namespace
+
 Rect box_footprint(const double* min_corner, const double* max_corner,
                    const int32_t* dims, const CameraBasis& basis,
                    const amrvr_camera& cam, int width, int height) {
+  const float aspect_f = static_cast<float>(width) / static_cast<float>(std::max(height, 1));
+  const double tan_half = std::tan(cam.fov_y_degrees * 0.5f * kPiF / 180.0f);
+  return footprint_core(min_corner, max_corner, dims, basis, tan_half, aspect_f, width, height);
+}
+
+// Footprints of a whole box table: the camera constants are evaluated once.
+void box_footprints(int n, const amrvr_box_record* recs, const CameraBasis& basis,
+                    const amrvr_camera& cam, int width, int height, Rect* out) {
+  const float aspect_f = static_cast<float>(width) / static_cast<float>(std::max(height, 1));
+  const double tan_half = std::tan(cam.fov_y_degrees * 0.5f * kPiF / 180.0f);
+  for (int g = 0; g < n; ++g)
+    out[g] = footprint_core(recs[g].min_corner, recs[g].max_corner, recs[g].dims, basis, tan_half,
+                            aspect_f, width, height);
+}
+
+namespace {
+Rect footprint_core(const double* min_corner, const double* max_corner, const int32_t* dims,
+                    const CameraBasis& basis, double tan_half, double aspect, int width, int height) {
   Rect full{0, 0, (width + 3) & ~3, height};
   if (dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 || width <= 0 || height <= 0)
     return Rect{0, 0, 0, 0};
-  const float aspect_f = static_cast<float>(width) / static_cast<float>(std::max(height, 1));
-  const double tan_half = std::tan(cam.fov_y_degrees * 0.5f * kPiF / 180.0f);
-  const double aspect = aspect_f;
   // the march sees float-truncated corners and a float eye
   double lo[3], hi[3], eye[3];
   double diag2 = 0.0;
@@ -490,6 +510,7 @@ Rect box_footprint(const double* min_corner, const double* max_corner,
   r.h = static_cast<int32_t>(y_hi - y_lo + 1);
   return r;
 }
+}  // namespace
 
 // ---------------------------------------------------------------------------
 // Visibility ordering

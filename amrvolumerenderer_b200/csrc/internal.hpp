@@ -99,6 +99,8 @@ struct Rect {
 Rect box_footprint(const double* min_corner, const double* max_corner,
                    const int32_t* dims, const CameraBasis& basis,
                    const amrvr_camera& cam, int width, int height);
+void box_footprints(int n, const amrvr_box_record* recs, const CameraBasis& basis,
+                    const amrvr_camera& cam, int width, int height, Rect* out);
 
 // Wireframe overlay geometry (reference: VolumeRenderer.cpp:139-335): projected
 // corners of the tight bounds; the per-pixel coverage runs in a kernel.
