@@ -3,16 +3,23 @@
 // index and blend arithmetic must round the same way.
 // Division and sqrt stay IEEE (-prec-div/-prec-sqrt defaults, no fast-math).
 //
-//   brick_stats_kernel      K2  min / max / min-positive / finite count (HBM: 8 B/cell)
-//   brick_quantise_batch_kernel K5  FAB doubles -> colour-table index bytes (HBM: 9 B/cell)
-//   raymarch_bricks_kernel  K1  all (box, 16x16 pixel tile) pairs of a rank, one launch
-//   fold_layers_kernel      K6  per-pixel run-structured depth-swap 'over'
-//   pack_slices_kernel      C6  gather row slices into per-destination send buffers
-//   downsample_kernel       K8  box filter
-//   overlay_kernel               wireframe coverage
-//   quantize_rgb8_kernel         float -> byte, rows flipped
-//   order_rank_kernel       K7  single-CTA LSD radix sort of box depth keys
-//   order_pairs_kernel      K7  all-pairs face-adjacency test
+//   brick_stats_kernel          K2  min / max / min-positive / finite count (HBM: 8 B/cell)
+//   brick_histogram_kernel      f4  histogram of the transformed scalar (HBM: 8 B/cell)
+//   brick_quantise_batch_kernel K5  FAB doubles -> colour-table index bytes, a group of
+//                                   bricks per launch (HBM: 9 B/cell)
+//   raymarch_bricks_kernel      K1  all (box, 16x16 pixel tile) pairs of a rank, one launch,
+//                                   persistent CTAs pulling tiles from a counter
+//   fold_bin_kernel             K6  per 8-row band: the ordered list of layers touching it
+//   fold_layers_kernel          K6  per-pixel run-structured depth-swap 'over'; reads peer
+//                                   GPUs' fragments over NVLink; <true>: overlay + RGB8 epilogue
+//   pack_slices_kernel          C6  row slices into per-destination send buffers (NCCL path)
+//   peer_barrier_kernel             flag barrier across the GPUs of one box, with time-out
+//   post_piece_kernel               overlay + bytes of a piece into the root's RGB8 frame
+//   downsample_kernel           K8  box filter
+//   overlay_kernel                  wireframe coverage on the float frame
+//   quantize_rgb8_kernel            float -> byte, rows flipped
+//   order_rank_kernel           K7  single-CTA LSD radix sort of box depth keys
+//   order_pairs_kernel          K7  all-pairs face-adjacency test
 #include <cuda_runtime.h>
 
 #include <algorithm>
