@@ -277,6 +277,61 @@ def load_plotfile_geometry(ctx: Context, plotfile_path, variable="", min_level=0
     return scene
 
 
+def resolve_scalar_options(summary, log_scale, scalar_range, color_map):
+    """The scalar part of VolumeRenderer::run after the scene is loaded
+    (VolumeRenderer.cpp:1478-1555): processed range check, scalar-range override
+    (SetSceneNormalizationRange, SceneBuilder.cpp:427-443) and the colour map
+    converted from physical to normalised scalar values.  Pure host arithmetic in
+    the reference's float/double types.  Returns (transform, (range_min,
+    range_max), colour-map points or None); `summary.transform` is updated in
+    place when the override applies."""
+    has_override = scalar_range is not None
+    pmin, pmax = _f32(summary.processed_range[0]), _f32(summary.processed_range[1])
+    span = _f32(np.float32(pmax) - np.float32(pmin))
+    if not (span > 0.0) or not math.isfinite(span):
+        raise RuntimeError("Failed to establish a finite scalar range for color mapping.")
+
+    def to_processed(value: float) -> np.float32:  # VolumeRenderer.cpp:1490-1504
+        value = np.float32(value)
+        if not np.isfinite(value):
+            raise ValueError("color_map scalar values must be finite.")
+        if log_scale:
+            if not (value > 0.0):
+                raise ValueError("color_map scalar values must be positive when log scaling "
+                                 "is enabled.")
+            return np.float32(math.log(float(value)))
+        return value
+
+    norm_min, norm_max = np.float32(pmin), np.float32(pmax)
+    transform = summary.transform
+    value_range = (float(summary.scalar_range[0]), float(summary.scalar_range[1]))
+    if has_override:
+        norm_min, norm_max = to_processed(scalar_range[0]), to_processed(scalar_range[1])
+        if not (norm_min < norm_max):
+            raise ValueError("scalar_range must contain two values with min < max.")
+    norm_span = np.float32(norm_max - norm_min)
+    if not (norm_span > 0.0) or not np.isfinite(norm_span):
+        raise RuntimeError("Failed to establish a finite scalar range for color mapping.")
+    if has_override:  # SetSceneNormalizationRange, SceneBuilder.cpp:427-443
+        dmin, dmax = float(norm_min), float(norm_max)
+        transform.normalize_to_unit_range = 1
+        transform.normalization_min = dmin
+        transform.normalization_max = dmax
+        transform.inverse_normalization_span = 1.0 / (dmax - dmin)
+        value_range = (0.0, 1.0)
+
+    points = None
+    if color_map is not None:  # VolumeRenderer.cpp:1543-1555
+        points = []
+        for p in color_map:
+            t = np.float32((to_processed(p[0]) - norm_min) / norm_span)
+            if not np.isfinite(t):
+                raise ValueError("color_map produced a non-finite normalized scalar value.")
+            points.append((float(min(max(t, np.float32(0.0)), np.float32(1.0))),
+                           *[float(c) for c in p[1:]]))
+    return transform, value_range, points
+
+
 # ------------------------------------------------------------------- render()
 def render(plotfile, width=512, height=512, box_transparency=0.0, antialiasing=1,
            visibility_graph=True, write_visibility_graph=False, variable=None, min_level=0,
@@ -330,49 +385,8 @@ def render(plotfile, width=512, height=512, box_transparency=0.0, antialiasing=1
         scene = load_plotfile_geometry(ctx, str(plotfile), variable or "", min_level, max_level,
                                        log_scale, normalize_to_data_range=not has_override)
         summary = scene.summary
-        pmin, pmax = _f32(summary.processed_range[0]), _f32(summary.processed_range[1])
-        span = _f32(np.float32(pmax) - np.float32(pmin))
-        if not (span > 0.0) or not math.isfinite(span):
-            raise RuntimeError("Failed to establish a finite scalar range for color mapping.")
-
-        def to_processed(value: float) -> np.float32:  # VolumeRenderer.cpp:1490-1504
-            value = np.float32(value)
-            if not np.isfinite(value):
-                raise ValueError("color_map scalar values must be finite.")
-            if log_scale:
-                if not (value > 0.0):
-                    raise ValueError("color_map scalar values must be positive when log scaling "
-                                     "is enabled.")
-                return np.float32(math.log(float(value)))
-            return value
-
-        norm_min, norm_max = np.float32(pmin), np.float32(pmax)
-        transform = summary.transform
-        value_range = (float(summary.scalar_range[0]), float(summary.scalar_range[1]))
-        if has_override:
-            norm_min, norm_max = to_processed(scalar_range[0]), to_processed(scalar_range[1])
-            if not (norm_min < norm_max):
-                raise ValueError("scalar_range must contain two values with min < max.")
-        norm_span = np.float32(norm_max - norm_min)
-        if not (norm_span > 0.0) or not np.isfinite(norm_span):
-            raise RuntimeError("Failed to establish a finite scalar range for color mapping.")
-        if has_override:  # SetSceneNormalizationRange, SceneBuilder.cpp:427-443
-            dmin, dmax = float(norm_min), float(norm_max)
-            transform.normalize_to_unit_range = 1
-            transform.normalization_min = dmin
-            transform.normalization_max = dmax
-            transform.inverse_normalization_span = 1.0 / (dmax - dmin)
-            value_range = (0.0, 1.0)
-
-        points = None
-        if color_map is not None:  # VolumeRenderer.cpp:1543-1555
-            points = []
-            for p in color_map:
-                t = np.float32((to_processed(p[0]) - norm_min) / norm_span)
-                if not np.isfinite(t):
-                    raise ValueError("color_map produced a non-finite normalized scalar value.")
-                points.append((float(min(max(t, np.float32(0.0)), np.float32(1.0))),
-                               *[float(c) for c in p[1:]]))
+        transform, value_range, points = resolve_scalar_options(summary, log_scale, scalar_range,
+                                                                color_map)
 
         if camera is None:  # renderScene without a camera, VolumeRenderer.cpp:975-1030
             camera = api.Camera()

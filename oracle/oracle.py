@@ -352,6 +352,51 @@ class Ref(_Base):
                 "scalar_range": (rmin.value, rmax.value), "bounds_min": list(bmin),
                 "bounds_max": list(bmax), "processed_range": tuple(proc), "original_range": tuple(orig)}
 
+    def register_plotfile(self, path, levels, names):
+        """Hand the CONTENT of a plotfile (list of amrvolumerenderer_b200.plotfile.
+        LevelSpec + variable names; prob_lo = 0) to the shim's PlotFileData under
+        `path`, so the reference's own loadPlotFileGeometry / run() can read it."""
+        ncomp = len(names)
+        clev = (RefLevel * max(len(levels), 1))()
+        keep = []
+        for li, L in enumerate(levels):
+            n = len(L.boxes)
+            lo = (C.c_int32 * max(3 * n, 1))()
+            hi = (C.c_int32 * max(3 * n, 1))()
+            owner = (C.c_int32 * max(n, 1))()
+            data = (C.c_void_p * max(n, 1))()
+            for i, (blo, arr) in enumerate(L.boxes):
+                arr = np.ascontiguousarray(arr if arr.ndim == 4 else arr[None], np.float64)
+                nz, ny, nx = arr.shape[1:]
+                for d, ext in enumerate((nx, ny, nz)):
+                    lo[3 * i + d] = int(blo[d])
+                    hi[3 * i + d] = int(blo[d] + ext - 1)
+                keep.append(arr)
+                data[i] = arr.ctypes.data
+            for d in range(3):
+                clev[li].prob_lo[d] = 0.0
+                clev[li].cell_size[d] = float(L.cell_size[d])
+            clev[li].nboxes, clev[li].ncomp = n, ncomp
+            clev[li].lo, clev[li].hi, clev[li].owner, clev[li].data = lo, hi, owner, data
+            keep += [lo, hi, owner, data]
+        cnames = (C.c_char_p * ncomp)(*[n.encode() for n in names])
+        self._check(self.lib.ref_register_plotfile(str(path).encode(), len(levels), clev, ncomp, cnames))
+
+    def run(self, plotfile, output, params, nranks=1, variable=None, min_level=0, max_level=-1,
+            log_scale=False, up_vector=None, scalar_range=None, camera=None, colormap=None):
+        """The reference's own VolumeRenderer::run(RunOptions) over a registered
+        plotfile -> image at `output`; returns its captured log.  Raises
+        AmrvrError with the reference's message (status 1 = std::invalid_argument)."""
+        log = C.create_string_buffer(1 << 16)
+        pts, npts = self._cmap(colormap)
+        sr = (C.c_float * 2)(*scalar_range) if scalar_range is not None else None
+        self._check(self.lib.ref_run(
+            int(nranks), str(plotfile).encode(), C.byref(params), str(output).encode(),
+            variable.encode() if variable else None, int(min_level), int(max_level),
+            int(bool(log_scale)), _d3(up_vector) if up_vector is not None else None, sr,
+            C.byref(camera) if camera is not None else None, pts, npts, log, len(log)))
+        return log.value.decode()
+
     def scene_histogram(self, built, bin_count):
         """The real detail::ComputeSceneHistogram on the scene build_scene returned."""
         counts = np.zeros(max(int(bin_count), 1), np.uint64)

@@ -261,6 +261,83 @@ int ref_render_scene(int nranks, int nboxes, const amrvr_box* boxes,
   });
 }
 
+// Registers the content of a plotfile under `path` for the shim's PlotFileData
+// (oracle/shim/amrex_shim.hpp); owners in `levels` are ignored -- get() deals
+// boxes to thread-ranks itself.
+int ref_register_plotfile(const char* path, int nlevels, const ref_level* levels,
+                          int nnames, const char* const* names) {
+  return guarded([&] {
+    amrex::shim::PlotContent content;
+    for (int c = 0; c < nnames; ++c) content.names.push_back(names[c]);
+    for (int l = 0; l < nlevels; ++l) {
+      const ref_level& level = levels[l];
+      if (level.ncomp != nnames) throw std::invalid_argument("component count differs from names");
+      amrex::shim::PlotLevel out;
+      for (int d = 0; d < 3; ++d) {
+        out.cellSize[d] = level.cell_size[d];
+        content.probLo[d] = level.prob_lo[d];
+      }
+      for (int b = 0; b < level.nboxes; ++b) {
+        out.boxes.emplace_back(
+            amrex::IntVect(level.lo[3 * b], level.lo[3 * b + 1], level.lo[3 * b + 2]),
+            amrex::IntVect(level.hi[3 * b], level.hi[3 * b + 1], level.hi[3 * b + 2]));
+        const std::size_t count =
+            static_cast<std::size_t>(out.boxes.back().numPts()) * level.ncomp;
+        out.data.emplace_back(level.data[b], level.data[b] + count);
+      }
+      content.levels.push_back(std::move(out));
+    }
+    amrex::shim::plotfiles()[path] = std::move(content);
+  });
+}
+
+// The reference's own VolumeRenderer::run(RunOptions) (VolumeRenderer.cpp:
+// 1341-1576) on `nranks` thread-ranks over a registered plotfile: argument
+// checks, loadPlotFileGeometry, scalar-range override, colour-map
+// normalisation, automatic or explicit camera, renderScene, image file.
+// customUp / scalarRange / camera / pts may be NULL (option not given).
+int ref_run(int nranks, const char* plotfile, const amrvr_frame_params* params,
+            const char* output, const char* variable, int minLevel, int maxLevel,
+            int logScale, const double* customUp, const float* scalarRange,
+            const amrvr_camera* camera, const amrvr_colormap_pt* pts, int npts,
+            char* log, int logCapacity) {
+  std::string text;
+  const int status = guarded([&] {
+    Capture capture;
+    try {
+      fake_mpi_run(
+          nranks,
+          [&](int) {
+            VolumeRenderer::RunOptions options;
+            options.parameters = toParameters(*params);
+            if (customUp != nullptr) {
+              options.parameters.cameraUp = amrex::RealVect(customUp[0], customUp[1], customUp[2]);
+              options.parameters.useCustomUp = true;
+            }
+            options.outputFilename = output;
+            options.plotfilePath = plotfile;
+            options.variableName = (variable != nullptr) ? variable : "";
+            options.minLevel = minLevel;
+            options.maxLevel = maxLevel;
+            options.logScaleInput = logScale != 0;
+            if (scalarRange != nullptr)
+              options.scalarRange = std::make_pair(scalarRange[0], scalarRange[1]);
+            if (camera != nullptr) options.camera = toCamera(*camera);
+            options.colorMap = toColorMap(pts, npts);
+            VolumeRenderer renderer;
+            if (renderer.run(options) != 0) throw std::runtime_error("run returned non-zero");
+          },
+          false);
+    } catch (...) {
+      text = capture.buffer.str();
+      throw;
+    }
+    text = capture.buffer.str();
+  });
+  copyLog(text, log, logCapacity);
+  return status;
+}
+
 // The real BuildSceneGeometry, collectively on `nranks` thread-ranks, from
 // ALREADY-CONVEX levels (convexify is un-vendored AMReX).
 int ref_build_scene(int nranks, int nlevels, const ref_level* levels,

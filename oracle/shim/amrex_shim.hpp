@@ -24,6 +24,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <limits>
+#include <map>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -500,25 +501,73 @@ struct Mpi_typemap<long long> {
 };
 }  // namespace ParallelDescriptor
 
-// ---------------------------------------------------------------- unavailable I/O
-// Plotfile parsing and convexify live in un-vendored AMReX; the oracle never
-// takes these paths (scenes are built at the SceneGeometry level).
+// ---------------------------------------------------------------- plotfile I/O
+// Plotfile parsing lives in un-vendored AMReX.  The shim does not parse files:
+// a test registers the CONTENT of a plotfile (what PlotFileData would expose)
+// under a path name, and PlotFileData(path) hands it to the reference's own
+// VolumeRenderer::loadPlotFileGeometry / run().  Unregistered paths throw, as
+// before.  get() deals box b to thread-rank b % nranks.
+namespace shim {
+struct PlotLevel {
+  std::vector<Box> boxes;
+  std::vector<std::vector<Real>> data;  // per box: ncomp * cells, component-major, i fastest
+  Array<Real, 3> cellSize{1.0, 1.0, 1.0};
+};
+struct PlotContent {
+  Vector<std::string> names;
+  int spaceDim = 3;
+  Array<Real, 3> probLo{0.0, 0.0, 0.0};
+  std::vector<PlotLevel> levels;
+  int refRatio = 2;
+};
+inline std::map<std::string, PlotContent>& plotfiles() {
+  static std::map<std::string, PlotContent> registry;
+  return registry;
+}
+}  // namespace shim
+
 class PlotFileData {
  public:
-  explicit PlotFileData(const std::string&) {
-    throw std::runtime_error(
-        "oracle shim: amrex::PlotFileData is unavailable (AMReX not vendored)");
+  explicit PlotFileData(const std::string& path) {
+    const auto it = shim::plotfiles().find(path);
+    if (it == shim::plotfiles().end())
+      throw std::runtime_error(
+          "oracle shim: amrex::PlotFileData is unavailable (AMReX not vendored) and '" + path +
+          "' was not registered");
+    m_content = &it->second;
   }
-  int spaceDim() const { return 3; }
-  const Vector<std::string>& varNames() const { return m_names; }
-  int finestLevel() const { return 0; }
-  MultiFab get(int, const std::string&) { return MultiFab(); }
-  IntVect refRatio(int) const { return IntVect(2); }
-  Array<Real, 3> probLo() const { return {0.0, 0.0, 0.0}; }
-  Array<Real, 3> cellSize(int) const { return {1.0, 1.0, 1.0}; }
+  int spaceDim() const { return m_content->spaceDim; }
+  const Vector<std::string>& varNames() const { return m_content->names; }
+  int finestLevel() const { return static_cast<int>(m_content->levels.size()) - 1; }
+  MultiFab get(int level, const std::string& name) {
+    const shim::PlotLevel& L = m_content->levels.at(static_cast<std::size_t>(level));
+    int comp = -1;
+    for (std::size_t c = 0; c < m_content->names.size(); ++c)
+      if (m_content->names[c] == name) comp = static_cast<int>(c);
+    if (comp < 0) throw std::runtime_error("oracle shim: no such plotfile variable");
+    int rank = 0, nranks = 1;
+    MPI_Comm_rank(MPI_COMM_WORLD, &rank);
+    MPI_Comm_size(MPI_COMM_WORLD, &nranks);
+    std::vector<int> owners(L.boxes.size());
+    for (std::size_t b = 0; b < owners.size(); ++b) owners[b] = static_cast<int>(b) % nranks;
+    MultiFab mf(L.boxes, owners, 1, rank);
+    for (std::size_t b = 0; b < owners.size(); ++b) {
+      if (owners[b] != rank) continue;
+      const std::size_t cells = static_cast<std::size_t>(L.boxes[b].numPts());
+      std::copy(L.data[b].begin() + static_cast<std::ptrdiff_t>(cells * comp),
+                L.data[b].begin() + static_cast<std::ptrdiff_t>(cells * (comp + 1)),
+                mf.dataPtr(static_cast<int>(b)));
+    }
+    return mf;
+  }
+  IntVect refRatio(int) const { return IntVect(m_content->refRatio); }
+  Array<Real, 3> probLo() const { return m_content->probLo; }
+  Array<Real, 3> cellSize(int level) const {
+    return m_content->levels.at(static_cast<std::size_t>(level)).cellSize;
+  }
 
  private:
-  Vector<std::string> m_names;
+  const shim::PlotContent* m_content = nullptr;
 };
 
 // convexify removes coarse cells covered by finer levels and re-cuts boxes; its
@@ -553,7 +602,7 @@ class Geometry {
 };
 
 namespace FileSystem {
-inline bool Exists(const std::string&) { return false; }
+inline bool Exists(const std::string& path) { return shim::plotfiles().count(path) != 0; }
 }  // namespace FileSystem
 
 }  // namespace amrex
