@@ -104,6 +104,41 @@ def test_host_order_random_boxes_with_cycles(oracle):
         assert failed == (not ok)
 
 
+@pytest.mark.parametrize("scale", [1.0, 37.5, 4096.0])
+def test_host_order_at_the_touching_tolerance(oracle, scale):
+    """Faces within, at and just beyond the 1e-5 * scale tolerance of
+    VisibilityOrdering.cpp:211-228, zero-thickness boxes, axis-parallel views and
+    coordinates far from the origin: the SIMD pair filter must keep every pair the
+    exact test would accept (same rank order as the oracle, which test_cpu_oracle.py
+    pins to the reference)."""
+    rng = np.random.default_rng(int(scale) + 5)
+    tol = 1e-5 * max(1.0, scale)
+    for trial in range(60):
+        n = int(rng.integers(2, 40))
+        recs = (api.BoxRecord * n)()
+        local = {}
+        for i in range(n):
+            lo = rng.integers(0, 3, size=3) * (scale / 3.0)
+            ext = rng.integers(0 if trial % 7 == 0 else 1, 3, size=3) * (scale / 3.0)  # 0: a flat box
+            jitter = rng.choice([0.0, 0.4 * tol, 0.99 * tol, 1.01 * tol, 2.5 * tol, -0.99 * tol, -3 * tol], size=6)
+            for d in range(3):
+                recs[i].min_corner[d] = lo[d] + jitter[d]
+                recs[i].max_corner[d] = lo[d] + ext[d] + jitter[3 + d]
+                recs[i].dims[d] = 4
+            recs[i].owner = int(i * 5 // n)
+            recs[i].local_index = local.get(recs[i].owner, 0)
+            local[recs[i].owner] = recs[i].local_index + 1
+        eye = tuple(rng.uniform(-2, 3, size=3) * scale)
+        if trial % 5 == 0:  # straight down an axis: |dir| components at the 1e-6 cut-off
+            eye = (0.5 * scale, 0.5 * scale, 3.0 * scale)
+        cam = scenes.make_camera(eye=eye, look_at=(0.5 * scale,) * 3, far=20.0 * scale)
+        for graph in (True, False):
+            want, ok = oracle.order(5, recs, n, cam, 1.0, graph)
+            got, failed = engine.order_boxes_host(5, recs, n, cam, 1.0, graph)
+            assert np.array_equal(got, want), (trial, graph)
+            assert failed == (not ok)
+
+
 def test_layer_order_and_hints_match_oracle(oracle):
     """computeBoxDepthHint + the (depth, owner, local index) sort, bit-exact."""
     for P, rule in ((1, "chunks"), (4, "round_robin"), (8, "chunks")):

@@ -98,6 +98,42 @@ def test_order_random_boxes_with_cycles_matches_reference(oracle, ref):
         assert np.array_equal(got, want), trial
 
 
+@pytest.mark.parametrize("scale", [1.0, 37.5, 4096.0])
+def test_order_at_the_touching_tolerance_matches_reference(oracle, ref, lib, scale):
+    """Faces within, at and just beyond the 1e-5 * scale tolerance
+    (VisibilityOrdering.cpp:211-228), flat boxes, axis-parallel views, large
+    coordinates: restatement AND the product's host ordering against the
+    reference's own BuildVisibilityOrderedGroup."""
+    from amrvolumerenderer_b200 import engine
+
+    rng = np.random.default_rng(int(scale) + 5)
+    tol = 1e-5 * max(1.0, scale)
+    for trial in range(40):
+        n = int(rng.integers(2, 36))
+        recs = (api.BoxRecord * n)()
+        local = {}
+        for i in range(n):
+            lo = rng.integers(0, 3, size=3) * (scale / 3.0)
+            ext = rng.integers(0 if trial % 7 == 0 else 1, 3, size=3) * (scale / 3.0)
+            jitter = rng.choice([0.0, 0.4 * tol, 0.99 * tol, 1.01 * tol, 2.5 * tol, -0.99 * tol, -3 * tol], size=6)
+            for d in range(3):
+                recs[i].min_corner[d] = lo[d] + jitter[d]
+                recs[i].max_corner[d] = lo[d] + ext[d] + jitter[3 + d]
+                recs[i].dims[d] = 4
+            recs[i].owner = int(i * 5 // n)
+            recs[i].local_index = local.get(recs[i].owner, 0)
+            local[recs[i].owner] = recs[i].local_index + 1
+        eye = tuple(rng.uniform(-2, 3, size=3) * scale)
+        if trial % 5 == 0:
+            eye = (0.5 * scale, 0.5 * scale, 3.0 * scale)
+        cam = scenes.make_camera(eye=eye, look_at=(0.5 * scale,) * 3, far=20.0 * scale)
+        want, _ = ref.order(5, recs, n, cam, 1.0)
+        got, _ = oracle.order(5, recs, n, cam, 1.0)
+        assert np.array_equal(got, want), trial
+        ours, _ = engine.order_boxes_host(5, recs, n, cam, 1.0)
+        assert np.array_equal(ours, want), trial
+
+
 @pytest.mark.parametrize("nranks,rule", [(1, "chunks"), (2, "chunks"), (3, "round_robin"), (5, "round_robin")])
 def test_compose_matches_reference(oracle, ref, nranks, rule):
     """DirectSendBase::composeLayered (DirectSend/Base/DirectSendBase.cpp:316-458)
