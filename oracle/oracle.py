@@ -382,6 +382,14 @@ class Ref(_Base):
         cnames = (C.c_char_p * ncomp)(*[n.encode() for n in names])
         self._check(self.lib.ref_register_plotfile(str(path).encode(), len(levels), clev, ncomp, cnames))
 
+    def set_convexify_override(self, pieces_per_level):
+        """Box cuts the shim's amrex::convexify returns (list of int32[n, 6] = lo, hi
+        per level); None or [] restores the default (single level only)."""
+        levels = [np.ascontiguousarray(p, np.int32).reshape(-1, 6) for p in (pieces_per_level or [])]
+        counts = (C.c_int32 * max(len(levels), 1))(*[len(p) for p in levels])
+        ptrs = (_P(C.c_int32) * max(len(levels), 1))(*[p.ctypes.data_as(_P(C.c_int32)) for p in levels])
+        self._check(self.lib.ref_set_convexify_override(len(levels), counts, ptrs))
+
     def run(self, plotfile, output, params, nranks=1, variable=None, min_level=0, max_level=-1,
             log_scale=False, up_vector=None, scalar_range=None, camera=None, colormap=None):
         """The reference's own VolumeRenderer::run(RunOptions) over a registered

@@ -291,6 +291,25 @@ int ref_register_plotfile(const char* path, int nlevels, const ref_level* levels
   });
 }
 
+// Installs (nlevels > 0) or clears (nlevels == 0) the box cuts the shim's
+// convexify hands back: boxes[l] = counts[l] boxes as lo[3], hi[3].
+int ref_set_convexify_override(int nlevels, const int32_t* counts,
+                               const int32_t* const* boxes) {
+  return guarded([&] {
+    amrex::shim::ConvexOverride& cuts = amrex::shim::convex_override();
+    cuts.boxes.clear();
+    cuts.active = nlevels > 0;
+    for (int l = 0; l < nlevels; ++l) {
+      std::vector<amrex::Box> list;
+      for (int b = 0; b < counts[l]; ++b)
+        list.emplace_back(
+            amrex::IntVect(boxes[l][6 * b], boxes[l][6 * b + 1], boxes[l][6 * b + 2]),
+            amrex::IntVect(boxes[l][6 * b + 3], boxes[l][6 * b + 4], boxes[l][6 * b + 5]));
+      cuts.boxes.push_back(std::move(list));
+    }
+  });
+}
+
 // The reference's own VolumeRenderer::run(RunOptions) (VolumeRenderer.cpp:
 // 1341-1576) on `nranks` thread-ranks over a registered plotfile: argument
 // checks, loadPlotFileGeometry, scalar-range override, colour-map

@@ -417,6 +417,8 @@ class MultiFab {
   int localCount() const { return static_cast<int>(m_local.size()); }
   int localToGlobal(int li) const { return m_local[li]; }
   const Box& box(int gi) const { return m_boxes[gi]; }
+  int owner(int gi) const { return m_owners[gi]; }
+  int myRank() const { return m_rank; }
   Real* dataPtr(int gi) { return m_data[gi].data(); }
   const Real* dataPtr(int gi) const { return m_data[gi].data(); }
 
@@ -573,17 +575,77 @@ class PlotFileData {
 // convexify removes coarse cells covered by finer levels and re-cuts boxes; its
 // source is un-vendored AMReX.  With ONE level there is nothing to remove, so
 // the shim returns a deep copy with the same boxes (parity unpinned: real
-// AMReX may also re-chop a single level's BoxArray).  Multi-level inputs must
-// be handed to the oracle already convex.
+// AMReX may also re-chop a single level's BoxArray).  For more levels a test
+// may install the cuts it wants the reference to see (shim::convex_override:
+// per level a list of boxes, each inside one source box); the shim then builds
+// the MultiFabs on those boxes and copies the cells over, every piece staying
+// on the rank of its source FAB.  Without an override multi-level input throws.
+namespace shim {
+struct ConvexOverride {
+  bool active = false;
+  std::vector<std::vector<Box>> boxes;  // [level][piece]
+};
+inline ConvexOverride& convex_override() {
+  static ConvexOverride instance;
+  return instance;
+}
+}  // namespace shim
+
 inline Vector<MultiFab> convexify(const Vector<MultiFab const*>& levels,
                                   const Vector<IntVect>&) {
-  if (levels.size() != 1) {
-    throw std::runtime_error(
-        "oracle shim: amrex::convexify for >1 level is unavailable (AMReX not "
-        "vendored); pass already-convex boxes");
-  }
+  const shim::ConvexOverride& cuts = shim::convex_override();
   Vector<MultiFab> out;
-  out.push_back(levels[0]->deepCopy());
+  if (!cuts.active) {
+    if (levels.size() != 1) {
+      throw std::runtime_error(
+          "oracle shim: amrex::convexify for >1 level is unavailable (AMReX not "
+          "vendored); pass already-convex boxes");
+    }
+    out.push_back(levels[0]->deepCopy());
+    return out;
+  }
+  if (cuts.boxes.size() < levels.size())
+    throw std::runtime_error("oracle shim: convexify override has too few levels");
+  for (std::size_t l = 0; l < levels.size(); ++l) {
+    const MultiFab& src = *levels[l];
+    const std::vector<Box>& pieces = cuts.boxes[l];
+    std::vector<int> owners(pieces.size(), 0), source(pieces.size(), -1);
+    for (std::size_t p = 0; p < pieces.size(); ++p) {
+      for (int g = 0; g < src.size() && source[p] < 0; ++g) {
+        bool inside = true;
+        for (int d = 0; d < 3; ++d)
+          inside = inside && src.box(g).smallEnd()[d] <= pieces[p].smallEnd()[d] &&
+                   pieces[p].bigEnd()[d] <= src.box(g).bigEnd()[d];
+        if (inside) source[p] = g;
+      }
+      if (source[p] < 0) throw std::runtime_error("oracle shim: convexify piece outside every box");
+      owners[p] = src.owner(source[p]);
+    }
+    MultiFab mf(pieces, owners, src.nComp(), src.myRank());
+    for (std::size_t p = 0; p < pieces.size(); ++p) {
+      if (owners[p] != src.myRank()) continue;
+      const Box& sb = src.box(source[p]);
+      const Box& pb = pieces[p];
+      const Real* from = src.dataPtr(source[p]);
+      Real* to = mf.dataPtr(static_cast<int>(p));
+      const Long scells = sb.numPts(), pcells = pb.numPts();
+      for (int n = 0; n < src.nComp(); ++n)
+        for (int k = pb.smallEnd()[2]; k <= pb.bigEnd()[2]; ++k)
+          for (int j = pb.smallEnd()[1]; j <= pb.bigEnd()[1]; ++j)
+            for (int i = pb.smallEnd()[0]; i <= pb.bigEnd()[0]; ++i) {
+              const Long s = (i - sb.smallEnd()[0]) +
+                             static_cast<Long>(sb.length(0)) *
+                                 ((j - sb.smallEnd()[1]) +
+                                  static_cast<Long>(sb.length(1)) * (k - sb.smallEnd()[2]));
+              const Long t = (i - pb.smallEnd()[0]) +
+                             static_cast<Long>(pb.length(0)) *
+                                 ((j - pb.smallEnd()[1]) +
+                                  static_cast<Long>(pb.length(1)) * (k - pb.smallEnd()[2]));
+              to[n * pcells + t] = from[n * scells + s];
+            }
+    }
+    out.push_back(std::move(mf));
+  }
   return out;
 }
 

@@ -144,3 +144,88 @@ def test_run_error_messages_match_the_reference(lib, ref, tmp_path):
             assert str(ours.value) == theirs.value.message.replace("scalar range", "scalar_range")
         else:
             assert str(ours.value) == theirs.value.message, (frame, ref_kw)
+
+
+def _convexified(lib, levels, component, upto):
+    """amrvr_convexify_levels over levels[0..upto] -> (convex Level array, pieces per level, keep)."""
+    nlev = upto + 1
+    clev, keep = _levels_struct(levels[:nlev], component)
+    ratios = (C.c_int32 * 3 * max(nlev - 1, 1))()
+    for l in range(nlev - 1):
+        for d in range(3):
+            ratios[l][d] = 2
+    out = (api.Fab * 1024)()
+    counts = (C.c_int32 * nlev)()
+    assert lib.amrvr_convexify_levels(nlev, clev, None, None, ratios, out, 1024, counts) == 0
+    convex = (api.Level * nlev)()
+    pieces, base = [], 0
+    for l in range(nlev):
+        convex[l].prob_lo, convex[l].cell_size = clev[l].prob_lo, clev[l].cell_size
+        convex[l].nfabs = counts[l]
+        convex[l].fabs = C.cast(C.byref(out, base * C.sizeof(api.Fab)), C.POINTER(api.Fab))
+        pieces.append(np.array([[out[base + k].lo[d] for d in range(3)] + [out[base + k].hi[d] for d in range(3)]
+                                for k in range(counts[l])], np.int32).reshape(-1, 6))
+        base += counts[l]
+    return convex, pieces, (keep, out, clev)
+
+
+def _view(b):
+    """The cells of an amrvr_box (a strided view into its source FAB) as a dense (nz, ny, nx) array."""
+    nx, ny, nz = b.dims
+    first = b.data + 8 * ((b.lo[0] - b.begin[0]) + (b.lo[1] - b.begin[1]) * b.jstride
+                          + (b.lo[2] - b.begin[2]) * b.kstride)
+    span = (nz - 1) * b.kstride + (ny - 1) * b.jstride + nx
+    flat = np.ctypeslib.as_array((C.c_double * span).from_address(first))
+    return np.ascontiguousarray(np.lib.stride_tricks.as_strided(
+        flat, shape=(nz, ny, nx), strides=(8 * b.kstride, 8 * b.jstride, 8)))
+
+
+@pytest.mark.parametrize("min_level,max_level,nranks", [(0, -1, 1), (1, 2, 1), (0, 1, 1), (0, -1, 2)])
+def test_multi_level_run_with_our_cuts_matches_the_reference(lib, oracle, ref, tmp_path, min_level,
+                                                             max_level, nranks):
+    """Three-level, NON-convex plotfile: the reference's run() is handed the box cuts
+    OUR convexify produced (through the shim's convexify override) and must then
+    write the same bytes as our chain -- views into the source FABs, scene build,
+    level window, automatic camera, frame.  What stays unpinned is only which
+    cuts AMReX itself would choose."""
+    levels, plo, phi = synthetic_hierarchy(base_cells=16, box_cells=8, nlevels=3, seed=41)
+    key = f"registered://multi/{min_level}/{max_level}/{nranks}"
+    ref.register_plotfile(key, levels, ("rho",))
+    finest = 2
+    hi = finest if (max_level < 0 or max_level > finest) else max_level
+    convex, pieces, keep = _convexified(lib, levels, 0, hi)
+    params = api.FrameParams(width=64, height=48, box_transparency=0.0, antialiasing=1,
+                             use_visibility_graph=1, count_samples=0, draw_bounding_box=1)
+    out = tmp_path / "ref.ppm"
+    ref.set_convexify_override(pieces)
+    try:
+        ref.run(key, out, params, nranks=nranks, min_level=min_level, max_level=max_level)
+    finally:
+        ref.set_convexify_override(None)
+    want = read_ppm(out)
+
+    boxes, summary, status = oracle.scene_build(convex, hi + 1, min_level=min_level, max_level=hi)
+    assert status == 0
+    transform, value_range, points = resolve_scalar_options(summary, False, None, None)
+    camera = api.Camera()
+    assert lib.amrvr_auto_camera(summary.bounds_min, summary.bounds_max, DEFAULT_CAMERA_SEED, None,
+                                 C.byref(camera)) == 0
+    # the shim deals SOURCE box b of every level to rank b % nranks and a piece stays with its source
+    owner_of = {}
+    for l in range(hi + 1):
+        for b, (lo, data) in enumerate(levels[l].boxes):
+            owner_of[(l, tuple(lo))] = b % nranks
+    specs = []
+    for i in range(summary.nboxes):
+        b = boxes[i]
+        level = int(np.argmin([abs(levels[l].cell_size[0] * summary.global_scale
+                                   - (b.max_corner[0] - b.min_corner[0]) / b.dims[0]) for l in range(3)]))
+        src_lo = tuple((b.lo[d] // 8) * 8 for d in range(3))  # 8^3 source boxes on an 8-aligned lattice
+        specs.append(scenes.BoxSpec(level, tuple(b.lo), tuple(b.dims), np.array(b.min_corner),
+                                    np.array(b.max_corner), _view(b), owner_of[(level, src_lo)], i))
+    specs.sort(key=lambda s: s.owner)
+    scene = scenes.Scene("multi", specs, transform, value_range, np.array(summary.bounds_min),
+                         np.array(summary.bounds_max), nranks, [])
+    got = oracle.render_frame(scene, camera, params)["rgb8"]
+    assert want.any()
+    assert np.array_equal(got, want), int(np.abs(got.astype(int) - want.astype(int)).max())
