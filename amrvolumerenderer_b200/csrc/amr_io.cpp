@@ -23,6 +23,7 @@
 #include <memory>
 #include <sstream>
 #include <stdexcept>
+#include <system_error>
 #include <thread>
 
 #include "internal.hpp"
@@ -33,10 +34,14 @@ using amrvr::report_error;
 
 struct IBox {
   int32_t lo[3], hi[3];
-  int64_t cells() const {
-    return static_cast<int64_t>(hi[0] - lo[0] + 1) * (hi[1] - lo[1] + 1) * (hi[2] - lo[2] + 1);
-  }
+  int64_t extent(int d) const { return static_cast<int64_t>(hi[d]) - lo[d] + 1; }
+  int64_t cells() const { return extent(0) * extent(1) * extent(2); }
   bool ok() const { return hi[0] >= lo[0] && hi[1] >= lo[1] && hi[2] >= lo[2]; }
+  // A box that holds data: not empty, and small enough that cells() and byte
+  // counts stay far inside int64 (no real FAB is 2^20 cells long on a side).
+  bool holds_data() const {
+    return ok() && extent(0) <= (1 << 20) && extent(1) <= (1 << 20) && extent(2) <= (1 << 20);
+  }
   bool intersects(const IBox& o) const {
     for (int d = 0; d < 3; ++d)
       if (std::max(lo[d], o.lo[d]) > std::min(hi[d], o.hi[d])) return false;
@@ -99,6 +104,7 @@ struct Scanner {
     int n = 0;
     for (;;) {
       const long long x = integer();
+      if (x < -(1LL << 30) || x > (1LL << 30)) bad("index out of range");
       if (n < 3) v[n] = static_cast<int32_t>(x);
       ++n;
       skip_ws();
@@ -185,7 +191,10 @@ void parse_vismf_header(amrvr_plotfile& pf, LevelData& L, const std::string& mf_
   (void)s.integer();  // hash
   if (n < 0 || n > (1 << 24)) s.bad("implausible box count");
   L.boxes.resize(static_cast<size_t>(n));
-  for (auto& b : L.boxes) b = s.box();
+  for (auto& b : L.boxes) {
+    b = s.box();
+    if (!b.holds_data()) s.bad("BoxArray holds an empty or implausibly large box");
+  }
   s.expect(')');
   const long long nf = s.integer();
   if (nf != n) s.bad("FabOnDisk table and BoxArray differ in length");
@@ -295,7 +304,7 @@ void read_fab_component(const amrvr_plotfile& pf, int level, int box, int compon
   const FabRecord r = read_fab_record(pf, f);
   const std::string& name = pf.file_names[f.file];
   if (component >= r.ncomp) throw std::runtime_error(name + ": FAB has too few components");
-  if (!r.box.ok() || !r.box.contains(valid))
+  if (!r.box.holds_data() || !r.box.contains(valid))
     throw std::runtime_error(name + ": FAB box does not cover its BoxArray entry");
   const int64_t fab_cells = r.box.cells();
   const int64_t at = r.data_offset + static_cast<int64_t>(component) * fab_cells * r.real_bytes;
@@ -586,7 +595,13 @@ extern "C" int amrvr_plotfile_read_level(const amrvr_plotfile* pf, int level, in
     }
   };
   std::vector<std::thread> pool;
-  for (int t = 1; t < nthreads; ++t) pool.emplace_back(work, t);
+  for (int t = 1; t < nthreads; ++t) {
+    try {
+      pool.emplace_back(work, t);
+    } catch (const std::system_error&) {
+      break;  // no more threads to be had: the ones running share the work
+    }
+  }
   work(0);
   for (auto& t : pool) t.join();
   for (const auto& e : errors)

@@ -113,6 +113,42 @@ def test_plotfile_errors(lib, tmp_path):
             pf.read_fab(0, 0, 4)
         with pytest.raises(RuntimeError, match="bad level"):
             pf.level(3)
+    # a BoxArray entry with lo > hi, an index that does not fit, a FAB record that
+    # does not cover its entry: refused when read, never turned into offsets
+    good = (path / "Level_0" / "Cell_H").read_text()
+    for old, new, msg in (("((0,0,0) (7,7,7)", "((9,0,0) (7,7,7)", "empty or implausibly large"),
+                          ("((0,0,0) (7,7,7)", "((0,0,0) (7,7,99999999999)", "index out of range"),
+                          ("((0,0,0) (7,7,7)", "((0,0,0) (7,7,3000000)", "empty or implausibly large")):
+        assert old in good
+        (path / "Level_0" / "Cell_H").write_text(good.replace(old, new, 1))
+        with pytest.raises(RuntimeError, match=msg):
+            PlotFile(path)
+    (path / "Level_0" / "Cell_H").write_text(good.replace("((0,0,0) (7,7,7)", "((0,0,0) (7,7,8)", 1))
+    with PlotFile(path) as pf:
+        with pytest.raises(RuntimeError, match="does not cover its BoxArray entry"):
+            pf.read_fab(0, 0, 0)
+    (path / "Level_0" / "Cell_H").write_text(good)
+    data = path / "Level_0" / "Cell_D_00000"
+    data.write_bytes(data.read_bytes()[:-100])
+    with PlotFile(path) as pf:
+        with pytest.raises(RuntimeError, match="short read"):
+            pf.read_fab(0, 0, 0)
+
+
+def test_plotfile_reader_survives_corrupted_files(tmp_path):
+    """200 seeded corruptions (truncation, byte flips, dropped / doubled / junk
+    header lines) of a two-level plotfile: every one either reads or raises the
+    ABI's error -- run in a child process so that a crash would be seen as one."""
+    import os
+    import subprocess
+    import sys
+
+    worker = os.path.join(os.path.dirname(__file__), "fuzz_plotfile_worker.py")
+    out = subprocess.run([sys.executable, worker, str(tmp_path), "7", "200"], capture_output=True,
+                         text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    opened, refused = (int(v) for v in out.stdout.split()[-2:])
+    assert opened + refused == 200 and opened > 20 and refused > 20
 
 
 def test_convexify_known_answer_cut_order(lib):
