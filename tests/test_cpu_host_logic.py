@@ -170,3 +170,18 @@ def test_reference_sample_distance_matches_oracle(oracle):
     empty = (api.BoxRecord * 1)()
     assert engine.reference_sample_distance(empty, 0, (0, 0, 0), (1, 2, 3)) == \
         oracle.reference_sample_distance(empty, 0, (0, 0, 0), (1, 2, 3))
+
+
+def test_null_arguments_are_refused():
+    """NULL pointers, negative counts and NULL handles through the C ABI come
+    back as AMRVR_ERR_INVALID with a message (the adapters rethrow it as the
+    reference's std::invalid_argument); nothing is dereferenced.  In a child
+    process, so that a crash shows up as a failure rather than as a dead suite."""
+    import os
+    import subprocess
+    import sys
+
+    worker = os.path.join(os.path.dirname(__file__), "abi_null_worker.py")
+    out = subprocess.run([sys.executable, worker], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    assert out.stdout.split()[-2] == "ok"
