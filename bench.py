@@ -84,6 +84,33 @@ def _ncu_traffic(kernel_tag="march"):
     return (total if seen == 2 else None), best.name
 
 
+def _ncu_issue(march_s, sm_clock_hz, n_sm=148):
+    """Issue-slot use of the march at the LIVE launch duration: warp instructions
+    per launch (smsp__inst_executed.sum of the committed ncu capture of this same
+    workload -- an instruction count, not a timing) / live duration / (SMs x 4
+    schedulers x SM clock).  None when there is no capture to read."""
+    import re
+
+    try:
+        _, name = _ncu_traffic()
+        if name is None or march_s <= 0 or sm_clock_hz <= 0:
+            return None
+        for ln in (ROOT / "profiles" / name).read_text().splitlines():
+            m = re.match(r"\s*smsp__inst_executed\.sum\s+([0-9.]+)\s+inst", ln)
+            if m:  # first block = the march
+                inst = float(m.group(1))
+                return {"warp_instructions_per_launch": inst,
+                        "achieved_per_sm_clock": inst / march_s / (n_sm * sm_clock_hz),
+                        "peak_per_sm_clock": 4.0,
+                        "frac": inst / march_s / (n_sm * 4.0 * sm_clock_hz),
+                        "source": f"profiles/{name} (instruction count, captured on the "
+                                  "sample-counting instantiation: an upper bound for the timed "
+                                  "one) / live launch duration"}
+    except Exception:  # never let a reporting extra break the bench line
+        return None
+    return None
+
+
 class ClockSampler(threading.Thread):
     """SM clock and throttle reasons of one GPU while the timed region runs
     (NVML in-process, every 5 ms; nvidia-smi as the fallback)."""
@@ -428,7 +455,9 @@ def main():
                                  "note": "TERTIARY: 8 B x samples, the reference's own access "
                                          "pattern; NOT DRAM traffic"},
                 "compute": {"samples_per_s_per_sm_clock": out["stats"].samples / march_s / (148 * sm_clock),
-                            "note": "samples per SM per clock; 128 FP32 lanes/SM"},
+                            "note": "samples per SM per clock; 128 FP32 lanes/SM",
+                            "issue": _ncu_issue(march_s, sm_clock)
+                            if args.workload == "C4" and world == 1 else None},
             },
         }
         # the composite: in peer-memory mode the fold kernel reads the other GPUs'
