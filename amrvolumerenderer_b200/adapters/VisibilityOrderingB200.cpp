@@ -8,11 +8,17 @@
 // falls back to the identity order.  The box table travels over MPI exactly as
 // there (:85-152); the depth-key sort and the pair test run in
 // amrvr_order_records (device radix sort / pair kernel from 1024 boxes up).
-// writeVisibilityGraph (the DOT dump, :319-352) is not provided.
+// writeVisibilityGraph (:319-352): rank 0 writes visibility_graph_<n>.dot per
+// round into the working directory from amrvr_order_graph_dot_host's text
+// (byte-identical to the reference's, tests/test_cpu_host_logic.py).
 #include <Common/VisibilityOrdering.hpp>
 
+#include <cstdint>
+#include <fstream>
 #include <iostream>
 #include <numeric>
+#include <sstream>
+#include <string>
 #include <vector>
 
 #include "B200Runtime.hpp"
@@ -27,7 +33,6 @@ MPI_Group BuildVisibilityOrderedGroup(
     bool writeVisibilityGraph,
     const std::vector<amrVolumeRenderer::volume::AmrBox>& localBoxes,
     MPI_Comm communicator) {
-  static_cast<void>(writeVisibilityGraph);
   std::vector<int> rankOrder(static_cast<std::size_t>(numProcs));
   std::iota(rankOrder.begin(), rankOrder.end(), 0);
 
@@ -74,6 +79,34 @@ MPI_Group BuildVisibilityOrderedGroup(
                       amrvr_order_records(ctx, numProcs, total, records.data(), &abiCamera, aspect,
                                           1, rankOrder.data(), &graphFailed),
                       "amrvr_order_records");
+    if (writeVisibilityGraph && rank == 0) {
+      static int graphFileCounter = 0;
+      int rounds = 1;
+      for (int round = 0; round < rounds; ++round) {
+        std::int64_t bytes = 0;
+        amrvr_b200::check(ctx,
+                          amrvr_order_graph_dot_host(numProcs, total, records.data(), &abiCamera,
+                                                     aspect, round, nullptr, 0, &bytes, &rounds),
+                          "amrvr_order_graph_dot_host");
+        if (round >= rounds) break;
+        std::string text(static_cast<std::size_t>(bytes), '\0');
+        amrvr_b200::check(ctx,
+                          amrvr_order_graph_dot_host(numProcs, total, records.data(), &abiCamera,
+                                                     aspect, round, text.data(), bytes, nullptr,
+                                                     nullptr),
+                          "amrvr_order_graph_dot_host");
+        std::ostringstream filename;
+        filename << "visibility_graph_" << graphFileCounter++ << ".dot";
+        std::ofstream dotFile(filename.str(), std::ios::binary);
+        if (!dotFile) {
+          std::cerr << "Failed to write visibility graph to '" << filename.str() << "'"
+                    << std::endl;
+          continue;
+        }
+        dotFile << text;
+        std::cout << "Wrote visibility graph to '" << filename.str() << "'" << std::endl;
+      }
+    }
     if (graphFailed != 0) {
       static bool warnedGraphFailure = false;
       if (!warnedGraphFailure && rank == 0) {

@@ -1100,11 +1100,32 @@ bool split_cycle_member(const std::vector<int>& cycle, std::vector<OrderBox>& bo
   return true;
 }
 
+// exportGraph (:319-352): nodes labelled with owner and NDC depth interval
+// (std::fixed, six decimals), then one line per edge, rows in node order.
+std::string graph_dot(const std::vector<OrderBox>& boxes, const Graph& g) {
+  std::string out = "digraph VisibilityGraph {\n  rankdir=LR;\n";
+  char line[256];
+  for (size_t i = 0; i < boxes.size(); ++i) {
+    std::snprintf(line, sizeof(line),
+                  "  box%zu [label=\"box %zu\\nrank %d\\nminDepth %.6f\\nmaxDepth %.6f\"];\n", i, i,
+                  boxes[i].owner, static_cast<double>(boxes[i].min_depth),
+                  static_cast<double>(boxes[i].max_depth));
+    out += line;
+  }
+  for (int from = 0; from < g.n; ++from)
+    for (int k = 0; k < g.degree(from); ++k) {
+      std::snprintf(line, sizeof(line), "  box%d -> box%d;\n", from, g.target(from, k));
+      out += line;
+    }
+  out += "}\n";
+  return out;
+}
+
 }  // namespace
 
 bool order_ranks(int nranks, int nglobal, const amrvr_box_record* recs,
                  const amrvr_camera& cam, float aspect, bool use_graph,
-                 OrderBackend& backend, int* rank_order) {
+                 OrderBackend& backend, int* rank_order, std::vector<std::string>* graph_dots) {
   for (int r = 0; r < nranks; ++r) rank_order[r] = r;
   if (!use_graph || nglobal <= 0) return true;
 
@@ -1129,6 +1150,7 @@ bool order_ranks(int nranks, int nglobal, const amrvr_box_record* recs,
     const int n = static_cast<int>(boxes.size());
     backend.pair_edges(boxes, m.dir, edges);
     build_graph(n, edges, g);
+    if (graph_dots != nullptr) graph_dots->push_back(graph_dot(boxes, g));
     backend.rank_boxes(boxes, priority);
     if (topo_order(g, priority, order, residual)) {
       std::vector<char> seen(static_cast<size_t>(nranks), 0);
@@ -1211,6 +1233,33 @@ void make_overlay_edges(const double* tight_min, const double* tight_max,
 }
 
 }  // namespace amrvr
+
+// ------------------------------------------------- visibility graph as DOT text
+extern "C" int amrvr_order_graph_dot_host(int nranks, int nglobal, const amrvr_box_record* records,
+                                          const amrvr_camera* camera, float aspect, int round,
+                                          char* text, int64_t capacity, int64_t* needed,
+                                          int* nrounds) {
+  if (nranks < 1 || nglobal < 0 || (nglobal > 0 && records == nullptr) || camera == nullptr ||
+      round < 0 || capacity < 0 || (needed == nullptr && nrounds == nullptr && text == nullptr))
+    return amrvr::report_error(AMRVR_ERR_INVALID, "bad argument");
+  std::vector<int> rank_order(static_cast<size_t>(nranks));
+  std::vector<std::string> dots;
+  amrvr::order_ranks(nranks, nglobal, records, *camera, aspect, true, *amrvr::host_order_backend(),
+                     rank_order.data(), &dots);
+  if (nrounds != nullptr) *nrounds = static_cast<int>(dots.size());
+  if (round >= static_cast<int>(dots.size())) {
+    if (needed != nullptr) *needed = 0;
+    if (text == nullptr) return AMRVR_OK;  // size query of a round that does not exist
+    return amrvr::report_error(AMRVR_ERR_INVALID, "round out of range");
+  }
+  const std::string& doc = dots[static_cast<size_t>(round)];
+  if (needed != nullptr) *needed = static_cast<int64_t>(doc.size());
+  if (text == nullptr) return AMRVR_OK;
+  if (capacity < static_cast<int64_t>(doc.size()))
+    return amrvr::report_error(AMRVR_ERR_INVALID, "text is too small");
+  std::memcpy(text, doc.data(), doc.size());
+  return AMRVR_OK;
+}
 
 // ------------------------------------------------------------ automatic camera
 // reference: VolumeRenderer/VolumeRenderer.cpp:975-1030 (renderScene without an

@@ -87,7 +87,10 @@ OrderBackend* host_order_backend();
 // true when the graph could be ordered; rank_order is identity otherwise.
 bool order_ranks(int nranks, int nglobal, const amrvr_box_record* recs,
                  const amrvr_camera& cam, float aspect, bool use_graph,
-                 OrderBackend& backend, int* rank_order);
+                 OrderBackend& backend, int* rank_order,
+                 std::vector<std::string>* graph_dots = nullptr);
+// graph_dots (optional): receives the DOT document of every round's graph, the
+// text exportGraph writes to visibility_graph_<n>.dot (:319-352).
 
 // Screen-space footprint of a box: a conservative pixel rectangle that
 // contains every pixel whose centre ray can hit the box.  x0 and w are

@@ -272,6 +272,8 @@ def _declare(lib):
                                               _P(i32)]),
         "amrvr_order_boxes_host": (C.c_int, [i32, i32, _P(BoxRecord), _P(Camera), f32, i32,
                                              _P(i32), _P(i32)]),
+        "amrvr_order_graph_dot_host": (C.c_int, [i32, i32, _P(BoxRecord), _P(Camera), f32, i32,
+                                                 C.c_char_p, C.c_int64, _P(C.c_int64), _P(i32)]),
         "amrvr_layer_order_host": (C.c_int, [i32, _P(BoxRecord), _P(Camera), _P(f32), _P(i32)]),
         "amrvr_piece_range": (C.c_int, [i32, i32, i32, _P(i32), _P(i32)]),
         "amrvr_reference_sample_distance": (C.c_int, [i32, _P(BoxRecord), _P(C.c_double),

@@ -285,6 +285,53 @@ def order_boxes_host(nranks, records, n, camera, aspect, use_graph=True):
     return out, bool(failed.value)
 
 
+def order_graph_dots_host(nranks, records, n, camera, aspect) -> list[bytes]:
+    """The DOT text of every round's visibility graph (exportGraph,
+    Common/VisibilityOrdering.cpp:319-352), byte for byte."""
+    lib = api.load_library()
+    docs = []
+    round_ = 0
+    while True:
+        needed, nrounds = C.c_int64(0), C.c_int(0)
+        _check(lib, None, lib.amrvr_order_graph_dot_host(nranks, n, records, C.byref(camera),
+                                                         float(aspect), round_, None, 0,
+                                                         C.byref(needed), C.byref(nrounds)))
+        if round_ >= nrounds.value:
+            return docs
+        buf = C.create_string_buffer(max(int(needed.value), 1))
+        _check(lib, None, lib.amrvr_order_graph_dot_host(nranks, n, records, C.byref(camera),
+                                                         float(aspect), round_, buf, needed.value,
+                                                         None, None))
+        docs.append(buf.raw[:needed.value])
+        round_ += 1
+
+
+_graph_file_counter = 0  # the reference's function-local static (VisibilityOrdering.cpp:324)
+
+
+def write_visibility_graphs(nranks, records, n, camera, aspect, directory=".") -> list[str]:
+    """What BuildVisibilityOrderedGroup does on rank 0 when writeVisibilityGraph
+    is set: visibility_graph_<counter>.dot per round in the working directory,
+    one "Wrote visibility graph to '...'" line each on stdout."""
+    import os
+    import sys
+
+    global _graph_file_counter
+    written = []
+    for doc in order_graph_dots_host(nranks, records, n, camera, aspect):
+        name = f"visibility_graph_{_graph_file_counter}.dot"
+        _graph_file_counter += 1
+        try:
+            with open(os.path.join(directory, name), "wb") as fh:
+                fh.write(doc)
+        except OSError:
+            print(f"Failed to write visibility graph to '{name}'", file=sys.stderr)
+            continue
+        print(f"Wrote visibility graph to '{name}'")
+        written.append(name)
+    return written
+
+
 def layer_order_host(records, n, camera):
     lib = api.load_library()
     hints = np.zeros(max(n, 1), np.float32)

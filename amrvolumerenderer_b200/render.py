@@ -395,11 +395,15 @@ def render(plotfile, width=512, height=512, box_transparency=0.0, antialiasing=1
                                                DEFAULT_CAMERA_SEED, up, C.byref(camera))
             if status != 0:
                 raise api.AmrvrError(status, ctx.lib.amrvr_last_error(None).decode())
-        if write_visibility_graph:
-            print("render: write_visibility_graph (Graphviz dump of the box graph, a debugging "
-                  "aid of the reference) is not produced by this implementation", file=sys.stderr)
-
         dscene = ctx.upload(scene.boxes, summary.nboxes, transform, value_range)
+        if write_visibility_graph and visibility_graph and ctx.rank == 0:
+            # exportGraph on rank 0 (VisibilityOrdering.cpp:319-352); the aspect is the
+            # render size's (VolumeRenderer.cpp:1116-1119, 1221-1224)
+            from .engine import write_visibility_graphs
+
+            records, nglobal = dscene.global_boxes()
+            write_visibility_graphs(ctx.nranks, records, nglobal, camera,
+                                    float(np.float32(width) / np.float32(height)))
         scene.release()  # the doubles are no longer needed: bricks are bytes now
         params = api.FrameParams(width=int(width), height=int(height),
                                  box_transparency=float(box_transparency),

@@ -344,6 +344,19 @@ int amrvr_order_boxes_host(int nranks, int nglobal,
                            const amrvr_camera* camera, float aspect,
                            int use_graph, int* rank_order, int* graph_failed);
 
+/* [host-only] a10, the debugging aid behind writeVisibilityGraph.  The DOT
+ * documents exportGraph writes to visibility_graph_<n>.dot (Common/
+ * VisibilityOrdering.cpp:319-352): one per round of the cycle-breaking loop
+ * (:567-569), byte for byte.  *nrounds = number of rounds the ordering took;
+ * *needed = bytes of round `round` (no terminator).  With text == NULL this is
+ * a size query; otherwise capacity must be >= *needed.  The caller decides
+ * where the text goes (the reference: the working directory of rank 0). */
+int amrvr_order_graph_dot_host(int nranks, int nglobal,
+                               const amrvr_box_record* records,
+                               const amrvr_camera* camera, float aspect,
+                               int round, char* text, int64_t capacity,
+                               int64_t* needed, int* nrounds);
+
 /* [host-only] a6 + a11.  computeBoxDepthHint (VolumeRenderer.cpp:541-553) for
  * every global box and the layer order of DirectSendBase.cpp:363-388:
  * order[k] = index into the global table of the k-th layer to blend. */

@@ -263,6 +263,34 @@ class Ref(_Base):
                                        len(log)))
         return out, log.value.decode()
 
+    def order_graphs(self, nranks, records, n, camera, aspect, workdir):
+        """BuildVisibilityOrderedGroup with writeVisibilityGraph = true, run with
+        `workdir` as the current directory: (rank order, [bytes of every
+        visibility_graph_<n>.dot the call wrote, in counter order], log)."""
+        import os
+        import re
+
+        workdir = os.fspath(workdir)
+        before = set(os.listdir(workdir))
+        out = np.zeros(nranks, np.int32)
+        log = C.create_string_buffer(1 << 16)
+        here = os.getcwd()
+        os.chdir(workdir)
+        try:
+            self._check(self.lib.ref_order_write_graph(nranks, n, records, C.byref(camera),
+                                                       C.c_float(aspect),
+                                                       out.ctypes.data_as(_P(C.c_int)), log, len(log)))
+        finally:
+            os.chdir(here)
+        new = [f for f in os.listdir(workdir)
+               if f not in before and re.fullmatch(r"visibility_graph_\d+\.dot", f)]
+        new.sort(key=lambda f: int(re.findall(r"\d+", f)[0]))
+        docs = []
+        for f in new:
+            with open(os.path.join(workdir, f), "rb") as fh:
+                docs.append(fh.read())
+        return out, docs, log.value.decode()
+
     def compose(self, nranks, width, height, layers, owners, hints, rank_order):
         n = len(layers)
         layers = [np.ascontiguousarray(l, np.float32) for l in layers]

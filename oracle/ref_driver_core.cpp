@@ -199,9 +199,35 @@ int ref_paint(const amrvr_box* box, const amrvr_scalar_transform* transform,
 // rank_order[i] = world rank at position i of the ordered group, as produced
 // by the real BuildVisibilityOrderedGroup running collectively on `nranks`
 // thread-ranks, each holding its own boxes of the global table.
+static int refOrderImpl(int nranks, int nglobal,
+                        const amrvr_box_record* records,
+                        const amrvr_camera* camera, float aspect, int useGraph,
+                        bool writeGraph, int* rankOrder, char* log,
+                        int logCapacity);
+
 int ref_order(int nranks, int nglobal, const amrvr_box_record* records,
               const amrvr_camera* camera, float aspect, int useGraph,
               int* rankOrder, char* log, int logCapacity) {
+  return refOrderImpl(nranks, nglobal, records, camera, aspect, useGraph, false,
+                      rankOrder, log, logCapacity);
+}
+
+// The same call with writeVisibilityGraph = true: rank 0 writes
+// visibility_graph_<n>.dot into the CURRENT DIRECTORY, n from a counter that
+// lives as long as this library is loaded (VisibilityOrdering.cpp:319-352).
+int ref_order_write_graph(int nranks, int nglobal,
+                          const amrvr_box_record* records,
+                          const amrvr_camera* camera, float aspect,
+                          int* rankOrder, char* log, int logCapacity) {
+  return refOrderImpl(nranks, nglobal, records, camera, aspect, 1, true,
+                      rankOrder, log, logCapacity);
+}
+
+static int refOrderImpl(int nranks, int nglobal,
+                        const amrvr_box_record* records,
+                        const amrvr_camera* camera, float aspect, int useGraph,
+                        bool writeGraph, int* rankOrder, char* log,
+                        int logCapacity) {
   return guarded([&] {
     CaptureStdout capture;
     const CameraParameters cam = toCamera(*camera);
@@ -224,7 +250,7 @@ int ref_order(int nranks, int nglobal, const amrvr_box_record* records,
       MPI_Group world = MPI_GROUP_NULL;
       MPI_Comm_group(MPI_COMM_WORLD, &world);
       MPI_Group ordered = BuildVisibilityOrderedGroup(
-          cam, aspect, world, rank, nranks, useGraph != 0, false, local,
+          cam, aspect, world, rank, nranks, useGraph != 0, writeGraph, local,
           MPI_COMM_WORLD);
       std::vector<int> positions(nranks), translated(nranks);
       for (int i = 0; i < nranks; ++i) positions[i] = i;

@@ -185,3 +185,53 @@ def test_null_arguments_are_refused():
     out = subprocess.run([sys.executable, worker], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert out.stdout.split()[-2] == "ok"
+
+
+def test_visibility_graph_dot_matches_the_reference(ref, tmp_path):
+    """writeVisibilityGraph: the DOT documents of every round (cycle-breaking
+    rounds included) against the files the reference's own
+    BuildVisibilityOrderedGroup writes (VisibilityOrdering.cpp:319-352)."""
+    cases = []
+    scene = scenes.scene_c4(box_cells=4, nranks=4, rule="round_robin")
+    recs, n = scene.records()
+    for eye in ((1.9, 1.3, 2.4), (-1.2, 0.3, 2.0), (0.5, 0.5, 3.0)):
+        cases.append((4, recs, n, scenes.make_camera(eye=eye), 1.25))
+    rng = np.random.default_rng(23)
+    for _ in range(30):  # random overlapping boxes: most need several rounds
+        n = int(rng.integers(1, 40))
+        recs = (api.BoxRecord * n)()
+        for i in range(n):
+            lo = rng.integers(0, 4, size=3) / 4.0
+            hi = lo + rng.integers(1, 3, size=3) / 4.0
+            for d in range(3):
+                recs[i].min_corner[d], recs[i].max_corner[d] = lo[d], hi[d]
+                recs[i].dims[d] = 4
+            recs[i].owner = int(i * 3 // n)
+        cases.append((3, recs, n, scenes.make_camera(eye=tuple(rng.uniform(-2, 3, size=3))), 1.0))
+    rounds = []
+    for k, (nranks, recs, n, cam, aspect) in enumerate(cases):
+        work = tmp_path / f"case{k}"
+        work.mkdir()
+        want_order, want_docs, _log = ref.order_graphs(nranks, recs, n, cam, aspect, work)
+        got_docs = engine.order_graph_dots_host(nranks, recs, n, cam, aspect)
+        assert len(got_docs) == len(want_docs) >= 1, k
+        for r, (got, want) in enumerate(zip(got_docs, want_docs)):
+            assert got == want, (k, r)
+        got_order, _failed = engine.order_boxes_host(nranks, recs, n, cam, aspect)
+        assert np.array_equal(got_order, want_order)
+        rounds.append(len(want_docs))
+    assert max(rounds) > 1  # the multi-round path was exercised
+
+
+def test_write_visibility_graphs_names_files_like_the_reference(tmp_path, capsys):
+    scene = scenes.scene_c3(box_cells=4)
+    recs, n = scene.records()
+    cam = scenes.make_camera()
+    start = engine._graph_file_counter
+    names = engine.write_visibility_graphs(1, recs, n, cam, 1.0, directory=tmp_path)
+    assert names == [f"visibility_graph_{start + k}.dot" for k in range(len(names))] and names
+    out = capsys.readouterr().out
+    assert out.splitlines() == [f"Wrote visibility graph to '{name}'" for name in names]
+    text = (tmp_path / names[0]).read_text()
+    assert text.startswith("digraph VisibilityGraph {\n  rankdir=LR;\n  box0 [label=\"box 0\\nrank 0\\nminDepth ")
+    assert text.endswith("}\n")
