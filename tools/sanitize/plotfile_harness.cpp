@@ -1,5 +1,6 @@
 #include "../../include/amrvr.h"
 #include <cstdio>
+#include <random>
 #include <string>
 #include <vector>
 namespace amrvr { int report_error(int status, const std::string& msg) { (void)msg; return status; } }
@@ -37,4 +38,34 @@ int main(int argc, char** argv) {
     if (bad) ++refused; else ++opened;
   }
   std::printf("opened %d refused %d\n", opened, refused);
+
+  // convexify on random (overlapping, misaligned, partly outside) box sets
+  std::mt19937 rng(11);
+  long pieces_total = 0;
+  for (int trial = 0; trial < 2000; ++trial) {
+    const int nc = static_cast<int>(rng() % 12), nf = static_cast<int>(rng() % 12);
+    std::vector<int32_t> coarse(6 * static_cast<size_t>(nc) + 6), fine(6 * static_cast<size_t>(nf) + 6);
+    auto fill = [&](std::vector<int32_t>& v, int n, int span) {
+      for (int b = 0; b < n; ++b)
+        for (int d = 0; d < 3; ++d) {
+          const int lo = static_cast<int>(rng() % span) - 4;
+          v[6 * b + d] = lo;
+          v[6 * b + 3 + d] = lo + static_cast<int>(rng() % 9);
+        }
+    };
+    fill(coarse, nc, 24);
+    fill(fine, nf, 48);
+    const int32_t ratio[3] = {1 + static_cast<int32_t>(rng() % 4), 1 + static_cast<int32_t>(rng() % 4),
+                              1 + static_cast<int32_t>(rng() % 4)};
+    int32_t npieces = 0;
+    amrvr_convexify_boxes(nc, coarse.data(), nf, fine.data(), ratio, nullptr, nullptr, 0, &npieces);
+    std::vector<int32_t> out(6 * static_cast<size_t>(npieces) + 6), src(static_cast<size_t>(npieces) + 1);
+    if (amrvr_convexify_boxes(nc, coarse.data(), nf, fine.data(), ratio, out.data(), src.data(), npieces,
+                              &npieces) != 0) {
+      std::printf("convexify failed at trial %d\n", trial);
+      return 1;
+    }
+    pieces_total += npieces;
+  }
+  std::printf("convexify pieces %ld\n", pieces_total);
 }
