@@ -332,6 +332,40 @@ def resolve_scalar_options(summary, log_scale, scalar_range, color_map):
     return transform, value_range, points
 
 
+# ------------------------------------------------------------------ runtime
+# initialize_runtime / finalize_runtime (module.cpp:104-119): in the reference
+# they keep MPI and AMReX up across several render() calls.  Here the thing
+# worth keeping is the GPU context (CUDA context, streams, pinned staging,
+# brick pools), so a held runtime means render() and compute_histogram() reuse
+# one Context instead of creating and destroying one per call.
+_runtime = {"refs": 0, "context": None}
+
+
+def initialize_runtime() -> None:
+    _runtime["refs"] += 1
+
+
+def finalize_runtime() -> None:
+    if _runtime["refs"] == 0:
+        raise RuntimeError("amrVolumeRenderer.finalize_runtime requires a matching "
+                           "initialize_runtime call")
+    _runtime["refs"] -= 1
+    if _runtime["refs"] == 0 and _runtime["context"] is not None:
+        _runtime["context"].close()
+        _runtime["context"] = None
+
+
+def _acquire_context(context):
+    """(context to use, whether the caller must close it)."""
+    if context is not None:
+        return context, False
+    if _runtime["refs"] > 0:
+        if _runtime["context"] is None:
+            _runtime["context"] = Context(device=0)
+        return _runtime["context"], False
+    return Context(device=0), True
+
+
 # ------------------------------------------------------------------- render()
 def render(plotfile, width=512, height=512, box_transparency=0.0, antialiasing=1,
            visibility_graph=True, write_visibility_graph=False, variable=None, min_level=0,
@@ -376,8 +410,7 @@ def render(plotfile, width=512, height=512, box_transparency=0.0, antialiasing=1
     if not Path(str(plotfile)).exists():
         raise RuntimeError(f"plotfile path '{plotfile}' does not exist")
 
-    own_ctx = context is None
-    ctx = Context(device=0) if own_ctx else context
+    ctx, own_ctx = _acquire_context(context)
     scene = None
     dscene = None
     try:
@@ -445,8 +478,7 @@ def compute_histogram(plotfile, variable=None, min_level=0, max_level=-1, log_sc
     (VolumeRenderer.cpp:880-897)."""
     if bins <= 0:
         raise ValueError("binCount must be positive")
-    own_ctx = context is None
-    ctx = Context(device=0) if own_ctx else context
+    ctx, own_ctx = _acquire_context(context)
     scene = None
     try:
         scene = load_plotfile_geometry(ctx, str(plotfile), variable or "", min_level, max_level,

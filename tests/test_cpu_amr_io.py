@@ -340,3 +340,47 @@ def test_convexify_three_levels_is_a_partition_of_the_domain(lib):
             covered[p[2] * scale:(p[5] + 1) * scale, p[1] * scale:(p[4] + 1) * scale,
                     p[0] * scale:(p[3] + 1) * scale] += 1
     assert covered.min() == 1 and covered.max() == 1, fine_domain
+
+
+def test_runtime_refcount_like_the_reference(monkeypatch):
+    """initialize_runtime / finalize_runtime (module.cpp:104-119): nested holds,
+    an unmatched finalize raises with the reference's text, and while a hold is
+    open render()/compute_histogram() share ONE context that the last finalize
+    closes (contexts are faked here: no GPU in this test)."""
+    from amrvolumerenderer_b200 import render as R
+
+    made = []
+
+    class FakeContext:
+        def __init__(self, device=0):
+            self.closed = False
+            made.append(self)
+
+        def close(self):
+            self.closed = True
+
+    monkeypatch.setattr(R, "Context", FakeContext)
+    assert R._runtime == {"refs": 0, "context": None}
+    with pytest.raises(RuntimeError, match="requires a matching initialize_runtime call"):
+        R.finalize_runtime()
+
+    ctx, owned = R._acquire_context(None)  # no hold: one context per call, closed by the caller
+    assert owned and len(made) == 1
+    mine = object()
+    assert R._acquire_context(mine) == (mine, False)  # an explicit context is never taken over
+
+    R.initialize_runtime()
+    R.initialize_runtime()
+    a, owned_a = R._acquire_context(None)
+    b, owned_b = R._acquire_context(None)
+    assert a is b and not owned_a and not owned_b and len(made) == 2
+    R.finalize_runtime()
+    assert not a.closed and R._acquire_context(None)[0] is a
+    R.finalize_runtime()
+    assert a.closed and R._runtime == {"refs": 0, "context": None}
+    with pytest.raises(RuntimeError, match="requires a matching initialize_runtime call"):
+        R.finalize_runtime()
+
+    import amrvolumerenderer_b200 as pkg
+
+    assert pkg.initialize_runtime is R.initialize_runtime and pkg.compute_histogram is R.compute_histogram
