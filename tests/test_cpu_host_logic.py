@@ -235,3 +235,19 @@ def test_write_visibility_graphs_names_files_like_the_reference(tmp_path, capsys
     text = (tmp_path / names[0]).read_text()
     assert text.startswith("digraph VisibilityGraph {\n  rankdir=LR;\n  box0 [label=\"box 0\\nrank 0\\nminDepth ")
     assert text.endswith("}\n")
+
+
+def test_documents_name_only_entry_points_the_header_declares():
+    """Every `amrvr_...` name in DESIGN.md / INTEGRATION.md / README.md is a
+    symbol, type or family prefix of include/amrvr.h (no stale names in the docs)."""
+    import pathlib
+    import re
+
+    root = pathlib.Path(__file__).resolve().parents[1]
+    declared = set(re.findall(r"\b(amrvr_[a-z0-9_]+)\b", (root / "include" / "amrvr.h").read_text()))
+    for doc in ("DESIGN.md", "INTEGRATION.md", "README.md"):
+        for name in set(re.findall(r"`(amrvr_[a-z0-9_]+)", (root / doc).read_text())):
+            if name.endswith("_"):  # a family, e.g. `amrvr_plotfile_*`
+                assert any(d.startswith(name) for d in declared), (doc, name)
+            else:
+                assert name in declared, (doc, name)
