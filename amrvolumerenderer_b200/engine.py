@@ -37,6 +37,29 @@ class Context:
         idbuf = C.create_string_buffer(nccl_id, api.NCCL_ID_BYTES) if nccl_id else None
         _check(self.lib, None, self.lib.amrvr_ctx_create(device, rank, nranks, idbuf, C.byref(self._h)))
 
+    @classmethod
+    def from_env(cls) -> "Context":
+        """The context of this process under `torch.distributed.run` (one process
+        per GPU), the counterpart of the reference being started under mpirun:
+        RANK / WORLD_SIZE / LOCAL_RANK pick rank and device, and rank 0's NCCL
+        id reaches the others through torch.distributed (the default group is
+        created over gloo when the caller has not initialised one; only this one
+        small object travels that way).  Without WORLD_SIZE > 1: device 0, one rank."""
+        import os
+
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        if world <= 1:
+            return cls(device=int(os.environ.get("LOCAL_RANK", "0")))
+        rank = int(os.environ["RANK"])
+        local = int(os.environ.get("LOCAL_RANK", rank))
+        import torch.distributed as dist
+
+        if not dist.is_initialized():
+            dist.init_process_group("gloo")
+        box = [nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        return cls(device=local, rank=rank, nranks=world, nccl_id=box[0])
+
     def close(self):
         if self._h:
             for ptr, _arr in self._pinned_pool.values():

@@ -361,9 +361,9 @@ def _acquire_context(context):
         return context, False
     if _runtime["refs"] > 0:
         if _runtime["context"] is None:
-            _runtime["context"] = Context(device=0)
+            _runtime["context"] = Context.from_env()
         return _runtime["context"], False
-    return Context(device=0), True
+    return Context.from_env(), True
 
 
 # ------------------------------------------------------------------- render()

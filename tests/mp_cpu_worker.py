@@ -17,7 +17,7 @@ sys.path.insert(0, str(ROOT))
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
-from amrvolumerenderer_b200 import engine, scenes  # noqa: E402
+from amrvolumerenderer_b200 import ctypes_api as api, engine, scenes  # noqa: E402
 from oracle.oracle import Oracle  # noqa: E402
 
 
@@ -91,6 +91,38 @@ def check_input_side(rank, world):
             assert most <= 1 and np.array_equal(got, want), (rank, l)
 
 
+def check_context_from_env(rank, world):
+    """Context.from_env() under torchrun: every rank receives rank 0's NCCL id
+    (seen through a wrapped constructor), picks its own rank / device from the
+    environment -- and, there being no GPU here, fails loudly instead of
+    falling back to anything."""
+    import torch
+
+    seen = {}
+    real_init = engine.Context.__init__
+
+    def spy(self, device=0, rank=0, nranks=1, nccl_id=None):
+        seen.update(device=device, rank=rank, nranks=nranks, nccl_id=nccl_id)
+        real_init(self, device=device, rank=rank, nranks=nranks, nccl_id=nccl_id)
+
+    engine.Context.__init__ = spy
+    try:
+        if torch.cuda.is_available():
+            return  # this check is about the CPU-only container
+        try:
+            engine.Context.from_env()
+            raise AssertionError("a context was created without a GPU")
+        except api.AmrvrError as e:
+            assert "no CUDA device" in str(e) or "CPU fallback" in str(e), str(e)
+    finally:
+        engine.Context.__init__ = real_init
+    assert seen["rank"] == rank and seen["nranks"] == world
+    assert seen["device"] == int(os.environ.get("LOCAL_RANK", rank))
+    ids = [None] * world
+    dist.all_gather_object(ids, seen["nccl_id"])
+    assert ids[0] is not None and len(ids[0]) == api.NCCL_ID_BYTES and all(i == ids[0] for i in ids)
+
+
 def main():
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
@@ -135,6 +167,7 @@ def main():
         assert covered[0][0] == 0 and covered[-1][1] == w * h
         assert all(a[1] == c[0] for a, c in zip(covered, covered[1:]))
     check_input_side(rank, world)
+    check_context_from_env(rank, world)
     dist.barrier()
     if rank == 0:
         print("mp_cpu_worker OK", flush=True)

@@ -356,6 +356,10 @@ def test_runtime_refcount_like_the_reference(monkeypatch):
             self.closed = False
             made.append(self)
 
+        @classmethod
+        def from_env(cls):
+            return cls()
+
         def close(self):
             self.closed = True
 
