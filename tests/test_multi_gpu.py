@@ -64,3 +64,19 @@ def test_four_ranks(case):
 @pytest.mark.parametrize("case", ["c4", "c3_aa4", "c1_few_boxes", "c5"])
 def test_eight_ranks(case):
     _run(8, case)
+
+
+@pytest.mark.xfail(reason="first multi-GPU run pending (added with no GPU budget left)", strict=False)
+def test_render_under_torchrun(tmp_path):
+    """render() without a context on 2 ranks (Context.from_env) against the
+    same plotfile rendered by one rank; worker: tests/mp_render_worker.py."""
+    if _gpu_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           str(ROOT / "tests" / "mp_render_worker.py"), str(tmp_path)]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, OMP_NUM_THREADS="1"), cwd=ROOT)
+    tail = (p.stdout + p.stderr)[-3000:]
+    assert p.returncode == 0, tail
+    assert "OK" in p.stdout, tail
