@@ -2,10 +2,7 @@
 visibility_graph_<n>.dot in the working directory, byte-identical to what the
 reference's BuildVisibilityOrderedGroup writes for the same box table
 (VisibilityOrdering.cpp:319-352).  The text path itself is pinned on the CPU
-(tests/test_cpu_host_logic.py); this covers the wiring through DeviceScene.
-
-Written after the round's GPU minutes were spent, so its first run on a B200
-is the driver's: non-strict xfail until it has been seen green once."""
+(tests/test_cpu_host_logic.py); this covers the wiring through DeviceScene."""
 import numpy as np
 import pytest
 
@@ -16,7 +13,6 @@ from amrvolumerenderer_b200.render import render
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.xfail(reason="first B200 run pending (added with no GPU budget left)", strict=False)
 def test_render_writes_the_visibility_graph(ctx, ref, tmp_path, monkeypatch, capsys):
     levels, plo, phi = synthetic_hierarchy(base_cells=16, box_cells=8, nlevels=3, seed=25)
     path = write_plotfile(tmp_path / "plt", levels, ("density",), plo, phi)
