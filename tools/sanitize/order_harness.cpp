@@ -32,6 +32,21 @@ int main() {
     double bmin[3] = {0,0,0}, bmax[3] = {1.4,1.4,1.4};
     checksum += (long)(1e6 * reference_sample_distance(n, recs.data(), bmin, bmax));
     CameraBasis basis; make_camera_basis(cam, basis);
+    // footprints (incl. cameras inside and behind boxes), overlay edges, automatic camera
+    const int W = 1 + static_cast<int>(rng() % 2048), H = 1 + static_cast<int>(rng() % 2048);
+    std::vector<Rect> rects(n);
+    box_footprints(n, recs.data(), basis, cam, W, H, rects.data());
+    for (const Rect& r : rects) {
+      if (r.w < 0 || r.h < 0 || r.x0 < 0 || r.y0 < 0 || r.y0 + r.h > H) { std::printf("bad rect\n"); return 1; }
+      checksum += r.w + r.h;
+    }
+    OverlayEdges edges;
+    make_overlay_edges(bmin, bmax, cam, 1 + static_cast<int>(rng() % 3), W, H, edges);
+    checksum += edges.count;
+    amrvr_camera autocam{};
+    const double up[3] = {0.0, 0.0, 1.0};
+    amrvr_auto_camera(bmin, bmax, static_cast<unsigned>(rng()), (trial & 1) ? up : nullptr, &autocam);
+    checksum += static_cast<long>(autocam.far_plane);
   }
   float table[1024];
   build_color_table(1.0f, 0.5f, 0.0f, 1.0f, nullptr, 0, table);
