@@ -446,6 +446,15 @@ def render(plotfile, width=512, height=512, box_transparency=0.0, antialiasing=1
         frame = ctx.render_frame(dscene, camera, params, colormap=points, root=0,
                                  want_rgba=return_frame, want_rgb8=True)
         if ctx.rank == 0:
+            # the reference's three stage lines and pixel count (VolumeRenderer.cpp:1121-1136,
+            # 1223, 1245, 1253, 1296-1299); times are this rank's CUDA-event stage times
+            stats = frame["stats"]
+            for label, ms in (("per-box rendering", stats.march_ms),
+                              ("visibility graph computation", stats.order_ms),
+                              ("compositing", stats.composite_ms)):
+                print(f"Render: {label} took {ms * 1e-3:.4f} s")
+            root_aa = max(int(round(math.sqrt(int(antialiasing)))), 1)
+            print(f"Render: composed {int(width) * root_aa * int(height) * root_aa} pixels on rank 0")
             save_image(output, frame["rgb8"])
             print(f"Saved volume composited image to '{output}'")
         if return_frame:
