@@ -2,7 +2,7 @@
 # Host code of the library under AddressSanitizer + UndefinedBehaviorSanitizer
 # (+ leak check): the visibility ordering on 300 random box tables (cycle
 # breaking and DOT dump included, plus footprints, overlay edges and the automatic camera on random cameras) and the plotfile reader on 400 corrupted
-# plotfiles, then 2000 random convexify calls.  CPU only; ~4 minutes.  Last run (round 1): no findings.
+# plotfiles, then 2000 random convexify calls.  CPU only; ~2 minutes.  Last run (round 1): no findings.
 set -e
 here="$(cd "$(dirname "$0")" && pwd)"
 src="$here/../../amrvolumerenderer_b200/csrc"
