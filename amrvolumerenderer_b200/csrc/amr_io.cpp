@@ -429,8 +429,9 @@ void box_diff(IBox b1, const IBox& b2, std::vector<IBox>& out) {
   }
 }
 
-int32_t floor_div(int32_t a, int32_t b) {
-  return (a >= 0) ? a / b : -((-a + b - 1) / b);  // amrex::coarsen
+int32_t floor_div(int32_t a, int32_t b) {  // amrex::coarsen; in 64 bits so that -a cannot overflow
+  const int64_t x = a, y = b;
+  return static_cast<int32_t>((x >= 0) ? x / y : -((-x + y - 1) / y));
 }
 
 void convexify_pair(int ncoarse, const int32_t* coarse, int nfine, const int32_t* fine,

@@ -160,6 +160,9 @@ def test_convexify_known_answer_cut_order(lib):
     # nothing to remove / everything removed / negative indices use floor division
     p, s = _convexify(lib, [[0, 0, 0, 3, 3, 3], [4, 0, 0, 7, 3, 3]], np.zeros((0, 6)), (2, 2, 2))
     assert p.tolist() == [[0, 0, 0, 3, 3, 3], [4, 0, 0, 7, 3, 3]] and s.tolist() == [0, 1]
+    # a fine box spanning the whole int32 range coarsens without overflow (INT_MIN / 2)
+    p, s = _convexify(lib, [[0, 0, 0, 7, 7, 7]], [[-2 ** 31, 0, 0, 2 ** 31 - 1, 3, 3]], (2, 2, 2))
+    assert p.tolist() == [[0, 0, 2, 7, 7, 7], [0, 2, 0, 7, 7, 1]]
     p, s = _convexify(lib, [[0, 0, 0, 3, 3, 3]], [[0, 0, 0, 7, 7, 7]], (2, 2, 2))
     assert len(p) == 0
     p, s = _convexify(lib, [[-4, -4, -4, -1, -1, -1]], [[-3, -8, -8, -1, -1, -1]], (2, 2, 2))
