@@ -1,5 +1,7 @@
 #include "../../include/amrvr.h"
+#include <cstdint>
 #include <cstdio>
+#include <utility>
 #include <random>
 #include <string>
 #include <vector>
@@ -68,4 +70,34 @@ int main(int argc, char** argv) {
     pieces_total += npieces;
   }
   std::printf("convexify pieces %ld\n", pieces_total);
+
+  // the same with coordinates at the ends of the int32 range mixed in
+  const int32_t ends[] = {INT32_MIN, INT32_MIN + 1, -1, 0, 1, INT32_MAX - 1, INT32_MAX, 1 << 30, -(1 << 30)};
+  long extreme_total = 0;
+  for (int trial = 0; trial < 20000; ++trial) {
+    const int nc = 1 + static_cast<int>(rng() % 3), nf = 1 + static_cast<int>(rng() % 3);
+    std::vector<int32_t> coarse(6 * static_cast<size_t>(nc)), fine(6 * static_cast<size_t>(nf));
+    auto fill = [&](std::vector<int32_t>& v, int n) {
+      for (int b = 0; b < n; ++b)
+        for (int d = 0; d < 3; ++d) {
+          int32_t a = ends[rng() % 9], z = ends[rng() % 9];
+          if (rng() % 2) {
+            a = static_cast<int32_t>(rng() % 16) - 4;
+            z = a + static_cast<int32_t>(rng() % 8);
+          }
+          if (a > z) std::swap(a, z);
+          v[6 * b + d] = a;
+          v[6 * b + 3 + d] = z;
+        }
+    };
+    fill(coarse, nc);
+    fill(fine, nf);
+    const int32_t ratio[3] = {1 + static_cast<int32_t>(rng() % 4), 1 + static_cast<int32_t>(rng() % 4),
+                              1 + static_cast<int32_t>(rng() % 4)};
+    int32_t npieces = 0;
+    std::vector<int32_t> out(6 * 4096), src(4096);
+    amrvr_convexify_boxes(nc, coarse.data(), nf, fine.data(), ratio, out.data(), src.data(), 4096, &npieces);
+    extreme_total += npieces;
+  }
+  std::printf("convexify pieces at the int32 ends %ld\n", extreme_total);
 }
