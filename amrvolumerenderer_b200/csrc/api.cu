@@ -124,6 +124,7 @@ struct amrvr_ctx {
   cudaEvent_t copy_ev[4] = {};  // copy-group fences (round-robin)
   cudaEvent_t copy_start = nullptr;
   int64_t launches = 0;
+  int64_t order_launches = 0;   // kernels of the visibility ordering (it may run on the helper thread)
   int order_device_min = 1024;  // global box count from which the ordering runs its device kernels
   std::string error;
   HostWorker worker;
@@ -156,6 +157,12 @@ struct amrvr_ctx {
   size_t param_host_bytes = 0;
   cudaEvent_t param_copied = nullptr;   // the last copy out of param_host has completed
   uint8_t* last_rgb8 = nullptr;         // RGB8 frame of the last amrvr_render_frame (root)
+  DeviceBuffer frame_pool;              // fragment pool of single-rank fused frames
+  std::vector<int> last_rank_order;     // visibility order of the last frame (BuildVisibilityOrderedGroup)
+  int last_graph_failed = 0;
+  int table_slot_boxes = 256;           // box records per rank in the upload's allgather (grows, same on all ranks)
+  bool poisoned = false;                // a frame barrier timed out: peers are out of step
+  unsigned long long* frame_stats_host = nullptr;  // pinned: [samples, pushed bytes, stolen tiles, error word]
   // transfer tables already built, keyed by every input of buildColorTable
   struct TableEntry {
     std::vector<unsigned char> key;
@@ -175,6 +182,12 @@ struct amrvr_scene {
   std::vector<LocalBox> local;
   int first_global = 0;  // global index of local box 0
   DeviceBuffer bricks;
+  // replicated: `bricks` holds the bricks of EVERY rank (allgathered once at
+  // upload, 1 B per cell), global box g at global_brick_off[g] -- any GPU can
+  // then march any tile of the frame.  Otherwise only the local bricks.
+  bool replicated = false;
+  std::vector<uint64_t> global_brick_off;
+  std::vector<MarchBox> march_const_global;  // like march_const, for every global box
   float range_min = 0.f, range_max = 1.f;
   // MarchBox fields that depend on the box alone (corners, cell sizes, exactness
   // of the reciprocal, epsilon, brick offset): built once, on the first frame
@@ -311,13 +324,28 @@ struct DeviceOrderBackend final : OrderBackend {
       status = AMRVR_ERR_CUDA;
       return;
     }
-    int max_owner = 0;
-    for (const OrderBox& b : boxes) max_owner = std::max(max_owner, b.owner);
-    int owner_bits = 0;
-    while ((1 << owner_bits) <= max_owner) ++owner_bits;
-    if (launch_order_rank(ctx->order_boxes.as<OrderBox>(), n, ctx->order_scratch_a.ptr,
-                          ctx->order_scratch_b.ptr, owner_bits, ctx->order_priority.as<int32_t>(),
-                          ctx->aux, &ctx->launches) != 0 ||
+    // up to 32 K boxes: rank by counting over all pairs (many CTAs, one launch);
+    // beyond that, or with AMRVR_ORDER_SORT=radix, the single-CTA LSD radix sort
+    const char* mode = std::getenv("AMRVR_ORDER_SORT");
+    const bool radix = n > 32768 || (mode != nullptr && std::strcmp(mode, "radix") == 0);
+    int launched;
+    if (radix) {
+      int max_owner = 0;
+      for (const OrderBox& b : boxes) max_owner = std::max(max_owner, b.owner);
+      int owner_bits = 0;
+      while ((1 << owner_bits) <= max_owner) ++owner_bits;
+      launched = launch_order_rank(ctx->order_boxes.as<OrderBox>(), n, ctx->order_scratch_a.ptr,
+                                   ctx->order_scratch_b.ptr, owner_bits,
+                                   ctx->order_priority.as<int32_t>(), ctx->aux, &ctx->order_launches);
+    } else {
+      launched = (cudaMemsetAsync(ctx->order_priority.ptr, 0, static_cast<size_t>(n) * 4, ctx->aux) ==
+                  cudaSuccess)
+                     ? launch_order_count(ctx->order_boxes.as<OrderBox>(), n,
+                                          ctx->order_priority.as<int32_t>(), ctx->aux,
+                                          &ctx->order_launches)
+                     : 1;
+    }
+    if (launched != 0 ||
         cudaMemcpyAsync(priority.data(), ctx->order_priority.ptr, static_cast<size_t>(n) * 4,
                         cudaMemcpyDeviceToHost, ctx->aux) != cudaSuccess ||
         cudaStreamSynchronize(ctx->aux) != cudaSuccess)
@@ -342,7 +370,7 @@ struct DeviceOrderBackend final : OrderBackend {
       int count = 0;
       if (cudaMemsetAsync(count_dev, 0, 16, ctx->aux) != cudaSuccess ||
           launch_order_pairs(ctx->order_boxes.as<OrderBox>(), n, dir[0], dir[1], dir[2], edges_dev,
-                             capacity, count_dev, ctx->aux, &ctx->launches) != 0 ||
+                             capacity, count_dev, ctx->aux, &ctx->order_launches) != 0 ||
           cudaMemcpyAsync(&count, count_dev, 4, cudaMemcpyDeviceToHost, ctx->aux) !=
               cudaSuccess ||
           cudaStreamSynchronize(ctx->aux) != cudaSuccess) {
@@ -532,7 +560,7 @@ int sym_reserve(amrvr_ctx* ctx, SymBuffer& buf, size_t bytes, bool* all_ok) {
 // Barrier kernel on the ctx stream (row `which` of the flag block).
 int peer_barrier(amrvr_ctx* ctx, int which) {
   ++ctx->barrier_epoch;
-  uint32_t* error_flag = static_cast<uint32_t*>(ctx->sym_flags.local) + kFlagRows * kMaxPeers;
+  uint32_t* error_flag = static_cast<uint32_t*>(ctx->sym_flags.local) + kCtlError;
   LAUNCH_TRY(ctx, launch_peer_barrier(peer_ptrs(ctx->sym_flags), ctx->rank, ctx->nranks, which,
                                       ctx->barrier_epoch, 10ull * 1000 * 1000 * 1000, error_flag,
                                       ctx->stream, &ctx->launches));
@@ -616,7 +644,7 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
     if (want_peer) {
       bool ok = false;
       amrvr_ctx* raw = ctx.get();
-      const int st = sym_reserve(raw, raw->sym_flags, (kFlagRows * kMaxPeers + 4) * sizeof(uint32_t), &ok);
+      const int st = sym_reserve(raw, raw->sym_flags, kCtlWords * sizeof(uint32_t), &ok);
       if (st != AMRVR_OK) {
         g_error = raw->error;
         return st;
@@ -638,6 +666,8 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
     sym_release(*b, ctx->rank);
   if (ctx->peer_error_host != nullptr) cudaFreeHost(ctx->peer_error_host);
   if (ctx->param_host != nullptr) cudaFreeHost(ctx->param_host);
+  if (ctx->frame_stats_host != nullptr) cudaFreeHost(ctx->frame_stats_host);
+  ctx->frame_pool.release();
   if (ctx->param_copied != nullptr) cudaEventDestroy(ctx->param_copied);
   if (ctx->comm != nullptr) nccl_api().CommDestroy(ctx->comm);
   for (DeviceBuffer* b :
@@ -667,7 +697,15 @@ extern "C" const char* amrvr_last_error(const amrvr_ctx* ctx) {
 }
 extern "C" void* amrvr_ctx_stream(amrvr_ctx* ctx) { return ctx ? ctx->stream : nullptr; }
 extern "C" int64_t amrvr_ctx_kernel_launches(const amrvr_ctx* ctx) {
-  return ctx ? ctx->launches : 0;
+  return ctx ? ctx->launches + ctx->order_launches : 0;
+}
+extern "C" int amrvr_ctx_last_rank_order(const amrvr_ctx* ctx, int* rank_order, int* graph_failed) {
+  if (ctx == nullptr || rank_order == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "NULL argument");
+  if (static_cast<int>(ctx->last_rank_order.size()) != ctx->nranks)
+    return fail(nullptr, AMRVR_ERR_INVALID, "no frame has been rendered on this context");
+  for (int i = 0; i < ctx->nranks; ++i) rank_order[i] = ctx->last_rank_order[i];
+  if (graph_failed) *graph_failed = ctx->last_graph_failed;
+  return AMRVR_OK;
 }
 extern "C" const uint8_t* amrvr_ctx_frame_rgb8_device(const amrvr_ctx* ctx) {
   return ctx ? ctx->last_rgb8 : nullptr;
@@ -923,6 +961,67 @@ extern "C" int amrvr_brick_stats(amrvr_ctx* ctx, int nboxes, const amrvr_box* bo
   return AMRVR_OK;
 }
 
+namespace {
+
+size_t padded_cells(const int32_t* dims) {
+  const size_t cells = static_cast<size_t>(std::max(dims[0], 0)) * std::max(dims[1], 0) *
+                       std::max(dims[2], 0);
+  return (cells + 255) & ~static_cast<size_t>(255);
+}
+
+// Global box table: every rank's records, owner-major (the MPI_Allgather(v) of
+// VisibilityOrdering.cpp:85-152 and DirectSendBase.cpp:329-361, once per scene).
+// ONE NCCL allgather of fixed slots [count | records...]; the slot capacity is a
+// per-context value every rank grows in step, so a second round happens only
+// the first time a rank brings more boxes than any rank had before.
+int gather_box_table(amrvr_ctx* ctx, const std::vector<amrvr_box_record>& mine,
+                     std::vector<amrvr_box_record>& global, int* first_global) {
+  const int P = ctx->nranks;
+  NcclApi& nc = nccl_api();
+  const int nboxes = static_cast<int>(mine.size());
+  for (;;) {
+    const int cap = ctx->table_slot_boxes;
+    const size_t slot = 16 + static_cast<size_t>(cap) * sizeof(amrvr_box_record);
+    DeviceBuffer& table = ctx->gather_table;
+    CUDA_TRY(ctx, table.reserve(slot * (P + 1)));
+    std::vector<char> send(slot, 0);
+    std::memcpy(send.data(), &nboxes, sizeof(int));
+    if (nboxes > 0)
+      std::memcpy(send.data() + 16, mine.data(),
+                  sizeof(amrvr_box_record) * static_cast<size_t>(std::min(nboxes, cap)));
+    char* send_dev = table.as<char>() + slot * P;
+    CUDA_TRY(ctx, cudaMemcpyAsync(send_dev, send.data(), slot, cudaMemcpyHostToDevice, ctx->stream));
+    NCCL_TRY(ctx, nc.AllGather(send_dev, table.ptr, slot, ncclChar, ctx->comm, ctx->stream));
+    std::vector<char> all(slot * P);
+    CUDA_TRY(ctx, cudaMemcpyAsync(all.data(), table.ptr, all.size(), cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    int most = 0;
+    for (int r = 0; r < P; ++r) {
+      int c = 0;
+      std::memcpy(&c, all.data() + slot * r, sizeof(int));
+      most = std::max(most, c);
+    }
+    if (most > cap) {  // every rank sees the same counts and grows the same way
+      int grown = cap;
+      while (grown < most) grown *= 2;
+      ctx->table_slot_boxes = grown;
+      continue;
+    }
+    global.clear();
+    for (int r = 0; r < P; ++r) {
+      int c = 0;
+      std::memcpy(&c, all.data() + slot * r, sizeof(int));
+      if (r == ctx->rank) *first_global = static_cast<int>(global.size());
+      const amrvr_box_record* recs = reinterpret_cast<const amrvr_box_record*>(all.data() + slot * r + 16);
+      global.insert(global.end(), recs, recs + c);
+    }
+    return AMRVR_OK;
+  }
+}
+
+}  // namespace
+
 extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                                   const amrvr_scalar_transform* transform, float range_min,
                                   float range_max, amrvr_scene** out) {
@@ -939,41 +1038,10 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
   scene->range_min = range_min;
   scene->range_max = range_max;
   scene->local.resize(static_cast<size_t>(nboxes));
-  size_t brick_bytes = 0;
-  for (int b = 0; b < nboxes; ++b) {
-    LocalBox& L = scene->local[b];
-    for (int d = 0; d < 3; ++d) {
-      L.min_corner[d] = boxes[b].min_corner[d];
-      L.max_corner[d] = boxes[b].max_corner[d];
-      L.dims[d] = boxes[b].dims[d];
-    }
-    L.brick_off = brick_bytes;
-    const size_t cells = static_cast<size_t>(std::max(L.dims[0], 0)) * std::max(L.dims[1], 0) *
-                         std::max(L.dims[2], 0);
-    brick_bytes += (cells + 255) & ~static_cast<size_t>(255);
-  }
-  {
-    const size_t need = std::max<size_t>(brick_bytes, 256);
-    for (size_t i = 0; i < ctx->brick_pools.size(); ++i)
-      if (ctx->brick_pools[i].bytes >= need && ctx->brick_pools[i].bytes <= 2 * need + (1u << 20)) {
-        scene->bricks = ctx->brick_pools[i];
-        ctx->brick_pools.erase(ctx->brick_pools.begin() + static_cast<long>(i));
-        break;
-      }
-    CUDA_TRY(ctx, scene->bricks.reserve(need));
-  }
   Trace tr;
-  tr.mark("upload_setup");
-  {
-    const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene);
-    if (st != AMRVR_OK) {
-      scene->bricks.release();
-      return st;
-    }
-  }
 
-  tr.mark("upload_enqueue");
-  // global table: every rank's records, owner-major (VisibilityOrdering.cpp:85-152)
+  // the box table travels first (nothing is queued on the stream yet, so its one
+  // synchronisation does not wait for FAB copies)
   std::vector<amrvr_box_record> mine(static_cast<size_t>(nboxes));
   for (int b = 0; b < nboxes; ++b) {
     std::memset(&mine[b], 0, sizeof(amrvr_box_record));
@@ -989,43 +1057,74 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
     scene->global = mine;
     scene->first_global = 0;
   } else {
-    NcclApi& nc = nccl_api();
-    const int P = ctx->nranks;
-    DeviceBuffer& tmp = ctx->gather_counts;
-    CUDA_TRY(ctx, tmp.reserve(static_cast<size_t>(P + 1) * sizeof(int)));
-    int* counts_dev = tmp.as<int>();
-    CUDA_TRY(ctx, cudaMemcpyAsync(counts_dev + P, &nboxes, sizeof(int), cudaMemcpyHostToDevice,
-                                  ctx->stream));
-    NCCL_TRY(ctx, nc.AllGather(counts_dev + P, counts_dev, sizeof(int), ncclChar, ctx->comm,
-                               ctx->stream));
-    std::vector<int> counts(static_cast<size_t>(P));
-    CUDA_TRY(ctx, cudaMemcpyAsync(counts.data(), counts_dev, sizeof(int) * P,
-                                  cudaMemcpyDeviceToHost, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    const int most = *std::max_element(counts.begin(), counts.end());
-    const size_t slot = static_cast<size_t>(std::max(most, 1)) * sizeof(amrvr_box_record);
-    DeviceBuffer& table = ctx->gather_table;
-    CUDA_TRY(ctx, table.reserve(slot * (P + 1)));
-    char* send = table.as<char>() + slot * P;
-    if (nboxes > 0)
-      CUDA_TRY(ctx, cudaMemcpyAsync(send, mine.data(), sizeof(amrvr_box_record) * nboxes,
-                                    cudaMemcpyHostToDevice, ctx->stream));
-    NCCL_TRY(ctx, nc.AllGather(send, table.ptr, slot, ncclChar, ctx->comm, ctx->stream));
-    std::vector<char> all(slot * P);
-    CUDA_TRY(ctx, cudaMemcpyAsync(all.data(), table.ptr, all.size(), cudaMemcpyDeviceToHost,
-                                  ctx->stream));
-    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    for (int r = 0; r < P; ++r) {
-      if (r == ctx->rank) scene->first_global = static_cast<int>(scene->global.size());
-      const amrvr_box_record* recs = reinterpret_cast<const amrvr_box_record*>(all.data() + slot * r);
-      scene->global.insert(scene->global.end(), recs, recs + counts[r]);
-    }
+    const int st = gather_box_table(ctx, mine, scene->global, &scene->first_global);
+    if (st != AMRVR_OK) return st;
   }
   tr.mark("upload_table");
+
+  // Brick layout.  On an NVLink box every GPU keeps every brick (1 B per cell: a
+  // 1024^3 volume is 1 GB of 180): rank r's bricks at r * slot, so that a frame
+  // can hand any tile to any GPU.  AMRVR_REPLICATE_MAX_MB bounds the pool
+  // (default 32 GB); above it, and without peer access, each rank keeps its own.
+  const int P = ctx->nranks;
+  std::vector<size_t> rank_bytes(static_cast<size_t>(P), 0);
+  for (const amrvr_box_record& r : scene->global)
+    if (r.owner >= 0 && r.owner < P) rank_bytes[r.owner] += padded_cells(r.dims);
+  const size_t slot = std::max<size_t>(*std::max_element(rank_bytes.begin(), rank_bytes.end()), 256);
+  size_t limit_mb = 32768;
+  if (const char* env = std::getenv("AMRVR_REPLICATE_MAX_MB")) limit_mb = std::strtoull(env, nullptr, 10);
+  scene->replicated = P > 1 && ctx->peer_ok && slot * P <= limit_mb * (size_t(1) << 20);
+  const size_t base = scene->replicated ? slot * ctx->rank : 0;
+  size_t brick_bytes = 0;
+  for (int b = 0; b < nboxes; ++b) {
+    LocalBox& L = scene->local[b];
+    for (int d = 0; d < 3; ++d) {
+      L.min_corner[d] = boxes[b].min_corner[d];
+      L.max_corner[d] = boxes[b].max_corner[d];
+      L.dims[d] = boxes[b].dims[d];
+    }
+    L.brick_off = base + brick_bytes;
+    brick_bytes += padded_cells(L.dims);
+  }
+  if (scene->replicated || P == 1) {
+    scene->global_brick_off.resize(scene->global.size());
+    std::vector<size_t> cursor(static_cast<size_t>(P), 0);
+    for (size_t g = 0; g < scene->global.size(); ++g) {
+      const int owner = scene->global[g].owner;
+      scene->global_brick_off[g] = (scene->replicated ? slot * owner : 0) + cursor[owner];
+      cursor[owner] += padded_cells(scene->global[g].dims);
+    }
+  }
+  {
+    const size_t need = scene->replicated ? slot * P : std::max<size_t>(brick_bytes, 256);
+    for (size_t i = 0; i < ctx->brick_pools.size(); ++i)
+      if (ctx->brick_pools[i].bytes >= need && ctx->brick_pools[i].bytes <= 2 * need + (1u << 20)) {
+        scene->bricks = ctx->brick_pools[i];
+        ctx->brick_pools.erase(ctx->brick_pools.begin() + static_cast<long>(i));
+        break;
+      }
+    CUDA_TRY(ctx, scene->bricks.reserve(need));
+  }
+  tr.mark("upload_setup");
+  {
+    const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene);
+    if (st != AMRVR_OK) {
+      scene->bricks.release();
+      return st;
+    }
+  }
+  tr.mark("upload_enqueue");
+  if (scene->replicated)  // in place: every rank contributes its own slot
+    NCCL_TRY(ctx, nccl_api().AllGather(scene->bricks.as<char>() + slot * ctx->rank, scene->bricks.ptr,
+                                       slot, ncclChar, ctx->comm, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // host FABs may be reused on return
   tr.mark("upload_sync");
   *out = scene.release();
   return AMRVR_OK;
+}
+
+extern "C" int amrvr_scene_is_replicated(const amrvr_scene* scene) {
+  return (scene != nullptr && scene->replicated) ? 1 : 0;
 }
 
 // ---------------------------------------------------------------------------
@@ -1424,28 +1523,56 @@ cudaError_t take_event(amrvr_ctx* ctx, cudaEvent_t* out) {
 }  // namespace
 
 namespace {
-// shared_pool: the layers go into the context's peer-mapped pool so that other
-// GPUs can fold them straight over NVLink (collective: every rank must make
-// the same call; used by amrvr_render_frame only)
-int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
-                  int width, int height, float box_transparency,
-                  float reference_sample_distance_, const amrvr_colormap_pt* pts,
-                  int npts, int count_samples, bool shared_pool, amrvr_layers** out);
+
+// The per-box part of a MarchBox that does not depend on the frame: corners, cell
+// sizes, exactness of the reciprocal, epsilon (VolumePainter.cpp:658-692).
+void fill_march_const(const double* min_corner, const double* max_corner, const int32_t* dims,
+                      uint64_t brick_off, MarchBox& M) {
+  bool pow2 = true;
+  for (int d = 0; d < 3; ++d) {
+    M.lo[d] = static_cast<float>(min_corner[d]);
+    M.hi[d] = static_cast<float>(max_corner[d]);
+    M.n[d] = dims[d];
+    M.cell[d] = (M.hi[d] - M.lo[d]) / static_cast<float>(dims[d]);  // VolumePainter.cpp:676-678
+    M.inv_cell_tiny[d] = std::ldexp(1.0f / M.cell[d], -149);
+    // 2^-149/cell must itself be a (subnormal) float: cell a power of two <= 1
+    pow2 = pow2 && is_pow2_float(M.cell[d]) && M.inv_cell_tiny[d] > 0.0f &&
+           std::ldexp(M.inv_cell_tiny[d], 149) == 1.0f / M.cell[d];
+  }
+  // :680-683 extent, float, x then y then z
+  const float ex = M.hi[0] - M.lo[0], ey = M.hi[1] - M.lo[1], ez = M.hi[2] - M.lo[2];
+  M.eps = std::sqrt(ex * ex + ey * ey + ez * ez) * 0.0001f;
+  M.exact_recip = pow2 ? 1 : 0;
+  M.brick_off = brick_off;
+}
+
+// Pinned staging block of the per-frame parameters: one host->device copy per
+// frame.  The previous copy out of it must have completed before it is rewritten.
+int param_staging(amrvr_ctx* ctx, size_t bytes, unsigned char** out) {
+  if (ctx->param_copied == nullptr)
+    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->param_copied, cudaEventDisableTiming));
+  else
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->param_copied));
+  if (ctx->param_host_bytes < bytes) {
+    if (ctx->param_host != nullptr) CUDA_TRY(ctx, cudaFreeHost(ctx->param_host));
+    ctx->param_host = nullptr;
+    ctx->param_host_bytes = 0;
+    const size_t want = (bytes + 65535) & ~static_cast<size_t>(65535);
+    CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->param_host), want));
+    ctx->param_host_bytes = want;
+  }
+  *out = ctx->param_host;
+  return AMRVR_OK;
+}
+
+constexpr size_t kParamHeader = 64;  // [samples u64 | pushed bytes u64 | stolen tiles u64 | tile counter u32 | ...]
+
 }  // namespace
 
 extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
                               int width, int height, float box_transparency,
                               float reference_sample_distance_, const amrvr_colormap_pt* pts,
                               int npts, int count_samples, amrvr_layers** out) {
-  return raymarch_impl(ctx, scene, camera, width, height, box_transparency,
-                       reference_sample_distance_, pts, npts, count_samples, false, out);
-}
-
-namespace {
-int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
-                  int width, int height, float box_transparency,
-                  float reference_sample_distance_, const amrvr_colormap_pt* pts,
-                  int npts, int count_samples, bool shared_pool, amrvr_layers** out) {
   if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
   REQUIRE(ctx, out != nullptr, "out is NULL");
   *out = nullptr;
@@ -1490,23 +1617,7 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
     mc.assign(static_cast<size_t>(n), MarchBox{});
     for (int b = 0; b < n; ++b) {
       const LocalBox& B = scene->local[b];
-      MarchBox& M = mc[b];
-      bool pow2 = true;
-      for (int d = 0; d < 3; ++d) {
-        M.lo[d] = static_cast<float>(B.min_corner[d]);
-        M.hi[d] = static_cast<float>(B.max_corner[d]);
-        M.n[d] = B.dims[d];
-        M.cell[d] = (M.hi[d] - M.lo[d]) / static_cast<float>(B.dims[d]);  // VolumePainter.cpp:676-678
-        M.inv_cell_tiny[d] = std::ldexp(1.0f / M.cell[d], -149);
-        // 2^-149/cell must itself be a (subnormal) float: cell a power of two <= 1
-        pow2 = pow2 && is_pow2_float(M.cell[d]) && M.inv_cell_tiny[d] > 0.0f &&
-               std::ldexp(M.inv_cell_tiny[d], 149) == 1.0f / M.cell[d];
-      }
-      // :680-683 extent, float, x then y then z
-      const float ex = M.hi[0] - M.lo[0], ey = M.hi[1] - M.lo[1], ez = M.hi[2] - M.lo[2];
-      M.eps = std::sqrt(ex * ex + ey * ey + ez * ez) * 0.0001f;
-      M.exact_recip = pow2 ? 1 : 0;
-      M.brick_off = B.brick_off;
+      fill_march_const(B.min_corner, B.max_corner, B.dims, B.brick_off, mc[b]);
     }
   }
   std::vector<MarchBox> mb(scene->march_const);
@@ -1554,25 +1665,8 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
   L->stats.rays = rays;
   L->stats.fragment_pixels = rays;
 
-  // layer pool: the peer-mapped one, or a recycled one when it is large enough
+  // layer pool: a recycled one when it is large enough
   const size_t need = std::max<size_t>(floats * sizeof(float), 256);
-  if (shared_pool) {
-    // every rank sizes the pool for the largest rank (all of them know every footprint)
-    std::vector<uint64_t> per_rank(static_cast<size_t>(ctx->nranks), 0);
-    for (size_t g = 0; g < scene->global.size(); ++g) {
-      const int owner = scene->global[g].owner;
-      if (owner >= 0 && owner < ctx->nranks)
-        per_rank[owner] += static_cast<uint64_t>(L->global_rects[g].w) * L->global_rects[g].h * 5;
-    }
-    const uint64_t most = *std::max_element(per_rank.begin(), per_rank.end());
-    bool ok = true;
-    const int st = sym_reserve(ctx, ctx->sym_pool, std::max<size_t>(most * sizeof(float), 256), &ok);
-    if (st != AMRVR_OK) return st;
-    if (!ok) return fail(ctx, AMRVR_ERR_CUDA, "peer-mapped layer pool could not be grown on every rank");
-    L->pool.ptr = ctx->sym_pool.local;
-    L->pool.bytes = ctx->sym_pool.cap;
-    L->pool_shared = true;
-  }
   for (size_t i = 0; L->pool.ptr == nullptr && i < ctx->layer_pools.size(); ++i)
     if (ctx->layer_pools[i].bytes >= need) {
       L->pool = ctx->layer_pools[i];
@@ -1581,44 +1675,39 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
     }
   if (L->pool.ptr == nullptr) CUDA_TRY(ctx, L->pool.reserve(need));
 
-  // one parameter block, one host->device copy: [counters 16 B | tables | boxes]
+  // one parameter block, one host->device copy: [header | tables | boxes]
   const size_t tables_bytes = tables.size() * sizeof(float);
   const size_t boxes_bytes = mb.size() * sizeof(MarchBox);
-  const size_t block_bytes = 16 + tables_bytes + boxes_bytes;
-  // staged in pinned memory so the copy is a plain enqueue; the previous copy out
-  // of the staging block must have completed before it is rewritten
-  if (ctx->param_copied == nullptr)
-    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->param_copied, cudaEventDisableTiming));
-  else
-    CUDA_TRY(ctx, cudaEventSynchronize(ctx->param_copied));
-  if (ctx->param_host_bytes < block_bytes) {
-    if (ctx->param_host != nullptr) CUDA_TRY(ctx, cudaFreeHost(ctx->param_host));
-    ctx->param_host = nullptr;
-    ctx->param_host_bytes = 0;
-    const size_t want = (block_bytes + 65535) & ~static_cast<size_t>(65535);
-    CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->param_host), want));
-    ctx->param_host_bytes = want;
+  const size_t block_bytes = kParamHeader + tables_bytes + boxes_bytes;
+  unsigned char* block = nullptr;
+  {
+    const int st = param_staging(ctx, block_bytes, &block);
+    if (st != AMRVR_OK) return st;
   }
-  unsigned char* block = ctx->param_host;
-  std::memset(block, 0, 16);  // counters start at zero
-  if (tables_bytes) std::memcpy(block + 16, tables.data(), tables_bytes);
-  if (boxes_bytes) std::memcpy(block + 16 + tables_bytes, mb.data(), boxes_bytes);
+  std::memset(block, 0, kParamHeader);  // counters start at zero
+  if (tables_bytes) std::memcpy(block + kParamHeader, tables.data(), tables_bytes);
+  if (boxes_bytes) std::memcpy(block + kParamHeader + tables_bytes, mb.data(), boxes_bytes);
   CUDA_TRY(ctx, ctx->march_boxes.reserve(block_bytes));
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->march_boxes.ptr, block, block_bytes, cudaMemcpyHostToDevice,
                                 ctx->stream));
   CUDA_TRY(ctx, cudaEventRecord(ctx->param_copied, ctx->stream));
   unsigned char* dev_block = ctx->march_boxes.as<unsigned char>();
   unsigned long long* counter = reinterpret_cast<unsigned long long*>(dev_block);
-  unsigned* tile_counter = reinterpret_cast<unsigned*>(counter + 1);
+  MarchQueues queues{};  // one queue, one pool: this rank's own boxes
+  queues.nqueues = 1;
+  queues.tile_begin[1] = tiles;
+  queues.counter[0] = reinterpret_cast<unsigned*>(dev_block + 24);
+  queues.pool[0] = L->pool.as<float>();
+  queues.stats = counter;
   CUDA_TRY(ctx, take_event(ctx, &L->t0));
   CUDA_TRY(ctx, take_event(ctx, &L->t1));
   CUDA_TRY(ctx, cudaEventRecord(L->t0, ctx->stream));
   if (n > 0)
-    LAUNCH_TRY(ctx, launch_raymarch(frame, reinterpret_cast<const MarchBox*>(dev_block + 16 + tables_bytes),
+    LAUNCH_TRY(ctx, launch_raymarch(frame, queues,
+                                    reinterpret_cast<const MarchBox*>(dev_block + kParamHeader + tables_bytes),
                                     scene->bricks.as<uint8_t>(),
-                                    reinterpret_cast<const float*>(dev_block + 16),
-                                    L->pool.as<float>(), counter, tile_counter, count_samples != 0,
-                                    ctx->stream, &ctx->launches));
+                                    reinterpret_cast<const float*>(dev_block + kParamHeader),
+                                    count_samples != 0, ctx->stream, &ctx->launches));
   CUDA_TRY(ctx, cudaEventRecord(L->t1, ctx->stream));
   if (count_samples) {
     unsigned long long host = 0;
@@ -1629,7 +1718,6 @@ int raymarch_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* 
   *out = L.release();
   return AMRVR_OK;
 }
-}  // namespace
 
 extern "C" int amrvr_layers_free(amrvr_ctx* ctx, amrvr_layers* layers) {
   if (layers == nullptr) return AMRVR_OK;
@@ -1728,7 +1816,7 @@ namespace {
 int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers* layers,
                    const amrvr_camera* camera, const int* rank_order, int* region_begin,
                    int* region_end, float** piece_out, int64_t* exchanged_bytes,
-                   float* piece_dst = nullptr, bool peer = false, const FoldBytes* bytes = nullptr) {
+                   float* piece_dst = nullptr, const FoldBytes* bytes = nullptr) {
   const int P = ctx->nranks, me = ctx->rank;
   const int W = layers->width, H = layers->height;
   {
@@ -1759,25 +1847,7 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
   std::vector<uint64_t> send_off(P + 1, 0), recv_off(P + 1, 0);
   std::vector<CopyJob> jobs;
   std::vector<uint64_t> recv_slot(static_cast<size_t>(n), 0);  // float offset in recv_buf per global box
-  // peer mode: no exchange step at all -- the fold kernel reads the other GPUs'
-  // fragments where they were marched, over NVLink.  pool_off[g] = float offset
-  // of box g's layer inside its owner's pool (owner-local prefix sum).
-  std::vector<uint64_t> pool_off;
-  if (peer) {
-    pool_off.assign(static_cast<size_t>(n), 0);
-    std::vector<uint64_t> cursor(static_cast<size_t>(P), 0);
-    uint64_t pulled = 0;
-    for (int g = 0; g < n; ++g) {
-      const int owner = scene->global[g].owner;
-      const Rect& r = plan.rects[g];
-      pool_off[g] = cursor[owner];
-      cursor[owner] += static_cast<uint64_t>(r.w) * r.h * 5;
-      int s0, s1;
-      if (owner != me && slice_rows(r, my_begin, my_end, W, &s0, &s1))
-        pulled += static_cast<uint64_t>(s1 - s0) * r.w * 5;
-    }
-    if (exchanged_bytes) *exchanged_bytes = static_cast<int64_t>(pulled * sizeof(float));
-  } else if (P > 1) {
+  if (P > 1) {
     std::vector<uint64_t> send_len(P, 0), recv_len(P, 0);
     for (int g = 0; g < n; ++g) {
       const int owner = scene->global[g].owner;
@@ -1861,9 +1931,6 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
     if (scene->global[g].owner == me) {
       F.base = layers->pool.as<float>() + layers->offs[g - scene->first_global] +
                static_cast<uint64_t>(s0 - r.y0) * r.w * 5;
-    } else if (peer) {
-      F.base = static_cast<const float*>(ctx->sym_pool.peer[scene->global[g].owner]) + pool_off[g] +
-               static_cast<uint64_t>(s0 - r.y0) * r.w * 5;
     } else {
       F.base = ctx->recv_buf.as<float>() + recv_slot[g];
     }
@@ -1887,6 +1954,8 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev[6], ctx->stream));
   CUDA_TRY(ctx, ctx->fold_bins.reserve(std::max<size_t>(
                     fold_scratch_bytes(static_cast<int>(fold.size()), W, my_begin, my_end), 256)));
+  LAUNCH_TRY(ctx, launch_fold_bin(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
+                                  my_begin, my_end, ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
   LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
                               my_begin, my_end, piece_dst, ctx->fold_bins.ptr, ctx->stream, &ctx->launches,
                               bytes));
@@ -2081,6 +2150,8 @@ extern "C" int amrvr_composite_dense(amrvr_ctx* ctx, int width, int height, int 
   }
   CUDA_TRY(ctx, ctx->fold_bins.reserve(std::max<size_t>(
                     fold_scratch_bytes(static_cast<int>(fold.size()), width, begin[me], end[me]), 256)));
+  LAUNCH_TRY(ctx, launch_fold_bin(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), width,
+                                  begin[me], end[me], ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
   LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), width,
                               begin[me], end[me], ctx->piece.as<float>(), ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
   if (piece5_host != nullptr && mine > 0)
@@ -2143,6 +2214,8 @@ extern "C" int amrvr_composite_virtual(amrvr_ctx* ctx, const amrvr_scene* scene,
   }
   CUDA_TRY(ctx, ctx->fold_bins.reserve(std::max<size_t>(
                     fold_scratch_bytes(static_cast<int>(fold.size()), W, 0, W * H), 256)));
+  LAUNCH_TRY(ctx, launch_fold_bin(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W, 0,
+                                  W * H, ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
   LAUNCH_TRY(ctx, launch_fold(ctx->fold_layers.as<FoldLayer>(), static_cast<int>(fold.size()), W,
                               0, W * H, full5_device, ctx->fold_bins.ptr, ctx->stream, &ctx->launches));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -2287,6 +2360,620 @@ extern "C" int amrvr_synchronize(amrvr_ctx* ctx) {
 // ---------------------------------------------------------------------------
 // whole frame
 // ---------------------------------------------------------------------------
+namespace {
+
+struct FrameGeometry {
+  int W, H, RW, RH, sqrt_aa, n;
+  double tmin[3], tmax[3];  // tight bounds of all boxes (VolumeRenderer.cpp:791-849)
+  float ref_step, aspect;
+};
+
+// Overlay edges in device memory (ctx->copy_jobs), or nullptr when the frame has none.
+int upload_overlay_edges(amrvr_ctx* ctx, const amrvr_frame_params* params, const amrvr_camera* camera,
+                         const FrameGeometry& G, const OverlayEdges** out) {
+  *out = nullptr;
+  if (!params->draw_bounding_box || G.n <= 0) return AMRVR_OK;
+  OverlayEdges edges;
+  make_overlay_edges(G.tmin, G.tmax, *camera, 1, G.W, G.H, edges);  // sqrtAA = 1 at :1313
+  CUDA_TRY(ctx, ctx->copy_jobs.reserve(sizeof(OverlayEdges)));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, &edges, sizeof(edges), cudaMemcpyHostToDevice,
+                                ctx->stream));
+  *out = ctx->copy_jobs.as<OverlayEdges>();
+  return AMRVR_OK;
+}
+
+// The root's steps after the gather (VolumeRenderer.cpp:1302-1327): downsample,
+// wireframe, float frame and bytes to the host.  ctx->full holds the RW x RH frame.
+int post_root(amrvr_ctx* ctx, const amrvr_frame_params* params, const amrvr_camera* camera,
+              const FrameGeometry& G, float* rgba5_host, uint8_t* rgb8_host) {
+  const int W = G.W, H = G.H;
+  const size_t out_floats = static_cast<size_t>(W) * H * 5;
+  float* image = ctx->full.as<float>();
+  if (G.sqrt_aa > 1) {
+    CUDA_TRY(ctx, ctx->small.reserve(out_floats * sizeof(float)));
+    LAUNCH_TRY(ctx, launch_downsample(ctx->full.as<float>(), W, H, G.sqrt_aa, ctx->small.as<float>(),
+                                      ctx->stream, &ctx->launches));
+    image = ctx->small.as<float>();
+  }
+  const bool want_bytes = rgb8_host != nullptr || params->rgb8_on_device;
+  const bool fused_bytes = want_bytes && rgba5_host == nullptr;  // overlay + bytes in one pass
+  if (params->draw_bounding_box && G.n > 0 && !fused_bytes) {
+    OverlayEdges edges;
+    make_overlay_edges(G.tmin, G.tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
+    LAUNCH_TRY(ctx, launch_overlay(edges, 1, W, H, image, ctx->stream, &ctx->launches));
+  }
+  if (rgba5_host != nullptr)
+    CUDA_TRY(ctx, cudaMemcpyAsync(rgba5_host, image, out_floats * sizeof(float), cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+  if (want_bytes) {
+    CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
+    if (fused_bytes) {
+      // nobody reads the float frame: the overlay is applied on the way to the bytes
+      const OverlayEdges* edges_dev = nullptr;
+      const int st = upload_overlay_edges(ctx, params, camera, G, &edges_dev);
+      if (st != AMRVR_OK) return st;
+      LAUNCH_TRY(ctx, launch_post_piece(image, 0, W * H, W, H, edges_dev, ctx->rgb8.as<uint8_t>(),
+                                        ctx->stream, &ctx->launches));
+    } else {
+      LAUNCH_TRY(ctx, launch_quantize_rgb8(image, W, H, ctx->rgb8.as<uint8_t>(), ctx->stream,
+                                           &ctx->launches));
+    }
+    ctx->last_rgb8 = ctx->rgb8.as<uint8_t>();
+    if (rgb8_host != nullptr)
+      CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->rgb8.ptr, static_cast<size_t>(W) * H * 3,
+                                    cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  return AMRVR_OK;
+}
+
+// The visibility ordering of the frame (BuildVisibilityOrderedGroup).  A few
+// hundred boxes are pure host work and run on the helper thread beside the
+// march enqueue; larger tables use the device kernels on the aux stream, also
+// from the helper thread.  join_order() must be called before the result is read.
+struct OrderJob {
+  std::vector<int> rank_order;
+  int graph_failed = 0;
+  int status = AMRVR_OK;
+  float host_ms = 0.0f;
+  bool on_thread = false;
+};
+
+void start_order(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera, float aspect,
+                 bool use_graph, OrderJob* job) {
+  const int P = ctx->nranks;
+  const int n = static_cast<int>(scene->global.size());
+  job->rank_order.assign(static_cast<size_t>(P), 0);
+  if (P == 1) return;  // one piece, one owner
+  job->on_thread = true;
+  const auto t0 = std::chrono::steady_clock::now();
+  const amrvr_box_record* recs = scene->global.data();
+  const amrvr_camera cam_copy = *camera;
+  const bool device = n >= ctx->order_device_min;
+  if (device) {  // grow the device buffers here: cudaMalloc on the helper thread would stall the frame
+    const size_t cap = static_cast<size_t>(2 * n + 64);
+    if (ctx->order_boxes.reserve(cap * sizeof(OrderBox)) != cudaSuccess ||
+        ctx->order_scratch_a.reserve(cap * 16) != cudaSuccess ||
+        ctx->order_scratch_b.reserve(cap * 16) != cudaSuccess ||
+        ctx->order_priority.reserve(cap * 4) != cudaSuccess ||
+        ctx->order_edges.reserve((16 * cap + 64) * sizeof(OrderEdge) + 16) != cudaSuccess) {
+      job->status = AMRVR_ERR_CUDA;
+      job->on_thread = false;
+      return;
+    }
+  }
+  ctx->worker.submit([=]() {
+    bool ok;
+    if (device) {
+      cudaSetDevice(ctx->device);
+      DeviceOrderBackend backend(ctx);
+      ok = order_ranks(P, n, recs, cam_copy, aspect, use_graph, backend, job->rank_order.data());
+      if (backend.status != 0) job->status = backend.status;
+    } else {
+      ok = order_ranks(P, n, recs, cam_copy, aspect, use_graph, *host_order_backend(),
+                       job->rank_order.data());
+    }
+    job->graph_failed = ok ? 0 : 1;
+    job->host_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  });
+}
+
+int join_order(amrvr_ctx* ctx, OrderJob* job) {
+  if (job->on_thread) {
+    ctx->worker.wait();
+    job->on_thread = false;
+  }
+  if (job->status != AMRVR_OK) return fail(ctx, job->status, "visibility ordering failed");
+  ctx->last_rank_order = job->rank_order;
+  ctx->last_graph_failed = job->graph_failed;
+  return AMRVR_OK;
+}
+
+// A rank that gives up in the middle of a sharded frame raises its flags on every
+// peer (so that nobody waits for it until the time-out) and their error words.
+void abort_sharded_frame(amrvr_ctx* ctx) {
+  if (!(ctx->peer_ok && ctx->nranks > 1)) return;
+  const PeerPtrs ctl = peer_ptrs(ctx->sym_flags);
+  std::vector<uint32_t> row(static_cast<size_t>(kMaxPeers), 0);
+  const uint32_t epoch = ctx->barrier_epoch, bad = 2u;
+  for (int r = 0; r < ctx->nranks; ++r) {
+    uint32_t* base = static_cast<uint32_t*>(ctl.p[r]);
+    cudaMemcpyAsync(base + kCtlError, &bad, 4, cudaMemcpyHostToDevice, ctx->stream);
+    for (int which = 0; which < 2; ++which)
+      cudaMemcpyAsync(base + which * kMaxPeers + ctx->rank, &epoch, 4, cudaMemcpyHostToDevice, ctx->stream);
+  }
+  cudaStreamSynchronize(ctx->stream);
+  (void)cudaGetLastError();
+  ctx->poisoned = true;
+}
+
+// One rank, or every GPU of an NVLink box with the bricks replicated: the whole
+// frame is four launches per GPU and no collective call.
+//   copy    one parameter block (tables, march items, fold table, overlay edges)
+//   bin     per-band layer lists of this GPU's piece (needs the plan only)
+//   march   queue per image piece, own piece first, then tiles of the others with
+//           the fragments stored into their GPU's pool over NVLink; last CTA
+//           raises "march finished" on every GPU
+//   fold    waits for every GPU's flag, folds the piece from LOCAL memory in the
+//           reference's order and run structure, writes overlay + bytes straight
+//           into the root's frame (and the float piece beside it); last CTA
+//           raises "piece finished"
+//   wait    every GPU waits for all pieces (the root's frame is complete; pools
+//           and queue counters are free for the next frame)
+// Piece p (getPieceRange(N, p, P), DirectSendBase.cpp:59-74) is folded on GPU p.
+// Which rank the REFERENCE would let own piece p -- rank_order[p] from the
+// visibility graph -- does not change a pixel of the gathered frame
+// (SURVEY.md fact 8), so the ordering runs beside the march on the helper thread
+// and is reported (amrvr_ctx_last_rank_order); amrvr_composite, the
+// Compositor::compose seam, places pieces by it.
+int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
+                const amrvr_frame_params* params, const amrvr_colormap_pt* pts, int npts, int root,
+                float* rgba5_host, uint8_t* rgb8_host, amrvr_frame_stats* stats,
+                const FrameGeometry& G, Trace& trace) {
+  const bool sharded = ctx->nranks > 1;
+  const int P = ctx->nranks, me = ctx->rank;
+  const int W = G.W, H = G.H, RW = G.RW, RH = G.RH, n = G.n;
+  const int npix = RW * RH;
+  cudaEvent_t* ev = ctx->ev;
+  if (ctx->poisoned)
+    return fail(ctx, AMRVR_ERR_RUNTIME,
+                "context unusable: an earlier frame lost a peer at a barrier; destroy and recreate it");
+  if (ctx->frame_stats_host == nullptr)
+    CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->frame_stats_host), 64));
+
+  OrderJob order;
+  start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
+  // from here on every return path joins the helper thread
+  auto bail = [&](int status) {
+    if (order.on_thread) ctx->worker.wait();
+    if (sharded) abort_sharded_frame(ctx);
+    return status;
+  };
+  if (sharded) ++ctx->barrier_epoch;
+  const uint32_t epoch = ctx->barrier_epoch;
+
+  // ---- geometry of the frame: footprints, tables, per-box march constants
+  CameraBasis basis;
+  make_camera_basis(*camera, basis);
+  MarchFrame frame{};
+  for (int d = 0; d < 3; ++d) {
+    frame.eye[d] = basis.eye[d];
+    frame.fwd[d] = basis.fwd[d];
+    frame.right[d] = basis.right[d];
+    frame.up[d] = basis.up[d];
+  }
+  frame.aspect = static_cast<float>(RW) / static_cast<float>(std::max(RH, 1));
+  frame.tan_half = std::tan(camera->fov_y_degrees * 0.5f * 3.14159265358979323846f / 180.0f);
+  frame.inv_w = 1.0f / static_cast<float>(RW);
+  frame.inv_h = 1.0f / static_cast<float>(RH);
+  frame.width = RW;
+  frame.height = RH;
+  std::vector<Rect> rects(static_cast<size_t>(n));
+  box_footprints(n, scene->global.data(), basis, *camera, RW, RH, rects.data());
+  if (scene->march_const_global.size() != static_cast<size_t>(n)) {
+    std::vector<MarchBox>& mc = const_cast<amrvr_scene*>(scene)->march_const_global;
+    mc.assign(static_cast<size_t>(n), MarchBox{});
+    for (int g = 0; g < n; ++g)
+      fill_march_const(scene->global[g].min_corner, scene->global[g].max_corner, scene->global[g].dims,
+                       scene->global_brick_off[g], mc[g]);
+  }
+  const float alpha_scale = std::min(std::max(1.0f - params->box_transparency, 0.0f), 1.0f);
+  std::vector<float> table_norm, tables;  // one table per distinct normalisation factor
+  std::vector<MarchBox> per_box(scene->march_const_global);
+  for (int g = 0; g < n; ++g) {
+    const amrvr_box_record& B = scene->global[g];
+    float step, norm;
+    box_sampling(B.min_corner, B.max_corner, B.dims, G.ref_step, &step, &norm);
+    int which = -1;
+    for (size_t t = 0; t < table_norm.size(); ++t)
+      if (std::memcmp(&table_norm[t], &norm, sizeof(float)) == 0) which = static_cast<int>(t);
+    if (which < 0) {
+      which = static_cast<int>(table_norm.size());
+      table_norm.push_back(norm);
+      tables.resize(tables.size() + 4 * AMRVR_COLOR_TABLE_SIZE);
+      std::memcpy(tables.data() + static_cast<size_t>(which) * 4 * AMRVR_COLOR_TABLE_SIZE,
+                  cached_color_table(ctx, alpha_scale, norm, scene->range_min, scene->range_max, pts, npts),
+                  4 * AMRVR_COLOR_TABLE_SIZE * sizeof(float));
+    }
+    per_box[g].table = which;
+    per_box[g].step = step;
+    per_box[g].margin = inside_margin(per_box[g], basis.eye);
+  }
+  // boxes by table, so that a launch moves through the AMR levels once
+  std::vector<int> by_table(static_cast<size_t>(n));
+  for (int g = 0; g < n; ++g) by_table[g] = g;
+  std::stable_sort(by_table.begin(), by_table.end(),
+                   [&](int a, int b) { return per_box[a].table < per_box[b].table; });
+
+  // ---- march items: queue p = the rows of every footprint that fall into piece p
+  std::vector<int> pbegin(static_cast<size_t>(P)), pend(static_cast<size_t>(P));
+  for (int p = 0; p < P; ++p) piece_range(npix, p, P, &pbegin[p], &pend[p]);
+  std::vector<MarchBox> items;
+  items.reserve(static_cast<size_t>(n) * 2);
+  std::vector<int> my_item(static_cast<size_t>(n), -1);  // global box -> its item in MY queue
+  MarchQueues queues{};
+  queues.nqueues = P;
+  queues.mine = sharded ? me : 0;
+  std::vector<uint64_t> pool_floats(static_cast<size_t>(P), 0);
+  int tiles = 0;
+  int64_t my_rays = 0;
+  for (int p = 0; p < P; ++p) {
+    queues.tile_begin[p] = tiles;
+    for (int k = 0; k < n; ++k) {
+      const int g = by_table[k];
+      const Rect& r = rects[g];
+      int s0, s1;
+      if (!slice_rows(r, pbegin[p], pend[p], RW, &s0, &s1)) continue;
+      MarchBox M = per_box[g];
+      M.rx0 = r.x0;
+      M.ry0 = s0;
+      M.rw = r.w;
+      M.rh = s1 - s0;
+      M.tiles_x = (r.w + 15) / 16;
+      M.tile_base = tiles;
+      tiles += M.tiles_x * ((M.rh + 15) / 16);
+      M.layer_off = pool_floats[p];
+      M.dest = p;
+      pool_floats[p] += static_cast<uint64_t>(M.rw) * M.rh * 5;
+      if (p == queues.mine) {
+        my_item[g] = static_cast<int>(items.size());
+        my_rays += static_cast<int64_t>(M.rw) * M.rh;
+      }
+      items.push_back(M);
+    }
+  }
+  queues.tile_begin[P] = tiles;
+  frame.nboxes = static_cast<int>(items.size());
+  frame.ntiles = tiles;
+  {  // the other queues, heaviest first
+    std::vector<int> others;
+    for (int p = 0; p < P; ++p)
+      if (p != queues.mine) others.push_back(p);
+    std::stable_sort(others.begin(), others.end(), [&](int a, int b) {
+      return queues.tile_begin[a + 1] - queues.tile_begin[a] > queues.tile_begin[b + 1] - queues.tile_begin[b];
+    });
+    for (size_t i = 0; i < others.size(); ++i) queues.steal_order[i] = others[i];
+  }
+  trace.mark("plan");
+
+  // ---- buffers (the peer-mapped ones grow collectively: every rank computes the same sizes)
+  const bool bytes_mode = G.sqrt_aa == 1;  // the fold writes overlay + RGB8 itself
+  const bool single_bytes = !sharded && bytes_mode && rgba5_host == nullptr &&
+                            (rgb8_host != nullptr || params->rgb8_on_device);
+  const size_t most_floats = *std::max_element(pool_floats.begin(), pool_floats.end());
+  float* pool_local = nullptr;
+  if (sharded) {
+    bool ok_a = true, ok_b = true, ok_c = true;
+    const size_t max_piece = static_cast<size_t>(npix) / P + static_cast<size_t>(npix) % P;
+    int st = sym_reserve(ctx, ctx->sym_pool, std::max<size_t>(most_floats * sizeof(float), 256), &ok_a);
+    if (st == AMRVR_OK) st = sym_reserve(ctx, ctx->sym_piece, std::max<size_t>(max_piece * 20, 256), &ok_b);
+    if (st == AMRVR_OK && bytes_mode)
+      st = sym_reserve(ctx, ctx->sym_rgb8, static_cast<size_t>(W) * H * 3, &ok_c);
+    if (st != AMRVR_OK) return bail(st);
+    if (!ok_a || !ok_b || !ok_c)
+      return bail(fail(ctx, AMRVR_ERR_CUDA, "peer-mapped frame buffers could not be grown on every rank"));
+    pool_local = static_cast<float*>(ctx->sym_pool.local);
+    for (int p = 0; p < P; ++p) {
+      queues.pool[p] = static_cast<float*>(ctx->sym_pool.peer[p]);
+      queues.ctl[p] = static_cast<unsigned*>(ctx->sym_flags.peer[p]);
+      queues.counter[p] = queues.ctl[p] + kCtlTileCounter;
+    }
+    queues.me = me;
+    queues.nranks = P;
+    queues.epoch = epoch;
+    queues.signal_row = 0;
+  } else {
+    if (cudaSuccess != ctx->frame_pool.reserve(std::max<size_t>(most_floats * sizeof(float), 256)))
+      return bail(fail(ctx, AMRVR_ERR_CUDA, "fragment pool allocation failed"));
+    pool_local = ctx->frame_pool.as<float>();
+    queues.pool[0] = pool_local;
+  }
+  if (me == root || !sharded) {
+    if (ctx->full.reserve(static_cast<size_t>(npix) * 20) != cudaSuccess)
+      return bail(fail(ctx, AMRVR_ERR_CUDA, "frame buffer allocation failed"));
+    if (single_bytes && ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3) != cudaSuccess)
+      return bail(fail(ctx, AMRVR_ERR_CUDA, "frame buffer allocation failed"));
+  }
+
+  // ---- fold table of my piece, in the reference's blend order with its run ids
+  // (DirectSendBase.cpp:363-407)
+  std::vector<int> blend_order(static_cast<size_t>(n));
+  layer_order(n, scene->global.data(), *camera, nullptr, blend_order.data());
+  std::vector<FoldLayer> fold;
+  fold.reserve(static_cast<size_t>(n));
+  {
+    int run = -1, prev_owner = -1;
+    for (int pos = 0; pos < n; ++pos) {
+      const int g = blend_order[pos];
+      if (pos == 0 || scene->global[g].owner != prev_owner) ++run;
+      prev_owner = scene->global[g].owner;
+      if (my_item[g] < 0) continue;
+      const MarchBox& M = items[static_cast<size_t>(my_item[g])];
+      FoldLayer F{};
+      F.base = pool_local + M.layer_off;
+      F.x0 = M.rx0;
+      F.w = M.rw;
+      F.row0 = M.ry0;
+      F.row1 = M.ry0 + M.rh;
+      F.run = run;
+      fold.push_back(F);
+    }
+  }
+  const int my_begin = pbegin[queues.mine], my_end = pend[queues.mine];
+  OverlayEdges edges{};
+  const bool overlay = bytes_mode && params->draw_bounding_box && n > 0;
+  if (overlay) make_overlay_edges(G.tmin, G.tmax, *camera, 1, W, H, edges);
+
+  // ---- one parameter block: [header | tables | items | fold table | overlay edges]
+  const size_t tables_bytes = tables.size() * sizeof(float);
+  const size_t items_bytes = items.size() * sizeof(MarchBox);
+  const size_t fold_bytes = fold.size() * sizeof(FoldLayer);
+  const size_t off_items = kParamHeader + tables_bytes;
+  const size_t off_fold = off_items + items_bytes;
+  const size_t off_edges = off_fold + fold_bytes;
+  const size_t block_bytes = off_edges + sizeof(OverlayEdges);
+  unsigned char* block = nullptr;
+  {
+    const int st = param_staging(ctx, block_bytes, &block);
+    if (st != AMRVR_OK) return bail(st);
+  }
+  std::memset(block, 0, kParamHeader);
+  if (tables_bytes) std::memcpy(block + kParamHeader, tables.data(), tables_bytes);
+  if (items_bytes) std::memcpy(block + off_items, items.data(), items_bytes);
+  if (fold_bytes) std::memcpy(block + off_fold, fold.data(), fold_bytes);
+  std::memcpy(block + off_edges, &edges, sizeof(OverlayEdges));
+  if (ctx->march_boxes.reserve(block_bytes) != cudaSuccess ||
+      ctx->fold_bins.reserve(std::max<size_t>(
+          fold_scratch_bytes(static_cast<int>(fold.size()), RW, my_begin, my_end), 256)) != cudaSuccess)
+    return bail(fail(ctx, AMRVR_ERR_CUDA, "parameter block allocation failed"));
+  unsigned char* dev_block = ctx->march_boxes.as<unsigned char>();
+  queues.stats = reinterpret_cast<unsigned long long*>(dev_block);
+  if (!sharded) queues.counter[0] = reinterpret_cast<unsigned*>(dev_block + 24);
+  const FoldLayer* fold_dev = reinterpret_cast<const FoldLayer*>(dev_block + off_fold);
+  trace.mark("tables");
+
+  auto try_cuda = [&](cudaError_t e, const char* what) {
+    return (e == cudaSuccess) ? AMRVR_OK
+                              : fail(ctx, AMRVR_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+  };
+  auto try_launch = [&](int e, const char* what) {
+    return (e == 0) ? AMRVR_OK
+                    : fail(ctx, AMRVR_ERR_CUDA,
+                           std::string(what) + ": " + cudaGetErrorString(static_cast<cudaError_t>(e)));
+  };
+  int st = try_cuda(cudaMemcpyAsync(dev_block, block, block_bytes, cudaMemcpyHostToDevice, ctx->stream),
+                    "parameter copy");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->param_copied, ctx->stream), "event");
+  if (st == AMRVR_OK)
+    st = try_launch(launch_fold_bin(fold_dev, static_cast<int>(fold.size()), RW, my_begin, my_end,
+                                    ctx->fold_bins.ptr, ctx->stream, &ctx->launches),
+                    "fold_bin");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[1], ctx->stream), "event");
+  if (st == AMRVR_OK)
+    st = try_launch(launch_raymarch(frame, queues, reinterpret_cast<const MarchBox*>(dev_block + off_items),
+                                    scene->bricks.as<uint8_t>(),
+                                    reinterpret_cast<const float*>(dev_block + kParamHeader),
+                                    params->count_samples != 0, ctx->stream, &ctx->launches),
+                    "march");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[2], ctx->stream), "event");
+  trace.mark("march_enqueue");
+
+  // ---- fold (+ bytes) of my piece
+  FoldSync sync{};
+  if (sharded) {
+    sync.ctl = peer_ptrs(ctx->sym_flags);
+    sync.me = me;
+    sync.nranks = P;
+    sync.wait_row = 0;
+    sync.signal_row = 1;
+    sync.epoch = epoch;
+    sync.timeout_ns = 10ull * 1000 * 1000 * 1000;
+  }
+  FoldBytes fb{nullptr, H, nullptr};
+  float* piece_dst;
+  if (sharded) {
+    piece_dst = static_cast<float*>(ctx->sym_piece.local);
+    if (bytes_mode) fb.rgb8 = static_cast<uint8_t*>(ctx->sym_rgb8.peer[root]);
+  } else {
+    piece_dst = single_bytes ? nullptr : ctx->full.as<float>();
+    if (single_bytes) fb.rgb8 = ctx->rgb8.as<uint8_t>();
+  }
+  if (fb.rgb8 != nullptr && overlay) fb.edges = reinterpret_cast<const OverlayEdges*>(dev_block + off_edges);
+  if (st == AMRVR_OK)
+    st = try_launch(launch_fold(fold_dev, static_cast<int>(fold.size()), RW, my_begin, my_end, piece_dst,
+                                ctx->fold_bins.ptr, ctx->stream, &ctx->launches,
+                                fb.rgb8 != nullptr ? &fb : nullptr, sharded ? &sync : nullptr),
+                    "fold");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[3], ctx->stream), "event");
+  if (st == AMRVR_OK && sharded)
+    st = try_launch(launch_peer_wait(sync.ctl, me, P, 1, epoch, sync.timeout_ns, ctx->stream, &ctx->launches),
+                    "wait");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[4], ctx->stream), "event");
+  if (st != AMRVR_OK) return bail(st);
+  trace.mark("fold_enqueue");
+
+  // ---- the root's frame
+  ctx->last_rgb8 = nullptr;
+  const bool is_root = !sharded || me == root;
+  if (is_root) {
+    const bool need_floats = rgba5_host != nullptr || !bytes_mode ||
+                             (!sharded && !single_bytes);
+    if (sharded && need_floats) {
+      // the root pulls the float pieces over NVLink (ImageColorOnly::Gather)
+      for (int p = 0; p < P; ++p)
+        if (pend[p] > pbegin[p])
+          if (cudaMemcpyAsync(ctx->full.as<float>() + static_cast<size_t>(pbegin[p]) * 5,
+                              ctx->sym_piece.peer[p], static_cast<size_t>(pend[p] - pbegin[p]) * 20,
+                              cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess)
+            return bail(fail(ctx, AMRVR_ERR_CUDA, "piece gather failed"));
+    }
+    if (fb.rgb8 != nullptr && !(sharded && !bytes_mode)) {
+      // the bytes are complete (the fold wrote overlay + RGB8)
+      uint8_t* built = sharded ? static_cast<uint8_t*>(ctx->sym_rgb8.local) : ctx->rgb8.as<uint8_t>();
+      ctx->last_rgb8 = built;
+      if (rgba5_host != nullptr) {
+        float* image = ctx->full.as<float>();
+        if (params->draw_bounding_box && n > 0) {
+          OverlayEdges e2;
+          make_overlay_edges(G.tmin, G.tmax, *camera, 1, W, H, e2);
+          if (launch_overlay(e2, 1, W, H, image, ctx->stream, &ctx->launches) != 0)
+            return bail(fail(ctx, AMRVR_ERR_CUDA, "overlay failed"));
+        }
+        if (cudaMemcpyAsync(rgba5_host, image, static_cast<size_t>(W) * H * 20, cudaMemcpyDeviceToHost,
+                            ctx->stream) != cudaSuccess)
+          return bail(fail(ctx, AMRVR_ERR_CUDA, "frame readback failed"));
+      }
+      if (rgb8_host != nullptr &&
+          cudaMemcpyAsync(rgb8_host, built, static_cast<size_t>(W) * H * 3, cudaMemcpyDeviceToHost,
+                          ctx->stream) != cudaSuccess)
+        return bail(fail(ctx, AMRVR_ERR_CUDA, "frame readback failed"));
+    } else {
+      st = post_root(ctx, params, camera, G, rgba5_host, rgb8_host);
+      if (st != AMRVR_OK) return bail(st);
+    }
+  }
+  if (cudaEventRecord(ev[5], ctx->stream) != cudaSuccess)
+    return bail(fail(ctx, AMRVR_ERR_CUDA, "event record failed"));
+  trace.mark("post_enqueue");
+
+  // ---- statistics and the barrier time-out word come back with one small copy
+  if (cudaMemcpyAsync(ctx->frame_stats_host, dev_block, 24, cudaMemcpyDeviceToHost, ctx->stream) !=
+      cudaSuccess)
+    return bail(fail(ctx, AMRVR_ERR_CUDA, "statistics readback failed"));
+  ctx->frame_stats_host[3] = 0;
+  if (sharded &&
+      cudaMemcpyAsync(ctx->frame_stats_host + 3, static_cast<uint32_t*>(ctx->sym_flags.local) + kCtlError,
+                      sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess)
+    return bail(fail(ctx, AMRVR_ERR_CUDA, "statistics readback failed"));
+  if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
+    if (order.on_thread) ctx->worker.wait();
+    ctx->poisoned = sharded;
+    return fail(ctx, AMRVR_ERR_CUDA, std::string("frame failed: ") + cudaGetErrorString(cudaGetLastError()));
+  }
+  trace.mark("final_sync");
+  st = join_order(ctx, &order);
+  if (st != AMRVR_OK) return st;
+  if (sharded && static_cast<uint32_t>(ctx->frame_stats_host[3]) != 0) {
+    ctx->poisoned = true;
+    return fail(ctx, AMRVR_ERR_RUNTIME,
+                static_cast<uint32_t>(ctx->frame_stats_host[3]) == 2u
+                    ? "a peer rank gave up in the middle of the frame"
+                    : "a peer GPU did not reach the frame barrier within 10 s");
+  }
+  if (stats != nullptr) {
+    std::memset(stats, 0, sizeof(*stats));
+    stats->samples = static_cast<int64_t>(ctx->frame_stats_host[0]);
+    stats->exchanged_bytes = static_cast<int64_t>(ctx->frame_stats_host[1]);
+    stats->stolen_tiles = static_cast<int64_t>(ctx->frame_stats_host[2]);
+    stats->tiles = tiles;
+    stats->fragment_pixels = my_rays;
+    stats->order_ms = order.host_ms;  // beside the march, on the helper thread: host wall time
+    cudaEventElapsedTime(&stats->march_ms, ev[1], ev[2]);
+    cudaEventElapsedTime(&stats->fold_ms, ev[2], ev[3]);
+    cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[4]);  // fold + both hand-shakes
+    stats->gather_ms = 0.0f;
+    cudaEventElapsedTime(&stats->post_ms, ev[4], ev[5]);
+  }
+  return AMRVR_OK;
+}
+
+// Ranks that cannot map each other's memory (or scenes too large to replicate):
+// every rank marches its own boxes, the fragments travel as one grouped NCCL
+// send/recv (alltoallv, DirectSendBase.cpp:76-177 without the empty frames), the
+// pieces are folded where the visibility order puts them and gathered on the root.
+int frame_exchange(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
+                   const amrvr_frame_params* params, const amrvr_colormap_pt* pts, int npts, int root,
+                   float* rgba5_host, uint8_t* rgb8_host, amrvr_frame_stats* stats,
+                   const FrameGeometry& G, Trace& trace) {
+  cudaEvent_t* ev = ctx->ev;
+  OrderJob order;
+  start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
+  amrvr_layers* layers = nullptr;
+  int st = amrvr_raymarch(ctx, scene, camera, G.RW, G.RH, params->box_transparency, G.ref_step, pts, npts,
+                          params->count_samples, &layers);
+  {
+    const int joined = join_order(ctx, &order);  // the helper thread writes into `order`
+    if (st == AMRVR_OK) st = joined;
+  }
+  if (st != AMRVR_OK) {
+    amrvr_layers_free(ctx, layers);
+    return st;
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
+  trace.mark("march_enqueue");
+  CUDA_TRY(ctx, cudaEventRecord(ev[2], ctx->stream));
+  trace.mark("order");
+  int begin = 0, end = 0;
+  float* piece = nullptr;
+  int64_t exchanged = 0;
+  if (ctx->rank == root) CUDA_TRY(ctx, ctx->full.reserve(static_cast<size_t>(G.RW) * G.RH * 20));
+  st = composite_impl(ctx, scene, layers, camera, order.rank_order.data(), &begin, &end, &piece,
+                      &exchanged);
+  if (st == AMRVR_OK) {
+    CUDA_TRY(ctx, cudaEventRecord(ev[3], ctx->stream));
+    trace.mark("composite_enqueue");
+    std::vector<int> spans(static_cast<size_t>(2 * ctx->nranks));
+    for (int pc = 0; pc < ctx->nranks; ++pc)
+      piece_range(G.RW * G.RH, pc, ctx->nranks, &spans[2 * order.rank_order[pc]],
+                  &spans[2 * order.rank_order[pc] + 1]);
+    st = gather_impl(ctx, piece, spans, root, ctx->full.as<float>());
+  }
+  if (st != AMRVR_OK) {
+    amrvr_layers_free(ctx, layers);
+    return st;
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ev[4], ctx->stream));
+  ctx->last_rgb8 = nullptr;
+  if (ctx->rank == root) {
+    st = post_root(ctx, params, camera, G, rgba5_host, rgb8_host);
+    if (st != AMRVR_OK) {
+      amrvr_layers_free(ctx, layers);
+      return st;
+    }
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ev[5], ctx->stream));
+  trace.mark("post_enqueue");
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  trace.mark("final_sync");
+  if (stats != nullptr) {
+    std::memset(stats, 0, sizeof(*stats));
+    amrvr_march_stats ms;
+    if (amrvr_layers_stats(layers, &ms) == AMRVR_OK) {
+      stats->samples = ms.samples;
+      stats->march_ms = ms.kernel_ms;
+      stats->fragment_pixels = ms.fragment_pixels;
+    }
+    stats->order_ms = order.host_ms;
+    cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[3]);
+    cudaEventElapsedTime(&stats->gather_ms, ev[3], ev[4]);
+    cudaEventElapsedTime(&stats->post_ms, ev[4], ev[5]);
+    cudaEventElapsedTime(&stats->fold_ms, ev[6], ev[7]);
+    stats->exchanged_bytes = exchanged;
+  }
+  amrvr_layers_free(ctx, layers);
+  return AMRVR_OK;
+}
+
+}  // namespace
 
 extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
                                   const amrvr_camera* camera, const amrvr_frame_params* params,
@@ -2296,263 +2983,84 @@ extern "C" int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
   REQUIRE(ctx, scene && camera && params, "NULL argument");
   REQUIRE(ctx, params->width > 0 && params->height > 0, "width and height must be positive");
   REQUIRE(ctx, root >= 0 && root < ctx->nranks, "root out of range");
-  const int sqrt_aa = static_cast<int>(std::lround(std::sqrt(static_cast<double>(params->antialiasing))));
-  REQUIRE(ctx, params->antialiasing >= 1 && sqrt_aa * sqrt_aa == params->antialiasing,
+  REQUIRE(ctx, npts >= 0 && (npts == 0 || pts != nullptr), "bad colour map");
+  FrameGeometry G{};
+  G.sqrt_aa = static_cast<int>(std::lround(std::sqrt(static_cast<double>(params->antialiasing))));
+  REQUIRE(ctx, params->antialiasing >= 1 && G.sqrt_aa * G.sqrt_aa == params->antialiasing,
           "antialiasing must be a positive perfect square");  // VolumeRenderer.cpp:425-437
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  const int W = params->width, H = params->height;
-  const int RW = W * sqrt_aa, RH = H * sqrt_aa;
-  const float aspect = static_cast<float>(W) / static_cast<float>(H);
-  const int n = static_cast<int>(scene->global.size());
-
+  G.W = params->width;
+  G.H = params->height;
+  G.RW = G.W * G.sqrt_aa;
+  G.RH = G.H * G.sqrt_aa;
+  REQUIRE(ctx, static_cast<int64_t>(G.RW) * G.RH < (1LL << 31), "frame too large");
+  G.aspect = static_cast<float>(G.W) / static_cast<float>(G.H);
+  G.n = static_cast<int>(scene->global.size());
   // tight bounds of all boxes (VolumeRenderer.cpp:791-849), also the fallback
   // bounds of the reference step
-  double tmin[3] = {0, 0, 0}, tmax[3] = {0, 0, 0};
-  for (int d = 0; d < 3 && n > 0; ++d) {
+  for (int d = 0; d < 3 && G.n > 0; ++d) {
     double lo = scene->global[0].min_corner[d], hi = scene->global[0].max_corner[d];
-    for (int g = 1; g < n; ++g) {
+    for (int g = 1; g < G.n; ++g) {
       lo = std::min(lo, scene->global[g].min_corner[d]);
       hi = std::max(hi, scene->global[g].max_corner[d]);
     }
-    tmin[d] = static_cast<double>(static_cast<float>(lo));
-    tmax[d] = static_cast<double>(static_cast<float>(hi));
+    G.tmin[d] = static_cast<double>(static_cast<float>(lo));
+    G.tmax[d] = static_cast<double>(static_cast<float>(hi));
   }
-  const float ref_step = reference_sample_distance(n, scene->global.data(), tmin, tmax);
+  G.ref_step = reference_sample_distance(G.n, scene->global.data(), G.tmin, G.tmax);
 
   Trace trace;
-  cudaEvent_t* ev = ctx->ev;
-  CUDA_TRY(ctx, cudaEventRecord(ev[0], ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
   trace.mark("setup");
-  amrvr_layers* layers = nullptr;
-  // Peer mode (all ranks on one NVLink box): layers, pieces and the byte frame
-  // live in peer-mapped buffers; the only cross-GPU steps are two flag barriers.
-  const bool peer = ctx->peer_ok && ctx->nranks > 1;
-  int st = AMRVR_OK;
-  if (peer) {
-    const size_t npix_render = static_cast<size_t>(RW) * RH;
-    const size_t max_piece = npix_render / ctx->nranks + npix_render % ctx->nranks;
-    bool ok_a = true, ok_b = true;
-    st = sym_reserve(ctx, ctx->sym_piece, std::max<size_t>(max_piece * 20, 256), &ok_a);
-    if (st == AMRVR_OK) st = sym_reserve(ctx, ctx->sym_rgb8, static_cast<size_t>(W) * H * 3, &ok_b);
-    if (st != AMRVR_OK) return st;
-    if (!ok_a || !ok_b) return fail(ctx, AMRVR_ERR_CUDA, "peer-mapped frame buffers could not be grown");
-  }
-  // The visibility ordering of a few hundred boxes is pure host work on the global
-  // table (no ctx state): it runs on a helper thread while this thread sets up and
-  // enqueues the march, so the composite is enqueued as soon as both are done.
-  std::vector<int> rank_order(static_cast<size_t>(ctx->nranks));
-  int graph_failed = 0;
-  const auto order_t0 = std::chrono::steady_clock::now();
-  const bool order_on_thread = ctx->nranks > 1 && n < ctx->order_device_min;
-  float order_thread_ms = 0.0f;
-  if (order_on_thread) {
-    const int P = ctx->nranks;
-    const bool use_graph = params->use_visibility_graph != 0;
-    int* out = rank_order.data();
-    int* failed = &graph_failed;
-    const amrvr_box_record* recs = scene->global.data();
-    const amrvr_camera cam_copy = *camera;
-    float* took = &order_thread_ms;
-    ctx->worker.submit([=]() {
-      const bool ok = order_ranks(P, n, recs, cam_copy, aspect, use_graph, *host_order_backend(), out);
-      *failed = ok ? 0 : 1;
-      *took = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
-    });
-  }
-  st = raymarch_impl(ctx, scene, camera, RW, RH, params->box_transparency, ref_step, pts, npts,
-                     params->count_samples, peer, &layers);
-  if (st != AMRVR_OK) {
-    if (order_on_thread) ctx->worker.wait();
-    return st;
-  }
-  CUDA_TRY(ctx, cudaEventRecord(ev[1], ctx->stream));
-  trace.mark("march_enqueue");
+  const bool fused = ctx->nranks == 1 || (ctx->peer_ok && scene->replicated);
+  return fused ? frame_fused(ctx, scene, camera, params, pts, npts, root, rgba5_host, rgb8_host, stats, G,
+                             trace)
+               : frame_exchange(ctx, scene, camera, params, pts, npts, root, rgba5_host, rgb8_host,
+                                stats, G, trace);
+}
 
-  float order_host_ms = 0.0f;
-  if (order_on_thread) {
-    ctx->worker.wait();
-    order_host_ms = order_thread_ms;
-  } else {
-    st = amrvr_order_boxes(ctx, scene, camera, aspect, params->use_visibility_graph,
-                           rank_order.data(), &graph_failed);
-    if (st != AMRVR_OK) {
-      amrvr_layers_free(ctx, layers);
-      return st;
-    }
-    order_host_ms =
-        std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - order_t0).count();
-  }
-  CUDA_TRY(ctx, cudaEventRecord(ev[2], ctx->stream));
-  trace.mark("order");
+// ---------------------------------------------------------------------------
+// NVLink probe
+// ---------------------------------------------------------------------------
 
-  int begin = 0, end = 0;
-  float* piece = nullptr;
-  int64_t exchanged = 0;
-  const size_t render_floats = static_cast<size_t>(RW) * RH * 5;
-  const size_t out_floats = static_cast<size_t>(W) * H * 5;
-  if (ctx->rank == root) CUDA_TRY(ctx, ctx->full.reserve(render_floats * sizeof(float)));
-  const bool fold_into_frame = ctx->nranks == 1;  // the piece IS the frame: no gather copy
-  // One rank, no antialiasing, nobody asks for the float frame: the fold's epilogue
-  // applies the overlay and writes the bytes itself (no 84 MB float frame at 2048^2
-  // written and read back).
-  const bool want_bytes_early = rgb8_host != nullptr || params->rgb8_on_device;
-  const bool fold_bytes = fold_into_frame && sqrt_aa == 1 && want_bytes_early && rgba5_host == nullptr;
-  FoldBytes fold_bytes_args{nullptr, H, nullptr};
-  if (fold_bytes) {
-    CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
-    fold_bytes_args.rgb8 = ctx->rgb8.as<uint8_t>();
-    if (params->draw_bounding_box && n > 0) {
-      OverlayEdges edges;
-      make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
-      CUDA_TRY(ctx, ctx->copy_jobs.reserve(sizeof(OverlayEdges)));
-      CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, &edges, sizeof(edges), cudaMemcpyHostToDevice,
-                                    ctx->stream));
-      fold_bytes_args.edges = ctx->copy_jobs.as<OverlayEdges>();
-    }
-  }
-  if (peer) st = peer_barrier(ctx, 0);  // every rank's layers are complete and visible
-  if (st == AMRVR_OK)
-    st = composite_impl(ctx, scene, layers, camera, rank_order.data(), &begin, &end, &piece,
-                        &exchanged,
-                        fold_into_frame ? ctx->full.as<float>()
-                                        : (peer ? static_cast<float*>(ctx->sym_piece.local) : nullptr),
-                        peer, fold_bytes ? &fold_bytes_args : nullptr);
-  if (st != AMRVR_OK) {
-    amrvr_layers_free(ctx, layers);
-    return st;
-  }
-  CUDA_TRY(ctx, cudaEventRecord(ev[3], ctx->stream));
-  trace.mark("composite_enqueue");
-
-  const bool bytes_by_pieces = peer && sqrt_aa == 1;  // every rank writes its bytes into the root's frame
-  if (peer) {
-    if (bytes_by_pieces) {
-      const OverlayEdges* edges_dev = nullptr;
-      if (params->draw_bounding_box && n > 0) {
-        OverlayEdges edges;
-        make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
-        CUDA_TRY(ctx, ctx->copy_jobs.reserve(sizeof(OverlayEdges)));
-        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, &edges, sizeof(edges), cudaMemcpyHostToDevice,
-                                      ctx->stream));
-        edges_dev = ctx->copy_jobs.as<OverlayEdges>();
-      }
-      LAUNCH_TRY(ctx, launch_post_piece(piece, begin, end, W, H, edges_dev,
-                                        static_cast<uint8_t*>(ctx->sym_rgb8.peer[root]), ctx->stream,
-                                        &ctx->launches));
-    }
-    st = peer_barrier(ctx, 1);  // pieces (and bytes) of every rank are in place
-    if (st == AMRVR_OK && ctx->rank == root && (!bytes_by_pieces || rgba5_host != nullptr)) {
-      // the root pulls the float pieces over NVLink (ImageColorOnly::Gather)
-      for (int pc = 0; pc < ctx->nranks && st == AMRVR_OK; ++pc) {
-        const int r = rank_order[pc];
-        int b0, e0;
-        piece_range(RW * RH, pc, ctx->nranks, &b0, &e0);
-        if (e0 > b0)
-          CUDA_TRY(ctx, cudaMemcpyAsync(ctx->full.as<float>() + static_cast<size_t>(b0) * 5,
-                                        ctx->sym_piece.peer[r], static_cast<size_t>(e0 - b0) * 20,
-                                        cudaMemcpyDeviceToDevice, ctx->stream));
-      }
-    }
-  } else if (!fold_into_frame) {
-    std::vector<int> spans(static_cast<size_t>(2 * ctx->nranks));
-    for (int pc = 0; pc < ctx->nranks; ++pc)
-      piece_range(RW * RH, pc, ctx->nranks, &spans[2 * rank_order[pc]], &spans[2 * rank_order[pc] + 1]);
-    st = gather_impl(ctx, piece, spans, root, ctx->full.as<float>());
-  }
-  if (st != AMRVR_OK) {
-    amrvr_layers_free(ctx, layers);
-    return st;
-  }
-  CUDA_TRY(ctx, cudaEventRecord(ev[4], ctx->stream));
-
-  ctx->last_rgb8 = nullptr;
-  if (ctx->rank == root && bytes_by_pieces) {
-    // the byte frame is already complete in the peer-mapped buffer
-    ctx->last_rgb8 = static_cast<uint8_t*>(ctx->sym_rgb8.local);
-    if (rgba5_host != nullptr) {
-      float* image = ctx->full.as<float>();
-      if (params->draw_bounding_box && n > 0) {
-        OverlayEdges edges;
-        make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);
-        LAUNCH_TRY(ctx, launch_overlay(edges, 1, W, H, image, ctx->stream, &ctx->launches));
-      }
-      CUDA_TRY(ctx, cudaMemcpyAsync(rgba5_host, image, out_floats * sizeof(float),
-                                    cudaMemcpyDeviceToHost, ctx->stream));
-    }
-    if (rgb8_host != nullptr)
-      CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->sym_rgb8.local, static_cast<size_t>(W) * H * 3,
-                                    cudaMemcpyDeviceToHost, ctx->stream));
-  } else if (ctx->rank == root) {
-    float* image = ctx->full.as<float>();
-    if (sqrt_aa > 1) {
-      CUDA_TRY(ctx, ctx->small.reserve(out_floats * sizeof(float)));
-      LAUNCH_TRY(ctx, launch_downsample(ctx->full.as<float>(), W, H, sqrt_aa, ctx->small.as<float>(),
-                                        ctx->stream, &ctx->launches));
-      image = ctx->small.as<float>();
-    }
-    const bool want_bytes = rgb8_host != nullptr || params->rgb8_on_device;
-    const bool fused_bytes = want_bytes && rgba5_host == nullptr;  // overlay + bytes in one pass
-    if (params->draw_bounding_box && n > 0 && !fused_bytes) {
-      OverlayEdges edges;
-      make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);  // sqrtAA = 1 at :1313
-      LAUNCH_TRY(ctx, launch_overlay(edges, 1, W, H, image, ctx->stream, &ctx->launches));
-    }
-    if (rgba5_host != nullptr)
-      CUDA_TRY(ctx, cudaMemcpyAsync(rgba5_host, image, out_floats * sizeof(float),
-                                    cudaMemcpyDeviceToHost, ctx->stream));
-    if (want_bytes) {
-      CUDA_TRY(ctx, ctx->rgb8.reserve(static_cast<size_t>(W) * H * 3));
-      if (fold_bytes) {
-        // the fold already wrote overlay + bytes
-      } else if (fused_bytes) {
-        // nobody reads the float frame: the overlay is applied on the way to the bytes
-        const OverlayEdges* edges_dev = nullptr;
-        if (params->draw_bounding_box && n > 0) {
-          OverlayEdges edges;
-          make_overlay_edges(tmin, tmax, *camera, 1, W, H, edges);
-          CUDA_TRY(ctx, ctx->copy_jobs.reserve(sizeof(OverlayEdges)));
-          CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, &edges, sizeof(edges),
-                                        cudaMemcpyHostToDevice, ctx->stream));
-          edges_dev = ctx->copy_jobs.as<OverlayEdges>();
-        }
-        LAUNCH_TRY(ctx, launch_post_piece(image, 0, W * H, W, H, edges_dev, ctx->rgb8.as<uint8_t>(),
-                                          ctx->stream, &ctx->launches));
-      } else {
-        LAUNCH_TRY(ctx, launch_quantize_rgb8(image, W, H, ctx->rgb8.as<uint8_t>(), ctx->stream,
-                                             &ctx->launches));
-      }
-      ctx->last_rgb8 = ctx->rgb8.as<uint8_t>();
-      if (rgb8_host != nullptr)
-        CUDA_TRY(ctx, cudaMemcpyAsync(rgb8_host, ctx->rgb8.ptr, static_cast<size_t>(W) * H * 3,
-                                      cudaMemcpyDeviceToHost, ctx->stream));
-    }
-  }
-  CUDA_TRY(ctx, cudaEventRecord(ev[5], ctx->stream));
-  trace.mark("post_enqueue");
-  if (peer)
-    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->peer_error_host,
-                                  static_cast<uint32_t*>(ctx->sym_flags.local) + kFlagRows * kMaxPeers,
-                                  sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+// Collective.  Every rank copies `bytes` between its own buffer and the buffer
+// of rank (rank + peer_offset) mod nranks with a plain load/store kernel --
+// write != 0: local -> peer (posted stores, what the march does with stolen
+// tiles); write == 0: peer -> local (loads) -- `iters` times, all ranks at once,
+// and reports its own rate.  This is the measured per-GPU, per-direction link
+// figure the composite numbers are quoted against.
+extern "C" int amrvr_peer_bandwidth(amrvr_ctx* ctx, size_t bytes, int peer_offset, int write, int iters,
+                                    float* gbytes_per_s) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, gbytes_per_s != nullptr && bytes >= 4096 && iters >= 1, "bad argument");
+  REQUIRE(ctx, ctx->nranks > 1 && ctx->peer_ok, "needs several ranks with peer access");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  bool ok = true;
+  const size_t want = 2 * bytes;  // [0, bytes): source of this rank; [bytes, 2*bytes): landing zone
+  const int st = sym_reserve(ctx, ctx->sym_pool, want, &ok);
+  if (st != AMRVR_OK) return st;
+  REQUIRE(ctx, ok, "peer-mapped buffer could not be grown");
+  const int P = ctx->nranks;
+  const int peer = ((ctx->rank + peer_offset) % P + P) % P;
+  char* mine = static_cast<char*>(ctx->sym_pool.local);
+  char* theirs = static_cast<char*>(ctx->sym_pool.peer[peer]);
+  const void* src = write ? mine : theirs;
+  void* dst = write ? theirs + bytes : mine + bytes;
+  int st2 = peer_barrier(ctx, 2);
+  if (st2 != AMRVR_OK) return st2;
+  cudaEvent_t e0 = ctx->ev[6], e1 = ctx->ev[7];
+  LAUNCH_TRY(ctx, launch_peer_copy(src, dst, bytes, 148 * 8, ctx->stream, &ctx->launches));  // warm-up
+  st2 = peer_barrier(ctx, 2);
+  if (st2 != AMRVR_OK) return st2;
+  CUDA_TRY(ctx, cudaEventRecord(e0, ctx->stream));
+  for (int i = 0; i < iters; ++i)
+    LAUNCH_TRY(ctx, launch_peer_copy(src, dst, bytes, 148 * 8, ctx->stream, &ctx->launches));
+  CUDA_TRY(ctx, cudaEventRecord(e1, ctx->stream));
+  st2 = peer_barrier(ctx, 2);
+  if (st2 != AMRVR_OK) return st2;
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  trace.mark("final_sync");
-  if (peer && *ctx->peer_error_host != 0) {
-    amrvr_layers_free(ctx, layers);
-    return fail(ctx, AMRVR_ERR_RUNTIME, "a peer GPU did not reach the frame barrier within 10 s");
-  }
-  if (stats != nullptr) {
-    std::memset(stats, 0, sizeof(*stats));
-    amrvr_march_stats ms;
-    if (amrvr_layers_stats(layers, &ms) == AMRVR_OK) {
-      stats->samples = ms.samples;
-      stats->march_ms = ms.kernel_ms;
-    }
-    stats->order_ms = order_host_ms;  // runs on the aux stream beside the march: host wall time
-    cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[3]);
-    cudaEventElapsedTime(&stats->gather_ms, ev[3], ev[4]);
-    cudaEventElapsedTime(&stats->post_ms, ev[4], ev[5]);
-    cudaEventElapsedTime(&stats->fold_ms, ev[6], ev[7]);
-    stats->exchanged_bytes = exchanged;
-  }
-  amrvr_layers_free(ctx, layers);
+  float ms = 0.0f;
+  CUDA_TRY(ctx, cudaEventElapsedTime(&ms, e0, e1));
+  *gbytes_per_s = (ms > 0.0f) ? static_cast<float>(static_cast<double>(bytes) * iters / (ms * 1e-3) / 1e9) : 0.0f;
   return AMRVR_OK;
 }

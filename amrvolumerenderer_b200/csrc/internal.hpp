@@ -139,7 +139,9 @@ struct MarchBox {
   float inv_cell_tiny[3];  // 2^-149 / cell (exact when cell is a power of two)
   float margin;        // > 0: shrink distance of the provably-inside stretch; 0: always check
   uint64_t brick_off;  // byte offset into the brick pool
-  uint64_t layer_off;  // float offset into the layer pool
+  uint64_t layer_off;  // float offset into the fragment pool of destination `dest`
+  int32_t dest;        // which pool the fragments go to (MarchQueues::pool index)
+  int32_t pad;
 };
 
 struct MarchFrame {
@@ -147,6 +149,44 @@ struct MarchFrame {
   float tan_half, aspect, inv_w, inv_h;
   int32_t width, height;
   int32_t nboxes, ntiles;
+};
+
+// Peer-memory exchange (one box, NVLink/NVSwitch): pointers to the same buffer on
+// every rank of the box, mapped into this process (CUDA IPC, or plain peer
+// access when the ranks are threads of one process).
+constexpr int kMaxPeers = 8;
+constexpr int kFlagRows = 4;  // flag rows on every rank: [kFlagRows][kMaxPeers] u32
+// Layout of the peer-mapped control block of a rank (u32 words): flag rows, then
+// the barrier time-out word, the tile counter of the rank's march queue (its own
+// 128 B line: peers hit it with atomics), the "queue q is drained" hints and the
+// count of finished CTAs of the running march / fold launch.
+constexpr int kCtlError = kFlagRows * kMaxPeers;  // word 32
+constexpr int kCtlTileCounter = 64;
+constexpr int kCtlHints = 96;                     // [kMaxPeers]
+constexpr int kCtlDoneMarch = 128;
+constexpr int kCtlDoneFold = 160;
+constexpr int kCtlWords = 192;
+struct PeerPtrs {
+  void* p[kMaxPeers];
+};
+
+// The tiles of one march launch, as up to kMaxPeers queues.  A single-GPU march
+// has one queue.  A frame sharded over the GPUs of a box has one queue per
+// image piece: queue q holds every (box, tile) whose rows lie in piece q, its
+// fragments go to pool[q] (the GPU that folds piece q) and its tile counter
+// lives on that GPU.  A GPU drains `mine` first and then helps with the other
+// queues in `steal_order`, writing the fragments of those tiles across NVLink.
+struct MarchQueues {
+  int32_t nqueues, mine;
+  int32_t me, nranks;              // nranks > 0: the last CTA raises flag row `signal_row` on every rank
+  int32_t tile_begin[kMaxPeers + 1];
+  int32_t steal_order[kMaxPeers];
+  unsigned* counter[kMaxPeers];    // next tile of queue q (relative to tile_begin[q])
+  float* pool[kMaxPeers];
+  unsigned* ctl[kMaxPeers];        // control block of rank r (hints, flags); [me] is the local one
+  unsigned long long* stats;       // [0] samples  [1] bytes written to other GPUs  [2] tiles taken from other queues
+  uint32_t epoch;
+  int32_t signal_row;
 };
 
 // One layer as the fold kernel sees it, already in global blend order.
@@ -157,15 +197,6 @@ struct FoldLayer {
   int32_t run;         // id of the same-owner run this layer belongs to
   int32_t interleaved; // 1: pixel (x,y) at base + ((y-row0)*w + x-x0)*5 (the reference's layout);
                        //    base may then point before the slice (only in-range pixels are read)
-};
-
-// Peer-memory exchange (one box, NVLink/NVSwitch): pointers to the same buffer on
-// every rank of the box, mapped into this process (CUDA IPC, or plain peer
-// access when the ranks are threads of one process).
-constexpr int kMaxPeers = 8;
-constexpr int kFlagRows = 4;  // flag block on every rank: [kFlagRows][kMaxPeers] u32 (+ error word)
-struct PeerPtrs {
-  void* p[kMaxPeers];
 };
 
 // A byte range to copy when packing slices for the exchange.
@@ -191,23 +222,49 @@ int launch_brick_histogram(const double* data, int64_t jstride, int64_t kstride,
 int launch_brick_quantise_batch(const QuantJob* jobs_dev, int njobs, long long max_cells,
                                 const amrvr_scalar_transform& t, float range_min, float range_max,
                                 void* stream, int64_t* launches);
-int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev,
-                    const uint8_t* bricks, const float* tables, float* layers,
-                    unsigned long long* sample_counter, unsigned* tile_counter /*zeroed*/,
-                    bool count_samples, void* stream, int64_t* launches);
+int launch_raymarch(const MarchFrame& frame, const MarchQueues& queues, const MarchBox* boxes_dev,
+                    const uint8_t* bricks, const float* tables, bool count_samples, void* stream,
+                    int64_t* launches);
 // scratch: fold_scratch_bytes() of device memory (per-band layer lists)
 size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end);
-// Byte epilogue of the fold (one rank, bytes-only frame): overlay edges in device
-// memory (nullptr: no overlay), frame height, RGB8 frame (top row first).
+// Byte epilogue of the fold: overlay edges in device memory (nullptr: no
+// overlay), frame height, RGB8 frame (top row first; may be the root's frame on
+// another GPU -- every rank writes the bytes of its own piece).
 struct FoldBytes {
   const OverlayEdges* edges;
   int height;
   uint8_t* rgb8;
 };
+// Cross-GPU hand-shake fused into the fold of a sharded frame: before the first
+// fragment is read every CTA waits until flag row `wait_row` of the own control
+// block holds `epoch` from all nranks ranks (= every march that may have written
+// into this GPU's pool has finished); the march queue counter is then reset for
+// the next frame; the last CTA to finish raises row `signal_row` on every rank.
+struct FoldSync {
+  PeerPtrs ctl;
+  int32_t me, nranks;
+  int32_t wait_row, signal_row;
+  uint32_t epoch;
+  unsigned long long timeout_ns;
+};
+// Pass 1 (fold_bin): per 8-row band the ordered list of layers touching it.  It
+// depends on the frame plan only, never on pixel data, so a frame launches it
+// BEFORE the march and the march hides it.
+int launch_fold_bin(const FoldLayer* layers_dev, int nlayers, int width, int pixel_begin,
+                    int pixel_end, void* scratch, void* stream, int64_t* launches);
+// Pass 2: the fold proper over the lists pass 1 left in `scratch`.
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int pixel_begin, int pixel_end, float* piece5, void* scratch,
                 void* stream, int64_t* launches,
-                const FoldBytes* bytes = nullptr);
+                const FoldBytes* bytes = nullptr, const FoldSync* sync = nullptr);
+// Wait (on the stream) until flag row `row` of the own control block holds
+// `epoch` from every rank; raises the time-out word instead of hanging.
+int launch_peer_wait(const PeerPtrs& ctl, int me, int nranks, int row, uint32_t epoch,
+                     unsigned long long timeout_ns, void* stream, int64_t* launches);
+// NVLink probe: copy `bytes` between two device buffers (either may be a peer
+// mapping) with plain 16 B loads and stores from `blocks` CTAs.
+int launch_peer_copy(const void* src, void* dst, size_t bytes, int blocks, void* stream,
+                     int64_t* launches);
 int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst,
                 void* stream, int64_t* launches);
 // Cross-GPU barrier on the stream: store `epoch` into slot `me` of every peer's
@@ -231,6 +288,10 @@ int launch_quantize_rgb8(const float* image5, int width, int height,
 int launch_order_rank(const OrderBox* boxes_dev, int n, void* scratch_a /*16 B per box*/,
                       void* scratch_b, int owner_bits, int32_t* priority_dev,
                       void* stream, int64_t* launches);
+// priority[i] = number of boxes that sort before box i (all-pairs count over the
+// same keys; any n, many CTAs, no passes).  priority_dev must be zeroed.
+int launch_order_count(const OrderBox* boxes_dev, int n, int32_t* priority_dev, void* stream,
+                       int64_t* launches);
 int launch_order_pairs(const OrderBox* boxes_dev, int n, float dx, float dy,
                        float dz, OrderEdge* edges_dev, int capacity,
                        int32_t* count_dev, void* stream, int64_t* launches);

@@ -91,6 +91,33 @@ __global__ void __launch_bounds__(256)
 brick_quantise_batch_kernel(const QuantJob* __restrict__ jobs, ValuePath p) {
   const QuantJob J = jobs[blockIdx.y];
   const int nx = J.nx, ny = J.ny;
+  if (J.jstride == nx && J.kstride == static_cast<long long>(nx) * ny &&
+      ((reinterpret_cast<uintptr_t>(J.src) & 15) == 0) && ((reinterpret_cast<uintptr_t>(J.dst) & 3) == 0)) {
+    // dense FAB (no ghost cells): the brick is one contiguous run of cells, no
+    // row arithmetic at all -- four cells per thread per step, two steps in flight
+    const long long ncells = static_cast<long long>(nx) * ny * J.nz;
+    const long long nq = ncells >> 2;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    const double2* src2 = reinterpret_cast<const double2*>(J.src);
+    uchar4* dst4 = reinterpret_cast<uchar4*>(J.dst);
+    long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    for (; q + stride < nq; q += 2 * stride) {
+      const double2 a = __ldcs(src2 + 2 * q), b = __ldcs(src2 + 2 * q + 1);
+      const double2 c = __ldcs(src2 + 2 * (q + stride)), d = __ldcs(src2 + 2 * (q + stride) + 1);
+      dst4[q] = make_uchar4(cell_to_index(a.x, p), cell_to_index(a.y, p), cell_to_index(b.x, p),
+                            cell_to_index(b.y, p));
+      dst4[q + stride] = make_uchar4(cell_to_index(c.x, p), cell_to_index(c.y, p),
+                                     cell_to_index(d.x, p), cell_to_index(d.y, p));
+    }
+    for (; q < nq; q += stride) {
+      const double2 a = __ldcs(src2 + 2 * q), b = __ldcs(src2 + 2 * q + 1);
+      dst4[q] = make_uchar4(cell_to_index(a.x, p), cell_to_index(a.y, p), cell_to_index(b.x, p),
+                            cell_to_index(b.y, p));
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (ncells & 3))
+      J.dst[4 * nq + threadIdx.x] = cell_to_index(J.src[4 * nq + threadIdx.x], p);
+    return;
+  }
   const int quads_per_row = (nx + 3) >> 2;
   const long long nquads = static_cast<long long>(quads_per_row) * ny * J.nz;
   for (long long q = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; q < nquads;
@@ -528,36 +555,92 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
 }
 
 // Persistent CTAs: the grid is (SM count x resident CTAs per SM) and every CTA
-// pulls 16x16 tiles from a global counter until none is left, heaviest launch
-// order preserved (tiles of one box are consecutive, so the box parameters and
-// the transfer table in shared memory are refilled only when they change --
-// three times per CTA on a three-level scene instead of once per tile).
-// Thread 0 claims tile i+1 and finds its box while the CTA marches tile i; the
-// claim lives in a two-slot mailbox indexed by iteration parity.
+// pulls 16x16 tiles from a queue counter until none is left.  Tiles of one item
+// are consecutive and items are sorted by transfer table, so the box parameters
+// in shared memory are refilled per tile but the table only when the launch
+// moves on to the next AMR level.
+//
+// Queues (MarchQueues): one for a single-GPU march.  A frame sharded over the
+// GPUs of a box has one queue per image piece; every GPU holds every brick, so
+// any GPU can march any tile.  A CTA drains its own GPU's queue first (the
+// fragments stay in local HBM) and then takes tiles from the other queues,
+// heaviest first, storing those fragments straight into the pool of the GPU
+// that folds the piece -- posted NVLink stores from an issue-bound kernel, the
+// exchange of DirectSendBase::PostSends/PostReceives (DirectSendBase.cpp:76-177)
+// overlapped with the march tile by tile.  The claim of the next tile is an
+// atomic on the owning GPU's counter: thread 0 issues it BEFORE marching its ray
+// and reads the answer AFTER, so the NVLink round trip of a remote claim hides
+// behind the march of the current tile.  "hints" keep CTAs from probing queues
+// another CTA already found drained.  The last CTA to finish raises this rank's
+// flag on every GPU: that is the barrier the fold of the piece waits on.
 #ifndef AMRVR_MARCH_MIN_BLOCKS
 #define AMRVR_MARCH_MIN_BLOCKS 4
 #endif
 
+__device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_volatile_u32(unsigned* p, unsigned v) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 template <bool kCount>
 __global__ void __launch_bounds__(kMarchThreads, AMRVR_MARCH_MIN_BLOCKS)
-raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __restrict__ boxes,
+raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_constant__ MarchQueues Q,
+                       const MarchBox* __restrict__ boxes,
                        const unsigned char* __restrict__ bricks,
-                       const float4* __restrict__ tables, float* __restrict__ layers,
-                       unsigned long long* __restrict__ sample_counter,
-                       unsigned* __restrict__ tile_counter) {
+                       const float4* __restrict__ tables) {
   __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE * kTableCopies];
   __shared__ MarchBox s_box;
   __shared__ int s_tile[2], s_which[2];
 
-  auto claim = [&](int slot) {  // thread 0 only
-    const int tile = static_cast<int>(atomicAdd(tile_counter, 1u));
+  // ---- thread 0 only; its bookkeeping lives in shared memory so that the march
+  // loop keeps its registers.  The try order is the own queue, then steal_order[].
+  __shared__ int s_cur;                          // position in the try order
+  __shared__ unsigned long long s_pushed, s_stolen;
+  auto queue_at = [&](int k) { return (k == 0) ? Q.mine : Q.steal_order[k - 1]; };
+  auto mark_drained = [&](int q) {
+    if (Q.nranks <= 0) return;
+    if (ld_volatile_u32(Q.ctl[Q.me] + kCtlHints + q) == Q.epoch) return;
+    if (q == Q.mine) {  // tell every GPU: nothing left to take here
+      for (int r = 0; r < Q.nranks; ++r) st_volatile_u32(Q.ctl[r] + kCtlHints + q, Q.epoch);
+    } else {
+      st_volatile_u32(Q.ctl[Q.me] + kCtlHints + q, Q.epoch);
+    }
+  };
+  auto known_drained = [&](int q) {
+    return Q.nranks > 0 && q != Q.mine && ld_volatile_u32(Q.ctl[Q.me] + kCtlHints + q) == Q.epoch;
+  };
+  auto tile_of = [&](int q, unsigned t) {  // -1: the queue is drained
+    return (t < static_cast<unsigned>(Q.tile_begin[q + 1] - Q.tile_begin[q]))
+               ? Q.tile_begin[q] + static_cast<int>(t)
+               : -1;
+  };
+  auto claim_blocking = [&]() {  // walks the try order; -1 when every queue is drained
+    int cur = s_cur, tile = -1;
+    while (cur < Q.nqueues) {
+      const int q = queue_at(cur);
+      if (!known_drained(q)) {
+        tile = tile_of(q, atomicAdd(Q.counter[q], 1u));
+        if (tile >= 0) break;
+        mark_drained(q);
+      }
+      ++cur;
+    }
+    s_cur = cur;
+    return tile;
+  };
+  auto publish = [&](int slot, int tile) {
     int lo = 0;
-    if (tile < f.ntiles) {  // last box whose first tile is <= tile
+    if (tile >= 0) {  // last item whose first tile is <= tile
       int hi = f.nboxes - 1;
       while (lo < hi) {
         const int mid = (lo + hi + 1) >> 1;
         if (__ldg(&boxes[mid].tile_base) <= tile) lo = mid; else hi = mid - 1;
       }
+      if (s_cur > 0) ++s_stolen;
     }
     s_tile[slot] = tile;
     s_which[slot] = lo;
@@ -567,11 +650,15 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __r
   const unsigned table_addr = smem_u32(s_table) + static_cast<unsigned>(lane % kTableCopies) * 16u;
   int have_box = -1, have_table = -1;
   unsigned nsamples = 0;
-  if (threadIdx.x == 0) claim(0);
+  if (threadIdx.x == 0) {
+    s_cur = 0;
+    s_pushed = s_stolen = 0;
+    publish(0, claim_blocking());
+  }
   for (int it = 0;; ++it) {
     __syncthreads();  // mailbox slot it&1 is written; everyone is done with the previous tile
     const int tile = s_tile[it & 1], which = s_which[it & 1];
-    if (tile >= f.ntiles) break;
+    if (tile < 0) break;
     if (which != have_box) {  // uniform across the CTA
       const int words = sizeof(MarchBox) / 4;
       const int* src = reinterpret_cast<const int*>(boxes + which);
@@ -587,14 +674,22 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __r
       have_box = which;
       __syncthreads();
     }
-    if (threadIdx.x == 0) claim((it + 1) & 1);  // overlaps with the march below
+    // the claim of the next tile: issued here, read after this thread's ray
+    unsigned pend_t = 0;
+    if (threadIdx.x == 0) {
+      int cur = s_cur;
+      while (cur < Q.nqueues && known_drained(queue_at(cur))) ++cur;
+      s_cur = cur;
+      if (cur < Q.nqueues) pend_t = atomicAdd(Q.counter[queue_at(cur)], 1u);
+    }
 
     const int local_tile = tile - s_box.tile_base;
     const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
     const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
     const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
     const int rw = s_box.rw;
-    const bool valid = x < rw && y < s_box.rh;
+    // footprints are padded to 4-pixel column multiples: columns past the frame are not rays
+    const bool valid = x < rw && y < s_box.rh && s_box.rx0 + x < f.width;
 
     const RayOut r = s_box.exact_recip
                          ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x,
@@ -607,16 +702,50 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const MarchBox* __r
     float depth = r.depth;
     if (!isfinite(depth) || out.w <= 0.0f) depth = INFINITY;
     if (valid) {
-      float* row = layers + s_box.layer_off + static_cast<size_t>(y) * rw * 5;
+      float* row = Q.pool[s_box.dest] + s_box.layer_off + static_cast<size_t>(y) * rw * 5;
       reinterpret_cast<float4*>(row)[x] = out;
       row[4 * rw + x] = depth;
     }
     if (kCount) nsamples += r.nsamples;
+
+    if (threadIdx.x == 0) {
+      if (Q.nranks > 0 && s_box.dest != Q.me) {
+        const int w = min(min(kTile, rw - tx * kTile), f.width - s_box.rx0 - tx * kTile);
+        const int h = min(kTile, s_box.rh - ty * kTile);
+        if (w > 0 && h > 0) s_pushed += 20ull * static_cast<unsigned>(w * h);
+      }
+      int next = -1;
+      if (s_cur < Q.nqueues) {
+        const int pend_q = queue_at(s_cur);
+        next = tile_of(pend_q, pend_t);
+        if (next < 0) {
+          mark_drained(pend_q);
+          ++s_cur;
+          next = claim_blocking();
+        }
+      }
+      publish((it + 1) & 1, next);
+    }
   }
   if (kCount) {
     for (int off = 16; off > 0; off >>= 1) nsamples += __shfl_down_sync(0xffffffffu, nsamples, off);
     if (lane == 0 && nsamples != 0)
-      atomicAdd(sample_counter, static_cast<unsigned long long>(nsamples));
+      atomicAdd(Q.stats, static_cast<unsigned long long>(nsamples));
+  }
+  if (threadIdx.x == 0) {
+    if (s_pushed != 0) atomicAdd(Q.stats + 1, s_pushed);
+    if (s_stolen != 0) atomicAdd(Q.stats + 2, s_stolen);
+    if (Q.nranks > 0) {
+      // every thread's fragment stores precede the barrier the loop was left through
+      __threadfence_system();
+      unsigned* done = Q.ctl[Q.me] + kCtlDoneMarch;
+      if (atomicAdd(done, 1u) + 1u == gridDim.x) {
+        st_volatile_u32(done, 0u);
+        __threadfence_system();
+        for (int r = 0; r < Q.nranks; ++r)
+          st_volatile_u32(Q.ctl[r] + Q.signal_row * kMaxPeers + Q.me, Q.epoch);
+      }
+    }
   }
 }
 
@@ -686,79 +815,79 @@ __device__ __forceinline__ void overlay_and_quantise(int px, int py, float c0, f
   }
 }
 
-constexpr int kFoldThreads = 256;
-constexpr int kFoldTileW = 32;   // one warp = 32 consecutive pixels of one row
-constexpr int kFoldBandRows = 8; // one CTA = 32 x 8 pixels; one band = 8 frame rows
-constexpr int kFoldDepth = 4;    // fragments in flight per thread (HBM and NVLink latency)
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 
-struct FoldEntry {  // FoldLayer narrowed for shared memory
+constexpr int kBinThreads = 256;  // fold_bin_kernel
+constexpr int kFoldThreads = 128; // fold_layers_kernel: 4 warps, each 32 pixels x 2 rows
+constexpr int kFoldTileW = 32;
+constexpr int kFoldBandRows = 8;  // one CTA tile = 32 x 8 pixels; one band = 8 frame rows
+constexpr int kFoldDepth = 4;     // list entries in flight per thread (x 2 pixels each)
+constexpr int kFoldWarpList = 64; // per-warp list of matched layers (shared memory)
+
+struct FoldEntry {  // FoldLayer narrowed for shared memory: 32 bytes
   const float* base;
   int x0, w, row0, row1, run, interleaved;
 };
 
-struct FoldBatch {
-  Px5 frag[kFoldDepth];
-  bool hit[kFoldDepth];
-  int runid[kFoldDepth];  // -2: past the end of the list
+__device__ __forceinline__ float4 ldcg_f4(const float4* p) { return __ldcg(p); }
+
+// One fragment of a layer at column cx of row r (r relative to E.row0).  Loads
+// bypass L1 (ld.global.cg): a fragment is read once, and in a sharded frame it
+// may have arrived over NVLink after this kernel started.
+__device__ __forceinline__ Px5 fold_load(const FoldEntry& E, int r, int cx) {
+  if (E.interleaved) {  // the reference's own layout: 5 floats per pixel
+    const float* q = E.base + (static_cast<long long>(r) * E.w + cx) * 5;
+    return Px5{__ldcg(q), __ldcg(q + 1), __ldcg(q + 2), __ldcg(q + 3), __ldcg(q + 4)};
+  }
+  const float* rowp = E.base + static_cast<size_t>(r) * E.w * 5;
+  const float4 c = ldcg_f4(reinterpret_cast<const float4*>(rowp) + cx);
+  return Px5{c.x, c.y, c.z, c.w, __ldcg(rowp + 4 * E.w + cx)};
+}
+
+// Running state of one pixel: the run being pre-blended and the accumulator
+// (DirectSendBase::composeLayered, DirectSendBase.cpp:400-446).
+struct FoldPixel {
+  Px5 acc, run;
+  bool have_acc, have_run;
+  int cur_run;
 };
 
-// Issue the loads of list entries [e0, e0 + kFoldDepth) that cover pixel (px, py).
-__device__ __forceinline__ void fold_fetch(FoldBatch& b, const FoldEntry* s_list, int e0, int total,
-                                           int px, int py) {
-#pragma unroll
-  for (int k = 0; k < kFoldDepth; ++k) {
-    b.hit[k] = false;
-    b.runid[k] = -2;
-    if (e0 + k < total) {
-      const FoldEntry& E = s_list[e0 + k];
-      b.runid[k] = E.run;
-      const int cx = px - E.x0;
-      if (py >= E.row0 && py < E.row1 && cx >= 0 && cx < E.w) {
-        b.hit[k] = true;
-        if (E.interleaved) {  // the reference's own layout: 5 floats per pixel
-          const float* q = E.base + (static_cast<long long>(py - E.row0) * E.w + cx) * 5;
-          b.frag[k] = Px5{__ldg(q), __ldg(q + 1), __ldg(q + 2), __ldg(q + 3), __ldg(q + 4)};
-        } else {
-          const float* rowp = E.base + static_cast<size_t>(py - E.row0) * E.w * 5;
-          const float4 c = __ldg(reinterpret_cast<const float4*>(rowp) + cx);
-          b.frag[k] = Px5{c.x, c.y, c.z, c.w, __ldg(rowp + 4 * E.w + cx)};
-        }
-      }
+__device__ __forceinline__ void fold_step(FoldPixel& P, int runid, bool hit, const Px5& frag) {
+  if (runid != P.cur_run) {
+    if (P.have_run) {
+      P.acc = P.have_acc ? blend_depth_swap(P.acc, P.run) : P.run;
+      P.have_acc = true;
+      P.have_run = false;
     }
+    P.cur_run = runid;
+  }
+  if (hit) {
+    P.run = P.have_run ? blend_depth_swap(P.run, frag) : frag;
+    P.have_run = true;
   }
 }
 
-// Blend a fetched batch in list order with the run structure of
-// DirectSendBase::composeLayered (DirectSendBase.cpp:400-446).
-__device__ __forceinline__ void fold_consume(const FoldBatch& b, Px5& acc, Px5& run, bool& have_acc,
-                                             bool& have_run, int& cur_run) {
-#pragma unroll
-  for (int k = 0; k < kFoldDepth; ++k) {
-    if (b.runid[k] != -2) {
-      if (b.runid[k] != cur_run) {
-        if (have_run) {
-          acc = have_acc ? blend_depth_swap(acc, run) : run;
-          have_acc = true;
-          have_run = false;
-        }
-        cur_run = b.runid[k];
-      }
-      if (b.hit[k]) {
-        run = have_run ? blend_depth_swap(run, b.frag[k]) : b.frag[k];
-        have_run = true;
-      }
-    }
+__device__ __forceinline__ Px5 fold_finish(FoldPixel& P) {
+  if (P.have_run) {
+    P.acc = P.have_acc ? blend_depth_swap(P.acc, P.run) : P.run;
+    P.have_acc = true;
   }
+  if (!P.have_acc) P.acc = Px5{0.f, 0.f, 0.f, 0.f, INFINITY};  // DirectSendBase.cpp:450-455
+  return P.acc;
 }
 
 // Pass 1: one CTA per band of 8 frame rows filters the globally ordered layer
 // table down to the layers whose rows touch the band (ordered compaction, so
 // the list keeps the blend order).  band_lists[band * nlayers + i], band_counts[band].
-__global__ void __launch_bounds__(kFoldThreads)
+__global__ void __launch_bounds__(kBinThreads)
 fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row,
                 int* __restrict__ band_lists, int* __restrict__ band_counts,
                 int2* __restrict__ band_xspan) {
-  __shared__ int s_warp_count[kFoldThreads / 32];
+  __shared__ int s_warp_count[kBinThreads / 32];
   __shared__ int s_xmin, s_xmax;
   if (threadIdx.x == 0) {
     s_xmin = INT_MAX;
@@ -771,7 +900,7 @@ fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int* list = band_lists + static_cast<size_t>(band) * nlayers;
   int written = 0;
-  for (int chunk = 0; chunk < nlayers; chunk += kFoldThreads) {
+  for (int chunk = 0; chunk < nlayers; chunk += kBinThreads) {
     const int l = chunk + threadIdx.x;
     bool keep = false;
     if (l < nlayers) {
@@ -787,7 +916,7 @@ fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row
     __syncthreads();
     int before = 0, total = 0;
 #pragma unroll
-    for (int w = 0; w < kFoldThreads / 32; ++w) {
+    for (int w = 0; w < kBinThreads / 32; ++w) {
       const int c = s_warp_count[w];
       if (w < warp) before += c;
       total += c;
@@ -811,143 +940,217 @@ fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row
   }
 }
 
-// Pass 2: one CTA = a 32 x 8 pixel tile of this rank's piece (pixels outside
-// [pixel_begin, pixel_end) are masked: a piece may start and end inside a row).
-// The CTA narrows its band's list to the layers whose rectangle touches the
-// tile (ordered compaction, 256 candidates per round), then every thread folds
-// its pixel over that short list, kFoldDepth fragments in flight: consecutive
+struct FoldArgs {
+  const FoldLayer* layers;
+  int nlayers;
+  const int* band_lists;
+  const int* band_counts;
+  const int2* band_xspan;
+  int first_row, bands, width, height;
+  int pixel_begin, pixel_end;
+  float* piece5;
+  const OverlayEdges* edges;
+  unsigned char* rgb8;
+  FoldSync sync;  // nranks == 0: no hand-shake
+};
+
+// Pass 2.  Persistent CTAs walk the 32 x 8 pixel tiles of this rank's piece
+// (pixels outside [pixel_begin, pixel_end) are masked: a piece may start and end
+// inside a row).  A warp owns 32 columns x 2 rows of the tile and works alone --
+// no CTA barrier anywhere: it scans its band's ordered layer list 32 entries at
+// a time, keeps the layers whose rectangle reaches its 64 pixels (one ballot
+// per chunk, ordered append to a warp-private list in shared memory) and folds
+// them, kFoldDepth layers x 2 pixels of loads in flight per thread: consecutive
 // layers of one run are blended first, then the run result is blended into the
 // accumulator -- DirectSendBase::composeLayered, per pixel
-// (DirectSendBase.cpp:400-446).  Fragments of other GPUs are read where they
-// were marched (peer memory over NVLink): the fold IS the exchange.
-// kBytes: the piece is the whole frame and nobody reads it as floats (one rank,
-// bytes-only frame), so the epilogue applies the overlay and the byte rule and
-// writes RGB8 rows (top row = y_max, SavePPM order) instead of 20 B per pixel
-// that a second kernel would read back.
+// (DirectSendBase.cpp:400-446).  In a sharded frame all fragments of the piece
+// already lie in this GPU's pool (the marches pushed them), so the fold reads
+// local HBM only; it first waits for every rank's "march finished" flag.
+// kBytes: the epilogue applies the overlay and the byte rule and writes RGB8
+// rows (top row = y_max, SavePPM order) -- into the root's frame, across NVLink
+// when the root is another GPU -- instead of 20 B per pixel.
 template <bool kBytes>
-__global__ void __launch_bounds__(kFoldThreads, 4)
-fold_layers_kernel(const FoldLayer* __restrict__ layers, int nlayers,
-                   const int* __restrict__ band_lists, const int* __restrict__ band_counts,
-                   const int2* __restrict__ band_xspan,
-                   int first_row, int width, int pixel_begin, int pixel_end,
-                   float* __restrict__ piece5, const OverlayEdges* __restrict__ edges_ptr,
-                   int height, unsigned char* __restrict__ rgb8) {
-  __shared__ FoldEntry s_list[kFoldThreads];
-  __shared__ int s_warp_count[kFoldThreads / 32];
-  __shared__ __align__(16) float s_out[kFoldThreads * 5];
-  __shared__ OverlayEdges s_edges;
-  if (kBytes && edges_ptr != nullptr) {
-    const int words = sizeof(OverlayEdges) / 4;
-    for (int i = threadIdx.x; i < words; i += kFoldThreads)
-      reinterpret_cast<int*>(&s_edges)[i] = reinterpret_cast<const int*>(edges_ptr)[i];
-    __syncthreads();
-  }
-
-  const int band = blockIdx.y;
+__global__ void __launch_bounds__(kFoldThreads)
+fold_layers_kernel(const __grid_constant__ FoldArgs A) {
+  __shared__ __align__(16) FoldEntry s_list[kFoldThreads / 32][kFoldWarpList];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tile_x0 = blockIdx.x * kFoldTileW;
-  const int tile_y0 = first_row + band * kFoldBandRows;
-  const int px = tile_x0 + lane, py = tile_y0 + warp;
-  const long long p_ll = static_cast<long long>(py) * width + px;
-  const bool live = px < width && p_ll >= pixel_begin && p_ll < pixel_end;
-  const int x_last = min(tile_x0 + kFoldTileW, width) - 1;
-  const int y_last = tile_y0 + kFoldBandRows - 1;
 
-  Px5 acc{0.f, 0.f, 0.f, 0.f, INFINITY}, run{0.f, 0.f, 0.f, 0.f, INFINITY};
-  bool have_acc = false, have_run = false;
-  int cur_run = -1;
-  const int* list = band_lists + static_cast<size_t>(band) * nlayers;
-  // no layer of this band reaches the tile's columns: nothing to scan, the tile is empty
-  const int2 xspan = band_xspan[band];
-  const int count = (xspan.x <= x_last && xspan.y > tile_x0) ? band_counts[band] : 0;
+  if (A.sync.nranks > 0) {
+    // every march that may have written into this pool has finished
+    if (warp == 0) {
+      unsigned* mine = static_cast<unsigned*>(A.sync.ctl.p[A.sync.me]);
+      if (lane < A.sync.nranks) {
+        const unsigned* flag = mine + A.sync.wait_row * kMaxPeers + lane;
+        const unsigned long long t0 = global_timer_ns();
+        while (static_cast<int>(ld_volatile_u32(flag) - A.sync.epoch) < 0) {
+          __nanosleep(32);
+          if (global_timer_ns() - t0 > A.sync.timeout_ns) {
+            st_volatile_u32(mine + kCtlError, 1u);
+            break;
+          }
+        }
+      }
+      __threadfence_system();
+      // nobody claims tiles any more: the march queue counter is free for the next frame
+      if (blockIdx.x == 0 && lane == 0) st_volatile_u32(mine + kCtlTileCounter, 0u);
+    }
+    __syncthreads();
+  }
 
-  for (int chunk = 0; chunk < count; chunk += kFoldThreads) {
-    const int i = chunk + threadIdx.x;
-    bool keep = false;
-    FoldLayer L;
-    if (i < count) {
-      L = layers[list[i]];
-      keep = L.row0 <= y_last && L.row1 > tile_y0 && L.x0 <= x_last && L.x0 + L.w > tile_x0;
-    }
-    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
-    if (lane == 0) s_warp_count[warp] = __popc(ballot);
-    __syncthreads();
-    int before = 0, total = 0;
+  FoldEntry* list = s_list[warp];
+  const int tiles_x = (A.width + kFoldTileW - 1) / kFoldTileW;
+  const int ntiles = tiles_x * A.bands;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int band = tile / tiles_x;
+    const int tile_x0 = (tile - band * tiles_x) * kFoldTileW;
+    const int y0 = A.first_row + band * kFoldBandRows + 2 * warp, y1 = y0 + 1;
+    const int px = tile_x0 + lane;
+    const long long p0 = static_cast<long long>(y0) * A.width + px;
+    const long long p1 = p0 + A.width;
+    const bool live0 = px < A.width && p0 >= A.pixel_begin && p0 < A.pixel_end;
+    const bool live1 = px < A.width && p1 >= A.pixel_begin && p1 < A.pixel_end;
+    const int x_last = min(tile_x0 + kFoldTileW, A.width) - 1;
+
+    FoldPixel P0{Px5{0.f, 0.f, 0.f, 0.f, INFINITY}, Px5{0.f, 0.f, 0.f, 0.f, INFINITY}, false, false, -1};
+    FoldPixel P1 = P0;
+    const int* band_list = A.band_lists + static_cast<size_t>(band) * A.nlayers;
+    // no layer of this band reaches the tile's columns: nothing to scan
+    const int2 xspan = __ldg(&A.band_xspan[band]);
+    const int count = (xspan.x <= x_last && xspan.y > tile_x0) ? __ldg(&A.band_counts[band]) : 0;
+
+    int nlist = 0;
+    for (int chunk = 0; chunk < count || nlist > 0; chunk += 32) {
+      if (chunk < count) {
+        const int i = chunk + lane;
+        bool keep = false;
+        FoldLayer L;
+        if (i < count) {
+          L = A.layers[__ldg(&band_list[i])];
+          keep = L.row0 <= y1 && L.row1 > y0 && L.x0 <= x_last && L.x0 + L.w > tile_x0;
+        }
+        const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+        if (keep)
+          list[nlist + __popc(ballot & ((1u << lane) - 1u))] =
+              FoldEntry{L.base, L.x0, L.w, L.row0, L.row1, L.run, L.interleaved};
+        nlist += __popc(ballot);
+        __syncwarp();
+        if (nlist <= kFoldWarpList - 32 && chunk + 32 < count) continue;  // room for another chunk
+      }
+      // fold the list: all loads of a batch are issued before its first blend
+      for (int e0 = 0; e0 < nlist; e0 += kFoldDepth) {
+        Px5 f0[kFoldDepth], f1[kFoldDepth];
+        bool h0[kFoldDepth], h1[kFoldDepth];
+        int runid[kFoldDepth];
 #pragma unroll
-    for (int w = 0; w < kFoldThreads / 32; ++w) {
-      const int c = s_warp_count[w];
-      if (w < warp) before += c;
-      total += c;
-    }
-    if (keep) {
-      const int slot = before + __popc(ballot & ((1u << lane) - 1u));
-      s_list[slot] = FoldEntry{L.base, L.x0, L.w, L.row0, L.row1, L.run, L.interleaved};
-    }
-    __syncthreads();
-    if (live) {
-      // kFoldDepth fragments in flight: all loads of a batch are issued before its first blend
-      for (int e0 = 0; e0 < total; e0 += kFoldDepth) {
-        FoldBatch A;
-        fold_fetch(A, s_list, e0, total, px, py);
-        fold_consume(A, acc, run, have_acc, have_run, cur_run);
-      }
-    }
-    __syncthreads();
-  }
-  if (have_run) {
-    acc = have_acc ? blend_depth_swap(acc, run) : run;
-    have_acc = true;
-  }
-  if (!have_acc) acc = Px5{0.f, 0.f, 0.f, 0.f, INFINITY};  // DirectSendBase.cpp:450-455
-  if (kBytes) {
-    unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_out);  // 96 B per warp
-    // which of the (at most 12) wireframe edges can reach this 32x8 tile at all:
-    // most tiles see none, and the per-pixel loop then has nothing to visit
-    __shared__ unsigned s_edge_mask;
-    if (edges_ptr != nullptr) {
-      if (warp == 0) {
-        const bool reach = lane < s_edges.count && lane < 12 && !(x_last < s_edges.x0[lane] ||
-                           tile_x0 > s_edges.x1[lane] || y_last < s_edges.y0[lane] ||
-                           tile_y0 > s_edges.y1[lane]);
-        const unsigned mask = __ballot_sync(0xffffffffu, reach);
-        if (lane == 0) s_edge_mask = mask;
-      }
-      __syncthreads();
-    }
-    overlay_and_quantise(px, py, acc.r, acc.g, acc.b, edges_ptr != nullptr ? &s_edges : nullptr, 0.5f,
-                         s_bytes + threadIdx.x * 3, edges_ptr != nullptr ? s_edge_mask : 0u);
-    __syncwarp();
-    if (py < height) {
-      unsigned char* row = rgb8 + 3 * (static_cast<size_t>(height - 1 - py) * width + tile_x0);
-      const int npx = min(width - tile_x0, kFoldTileW);  // pixels of this row segment
-      if ((width & 3) == 0) {
-        // tile_x0 is a multiple of 32 and the width of 4: whole aligned words
-        if (lane < (npx * 3) / 4)
-          reinterpret_cast<unsigned*>(row)[lane] = reinterpret_cast<const unsigned*>(s_bytes + warp * 96)[lane];
-      } else if (lane < npx) {
-        for (int k = 0; k < 3; ++k) row[lane * 3 + k] = s_bytes[threadIdx.x * 3 + k];
-      }
-    }
-    return;
-  }
-  float* o = s_out + threadIdx.x * 5;
-  o[0] = acc.r;
-  o[1] = acc.g;
-  o[2] = acc.b;
-  o[3] = acc.a;
-  o[4] = acc.d;
-  __syncwarp();
-  // each warp writes its own row segment: up to 32 pixels x 5 floats, contiguous
-  const int row_first = py * width + tile_x0;  // pixel index of lane 0 (frame < 2^31 pixels)
-  const int seg_lo = max(pixel_begin - row_first, 0);
-  const int seg_hi = min(min(pixel_end - row_first, width - tile_x0), kFoldTileW);
-  const float* src = s_out + warp * 32 * 5;
-  float* dst = piece5 + (static_cast<long long>(row_first) - pixel_begin) * 5;
+        for (int k = 0; k < kFoldDepth; ++k) {
+          h0[k] = h1[k] = false;
+          runid[k] = -2;  // past the end of the list
+          if (e0 + k < nlist) {
+            const FoldEntry E = list[e0 + k];  // same address in every lane: broadcast
+            runid[k] = E.run;
+            const int cx = px - E.x0;
+            const bool inx = cx >= 0 && cx < E.w;
+            h0[k] = live0 && inx && y0 >= E.row0 && y0 < E.row1;
+            h1[k] = live1 && inx && y1 >= E.row0 && y1 < E.row1;
+            if (h0[k]) f0[k] = fold_load(E, y0 - E.row0, cx);
+            if (h1[k]) f1[k] = fold_load(E, y1 - E.row0, cx);
+          }
+        }
 #pragma unroll
-  for (int j = 0; j < 5; ++j) {
-    const int f = lane + 32 * j;  // float within the row segment
-    const int pix = f / 5;        // pixel within the segment
-    if (pix >= seg_lo && pix < seg_hi) dst[f] = src[f];
+        for (int k = 0; k < kFoldDepth; ++k) {
+          if (runid[k] != -2) {
+            fold_step(P0, runid[k], h0[k], f0[k]);
+            fold_step(P1, runid[k], h1[k], f1[k]);
+          }
+        }
+      }
+      nlist = 0;
+      __syncwarp();  // the list is rewritten by the next chunk
+    }
+    const Px5 a0 = fold_finish(P0), a1 = fold_finish(P1);
+
+    // the warp's list doubles as its output staging (2 rows x 32 pixels x 20 B = 1280 B)
+    if (!kBytes || A.piece5 != nullptr) {
+      float* s_out = reinterpret_cast<float*>(list);  // 160 floats per row
+      const Px5 a[2] = {a0, a1};
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        float* o = s_out + 160 * r + lane * 5;
+        o[0] = a[r].r;
+        o[1] = a[r].g;
+        o[2] = a[r].b;
+        o[3] = a[r].a;
+        o[4] = a[r].d;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        // up to 32 pixels x 5 floats, contiguous in the piece
+        const long long row_first = static_cast<long long>(y0 + r) * A.width + tile_x0;
+        const long long seg_lo = max(static_cast<long long>(A.pixel_begin) - row_first, 0LL);
+        const long long seg_hi = min(min(static_cast<long long>(A.pixel_end) - row_first,
+                                         static_cast<long long>(A.width - tile_x0)),
+                                     static_cast<long long>(kFoldTileW));
+        const float* src = s_out + 160 * r;
+        float* dst = A.piece5 + (row_first - A.pixel_begin) * 5;
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+          const int fl = lane + 32 * j;  // float within the row segment
+          const int pix = fl / 5;        // pixel within the segment
+          if (pix >= seg_lo && pix < seg_hi) dst[fl] = src[fl];
+        }
+      }
+      __syncwarp();
+    }
+    if (kBytes) {
+      unsigned char* s_bytes = reinterpret_cast<unsigned char*>(list);  // 96 B per row
+      // which of the (at most 12) wireframe edges can reach these 32 x 2 pixels at all:
+      // most see none, and the per-pixel loop then has nothing to visit
+      unsigned edge_mask = 0u;
+      if (A.edges != nullptr) {
+        const int ecount = __ldg(&A.edges->count);
+        const bool reach = lane < ecount && lane < 12 &&
+                           !(x_last < __ldg(&A.edges->x0[lane]) || tile_x0 > __ldg(&A.edges->x1[lane]) ||
+                             y1 < __ldg(&A.edges->y0[lane]) || y0 > __ldg(&A.edges->y1[lane]));
+        edge_mask = __ballot_sync(0xffffffffu, reach);
+      }
+      overlay_and_quantise(px, y0, a0.r, a0.g, a0.b, A.edges, 0.5f, s_bytes + lane * 3, edge_mask);
+      overlay_and_quantise(px, y1, a1.r, a1.g, a1.b, A.edges, 0.5f, s_bytes + 96 + lane * 3, edge_mask);
+      __syncwarp();
+      const int npx = min(A.width - tile_x0, kFoldTileW);  // pixels of this row segment
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const int y = y0 + r;
+        if (y >= A.height) continue;
+        const long long first = static_cast<long long>(y) * A.width + tile_x0;  // pixel index of lane 0
+        unsigned char* row = A.rgb8 + 3 * (static_cast<size_t>(A.height - 1 - y) * A.width + tile_x0);
+        const bool whole = first >= A.pixel_begin && first + npx <= A.pixel_end;
+        if (whole && (A.width & 3) == 0 && (npx & 3) == 0) {
+          // tile_x0 is a multiple of 32 and the width of 4: whole aligned words
+          if (lane < (npx * 3) / 4)
+            reinterpret_cast<unsigned*>(row)[lane] = reinterpret_cast<const unsigned*>(s_bytes + 96 * r)[lane];
+        } else if (r == 0 ? live0 : live1) {
+          for (int k = 0; k < 3; ++k) row[lane * 3 + k] = s_bytes[96 * r + lane * 3 + k];
+        }
+      }
+      __syncwarp();
+    }
+  }
+
+  if (A.sync.nranks > 0) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();  // this CTA's bytes / pixels are out before the count
+      unsigned* mine = static_cast<unsigned*>(A.sync.ctl.p[A.sync.me]);
+      unsigned* done = mine + kCtlDoneFold;
+      if (atomicAdd(done, 1u) + 1u == gridDim.x) {
+        st_volatile_u32(done, 0u);
+        __threadfence_system();
+        for (int r = 0; r < A.sync.nranks; ++r)
+          st_volatile_u32(static_cast<unsigned*>(A.sync.ctl.p[r]) + A.sync.signal_row * kMaxPeers + A.sync.me,
+                          A.sync.epoch);
+      }
+    }
   }
 }
 
@@ -1059,11 +1262,6 @@ quantize_rgb8_kernel(const float* __restrict__ image5, int width, int height,
 // ------------------------------------------------------- peer-memory exchange
 
 
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
 
 __global__ void __launch_bounds__(32)
 peer_barrier_kernel(const __grid_constant__ PeerPtrs flags, int me, int nranks, int which,
@@ -1084,6 +1282,43 @@ peer_barrier_kernel(const __grid_constant__ PeerPtrs flags, int me, int nranks, 
     }
   }
   __threadfence_system();
+}
+
+// Wait half of the barrier: the signals were raised by the last CTA of a fold (or
+// march) on every rank.
+__global__ void __launch_bounds__(32)
+peer_wait_kernel(const __grid_constant__ PeerPtrs ctl, int me, int nranks, int row, unsigned epoch,
+                 unsigned long long timeout_ns) {
+  const int q = threadIdx.x;
+  unsigned* mine = static_cast<unsigned*>(ctl.p[me]);
+  if (q < nranks) {
+    const unsigned* flag = mine + row * kMaxPeers + q;
+    const unsigned long long t0 = global_timer_ns();
+    while (static_cast<int>(ld_volatile_u32(flag) - epoch) < 0) {
+      __nanosleep(32);
+      if (global_timer_ns() - t0 > timeout_ns) {
+        st_volatile_u32(mine + kCtlError, 1u);
+        break;
+      }
+    }
+  }
+  __threadfence_system();
+}
+
+// NVLink probe: a plain grid-stride copy, 16 B per thread per step, four loads in
+// flight; src or dst may be another GPU's memory.
+__global__ void __launch_bounds__(256)
+peer_copy_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t n16) {
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  for (; i + 3 * stride < n16; i += 4 * stride) {
+    const uint4 a = src[i], b = src[i + stride], c = src[i + 2 * stride], d = src[i + 3 * stride];
+    dst[i] = a;
+    dst[i + stride] = b;
+    dst[i + 2 * stride] = c;
+    dst[i + 3 * stride] = d;
+  }
+  for (; i < n16; i += stride) dst[i] = src[i];
 }
 
 // reference: VolumeRenderer/VolumeRenderer.cpp:228-333 (overlay, same arithmetic as
@@ -1240,6 +1475,44 @@ order_rank_kernel(const OrderBox* __restrict__ boxes, int n, uint4* __restrict__
   for (int i = t; i < n; i += kSortThreads) priority[in[i].w] = i;
 }
 
+// The same total order by counting: priority[i] = number of boxes whose key
+// (minDepth, maxDepth, owner, index) is smaller than box i's.  The keys are
+// distinct (the index is part of them), so the counts are a permutation -- the
+// one a stable sort by (minDepth, maxDepth, owner) produces.  CTA (bx, by)
+// compares 256 boxes against 256 others held in shared memory; n = 4096 is
+// 256 CTAs of 64 K key comparisons each, no passes and no scans, against the
+// 17 dependent passes of the single-CTA radix sort.
+__global__ void __launch_bounds__(256)
+order_count_kernel(const OrderBox* __restrict__ boxes, int n, int* __restrict__ priority) {
+  __shared__ uint4 s_key[256];
+  const int j0 = blockIdx.y * 256;
+  {
+    const int j = j0 + threadIdx.x;
+    uint4 k = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);
+    if (j < n) {
+      const OrderBox b = boxes[j];
+      k = make_uint4(ordered_bits(b.min_depth), ordered_bits(b.max_depth),
+                     static_cast<unsigned>(b.owner), static_cast<unsigned>(j));
+    }
+    s_key[threadIdx.x] = k;
+  }
+  __syncthreads();
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const OrderBox me = boxes[i];
+  const unsigned a0 = ordered_bits(me.min_depth), a1 = ordered_bits(me.max_depth);
+  const unsigned a2 = static_cast<unsigned>(me.owner), a3 = static_cast<unsigned>(i);
+  const int m = min(256, n - j0);
+  int before = 0;
+  for (int t = 0; t < m; ++t) {
+    const uint4 k = s_key[t];
+    const bool less = (k.x != a0) ? (k.x < a0)
+                                  : ((k.y != a1) ? (k.y < a1) : ((k.z != a2) ? (k.z < a2) : (k.w < a3)));
+    before += less ? 1 : 0;
+  }
+  if (before != 0) atomicAdd(&priority[i], before);
+}
+
 __device__ __forceinline__ float fmax_std(float a, float b) { return (a < b) ? b : a; }
 __device__ __forceinline__ float fmin_std(float a, float b) { return (b < a) ? b : a; }
 
@@ -1387,19 +1660,20 @@ int march_grid_size(bool count_samples) {
   return grid;
 }
 
-int launch_raymarch(const MarchFrame& frame, const MarchBox* boxes_dev, const uint8_t* bricks,
-                    const float* tables, float* layers, unsigned long long* sample_counter,
-                    unsigned* tile_counter, bool count_samples, void* stream, int64_t* launches) {
-  if (frame.ntiles <= 0) return 0;
-  const int grid = std::min(march_grid_size(count_samples), frame.ntiles);
+int launch_raymarch(const MarchFrame& frame, const MarchQueues& queues, const MarchBox* boxes_dev,
+                    const uint8_t* bricks, const float* tables, bool count_samples, void* stream,
+                    int64_t* launches) {
+  if (frame.ntiles <= 0 && queues.nranks <= 0) return 0;
+  // a sharded frame launches even without tiles of its own: the CTAs help with the
+  // other queues and the last one raises this rank's "march finished" flag
+  int grid = march_grid_size(count_samples);
+  if (queues.nranks <= 0) grid = std::min(grid, frame.ntiles);
   if (count_samples) {
     raymarch_bricks_kernel<true><<<grid, kMarchThreads, 0, as_stream(stream)>>>(
-        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter,
-        tile_counter);
+        frame, queues, boxes_dev, bricks, reinterpret_cast<const float4*>(tables));
   } else {
     raymarch_bricks_kernel<false><<<grid, kMarchThreads, 0, as_stream(stream)>>>(
-        frame, boxes_dev, bricks, reinterpret_cast<const float4*>(tables), layers, sample_counter,
-        tile_counter);
+        frame, queues, boxes_dev, bricks, reinterpret_cast<const float4*>(tables));
   }
   ++*launches;
   return static_cast<int>(cudaGetLastError());
@@ -1412,32 +1686,103 @@ size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end
   return bands * (static_cast<size_t>(std::max(nlayers, 1)) + 3) * sizeof(int);
 }
 
+namespace {
+struct FoldScratch {
+  int first_row, bands;
+  int2* band_xspan;
+  int* band_counts;
+  int* band_lists;
+};
+FoldScratch fold_scratch_layout(void* scratch, int width, int pixel_begin, int pixel_end) {
+  FoldScratch L;
+  L.first_row = pixel_begin / width;
+  const int last_row = (pixel_end - 1) / width;
+  L.bands = (last_row - L.first_row) / kFoldBandRows + 1;
+  L.band_xspan = static_cast<int2*>(scratch);
+  L.band_counts = reinterpret_cast<int*>(L.band_xspan + L.bands);
+  L.band_lists = L.band_counts + L.bands;
+  return L;
+}
+int fold_grid_size(bool bytes) {
+  static int cached[2] = {0, 0};
+  int& grid = cached[bytes ? 1 : 0];
+  if (grid == 0) {
+    int device = 0, sms = 148, per_sm = 1;
+    cudaGetDevice(&device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (bytes)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fold_layers_kernel<true>, kFoldThreads, 0);
+    else
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fold_layers_kernel<false>, kFoldThreads, 0);
+    grid = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  return grid;
+}
+}  // namespace
+
+int launch_fold_bin(const FoldLayer* layers_dev, int nlayers, int width, int pixel_begin,
+                    int pixel_end, void* scratch, void* stream, int64_t* launches) {
+  if (pixel_end <= pixel_begin) return 0;
+  const FoldScratch L = fold_scratch_layout(scratch, width, pixel_begin, pixel_end);
+  fold_bin_kernel<<<L.bands, kBinThreads, 0, as_stream(stream)>>>(layers_dev, nlayers, L.first_row,
+                                                                  L.band_lists, L.band_counts,
+                                                                  L.band_xspan);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int pixel_begin, int pixel_end, float* piece5, void* scratch, void* stream,
-                int64_t* launches, const FoldBytes* bytes) {
+                int64_t* launches, const FoldBytes* bytes, const FoldSync* sync) {
   const int npix = pixel_end - pixel_begin;
-  if (npix <= 0) return 0;
-  const int first_row = pixel_begin / width, last_row = (pixel_end - 1) / width;
-  const int bands = (last_row - first_row) / kFoldBandRows + 1;
-  int2* band_xspan = static_cast<int2*>(scratch);
-  int* band_counts = reinterpret_cast<int*>(band_xspan + bands);
-  int* band_lists = band_counts + bands;
-  fold_bin_kernel<<<bands, kFoldThreads, 0, as_stream(stream)>>>(layers_dev, nlayers, first_row,
-                                                                 band_lists, band_counts, band_xspan);
-  ++*launches;
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return static_cast<int>(e);
-  const dim3 grid((width + kFoldTileW - 1) / kFoldTileW, bands);
-  if (bytes != nullptr && bytes->rgb8 != nullptr) {
-    if (pixel_begin != 0 || pixel_end != width * bytes->height) return static_cast<int>(cudaErrorInvalidValue);
-    fold_layers_kernel<true><<<grid, kFoldThreads, 0, as_stream(stream)>>>(
-        layers_dev, nlayers, band_lists, band_counts, band_xspan, first_row, width, pixel_begin,
-        pixel_end, nullptr, bytes->edges, bytes->height, bytes->rgb8);
-  } else {
-    fold_layers_kernel<false><<<grid, kFoldThreads, 0, as_stream(stream)>>>(
-        layers_dev, nlayers, band_lists, band_counts, band_xspan, first_row, width, pixel_begin,
-        pixel_end, piece5, nullptr, 0, nullptr);
+  const bool sharded = sync != nullptr && sync->nranks > 0;
+  if (npix <= 0 && !sharded) return 0;
+  FoldArgs A{};
+  A.layers = layers_dev;
+  A.nlayers = nlayers;
+  A.width = width;
+  A.pixel_begin = pixel_begin;
+  A.pixel_end = pixel_end;
+  if (npix > 0) {
+    const FoldScratch L = fold_scratch_layout(scratch, width, pixel_begin, pixel_end);
+    A.first_row = L.first_row;
+    A.bands = L.bands;
+    A.band_xspan = L.band_xspan;
+    A.band_counts = L.band_counts;
+    A.band_lists = L.band_lists;
   }
+  A.piece5 = piece5;
+  if (sharded) A.sync = *sync;
+  const bool as_bytes = bytes != nullptr && bytes->rgb8 != nullptr;
+  const int tiles = A.bands * ((width + kFoldTileW - 1) / kFoldTileW);
+  // an empty piece of a sharded frame still takes part in the hand-shake
+  const int grid = std::max(1, std::min(fold_grid_size(as_bytes), tiles));
+  if (as_bytes) {
+    A.edges = bytes->edges;
+    A.height = bytes->height;
+    A.rgb8 = bytes->rgb8;
+    fold_layers_kernel<true><<<grid, kFoldThreads, 0, as_stream(stream)>>>(A);
+  } else {
+    A.height = 0;
+    fold_layers_kernel<false><<<grid, kFoldThreads, 0, as_stream(stream)>>>(A);
+  }
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_peer_wait(const PeerPtrs& ctl, int me, int nranks, int row, uint32_t epoch,
+                     unsigned long long timeout_ns, void* stream, int64_t* launches) {
+  if (nranks > kMaxPeers || row < 0 || row >= kFlagRows) return static_cast<int>(cudaErrorInvalidValue);
+  peer_wait_kernel<<<1, 32, 0, as_stream(stream)>>>(ctl, me, nranks, row, epoch, timeout_ns);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_peer_copy(const void* src, void* dst, size_t bytes, int blocks, void* stream,
+                     int64_t* launches) {
+  if (bytes < 16) return 0;
+  peer_copy_kernel<<<blocks, 256, 0, as_stream(stream)>>>(static_cast<const uint4*>(src),
+                                                          static_cast<uint4*>(dst), bytes / 16);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }
@@ -1508,6 +1853,15 @@ int launch_order_rank(const OrderBox* boxes_dev, int n, void* scratch_a, void* s
   order_rank_kernel<<<1, kSortThreads, 0, as_stream(stream)>>>(
       boxes_dev, n, static_cast<uint4*>(scratch_a), static_cast<uint4*>(scratch_b), owner_bits,
       priority_dev);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_order_count(const OrderBox* boxes_dev, int n, int32_t* priority_dev, void* stream,
+                       int64_t* launches) {
+  if (n <= 0) return 0;
+  const unsigned blocks = static_cast<unsigned>((n + 255) / 256);
+  order_count_kernel<<<dim3(blocks, blocks), 256, 0, as_stream(stream)>>>(boxes_dev, n, priority_dev);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }

@@ -128,6 +128,9 @@ class FrameStats(C.Structure):
         ("fold_ms", C.c_float),
         ("samples", C.c_int64),
         ("exchanged_bytes", C.c_int64),
+        ("stolen_tiles", C.c_int64),
+        ("tiles", C.c_int64),
+        ("fragment_pixels", C.c_int64),
     ]
 
 
@@ -239,6 +242,9 @@ def _declare(lib):
         "amrvr_ctx_kernel_launches": (i64, [vp]),
         "amrvr_ctx_set_order_device_min_boxes": (C.c_int, [vp, i32]),
         "amrvr_ctx_frame_rgb8_device": (vp, [vp]),
+        "amrvr_ctx_last_rank_order": (C.c_int, [vp, _P(i32), _P(i32)]),
+        "amrvr_scene_is_replicated": (C.c_int, [vp]),
+        "amrvr_peer_bandwidth": (C.c_int, [vp, C.c_size_t, i32, i32, i32, _P(f32)]),
         "amrvr_brick_stats": (C.c_int, [vp, i32, _P(Box), _P(C.c_double), _P(C.c_double),
                                         _P(C.c_double), _P(i64)]),
         "amrvr_scene_upload": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),

@@ -97,6 +97,22 @@ class Context:
     def kernel_launches(self) -> int:
         return int(self.lib.amrvr_ctx_kernel_launches(self._h))
 
+    def last_rank_order(self):
+        """(rank_order, graph_failed) of the last render_frame: the visibility order
+        BuildVisibilityOrderedGroup would hand to the compositor."""
+        out = np.zeros(self.nranks, np.int32)
+        failed = C.c_int(0)
+        self.check(self.lib.amrvr_ctx_last_rank_order(self._h, out.ctypes.data_as(_P(C.c_int)),
+                                                      C.byref(failed)))
+        return out, bool(failed.value)
+
+    def peer_bandwidth(self, nbytes: int, peer_offset: int = 1, write: bool = True, iters: int = 10) -> float:
+        """Measured NVLink rate of this rank (GB/s), all ranks copying at once (collective)."""
+        out = C.c_float(0)
+        self.check(self.lib.amrvr_peer_bandwidth(self._h, int(nbytes), int(peer_offset), int(bool(write)),
+                                                 int(iters), C.byref(out)))
+        return float(out.value)
+
     def set_order_device_min_boxes(self, n: int):
         """Box count from which the visibility ordering uses its device kernels."""
         self.check(self.lib.amrvr_ctx_set_order_device_min_boxes(self._h, int(n)))
@@ -243,6 +259,10 @@ class DeviceScene:
         if self._h:
             self.ctx.lib.amrvr_scene_free(self.ctx._h, self._h)
             self._h = C.c_void_p()
+
+    @property
+    def replicated(self) -> bool:
+        return bool(self.ctx.lib.amrvr_scene_is_replicated(self._h))
 
     def global_boxes(self):
         n = C.c_int(0)

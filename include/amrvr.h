@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define AMRVR_ABI_VERSION 1
+#define AMRVR_ABI_VERSION 2
 
 enum {
   AMRVR_OK = 0,
@@ -135,6 +135,10 @@ int64_t amrvr_ctx_kernel_launches(const amrvr_ctx* ctx);
 /* Device pointer of the RGB8 image (width*height*3, top row first) the last
  * amrvr_render_frame built on this ctx (root only); valid until the next frame. */
 const uint8_t* amrvr_ctx_frame_rgb8_device(const amrvr_ctx* ctx);
+/* The visibility order amrvr_render_frame computed for its last frame
+ * (BuildVisibilityOrderedGroup): rank_order[i] = rank the reference lets own
+ * image piece i.  rank_order has nranks entries. */
+int amrvr_ctx_last_rank_order(const amrvr_ctx* ctx, int* rank_order, int* graph_failed);
 /* amrvr_order_boxes / amrvr_order_records run the device radix sort and the
  * device pair test from this many global boxes upwards (default 1024); below
  * it the same sequential driver uses its host back end, which is faster than a
@@ -159,6 +163,9 @@ int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                        const amrvr_scalar_transform* transform,
                        float range_min, float range_max, amrvr_scene** out);
 int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene);
+/* 1 when every rank holds the bricks of all ranks (NVLink box: allgathered at
+ * upload), so that amrvr_render_frame deals march tiles, not boxes, to GPUs. */
+int amrvr_scene_is_replicated(const amrvr_scene* scene);
 /* Global box table (all ranks, owner-major, owner-local order). */
 int amrvr_scene_global_boxes(const amrvr_scene* scene, int* nglobal,
                              const amrvr_box_record** records);
@@ -499,11 +506,14 @@ typedef struct amrvr_frame_params {
 
 typedef struct amrvr_frame_stats {
   float march_ms, order_ms, composite_ms, gather_ms, post_ms;
-  float fold_ms;           /* the fold kernel alone (inside composite_ms); in peer-memory mode
-                              it is also the NVLink transfer: other GPUs' fragments are read
-                              by the fold itself */
-  int64_t samples;
-  int64_t exchanged_bytes; /* bytes this rank sent to (NCCL) or pulled from (peer memory) other ranks */
+  float fold_ms;           /* the fold kernel alone (inside composite_ms); in a sharded frame it
+                              starts by waiting for the slowest GPU's march */
+  int64_t samples;         /* samples THIS rank marched (any box: a sharded frame deals tiles, not boxes) */
+  int64_t exchanged_bytes; /* fragment bytes this rank sent to other ranks: stored into their pools
+                              over NVLink by the march (sharded frame) or sent with NCCL */
+  int64_t stolen_tiles;    /* march tiles this rank took from other GPUs' queues (sharded frame) */
+  int64_t tiles;           /* march tiles of the whole frame */
+  int64_t fragment_pixels; /* (pixel, layer) fragments stored for this rank's piece */
 } amrvr_frame_stats;
 
 /* a1-a17 in one call = VolumeRenderer::renderSingleTrial
@@ -517,6 +527,15 @@ int amrvr_render_frame(amrvr_ctx* ctx, const amrvr_scene* scene,
                        const amrvr_colormap_pt* pts, int npts, int root,
                        float* rgba5_host, uint8_t* rgb8_host,
                        amrvr_frame_stats* stats);
+
+/* NVLink probe (collective, nranks > 1 with peer access): every rank copies
+ * `bytes` between its own memory and that of rank (rank + peer_offset) mod
+ * nranks with a plain load/store kernel, `iters` times, all ranks at once.
+ * write != 0: stores into the peer (what the march does with the tiles it takes
+ * from another GPU's queue); write == 0: loads from the peer.  *gbytes_per_s is
+ * this rank's rate: the measured per-GPU, per-direction link figure. */
+int amrvr_peer_bandwidth(amrvr_ctx* ctx, size_t bytes, int peer_offset, int write,
+                         int iters, float* gbytes_per_s);
 
 #ifdef __cplusplus
 }

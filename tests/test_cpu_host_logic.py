@@ -14,7 +14,7 @@ def test_library_exports_every_declared_symbol(lib):
     assert len(names) >= 40
     missing = [n for n in names if not hasattr(lib, n)]
     assert not missing, missing
-    assert lib.amrvr_abi_version() == 1
+    assert lib.amrvr_abi_version() == 2
 
 
 def test_every_declared_symbol_has_a_ctypes_prototype(lib):

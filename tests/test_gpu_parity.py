@@ -160,6 +160,15 @@ def test_layers_user_colormap_and_inside_camera(ctx, oracle):
     _check_layers(ctx, oracle, scene, cam, 96, 64, colormap=cmap)
 
 
+def test_layers_width_not_multiple_of_four(ctx, oracle):
+    """Footprints are padded to 4-column multiples; columns past the frame edge are
+    not rays: the sample count must still equal the reference's (50 x 37 frame)."""
+    scene = scenes.scene_c2(box_cells=8)
+    _check_layers(ctx, oracle, scene, scenes.make_camera(), 50, 37)
+    cam = scenes.make_camera(eye=(0.52, 0.47, 0.55), look_at=(0.9, 0.6, 0.1), fov_y=70.0)
+    _check_layers(ctx, oracle, scene, cam, 50, 37)  # eye inside: full-frame footprints
+
+
 # ------------------------------------------------------------- whole frame
 
 def _check_frame(ctx, oracle, scene, camera, params, colormap=None):
@@ -173,6 +182,29 @@ def _check_frame(ctx, oracle, scene, camera, params, colormap=None):
     assert got["stats"].samples == want["samples"]
     ds.free()
     return err, lsb
+
+
+def test_frame_odd_size(ctx, oracle):
+    """50 x 37: byte rows that are not whole words, fold tiles cut by the frame edge."""
+    _check_frame(ctx, oracle, scenes.scene_c2(box_cells=8), scenes.make_camera(), _params(50, 37))
+    _check_frame(ctx, oracle, scenes.scene_c4(box_cells=8), scenes.make_camera(), _params(37, 50))
+
+
+def test_frame_bytes_only_matches_float_path(ctx, oracle):
+    """The fold's own overlay + RGB8 epilogue (nobody asks for the float frame)
+    gives the bytes of the float frame quantised afterwards."""
+    scene = scenes.scene_c4(box_cells=8)
+    cam = scenes.make_camera()
+    for (w, h) in ((128, 96), (50, 37)):
+        params = _params(w, h)
+        ds = ctx.upload_scene(scene)
+        both = ctx.render_frame(ds, cam, params)
+        want = both["rgb8"].copy()
+        only = ctx.render_frame(ds, cam, params, want_rgba=False)
+        assert np.array_equal(only["rgb8"], want)
+        lsb = int(np.abs(want.astype(int) - oracle.render_frame(scene, cam, params)["rgb8"].astype(int)).max())
+        assert lsb <= 1
+        ds.free()
 
 
 def test_frame_c1(ctx, oracle):
