@@ -188,6 +188,8 @@ struct amrvr_scene {
   bool replicated = false;
   std::vector<uint64_t> global_brick_off;
   std::vector<MarchBox> march_const_global;  // like march_const, for every global box
+  cudaEvent_t up0 = nullptr, up1 = nullptr;  // around the FAB copies + quantise launches of the upload
+  int64_t fab_bytes = 0, fab_cells = 0;
   float range_min = 0.f, range_max = 1.f;
   // MarchBox fields that depend on the box alone (corners, cell sizes, exactness
   // of the reciprocal, epsilon, brick offset): built once, on the first frame
@@ -721,6 +723,15 @@ extern "C" int amrvr_ctx_set_order_device_min_boxes(amrvr_ctx* ctx, int min_boxe
 // ---------------------------------------------------------------------------
 namespace {
 
+cudaError_t take_event(amrvr_ctx* ctx, cudaEvent_t* out) {
+  if (!ctx->event_pool.empty()) {
+    *out = ctx->event_pool.back();
+    ctx->event_pool.pop_back();
+    return cudaSuccess;
+  }
+  return cudaEventCreate(out);
+}
+
 struct StagedBox {
   const double* dev;  // device-visible pointer to the first valid cell
   int64_t jstride, kstride;
@@ -1106,6 +1117,15 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
     CUDA_TRY(ctx, scene->bricks.reserve(need));
   }
   tr.mark("upload_setup");
+  CUDA_TRY(ctx, take_event(ctx, &scene->up0));
+  CUDA_TRY(ctx, take_event(ctx, &scene->up1));
+  for (int b = 0; b < nboxes; ++b) {
+    const int64_t cells = static_cast<int64_t>(std::max(boxes[b].dims[0], 0)) *
+                          std::max(boxes[b].dims[1], 0) * std::max(boxes[b].dims[2], 0);
+    scene->fab_cells += cells;
+    scene->fab_bytes += cells * static_cast<int64_t>(sizeof(double));
+  }
+  CUDA_TRY(ctx, cudaEventRecord(scene->up0, ctx->stream));
   {
     const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene);
     if (st != AMRVR_OK) {
@@ -1113,6 +1133,7 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
       return st;
     }
   }
+  CUDA_TRY(ctx, cudaEventRecord(scene->up1, ctx->stream));
   tr.mark("upload_enqueue");
   if (scene->replicated)  // in place: every rank contributes its own slot
     NCCL_TRY(ctx, nccl_api().AllGather(scene->bricks.as<char>() + slot * ctx->rank, scene->bricks.ptr,
@@ -1125,6 +1146,22 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
 
 extern "C" int amrvr_scene_is_replicated(const amrvr_scene* scene) {
   return (scene != nullptr && scene->replicated) ? 1 : 0;
+}
+
+extern "C" int amrvr_scene_upload_stats(const amrvr_scene* scene, float* device_ms, int64_t* fab_bytes,
+                                        int64_t* cells) {
+  if (scene == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "scene is NULL");
+  if (device_ms) {
+    *device_ms = 0.0f;
+    if (scene->up0 != nullptr && scene->up1 != nullptr &&
+        cudaEventElapsedTime(device_ms, scene->up0, scene->up1) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return fail(nullptr, AMRVR_ERR_CUDA, "event timing failed");
+    }
+  }
+  if (fab_bytes) *fab_bytes = scene->fab_bytes;
+  if (cells) *cells = scene->fab_cells;
+  return AMRVR_OK;
 }
 
 // ---------------------------------------------------------------------------
@@ -1363,6 +1400,11 @@ extern "C" int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene) {
     scene->bricks = DeviceBuffer{};
   }
   scene->bricks.release();
+  for (cudaEvent_t e : {scene->up0, scene->up1}) {
+    if (e == nullptr) continue;
+    if (ctx != nullptr && ctx->event_pool.size() < 16) ctx->event_pool.push_back(e);
+    else cudaEventDestroy(e);
+  }
   delete scene;
   return AMRVR_OK;
 }
@@ -1511,14 +1553,6 @@ const float* cached_color_table(amrvr_ctx* ctx, float alpha_scale, float norm, f
   return cache[0].rgba.data();
 }
 
-cudaError_t take_event(amrvr_ctx* ctx, cudaEvent_t* out) {
-  if (!ctx->event_pool.empty()) {
-    *out = ctx->event_pool.back();
-    ctx->event_pool.pop_back();
-    return cudaSuccess;
-  }
-  return cudaEventCreate(out);
-}
 
 }  // namespace
 

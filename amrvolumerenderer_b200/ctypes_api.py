@@ -244,6 +244,7 @@ def _declare(lib):
         "amrvr_ctx_frame_rgb8_device": (vp, [vp]),
         "amrvr_ctx_last_rank_order": (C.c_int, [vp, _P(i32), _P(i32)]),
         "amrvr_scene_is_replicated": (C.c_int, [vp]),
+        "amrvr_scene_upload_stats": (C.c_int, [vp, _P(f32), _P(i64), _P(i64)]),
         "amrvr_peer_bandwidth": (C.c_int, [vp, C.c_size_t, i32, i32, i32, _P(f32)]),
         "amrvr_brick_stats": (C.c_int, [vp, i32, _P(Box), _P(C.c_double), _P(C.c_double),
                                         _P(C.c_double), _P(i64)]),

@@ -264,6 +264,13 @@ class DeviceScene:
     def replicated(self) -> bool:
         return bool(self.ctx.lib.amrvr_scene_is_replicated(self._h))
 
+    def upload_stats(self):
+        """(device ms of the FAB copies + quantise, FAB bytes, cells) of this rank's upload."""
+        ms, nbytes, cells = C.c_float(0), C.c_int64(0), C.c_int64(0)
+        self.ctx.check(self.ctx.lib.amrvr_scene_upload_stats(self._h, C.byref(ms), C.byref(nbytes),
+                                                             C.byref(cells)))
+        return float(ms.value), int(nbytes.value), int(cells.value)
+
     def global_boxes(self):
         n = C.c_int(0)
         recs = _P(api.BoxRecord)()

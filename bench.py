@@ -4,13 +4,17 @@ ray-march + frames/s 2048^2 3-level AMR at 1/2/4/8 B200").
 
 A step = one frame of workload C4 (synthetic 3-level AMR, 1024^3 effective, 176
 boxes of 64^3, 2048x2048, visibility graph on) through
-amrvr_render_frame: ray-march of this rank's bricks -> visibility order ->
-sort-last composite -> gather -> byte image.  The boxes are sharded over the N
-ranks (contiguous chunks of the (level,k,j,i) order); the frame is fixed, so
-scaling is "strong".  `value` = ray-march samples of the whole frame / device
-time per frame, bricks resident in HBM.  `e2e` = the same frame through the
-public API from pinned HOST FABs: amrvr_scene_upload (H2D + quantise) +
-amrvr_render_frame + D2H of the RGB8 image, all inside the timed region.
+amrvr_render_frame: ray-march -> visibility order -> sort-last composite ->
+byte image on the root.  The boxes are dealt to the N ranks (the box->rank map
+fixes the reference's blend structure); the frame is fixed, so scaling is
+"strong".  `value` = ray-march samples of the whole frame / device time per
+frame, bricks resident in HBM.  `e2e` = the same frame through the public API
+from pinned HOST FABs: amrvr_scene_upload (H2D + quantise) + amrvr_render_frame
++ D2H of the RGB8 image, all inside the timed region.
+
+Every line carries `parity`: the same scene, box->rank map and rank count
+rendered at a reduced frame size and compared, untimed, with the oracle (and
+with the reference's own PPM); a broken tolerance makes the run exit non-zero.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 """
@@ -49,7 +53,9 @@ WORKLOADS = {
     "C5-16": (functools.partial(scenes.scene_c5, n=16), 4096, 4096, 1, 0.0),
 }
 DEAL = "skewed"  # box i -> rank (i + i div P) mod P over the (level, k, j, i) order
-NVLINK_PEAK_GBPS = 900.0  # NVLink 5, per direction per GPU (B200_PROFILING.md); no measured link figure
+NVLINK_NOMINAL_GBPS = 900.0  # NVLink 5, per direction per GPU (B200_PROFILING.md)
+RGBA_TOL = 1e-4  # north_star: float RGBA within 1e-4 absolute per channel
+LSB_TOL = 1      # north_star: 8-bit output within 1 LSB
 
 
 def _peaks():
@@ -60,55 +66,55 @@ def _peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def _ncu_traffic(kernel_tag="march"):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch,
-    from the newest committed `ncu --set full` summary under profiles/ (a capture of
-    the same workload; ncu is never run inside the bench)."""
+def _ncu_value(pattern, kernel="march"):
+    """A number of the newest committed `ncu --set full` summary of `kernel` under
+    profiles/ (a capture of this same workload; ncu is never run inside the bench)."""
     import re
 
-    best = None
-    for f in sorted((ROOT / "profiles").glob(f"r*_{kernel_tag}_v*_full.txt")):
-        best = f
-    for f in sorted((ROOT / "profiles").glob(f"r*_{kernel_tag}_fold_current_full.txt")):
-        best = f  # the capture of the code as committed; its first block is the march
-    if best is None:
+    files = sorted((ROOT / "profiles").glob(f"r*_{kernel}_full.txt"))
+    if not files:
+        return None, None
+    best = files[-1]
+    for ln in best.read_text().splitlines():
+        m = re.match(pattern, ln)
+        if m:
+            return m, best.name
+    return None, best.name
+
+
+def _ncu_traffic(kernel="march"):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the kernel."""
+    import re
+
+    files = sorted((ROOT / "profiles").glob(f"r*_{kernel}_full.txt"))
+    if not files:
         return None, None
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    total = 0.0
-    seen = 0
-    for ln in best.read_text().splitlines():
+    total, seen = 0.0, 0
+    for ln in files[-1].read_text().splitlines():
         m = re.match(r"\s*dram__bytes_(read|write)\.sum\s+([0-9.]+)\s+(\w+)", ln)
         if m and seen < 2:
             total += float(m.group(2)) * unit.get(m.group(3), 1.0)
             seen += 1
-    return (total if seen == 2 else None), best.name
+    return (total if seen == 2 else None), files[-1].name
 
 
 def _ncu_issue(march_s, sm_clock_hz, n_sm=148):
-    """Issue-slot use of the march at the LIVE launch duration: warp instructions
-    per launch (smsp__inst_executed.sum of the committed ncu capture of this same
-    workload -- an instruction count, not a timing) / live duration / (SMs x 4
-    schedulers x SM clock).  None when there is no capture to read."""
-    import re
-
+    """Issue-slot use of the march at the LIVE launch duration: warp instructions per
+    launch (smsp__inst_executed.sum of the committed ncu capture of this workload --
+    an instruction count, not a timing) / live duration / (SMs x 4 schedulers x clock)."""
     try:
-        _, name = _ncu_traffic()
-        if name is None or march_s <= 0 or sm_clock_hz <= 0:
+        m, name = _ncu_value(r"\s*smsp__inst_executed\.sum\s+([0-9.]+)\s+inst")
+        if m is None or march_s <= 0 or sm_clock_hz <= 0:
             return None
-        for ln in (ROOT / "profiles" / name).read_text().splitlines():
-            m = re.match(r"\s*smsp__inst_executed\.sum\s+([0-9.]+)\s+inst", ln)
-            if m:  # first block = the march
-                inst = float(m.group(1))
-                return {"warp_instructions_per_launch": inst,
-                        "achieved_per_sm_clock": inst / march_s / (n_sm * sm_clock_hz),
-                        "peak_per_sm_clock": 4.0,
-                        "frac": inst / march_s / (n_sm * 4.0 * sm_clock_hz),
-                        "source": f"profiles/{name} (instruction count, captured on the "
-                                  "sample-counting instantiation: an upper bound for the timed "
-                                  "one) / live launch duration"}
+        inst = float(m.group(1))
+        return {"warp_instructions_per_launch": inst,
+                "achieved_per_sm_clock": inst / march_s / (n_sm * sm_clock_hz),
+                "peak_per_sm_clock": 4.0,
+                "frac": inst / march_s / (n_sm * 4.0 * sm_clock_hz),
+                "source": f"profiles/{name} (instruction count of the timed instantiation) / live launch duration"}
     except Exception:  # never let a reporting extra break the bench line
         return None
-    return None
 
 
 class ClockSampler(threading.Thread):
@@ -198,23 +204,46 @@ def pin_scene(lib, scene, rank, nranks):
     return base, total
 
 
+def _host_cores():
+    return len(os.sched_getaffinity(0))
+
+
+def _mem_available_gb():
+    try:
+        for ln in open("/proc/meminfo"):
+            if ln.startswith("MemAvailable:"):
+                return int(ln.split()[1]) / (1 << 20)
+    except OSError:
+        pass
+    return 0.0
+
+
+def _sample_params(workload, size):
+    _, W, H, aa, transp = WORKLOADS[workload]
+    root = int(round(aa ** 0.5))
+    return api.FrameParams(width=size // root, height=size // root, box_transparency=transp,
+                           antialiasing=aa, use_visibility_graph=1, count_samples=1, draw_bounding_box=1)
+
+
 def reference_arm(args, workload):
-    """The reference's own CPU implementation (oracle/_ref: its unmodified
-    sources against the AMReX/MPI shim; ranks are threads) on a bounded sample."""
+    """The reference's own CPU implementation (oracle/_ref: its unmodified sources
+    against the AMReX/MPI shim; ranks are threads).  Each step is a bounded sample
+    of the workload -- the same boxes and camera at 512x512, 1/16 of the rays --
+    because a full 2048^2 frame takes its dense layers 14.8 GB and ~20 s; ONE such
+    full-size frame is timed as well (`full_size_check`) so that the rate the
+    sample gives can be compared with the rate of the real frame."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from oracle.oracle import Oracle, Ref, RefUnavailable
 
     factory, W, H, aa, transp = WORKLOADS[workload]
-    cores = len(os.sched_getaffinity(0))
+    cores = _host_cores()
     P = max(1, min(8, cores))
     scene = factory(nranks=P, rule=DEAL)
     camera = scenes.make_camera()
-    sw, sh = 512, 512  # bounded sample: same boxes and camera, 1/16 of the rays
-    params = api.FrameParams(width=sw // int(round(aa ** 0.5)), height=sh // int(round(aa ** 0.5)),
-                             box_transparency=transp, antialiasing=aa, use_visibility_graph=1,
-                             count_samples=1, draw_bounding_box=1)
+    sw = sh = 512
+    params = _sample_params(workload, sw)
     kind = "reference"
     try:
         eng = Ref()
@@ -234,16 +263,35 @@ def reference_arm(args, workload):
             times.append(dt)
     ms = 1e3 * float(np.mean(times))
     value = samples / (ms * 1e-3) / 1e9
+    full = None
+    if kind == "reference" and workload == "C4" and not args.no_full_size:
+        need_gb = len(scene.boxes) * W * H * 20 / (1 << 30) * 1.25 + 2.0
+        if _mem_available_gb() >= need_gb:
+            fp = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
+                                 use_visibility_graph=1, count_samples=1, draw_bounding_box=1)
+            t0 = time.perf_counter()
+            o = eng.render_scene(scene, camera, fp, "/tmp/amrvr_bench_ref_full.ppm")
+            dt = time.perf_counter() - t0
+            full = {"size": f"{W}x{H}", "ms": dt * 1e3, "samples": o["samples"],
+                    "gsamples_per_s": o["samples"] / dt / 1e9,
+                    "rate_vs_sample": (o["samples"] / dt / 1e9) / value if value > 0 else None,
+                    "stages": eng.stage_seconds(o["log"]),
+                    "note": "one full-size frame of the same scene, timed once: the reference's rate on "
+                            "the real frame next to the rate its 512x512 sample gives"}
+        else:
+            full = {"skipped": f"needs ~{need_gb:.0f} GB of host memory for the reference's dense layers, "
+                               f"{_mem_available_gb():.0f} GB available"}
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload, "sample": f"{sw}x{sh} frame of the {W}x{H} workload",
                    "boxes": len(scene.boxes), "cells": scene.total_cells()},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": P, "kind": kind,
-                         "sample": f"{workload} scene, {sw}x{sh} render size, {P} ranks-as-threads, "
-                                   f"full frame incl. composite; stages {stages}"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": P, "host_cores": cores, "kind": kind,
+                         "sample": f"{workload} scene, {sw}x{sh} render size, {P} ranks-as-threads on "
+                                   f"{cores} host cores, full frame incl. composite; stages {stages}"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "full_size_check": full,
     }
     print(json.dumps(line), flush=True)
 
@@ -252,15 +300,12 @@ def cpu_baseline(workload):
     """Bounded CPU sample for the product line (rank 0, N=1)."""
     from oracle.oracle import Oracle, Ref, RefUnavailable
 
-    factory, W, H, aa, transp = WORKLOADS[workload]
-    cores = len(os.sched_getaffinity(0))
+    cores = _host_cores()
     P = max(1, min(8, cores))
+    factory = WORKLOADS[workload][0]
     scene = factory(nranks=P, rule=DEAL)
     sw = sh = 512
-    root = int(round(aa ** 0.5))
-    params = api.FrameParams(width=sw // root, height=sh // root, box_transparency=transp,
-                             antialiasing=aa, use_visibility_graph=1, count_samples=1,
-                             draw_bounding_box=1)
+    params = _sample_params(workload, sw)
     try:
         eng, kind = Ref(), "reference"
     except (RefUnavailable, OSError):
@@ -273,10 +318,101 @@ def cpu_baseline(workload):
         out = eng.render_frame(scene, scenes.make_camera(), params)
         stages, P = {}, 1
     dt = time.perf_counter() - t0
-    return {"value": out["samples"] / dt / 1e9, "unit": UNIT, "cores": P, "kind": kind,
+    return {"value": out["samples"] / dt / 1e9, "unit": UNIT, "cores": P, "host_cores": cores, "kind": kind,
             "sample": f"{workload} scene at {sw}x{sh} render size ({out['samples']} samples, "
-                      f"{dt:.2f} s wall, {P} ranks-as-threads); reference stage times {stages}",
+                      f"{dt:.2f} s wall, {P} ranks-as-threads on {cores} host cores); reference stage "
+                      f"times {stages}",
             "march_only_value": (out["samples"] / stages["march_s"] / 1e9) if stages.get("march_s") else None}
+
+
+# --------------------------------------------------------------------- parity
+
+def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
+    """Untimed: the bench's own scene, box->rank map and rank count at a reduced frame
+    size, against the oracle (same rank count: the reference's blend fold is not
+    associative) and against the PPM the reference itself writes.  Visibility order
+    and pixel ownership bit-exact, sample count exact, float RGBA <= 1e-4, bytes <= 1 LSB."""
+    import torch
+
+    size = 512 if len(scene.boxes) <= 512 else 128  # the oracle's layers are dense frames
+    params = _sample_params(workload, size)
+    root = int(round(params.antialiasing ** 0.5))
+    rw, rh = params.width * root, params.height * root
+    ds = ctx.upload_scene(scene)
+    got = ctx.render_frame(ds, camera, params)
+    samples = torch.tensor([got["stats"].samples], dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(samples)
+    frame_order, frame_failed = ctx.last_rank_order()
+    # ownership through the Compositor::compose seam: every rank's region
+    order, failed = ctx.order_boxes(ds, camera, params.width / params.height)
+    recs, n = scene.records()
+    from amrvolumerenderer_b200.engine import reference_sample_distance
+
+    ref_d = reference_sample_distance(
+        recs, n, [min(float(r.min_corner[d]) for r in recs[:n]) for d in range(3)],
+        [max(float(r.max_corner[d]) for r in recs[:n]) for d in range(3)])
+    layers = ctx.raymarch(ds, camera, rw, rh, params.box_transparency, ref_d)
+    begin, end, _piece = ctx.composite(ds, layers, camera, order)
+    spans = [None] * world
+    if world > 1:
+        dist.all_gather_object(spans, (rank, begin, end))
+    else:
+        spans = [(0, begin, end)]
+    out = None
+    if rank == 0:
+        from oracle.oracle import Oracle, Ref, RefUnavailable, read_ppm
+
+        orc = Oracle()
+        want = orc.render_frame(scene, camera, params)
+        want_order, graph_ok = orc.order(world, recs, n, camera, params.width / params.height)
+        own_ok = True
+        for piece_index, owner in enumerate(want_order):
+            b, e = orc.piece_range(rw * rh, piece_index, world)
+            own_ok = own_ok and tuple(spans[owner]) == (int(owner), b, e)
+        err = float(np.abs(got["final5"][..., :4] - want["final5"][..., :4]).max())
+        lsb = int(np.abs(got["rgb8"].astype(int) - want["rgb8"].astype(int)).max())
+        out = {"ranks": world, "size": f"{params.width}x{params.height} AA{params.antialiasing}",
+               "rank_order_equal": bool(np.array_equal(order, want_order) and
+                                        np.array_equal(frame_order, want_order) and
+                                        failed == (not graph_ok) and frame_failed == (not graph_ok)),
+               "ownership_equal": bool(own_ok),
+               "samples_equal": bool(int(samples.item()) == int(want["samples"])),
+               "max_abs_rgba": err, "max_lsb": lsb, "against": "oracle, same rank count and box->rank map"}
+        try:  # the reference's own frame: real VolumeRenderer::renderScene, ranks as threads
+            ref = Ref()
+            ref.render_scene(scene, camera, params, "/tmp/amrvr_bench_parity.ppm")
+            ppm = read_ppm("/tmp/amrvr_bench_parity.ppm")
+            out["reference_ppm_max_lsb"] = int(np.abs(got["rgb8"].astype(int) - ppm.astype(int)).max())
+        except (RefUnavailable, OSError) as exc:
+            out["reference_ppm_max_lsb"] = None
+            out["reference_ppm_note"] = f"oracle/_ref unavailable: {exc}"
+        out["ok"] = bool(out["rank_order_equal"] and out["ownership_equal"] and out["samples_equal"] and
+                         err <= RGBA_TOL and lsb <= LSB_TOL and
+                         (out["reference_ppm_max_lsb"] is None or out["reference_ppm_max_lsb"] <= LSB_TOL))
+    layers.free()
+    ds.free()
+    return out
+
+
+def full_size_check(scene, camera, workload, rgb8):
+    """N=1, once, untimed: the timed frame itself (full size) against the oracle's."""
+    from oracle.oracle import Oracle
+
+    _, W, H, aa, transp = WORKLOADS[workload]
+    root = int(round(aa ** 0.5))
+    need_gb = len(scene.boxes) * W * root * H * root * 20 / (1 << 30) * 1.1 + 2.0
+    if _mem_available_gb() < need_gb:
+        return {"skipped": f"the oracle's dense layers need ~{need_gb:.0f} GB of host memory, "
+                           f"{_mem_available_gb():.0f} GB available"}
+    params = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
+                             use_visibility_graph=1, count_samples=1, draw_bounding_box=1)
+    t0 = time.perf_counter()
+    want = Oracle().render_frame(scene, camera, params)
+    lsb = np.abs(rgb8.astype(int) - want["rgb8"].astype(int))
+    return {"size": f"{W}x{H}", "max_lsb": int(lsb.max()), "pixels_off_by_one": int((lsb.max(axis=-1) > 0).sum()),
+            "samples_oracle": int(want["samples"]), "oracle_s": time.perf_counter() - t0,
+            "against": "oracle (1 rank), whole RGB8 frame", "ok": bool(lsb.max() <= LSB_TOL)}
 
 
 def main():
@@ -287,6 +423,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-full-size", action="store_true",
+                    help="skip the one full-size comparison with the oracle (N=1) / full-size reference frame")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -305,6 +444,7 @@ def main():
     if world != args.gpus:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
     torch.cuda.set_device(local)
+    device = f"cuda:{local}"
     nccl_id = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -317,33 +457,52 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def gather_all(obj):
+        if world == 1:
+            return [obj]
+        out = [None] * world
+        dist.all_gather_object(out, obj)
+        return out
+
     factory, W, H, aa, transp = WORKLOADS[args.workload]
     # box -> rank: skewed round-robin over the (level, k, j, i) order, so every rank
     # holds the same number of boxes of every level and of every grid column
-    # (contiguous chunks would give rank 0 all of level 0, i.e. 3/4 of the samples)
     scene = factory(nranks=world, rule=DEAL)
     camera = scenes.make_camera()
     lib = api.load_library()
     pinned, fab_bytes = pin_scene(lib, scene, rank, world)
     ctx = Context(device=local, rank=rank, nranks=world, nccl_id=nccl_id)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")  # > 126 MB L2
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=device)  # > 126 MB L2
 
-    params = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
-                             use_visibility_graph=1, count_samples=0, draw_bounding_box=1)
-    # device-resident arm: the RGB8 frame is built on the root GPU and stays there
-    resident = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
-                               use_visibility_graph=1, count_samples=0, draw_bounding_box=1,
-                               rgb8_on_device=1)
-    counting = api.FrameParams(width=W, height=H, box_transparency=transp, antialiasing=aa,
-                               use_visibility_graph=1, count_samples=1, draw_bounding_box=1)
+    def fp(**kw):
+        base = dict(width=W, height=H, box_transparency=transp, antialiasing=aa, use_visibility_graph=1,
+                    count_samples=0, draw_bounding_box=1)
+        base.update(kw)
+        return api.FrameParams(**base)
+
+    params = fp()
+    resident = fp(rgb8_on_device=1)  # device-resident arm: the RGB8 frame stays on the root GPU
+    counting = fp(count_samples=1)
+
+    # ---- parity first (untimed); a broken tolerance fails the run after the line is printed
+    parity = None
+    if not args.no_parity:
+        parity = parity_check(ctx, dist, scene, camera, args.workload, world, rank, device)
 
     dscene = ctx.upload_scene(scene)
-    out = ctx.render_frame(dscene, camera, counting, want_rgba=False)  # untimed: count the samples
-    samples = torch.tensor([out["stats"].samples], dtype=torch.int64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(samples)
-    total_samples = int(samples.item())
+    replicated = dscene.replicated
+    # untimed: one frame of the sample-counting instantiation.  Its per-rank figures
+    # (samples marched, bytes pushed, march ms) come from ONE launch on ONE rank each.
+    out = ctx.render_frame(dscene, camera, counting, want_rgba=False)
+    cs = out["stats"]
+    counted = gather_all({"rank": rank, "samples": int(cs.samples), "march_ms": float(cs.march_ms),
+                          "pushed_bytes": int(cs.exchanged_bytes), "stolen_tiles": int(cs.stolen_tiles),
+                          "fragment_pixels": int(cs.fragment_pixels), "tiles": int(cs.tiles)})
+    total_samples = sum(c["samples"] for c in counted)
+    full_check = None
+    if rank == 0 and world == 1 and not args.no_full_size and not args.no_parity and args.workload == "C4":
+        full_check = full_size_check(scene, camera, args.workload, out["rgb8"])
 
     def one_frame():
         return ctx.render_frame(dscene, camera, resident, want_rgba=False, want_rgb8=False)
@@ -353,8 +512,10 @@ def main():
         one_frame()
     sampler = ClockSampler(local)
     launches0 = ctx.kernel_launches
-    frame_ms, march_ms = [], []
-    stage = {"order": [], "composite": [], "fold": [], "gather": [], "post": []}
+    frame_ms = []
+    keys = ("march_ms", "order_ms", "composite_ms", "fold_ms", "gather_ms", "post_ms")
+    stage = {k: [] for k in keys}
+    pushed, stolen = [], []
     barrier()
     sampler.start()
     for _ in range(args.steps):
@@ -367,30 +528,33 @@ def main():
         e1.record(stream)
         barrier()
         frame_ms.append(e0.elapsed_time(e1))
-        march_ms.append(res["stats"].march_ms)
-        stage["order"].append(res["stats"].order_ms)
-        stage["composite"].append(res["stats"].composite_ms)
-        stage["fold"].append(res["stats"].fold_ms)
-        stage["gather"].append(res["stats"].gather_ms)
-        stage["post"].append(res["stats"].post_ms)
+        for k in keys:
+            stage[k].append(getattr(res["stats"], k))
+        pushed.append(res["stats"].exchanged_bytes)
+        stolen.append(res["stats"].stolen_tiles)
     clocks = sampler.finish()
     launches = ctx.kernel_launches - launches0
-    exchanged = res["stats"].exchanged_bytes
+    mine = {"rank": rank, "frame_ms": float(np.mean(frame_ms)),
+            **{k: float(np.mean(v)) for k, v in stage.items()},
+            "pushed_bytes": float(np.mean(pushed)), "stolen_tiles": float(np.mean(stolen)),
+            "fragment_pixels": int(res["stats"].fragment_pixels), "tiles": int(res["stats"].tiles)}
+    per_rank = gather_all(mine)
+    ms_per_step = max(r["frame_ms"] for r in per_rank)
 
-    t = torch.tensor([float(np.mean(frame_ms)), float(np.mean(march_ms)), float(np.mean(stage["fold"])),
-                      float(np.mean(stage["composite"])), float(exchanged)], dtype=torch.float64,
-                     device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_per_step, march_mean = float(t[0].item()), float(t[1].item())
-    fold_max_ms, composite_max_ms, pulled_max = float(t[2].item()), float(t[3].item()), float(t[4].item())
+    # ---- NVLink: measured per-GPU rate of plain stores / loads into the ring neighbour, all ranks at once
+    link = None
+    if world > 1 and replicated:
+        wr = ctx.peer_bandwidth(256 << 20, 1, True, 10)
+        rd = ctx.peer_bandwidth(256 << 20, 1, False, 10)
+        link = gather_all({"rank": rank, "write_GBps": wr, "read_GBps": rd})
 
     # ---- end-to-end arm: pinned host FABs -> upload -> frame -> host RGB8
-    e2e_ms = []
+    e2e_ms, up_ms = [], []
     for it in range(2 + min(args.steps, 10)):
         barrier()
         t0 = time.perf_counter()
         ds2 = ctx.upload_scene(scene)
+        t1 = time.perf_counter()
         o2 = ctx.render_frame(ds2, camera, params, want_rgba=False)
         assert o2["rgb8"] is not None or rank != 0
         barrier()
@@ -398,28 +562,66 @@ def main():
         ds2.free()
         if it >= 2:
             e2e_ms.append(dt)
-    t = torch.tensor([float(np.mean(e2e_ms))], dtype=torch.float64, device=f"cuda:{local}")
-    fab = torch.tensor([fab_bytes], dtype=torch.int64, device=f"cuda:{local}")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(fab)
-    e2e_ms_mean = float(t[0].item())
+            up_ms.append((t1 - t0) * 1e3)
+    e2e_all = gather_all({"rank": rank, "e2e_ms": float(np.mean(e2e_ms)), "upload_ms": float(np.mean(up_ms)),
+                          "fab_bytes": int(fab_bytes)})
+    e2e_ms_mean = max(r["e2e_ms"] for r in e2e_all)
+    h2d_total = sum(r["fab_bytes"] for r in e2e_all)
 
+    # ---- in-situ case: the FABs already live in HBM (SceneBuilder.cpp:160-187 hands out
+    # views of device memory when the simulation runs on the GPU)
+    dev_fabs = None
+    if world == 1:
+        keep = []
+        host_data = [b.data for b in scene.boxes]
+        for b in scene.boxes:
+            t = torch.from_numpy(np.ascontiguousarray(b.data)).to(device)
+            keep.append(t)
+            b.data = _DeviceArray(t)
+        scene.__dict__.pop("_cbox_cache", None)
+        dms, kms = [], []
+        for it in range(2 + min(args.steps, 10)):
+            torch.cuda.synchronize()
+            with torch.cuda.stream(stream):
+                flush.zero_()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ds3 = ctx.upload(*_device_boxes(scene), scene.transform, scene.scalar_range)
+            o3 = ctx.render_frame(ds3, camera, params, want_rgba=False)
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) * 1e3
+            k5_ms, k5_bytes, k5_cells = ds3.upload_stats()
+            ds3.free()
+            if it >= 2:
+                dms.append(dt)
+                kms.append(k5_ms)
+        for b, d in zip(scene.boxes, host_data):
+            b.data = d
+        scene.__dict__.pop("_cbox_cache", None)
+        peak, _src = _peaks()
+        k5 = float(np.mean(kms))
+        dev_fabs = {"ms_per_step": float(np.mean(dms)), "value": total_samples / (np.mean(dms) * 1e-3) / 1e9,
+                    "unit": UNIT, "scope": "FABs resident in HBM -> quantise -> frame -> RGB8 on the host",
+                    "quantise": {"kernel": "brick_quantise_batch_kernel", "ms": k5, "cells": int(k5_cells),
+                                 "algorithmic_bytes": 9 * int(k5_cells),
+                                 "achieved_GBps": 9 * k5_cells / (k5 * 1e-3) / 1e9 if k5 > 0 else None,
+                                 "frac_of_hbm_peak": (9 * k5_cells / (k5 * 1e-3) / 1e9 / peak) if k5 > 0 else None,
+                                 "note": "K5: 8 B read + 1 B written per cell, one launch over all bricks, L2 "
+                                         "flushed first, CUDA events on the ctx stream"}}
+        del keep
+
+    fail = False
     if rank == 0:
         peak, peak_src = _peaks()
         cells = scene.total_cells()
-        frag_pixels = out["stats"].samples  # placeholder replaced below
-        # algorithmic bytes of the march (SURVEY.md 8d PRIMARY): 8 B per brick cell
-        # (the reference's FAB doubles, each needed at least once) + 20 B per
-        # fragment written.  Fragments = footprint pixels of all layers.
-        lay = ctx.raymarch(dscene, camera, W * int(round(aa ** 0.5)), H * int(round(aa ** 0.5)),
-                           transp, 0.001)
-        frag_pixels = lay.stats().fragment_pixels
-        lay.free()
-        local_cells = sum(int(np.prod(b.dims)) for b in scene.boxes if world == 1 or b.owner == 0)
-        alg_bytes = 8 * local_cells + 20 * frag_pixels
-        march_s = march_mean * 1e-3
+        frag_pixels = sum(r["fragment_pixels"] for r in per_rank)  # pieces partition the frame
+        # algorithmic bytes of the march (SURVEY.md 8d PRIMARY): 8 B per brick cell (the
+        # reference's FAB doubles, each needed at least once) + 20 B per fragment written
+        alg_bytes = 8 * cells + 20 * frag_pixels
+        march_max = max(r["march_ms"] for r in per_rank) * 1e-3
         sm_clock = (clocks["sm_mhz"] or 1965.0) * 1e6
+        stage_ms = {k[:-3]: max(r[k] for r in per_rank) for k in keys}
+        stage_ms["frame_minus_march"] = ms_per_step - stage_ms["march"]
         line = {
             "metric": METRIC, "value": total_samples / (ms_per_step * 1e-3) / 1e9, "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -431,64 +633,139 @@ def main():
                        "value_scope": "bricks resident in HBM, RGB8 frame left on the root GPU",
                        "e2e_scope": "pinned host FABs -> upload+quantise -> frame -> RGB8 on the host",
                        "l2": "256 MiB buffer written between timed frames (L2 flush)",
+                       "placement": ("bricks replicated on every GPU at upload; march tiles dealt by image "
+                                     "piece, stolen across GPUs, fragments stored into the folding GPU's pool")
+                       if replicated else "one rank" if world == 1 else "boxes marched by their owner, NCCL exchange",
                        "samples_per_frame": total_samples,
                        "frames_per_s": 1e3 / ms_per_step,
-                       "stage_ms": {"march": march_mean, **{k: float(np.mean(v)) for k, v in stage.items()}},
-                       "exchanged_bytes_rank0": int(exchanged)},
+                       "stage_ms": stage_ms},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": total_samples / (e2e_ms_mean * 1e-3) / 1e9, "unit": UNIT,
                     "ms_per_step": e2e_ms_mean, "frames_per_s": 1e3 / e2e_ms_mean,
-                    "h2d_bytes_per_step": int(fab.item()), "d2h_bytes_per_step": W * H * 3},
+                    "h2d_bytes_per_step": int(h2d_total), "d2h_bytes_per_step": W * H * 3,
+                    "upload_ms_max_rank": max(r["upload_ms"] for r in e2e_all),
+                    "h2d_GBps_per_rank": [r["fab_bytes"] / (r["upload_ms"] * 1e-3) / 1e9 for r in e2e_all]},
+            "parity": parity,
             "roofline": {
                 "kernel": "raymarch_bricks_kernel", "bound": "hbm",
-                "achieved": alg_bytes / march_s / 1e9, "peak": peak, "unit": "GB/s",
-                "frac": alg_bytes / march_s / 1e9 / peak,
+                "achieved": alg_bytes / world / march_max / 1e9, "peak": peak, "unit": "GB/s",
+                "frac": alg_bytes / world / march_max / 1e9 / peak,
                 "traffic": _ncu_traffic()[0] if args.workload == "C4" and world == 1 else None,
                 "traffic_source": f"profiles/{_ncu_traffic()[1]} (ncu --set full, C4, 1 GPU, per launch)",
                 "peak_source": peak_src,
-                "algorithmic_bytes": alg_bytes,
-                "note": "PRIMARY accounting (8 B/cell + 20 B/fragment); the march is issue-bound, "
-                        "see compute and sample_fetch",
-                "march_gsamples_per_s": (out["stats"].samples / march_s / 1e9),
-                "sample_fetch": {"achieved_GBps": 8 * out["stats"].samples / march_s / 1e9,
-                                 "frac_of_hbm_peak": 8 * out["stats"].samples / march_s / 1e9 / peak,
-                                 "note": "TERTIARY: 8 B x samples, the reference's own access "
+                "algorithmic_bytes": alg_bytes // world,
+                "note": "PRIMARY accounting (8 B/cell + 20 B/fragment of the whole frame / GPUs, over the "
+                        "slowest GPU's march); the march is issue-bound, see compute and sample_fetch",
+                "march_gsamples_per_s": total_samples / march_max / 1e9,
+                "sample_fetch": {"achieved_GBps": 8 * total_samples / world / march_max / 1e9,
+                                 "frac_of_hbm_peak": 8 * total_samples / world / march_max / 1e9 / peak,
+                                 "note": "TERTIARY, per GPU: 8 B x samples, the reference's own access "
                                          "pattern; NOT DRAM traffic"},
-                "compute": {"samples_per_s_per_sm_clock": out["stats"].samples / march_s / (148 * sm_clock),
+                "compute": {"samples_per_s_per_sm_clock": total_samples / world / march_max / (148 * sm_clock),
                             "note": "samples per SM per clock; 128 FP32 lanes/SM",
-                            "issue": _ncu_issue(march_s, sm_clock)
+                            "issue": _ncu_issue(march_max, sm_clock)
                             if args.workload == "C4" and world == 1 else None},
+                # one launch, one rank each: samples and bytes of the counting frame over ITS march time
+                "per_rank_counting_frame": [
+                    {"rank": c["rank"], "samples": c["samples"], "march_ms": c["march_ms"],
+                     "gsamples_per_s": c["samples"] / (c["march_ms"] * 1e-3) / 1e9 if c["march_ms"] > 0 else None,
+                     "sample_fetch_frac": 8 * c["samples"] / (c["march_ms"] * 1e-3) / 1e9 / peak
+                     if c["march_ms"] > 0 else None,
+                     "pushed_bytes": c["pushed_bytes"], "stolen_tiles": c["stolen_tiles"]} for c in counted],
             },
         }
-        # the composite: in peer-memory mode the fold kernel reads the other GPUs'
-        # fragments over NVLink itself, so link bytes / fold time is the link rate
-        frag_bytes = 20 * frag_pixels
+        # the composite: fold of the own piece from local HBM; the exchange is the march's
+        # stores into other GPUs' pools (stolen tiles), overlapped with the march
+        fold_rows = []
+        for r in per_rank:
+            px = (W * H * aa) // world
+            rd = 20 * r["fragment_pixels"]
+            wr = (3 * px if aa == 1 else 0) + (20 * px if (world > 1 or aa > 1) else 0)
+            fold_rows.append({"rank": r["rank"], "fold_ms": r["fold_ms"], "composite_ms": r["composite_ms"],
+                              "fragment_bytes_read": rd, "bytes_written": wr,
+                              "hbm_GBps": (rd + wr) / (r["fold_ms"] * 1e-3) / 1e9 if r["fold_ms"] > 0 else None,
+                              "pushed_bytes": r["pushed_bytes"], "stolen_tiles": r["stolen_tiles"],
+                              "march_ms": r["march_ms"],
+                              "push_GBps": r["pushed_bytes"] / (r["march_ms"] * 1e-3) / 1e9
+                              if r["march_ms"] > 0 else None})
+        link_peak = None
+        if link:
+            link_peak = {"write_GBps_min": min(l["write_GBps"] for l in link),
+                         "write_GBps_max": max(l["write_GBps"] for l in link),
+                         "read_GBps_min": min(l["read_GBps"] for l in link),
+                         "read_GBps_max": max(l["read_GBps"] for l in link),
+                         "how": "256 MiB between ring neighbours, all ranks at once, plain 16 B loads/stores "
+                                "from 148x8 CTAs, CUDA events, 10 iterations"}
         line["composite"] = {
-            "fold_ms_max_rank": fold_max_ms, "composite_ms_max_rank": composite_max_ms,
-            "layers": len(scene.boxes), "fragment_bytes_rank0": int(frag_bytes),
-            "link_bytes_max_rank": int(pulled_max),
-            "nvlink_GBps": (pulled_max / (fold_max_ms * 1e-3) / 1e9) if world > 1 and fold_max_ms > 0 else None,
-            "nvlink_peak_GBps": NVLINK_PEAK_GBPS,
-            "nvlink_frac": (pulled_max / (fold_max_ms * 1e-3) / 1e9 / NVLINK_PEAK_GBPS)
-            if world > 1 and fold_max_ms > 0 else None,
-            "fold_hbm_GBps": ((frag_bytes + 20 * W * H * aa) / (fold_max_ms * 1e-3) / 1e9)
-            if world == 1 and fold_max_ms > 0 else None,
-            "note": "fold_hbm_GBps (N=1): 20 B per stored fragment read + 20 B per pixel written; "
-                    "nvlink_GBps (N>1): bytes the busiest rank pulled from peers / its fold time; "
-                    "peak = NVLink 5 nominal per direction (no measured link figure on this pool)",
+            "fold_ms_max_rank": max(r["fold_ms"] for r in per_rank),
+            "composite_ms_max_rank": max(r["composite_ms"] for r in per_rank),
+            "layers": len(scene.boxes), "per_rank": fold_rows,
+            "pushed_bytes_per_rank": [int(r["pushed_bytes"]) for r in per_rank],
+            "stolen_tiles_per_rank": [int(r["stolen_tiles"]) for r in per_rank],
+            "tiles": per_rank[0]["tiles"],
+            "nvlink_measured": link_peak, "nvlink_nominal_GBps": NVLINK_NOMINAL_GBPS,
+            "nvlink_frac_of_measured_write_peak": [
+                (fr["push_GBps"] / link_peak["write_GBps_min"]) if (link_peak and fr["push_GBps"] is not None)
+                else None for fr in fold_rows] if link_peak else None,
+            "note": "fold_ms includes the wait for the slowest GPU's march (the hand-shake is inside the fold "
+                    "kernel); hbm_GBps = (20 B per stored fragment of the piece + bytes written) / fold_ms of "
+                    "the same rank; push_GBps = fragment bytes this rank's march stored into other GPUs' "
+                    "pools / its own march time -- the exchange rides on the march, it has no time of its own",
         }
+        if dev_fabs is not None:
+            line["e2e_device_fabs"] = dev_fabs
+        if full_check is not None:
+            line["parity_full_size"] = full_check
         if world == 1 and not args.no_cpu_baseline:
             try:
                 line["cpu_baseline"] = cpu_baseline(args.workload)
             except Exception as exc:  # the oracle always exists; report rather than hide
                 line["cpu_baseline"] = {"error": repr(exc)}
         print(json.dumps(line), flush=True)
+        fail = (parity is not None and not parity["ok"]) or \
+               (full_check is not None and full_check.get("ok") is False)
 
     dscene.free()
     ctx.close()
     lib.amrvr_host_free_pinned(pinned)
     if world > 1:
+        flag = torch.tensor([1 if fail else 0], device=device)
+        dist.broadcast(flag, src=0)
+        fail = bool(int(flag.item()))
         dist.destroy_process_group()
+    if fail:
+        print("bench.py: PARITY BROKEN (see the line's parity objects)", file=sys.stderr)
+        sys.exit(3)
+
+
+class _DeviceArray:
+    """A FAB that lives in device memory: just enough of the ndarray face for Scene.c_boxes()."""
+
+    def __init__(self, tensor):
+        self.tensor = tensor
+        self.nbytes = tensor.numel() * 8
+        self.shape = tuple(tensor.shape)
+        self.size = tensor.numel()
+
+
+def _device_boxes(scene):
+    """(amrvr_box array, n) whose data pointers are device addresses."""
+    arr = (api.Box * max(len(scene.boxes), 1))()
+    for i, b in enumerate(scene.boxes):
+        nx, ny, nz = b.dims
+        cb = arr[i]
+        for d in range(3):
+            cb.min_corner[d] = float(b.min_corner[d])
+            cb.max_corner[d] = float(b.max_corner[d])
+            cb.dims[d] = int(b.dims[d])
+            cb.lo[d] = int(b.lo[d])
+            cb.begin[d] = int(b.lo[d])
+        cb.data = b.data.tensor.data_ptr()
+        cb.jstride = nx
+        cb.kstride = nx * ny
+        cb.nstride = nx * ny * nz
+        cb.component = 0
+    return arr, len(scene.boxes)
 
 
 if __name__ == "__main__":

@@ -166,6 +166,10 @@ int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene);
 /* 1 when every rank holds the bricks of all ranks (NVLink box: allgathered at
  * upload), so that amrvr_render_frame deals march tiles, not boxes, to GPUs. */
 int amrvr_scene_is_replicated(const amrvr_scene* scene);
+/* Device time of the upload's FAB copies + quantise launches (CUDA events on the
+ * ctx stream), FAB bytes and cells this rank brought.  Any pointer may be NULL. */
+int amrvr_scene_upload_stats(const amrvr_scene* scene, float* device_ms,
+                             int64_t* fab_bytes, int64_t* cells);
 /* Global box table (all ranks, owner-major, owner-local order). */
 int amrvr_scene_global_boxes(const amrvr_scene* scene, int* nglobal,
                              const amrvr_box_record** records);

@@ -57,6 +57,9 @@ def main():
     ctx = Context(device=local, rank=rank, nranks=world, nccl_id=box[0])
     ds = ctx.upload_scene(scene)
     got = ctx.render_frame(ds, camera, params)
+    frame_order, frame_failed = ctx.last_rank_order()  # the ordering the frame itself computed
+    stolen = [None] * world
+    dist.all_gather_object(stolen, (int(got["stats"].stolen_tiles), int(got["stats"].exchanged_bytes)))
 
     # stand-alone entry points: order, march, composite, gather
     root_aa = int(round(aa ** 0.5))
@@ -93,9 +96,12 @@ def main():
         if not np.array_equal(order, want_order):
             ok = False
             msg.append(f"rank order {order} != oracle {want_order}")
-        if failed != (not graph_ok):
+        if failed != (not graph_ok) or frame_failed != (not graph_ok):
             ok = False
             msg.append("graph_failed flag differs")
+        if not np.array_equal(frame_order, want_order):
+            ok = False
+            msg.append(f"rank order of the frame {frame_order} != oracle {want_order}")
         for piece_index, owner in enumerate(want_order):
             b, e = orc.piece_range(rw * rh, piece_index, world)
             if spans[owner] != (owner, b, e):
@@ -125,7 +131,8 @@ def main():
         ctx.lib.amrvr_device_free(ctx._h, full)
         print(f"[mp_frame_worker] case={case} P={world} err={err:.3g} lsb={lsb} "
               f"samples={int(samples.item())} order={list(order)} "
-              f"exchanged_rank0={got['stats'].exchanged_bytes} exchange={os.environ.get('AMRVR_EXCHANGE', 'peer')} "
+              f"replicated={ds.replicated} (stolen tiles, pushed bytes) per rank={stolen} "
+              f"exchange={os.environ.get('AMRVR_EXCHANGE', 'peer')} "
               f"{'OK' if ok else 'FAIL ' + '; '.join(msg)}",
               flush=True)
     flag = torch.tensor([1 if ok else 0], device="cuda")
