@@ -825,59 +825,41 @@ constexpr int kBinThreads = 256;  // fold_bin_kernel
 constexpr int kFoldThreads = 128; // fold_layers_kernel: 4 warps, each 32 pixels x 2 rows
 constexpr int kFoldTileW = 32;
 constexpr int kFoldBandRows = 8;  // one CTA tile = 32 x 8 pixels; one band = 8 frame rows
-constexpr int kFoldDepth = 4;     // list entries in flight per thread (x 2 pixels each)
+constexpr int kFoldDepth = 2;     // list entries in flight per thread (x 2 pixels each)
 constexpr int kFoldWarpList = 64; // per-warp list of matched layers (shared memory)
+#ifndef AMRVR_FOLD_MIN_BLOCKS
+#define AMRVR_FOLD_MIN_BLOCKS 8   // 64 registers: 32 warps per SM keep the HBM pipe full
+#endif
 
-struct FoldEntry {  // FoldLayer narrowed for shared memory: 32 bytes
-  const float* base;
-  int x0, w, row0, row1, run, interleaved;
+// A layer as one warp sees it: the address of the warp's first row inside the
+// layer (never dereferenced when that row lies outside the slice), the column
+// range, which of the warp's two rows the slice holds, the run id.  32 bytes.
+struct FoldEntry {
+  const float* row;  // row y0 of the layer: base + (y0 - row0) * w * 5
+  int x0, w;
+  int rows;          // bit 0: row y0 is in the slice, bit 1: row y0 + 1, bit 2: interleaved layout
+  int run;
+  int pad[2];
 };
 
-__device__ __forceinline__ float4 ldcg_f4(const float4* p) { return __ldcg(p); }
+// The fully transparent pixel (DirectSendBase.cpp:427-432, 450-455).  It is a
+// bit-exact identity of blend_depth_swap on either side for finite colours:
+// x + 0 * (1 - a) == x and 0 + x * 1 == x, and min(d, inf) == d.  The fold
+// therefore starts runs and the accumulator from it instead of carrying "have
+// a value yet" flags -- every lane of a warp then runs the same control flow.
+__device__ __forceinline__ Px5 transparent_px() { return Px5{0.f, 0.f, 0.f, 0.f, INFINITY}; }
 
-// One fragment of a layer at column cx of row r (r relative to E.row0).  Loads
+// One fragment of a layer at column cx of the warp's row r (0 or 1).  Loads
 // bypass L1 (ld.global.cg): a fragment is read once, and in a sharded frame it
 // may have arrived over NVLink after this kernel started.
 __device__ __forceinline__ Px5 fold_load(const FoldEntry& E, int r, int cx) {
-  if (E.interleaved) {  // the reference's own layout: 5 floats per pixel
-    const float* q = E.base + (static_cast<long long>(r) * E.w + cx) * 5;
+  if (E.rows & 4) {  // the reference's own layout: 5 floats per pixel
+    const float* q = E.row + (static_cast<long long>(r) * E.w + cx) * 5;
     return Px5{__ldcg(q), __ldcg(q + 1), __ldcg(q + 2), __ldcg(q + 3), __ldcg(q + 4)};
   }
-  const float* rowp = E.base + static_cast<size_t>(r) * E.w * 5;
-  const float4 c = ldcg_f4(reinterpret_cast<const float4*>(rowp) + cx);
+  const float* rowp = E.row + static_cast<size_t>(r) * E.w * 5;
+  const float4 c = __ldcg(reinterpret_cast<const float4*>(rowp) + cx);
   return Px5{c.x, c.y, c.z, c.w, __ldcg(rowp + 4 * E.w + cx)};
-}
-
-// Running state of one pixel: the run being pre-blended and the accumulator
-// (DirectSendBase::composeLayered, DirectSendBase.cpp:400-446).
-struct FoldPixel {
-  Px5 acc, run;
-  bool have_acc, have_run;
-  int cur_run;
-};
-
-__device__ __forceinline__ void fold_step(FoldPixel& P, int runid, bool hit, const Px5& frag) {
-  if (runid != P.cur_run) {
-    if (P.have_run) {
-      P.acc = P.have_acc ? blend_depth_swap(P.acc, P.run) : P.run;
-      P.have_acc = true;
-      P.have_run = false;
-    }
-    P.cur_run = runid;
-  }
-  if (hit) {
-    P.run = P.have_run ? blend_depth_swap(P.run, frag) : frag;
-    P.have_run = true;
-  }
-}
-
-__device__ __forceinline__ Px5 fold_finish(FoldPixel& P) {
-  if (P.have_run) {
-    P.acc = P.have_acc ? blend_depth_swap(P.acc, P.run) : P.run;
-    P.have_acc = true;
-  }
-  if (!P.have_acc) P.acc = Px5{0.f, 0.f, 0.f, 0.f, INFINITY};  // DirectSendBase.cpp:450-455
-  return P.acc;
 }
 
 // Pass 1: one CTA per band of 8 frame rows filters the globally ordered layer
@@ -970,7 +952,7 @@ struct FoldArgs {
 // rows (top row = y_max, SavePPM order) -- into the root's frame, across NVLink
 // when the root is another GPU -- instead of 20 B per pixel.
 template <bool kBytes>
-__global__ void __launch_bounds__(kFoldThreads)
+__global__ void __launch_bounds__(kFoldThreads, AMRVR_FOLD_MIN_BLOCKS)
 fold_layers_kernel(const __grid_constant__ FoldArgs A) {
   __shared__ __align__(16) FoldEntry s_list[kFoldThreads / 32][kFoldWarpList];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1011,63 +993,73 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
     const bool live1 = px < A.width && p1 >= A.pixel_begin && p1 < A.pixel_end;
     const int x_last = min(tile_x0 + kFoldTileW, A.width) - 1;
 
-    FoldPixel P0{Px5{0.f, 0.f, 0.f, 0.f, INFINITY}, Px5{0.f, 0.f, 0.f, 0.f, INFINITY}, false, false, -1};
-    FoldPixel P1 = P0;
+    // run being pre-blended and accumulator of the two pixels; the run id is the same
+    // in every lane (all lanes walk the same list), so run changes never diverge
+    Px5 run0 = transparent_px(), run1 = run0, acc0 = run0, acc1 = run0;
+    int cur_run = -1;
     const int* band_list = A.band_lists + static_cast<size_t>(band) * A.nlayers;
     // no layer of this band reaches the tile's columns: nothing to scan
     const int2 xspan = __ldg(&A.band_xspan[band]);
     const int count = (xspan.x <= x_last && xspan.y > tile_x0) ? __ldg(&A.band_counts[band]) : 0;
 
     int nlist = 0;
-    for (int chunk = 0; chunk < count || nlist > 0; chunk += 32) {
-      if (chunk < count) {
-        const int i = chunk + lane;
-        bool keep = false;
-        FoldLayer L;
-        if (i < count) {
-          L = A.layers[__ldg(&band_list[i])];
-          keep = L.row0 <= y1 && L.row1 > y0 && L.x0 <= x_last && L.x0 + L.w > tile_x0;
-        }
-        const unsigned ballot = __ballot_sync(0xffffffffu, keep);
-        if (keep)
-          list[nlist + __popc(ballot & ((1u << lane) - 1u))] =
-              FoldEntry{L.base, L.x0, L.w, L.row0, L.row1, L.run, L.interleaved};
-        nlist += __popc(ballot);
-        __syncwarp();
-        if (nlist <= kFoldWarpList - 32 && chunk + 32 < count) continue;  // room for another chunk
+    for (int chunk = 0; chunk < count; chunk += 32) {
+      const int i = chunk + lane;
+      bool keep = false;
+      FoldLayer L;
+      if (i < count) {
+        L = A.layers[__ldg(&band_list[i])];
+        keep = L.row0 <= y1 && L.row1 > y0 && L.x0 <= x_last && L.x0 + L.w > tile_x0;
       }
+      const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+      if (keep) {
+        FoldEntry E;
+        E.row = L.base + (static_cast<long long>(y0) - L.row0) * L.w * 5;
+        E.x0 = L.x0;
+        E.w = L.w;
+        E.rows = ((y0 >= L.row0 && y0 < L.row1) ? 1 : 0) | ((y1 >= L.row0 && y1 < L.row1) ? 2 : 0) |
+                 (L.interleaved ? 4 : 0);
+        E.run = L.run;
+        E.pad[0] = E.pad[1] = 0;
+        list[nlist + __popc(ballot & ((1u << lane) - 1u))] = E;
+      }
+      nlist += __popc(ballot);
+      __syncwarp();
+      if (nlist <= kFoldWarpList - 32 && chunk + 32 < count) continue;  // room for another chunk
       // fold the list: all loads of a batch are issued before its first blend
       for (int e0 = 0; e0 < nlist; e0 += kFoldDepth) {
         Px5 f0[kFoldDepth], f1[kFoldDepth];
-        bool h0[kFoldDepth], h1[kFoldDepth];
         int runid[kFoldDepth];
 #pragma unroll
         for (int k = 0; k < kFoldDepth; ++k) {
-          h0[k] = h1[k] = false;
-          runid[k] = -2;  // past the end of the list
+          f0[k] = transparent_px();
+          f1[k] = transparent_px();
+          runid[k] = cur_run;  // past the end of the list: blends a transparent pixel, changes nothing
           if (e0 + k < nlist) {
             const FoldEntry E = list[e0 + k];  // same address in every lane: broadcast
             runid[k] = E.run;
             const int cx = px - E.x0;
             const bool inx = cx >= 0 && cx < E.w;
-            h0[k] = live0 && inx && y0 >= E.row0 && y0 < E.row1;
-            h1[k] = live1 && inx && y1 >= E.row0 && y1 < E.row1;
-            if (h0[k]) f0[k] = fold_load(E, y0 - E.row0, cx);
-            if (h1[k]) f1[k] = fold_load(E, y1 - E.row0, cx);
+            if (live0 && inx && (E.rows & 1)) f0[k] = fold_load(E, 0, cx);
+            if (live1 && inx && (E.rows & 2)) f1[k] = fold_load(E, 1, cx);
           }
         }
 #pragma unroll
         for (int k = 0; k < kFoldDepth; ++k) {
-          if (runid[k] != -2) {
-            fold_step(P0, runid[k], h0[k], f0[k]);
-            fold_step(P1, runid[k], h1[k], f1[k]);
+          if (runid[k] != cur_run) {  // uniform: the run closes (DirectSendBase.cpp:441-445)
+            acc0 = blend_depth_swap(acc0, run0);
+            acc1 = blend_depth_swap(acc1, run1);
+            run0 = run1 = transparent_px();
+            cur_run = runid[k];
           }
+          run0 = blend_depth_swap(run0, f0[k]);  // :413-426
+          run1 = blend_depth_swap(run1, f1[k]);
         }
       }
       nlist = 0;
       __syncwarp();  // the list is rewritten by the next chunk
     }
-    const Px5 a0 = fold_finish(P0), a1 = fold_finish(P1);
+    const Px5 a0 = blend_depth_swap(acc0, run0), a1 = blend_depth_swap(acc1, run1);
 
     // the warp's list doubles as its output staging (2 rows x 32 pixels x 20 B = 1280 B)
     if (!kBytes || A.piece5 != nullptr) {

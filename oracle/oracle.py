@@ -380,6 +380,67 @@ class Ref(_Base):
                 "scalar_range": (rmin.value, rmax.value), "bounds_min": list(bmin),
                 "bounds_max": list(bmax), "processed_range": tuple(proc), "original_range": tuple(orig)}
 
+    def _single_level(self, scene, ncomp=1, component=0):
+        """ref_level of a one-level scene (boxes in generation order) + keepalive."""
+        boxes = sorted(scene.boxes, key=lambda b: b.gen_index)
+        n = len(boxes)
+        level = RefLevel()
+        lo = (C.c_int32 * max(3 * n, 1))()
+        hi = (C.c_int32 * max(3 * n, 1))()
+        owner = (C.c_int32 * max(n, 1))()
+        data = (C.c_void_p * max(n, 1))()
+        keep = [lo, hi, owner, data]
+        for i, b in enumerate(boxes):
+            for d in range(3):
+                lo[3 * i + d] = int(b.lo[d])
+                hi[3 * i + d] = int(b.lo[d] + b.dims[d] - 1)
+            owner[i] = int(b.owner)
+            if ncomp == 1:
+                arr = b.data
+            else:
+                arr = np.full((ncomp,) + b.data.shape, 1e30, np.float64)
+                arr[component] = b.data
+            keep.append(arr)
+            data[i] = arr.ctypes.data
+        prob_lo, cs = scene.levels[0]
+        for d in range(3):
+            level.prob_lo[d] = float(prob_lo[d])
+            level.cell_size[d] = float(cs[d])
+        level.nboxes, level.ncomp = n, ncomp
+        level.lo, level.hi, level.owner, level.data = lo, hi, owner, data
+        return level, keep
+
+    def api_render(self, scene, params, out_path, component=0, ncomp=1, log_scale=False,
+                   scalar_range=None, up_vector=None, camera=None, colormap=None):
+        """The real api::Render(AmrData, RenderOptions) (VolumeRendererApi.cpp:257-395) on a
+        one-level scene, scene.nranks thread-ranks -> image at out_path (rank 0)."""
+        level, _keep = self._single_level(scene, ncomp, component)
+        samples = C.c_longlong(0)
+        log = C.create_string_buffer(1 << 16)
+        pts, npts = self._cmap(colormap)
+        rng = (C.c_float * 2)(*[float(v) for v in scalar_range]) if scalar_range is not None else None
+        up = (C.c_double * 3)(*[float(v) for v in up_vector]) if up_vector is not None else None
+        self._check(self.lib.ref_api_render(
+            scene.nranks, C.byref(level), C.byref(params), int(component), int(bool(log_scale)), rng, up,
+            C.byref(camera) if camera is not None else None, pts, npts, str(out_path).encode(),
+            C.byref(samples), log, len(log)))
+        return {"samples": samples.value, "log": log.value.decode()}
+
+    def api_histogram(self, scene, bin_count, component=0, ncomp=1, log_scale=False):
+        """The real api::ComputeHistogram on a one-level scene -> dict."""
+        level, _keep = self._single_level(scene, ncomp, component)
+        counts = np.zeros(max(int(bin_count), 1), np.uint64)
+        total = C.c_uint64(0)
+        ranges = (C.c_float * 6)()
+        flags = (C.c_int * 2)()
+        self._check(self.lib.ref_api_histogram(scene.nranks, C.byref(level), int(component),
+                                               int(bool(log_scale)), int(bin_count),
+                                               counts.ctypes.data_as(_P(C.c_uint64)), C.byref(total),
+                                               ranges, flags))
+        return {"counts": counts, "samples": int(total.value), "normalized_range": tuple(ranges[0:2]),
+                "processed_range": tuple(ranges[2:4]), "original_range": tuple(ranges[4:6]),
+                "has_processed": bool(flags[0]), "has_original": bool(flags[1])}
+
     def register_plotfile(self, path, levels, names):
         """Hand the CONTENT of a plotfile (list of amrvolumerenderer_b200.plotfile.
         LevelSpec + variable names; prob_lo = 0) to the shim's PlotFileData under

@@ -4,6 +4,7 @@
 //   ref_render_scene -> VolumeRenderer::renderScene     (VolumeRenderer.cpp:947-1101 -> :1103-1339)
 //   ref_build_scene  -> detail::BuildSceneGeometry      (SceneBuilder.cpp:113-425)
 //   ref_api_render   -> api::Render                     (VolumeRendererApi.cpp:257-395), single level
+//   ref_api_histogram-> api::ComputeHistogram           (VolumeRendererApi.cpp:397-415), single level
 // See ref_driver_core.cpp for the conventions.
 #include <AMReX_Geometry.H>
 #include <AMReX_MultiFab.H>
@@ -525,6 +526,60 @@ int ref_api_render(int nranks, const ref_level* level,
       for (long long r : reads) *samples += r;
     }
     copyLog(capture.buffer.str(), log, logCapacity);
+  });
+}
+
+// The real api::ComputeHistogram (VolumeRendererApi.cpp:397-415) for ONE level on
+// `nranks` thread-ranks; counts and ranges as rank 0 sees them.
+int ref_api_histogram(int nranks, const ref_level* level, int component, int logScale,
+                      int binCount, uint64_t* counts, uint64_t* sampleCount,
+                      float* ranges /*[6]: normalized, processed, original*/,
+                      int* flags /*[2]: hasProcessedRange, hasOriginalRange*/) {
+  return guarded([&] {
+    Capture quiet;
+    std::vector<VolumeRenderer::ScalarHistogram> results(nranks);
+    fake_mpi_run(nranks, [&](int rank) {
+      std::vector<amrex::Box> boxList;
+      std::vector<int> ownerList;
+      for (int b = 0; b < level->nboxes; ++b) {
+        boxList.emplace_back(
+            amrex::IntVect(level->lo[3 * b], level->lo[3 * b + 1], level->lo[3 * b + 2]),
+            amrex::IntVect(level->hi[3 * b], level->hi[3 * b + 1], level->hi[3 * b + 2]));
+        ownerList.push_back(level->owner[b]);
+      }
+      amrex::MultiFab mf(boxList, ownerList, level->ncomp, rank);
+      for (int b = 0; b < level->nboxes; ++b) {
+        if (level->owner[b] != rank) continue;
+        std::memcpy(mf.dataPtr(b), level->data[b],
+                    sizeof(double) * static_cast<std::size_t>(mf.box(b).numPts()) * level->ncomp);
+      }
+      amrVolumeRenderer::api::AmrData data;
+      data.levelData.push_back(&mf);
+      data.levelGeometry.push_back(amrex::Geometry(
+          {level->prob_lo[0], level->prob_lo[1], level->prob_lo[2]},
+          {level->cell_size[0], level->cell_size[1], level->cell_size[2]}));
+      amrVolumeRenderer::api::HistogramOptions options;
+      options.component = component;
+      options.logScaleInput = logScale != 0;
+      options.binCount = binCount;
+      results[rank] = amrVolumeRenderer::api::ComputeHistogram(data, options);
+    });
+    const VolumeRenderer::ScalarHistogram& h = results[0];
+    for (int b = 0; b < binCount && b < static_cast<int>(h.binCounts.size()); ++b)
+      counts[b] = h.binCounts[static_cast<std::size_t>(b)];
+    if (sampleCount) *sampleCount = h.sampleCount;
+    if (ranges) {
+      ranges[0] = h.normalizedRange.first;
+      ranges[1] = h.normalizedRange.second;
+      ranges[2] = h.processedRange.first;
+      ranges[3] = h.processedRange.second;
+      ranges[4] = h.originalRange.first;
+      ranges[5] = h.originalRange.second;
+    }
+    if (flags) {
+      flags[0] = h.hasProcessedRange ? 1 : 0;
+      flags[1] = h.hasOriginalRange ? 1 : 0;
+    }
   });
 }
 
