@@ -1034,7 +1034,7 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
         for (int k = 0; k < kFoldDepth; ++k) {
           f0[k] = transparent_px();
           f1[k] = transparent_px();
-          runid[k] = cur_run;  // past the end of the list: blends a transparent pixel, changes nothing
+          runid[k] = INT_MIN;  // past the end of the list: blends a transparent pixel, closes no run
           if (e0 + k < nlist) {
             const FoldEntry E = list[e0 + k];  // same address in every lane: broadcast
             runid[k] = E.run;
@@ -1046,7 +1046,7 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
         }
 #pragma unroll
         for (int k = 0; k < kFoldDepth; ++k) {
-          if (runid[k] != cur_run) {  // uniform: the run closes (DirectSendBase.cpp:441-445)
+          if (runid[k] != cur_run && runid[k] != INT_MIN) {  // uniform: the run closes (DirectSendBase.cpp:441-445)
             acc0 = blend_depth_swap(acc0, run0);
             acc1 = blend_depth_swap(acc1, run1);
             run0 = run1 = transparent_px();

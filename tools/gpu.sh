@@ -41,7 +41,7 @@ bench() {  # bench N WORKLOAD NAME [extra args]
 }
 case "$1" in
 one)
-  timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu_1.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/${TAG}_pytest_gpu_1.log
+  timeout 900 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_pytest_gpu_1.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/${TAG}_pytest_gpu_1.log
   bench 1 C4 C4_n1
   line C4_n1
   ;;
