@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <climits>
 #include <condition_variable>
 #include <functional>
 #include <mutex>
@@ -156,6 +157,7 @@ struct amrvr_ctx {
   unsigned char* param_host = nullptr;  // pinned staging of the per-frame march parameter block
   size_t param_host_bytes = 0;
   cudaEvent_t param_copied = nullptr;   // the last copy out of param_host has completed
+  cudaEvent_t bin_done = nullptr;       // frame_fused: fold table copied and binned on the aux stream
   uint8_t* last_rgb8 = nullptr;         // RGB8 frame of the last amrvr_render_frame (root)
   DeviceBuffer frame_pool;              // fragment pool of single-rank fused frames
   std::vector<int> last_rank_order;     // visibility order of the last frame (BuildVisibilityOrderedGroup)
@@ -671,6 +673,7 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   if (ctx->frame_stats_host != nullptr) cudaFreeHost(ctx->frame_stats_host);
   ctx->frame_pool.release();
   if (ctx->param_copied != nullptr) cudaEventDestroy(ctx->param_copied);
+  if (ctx->bin_done != nullptr) cudaEventDestroy(ctx->bin_done);
   if (ctx->comm != nullptr) nccl_api().CommDestroy(ctx->comm);
   for (DeviceBuffer* b :
        {&ctx->stage, &ctx->march_boxes, &ctx->tables, &ctx->counter, &ctx->fold_layers, &ctx->fold_bins,
@@ -1599,7 +1602,7 @@ int param_staging(amrvr_ctx* ctx, size_t bytes, unsigned char** out) {
   return AMRVR_OK;
 }
 
-constexpr size_t kParamHeader = 64;  // [samples u64 | pushed bytes u64 | stolen tiles u64 | tile counter u32 | ...]
+constexpr size_t kParamHeader = 64;  // u64 words: [samples | pushed bytes | stolen tiles | tile counter (u32) | CTA busy ns | ~first start | last end | table staging ns]
 
 }  // namespace
 
@@ -1730,6 +1733,7 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
   MarchQueues queues{};  // one queue, one pool: this rank's own boxes
   queues.nqueues = 1;
   queues.tile_begin[1] = tiles;
+  queues.piece_begin[1] = INT_MAX;  // every pixel of the frame
   queues.counter[0] = reinterpret_cast<unsigned*>(dev_block + 24);
   queues.pool[0] = L->pool.as<float>();
   queues.stats = counter;
@@ -2572,7 +2576,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
     return fail(ctx, AMRVR_ERR_RUNTIME,
                 "context unusable: an earlier frame lost a peer at a barrier; destroy and recreate it");
   if (ctx->frame_stats_host == nullptr)
-    CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->frame_stats_host), 64));
+    CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->frame_stats_host), 128));
 
   OrderJob order;
   start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
@@ -2610,6 +2614,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
       fill_march_const(scene->global[g].min_corner, scene->global[g].max_corner, scene->global[g].dims,
                        scene->global_brick_off[g], mc[g]);
   }
+  trace.mark("footprints");
   const float alpha_scale = std::min(std::max(1.0f - params->box_transparency, 0.0f), 1.0f);
   std::vector<float> table_norm, tables;  // one table per distinct normalisation factor
   std::vector<MarchBox> per_box(scene->march_const_global);
@@ -2638,6 +2643,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   std::stable_sort(by_table.begin(), by_table.end(),
                    [&](int a, int b) { return per_box[a].table < per_box[b].table; });
 
+  trace.mark("boxconst");
   // ---- march items: queue p = the rows of every footprint that fall into piece p
   std::vector<int> pbegin(static_cast<size_t>(P)), pend(static_cast<size_t>(P));
   for (int p = 0; p < P; ++p) piece_range(npix, p, P, &pbegin[p], &pend[p]);
@@ -2676,6 +2682,8 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
     }
   }
   queues.tile_begin[P] = tiles;
+  for (int p = 0; p < P; ++p) queues.piece_begin[p] = pbegin[p];
+  queues.piece_begin[P] = npix;
   frame.nboxes = static_cast<int>(items.size());
   frame.ntiles = tiles;
   {  // the other queues, heaviest first
@@ -2728,8 +2736,57 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
       return bail(fail(ctx, AMRVR_ERR_CUDA, "frame buffer allocation failed"));
   }
 
+  // ---- one parameter block: [header | tables | items | fold table | overlay edges].  The
+  // march needs the first three only: they are copied and the march is launched BEFORE
+  // the host builds the fold table, which then travels while the march runs.
+  const int my_begin = pbegin[queues.mine], my_end = pend[queues.mine];
+  const size_t tables_bytes = tables.size() * sizeof(float);
+  const size_t items_bytes = items.size() * sizeof(MarchBox);
+  const size_t fold_bytes_max = static_cast<size_t>(n) * sizeof(FoldLayer);
+  const size_t off_items = kParamHeader + tables_bytes;
+  const size_t off_fold = off_items + items_bytes;
+  const size_t off_edges = off_fold + fold_bytes_max;
+  const size_t block_bytes = off_edges + sizeof(OverlayEdges);
+  unsigned char* block = nullptr;
+  {
+    const int st = param_staging(ctx, block_bytes, &block);
+    if (st != AMRVR_OK) return bail(st);
+  }
+  std::memset(block, 0, kParamHeader);
+  if (tables_bytes) std::memcpy(block + kParamHeader, tables.data(), tables_bytes);
+  if (items_bytes) std::memcpy(block + off_items, items.data(), items_bytes);
+  if (ctx->march_boxes.reserve(block_bytes) != cudaSuccess ||
+      ctx->fold_bins.reserve(std::max<size_t>(fold_scratch_bytes(n, RW, my_begin, my_end), 256)) != cudaSuccess)
+    return bail(fail(ctx, AMRVR_ERR_CUDA, "parameter block allocation failed"));
+  unsigned char* dev_block = ctx->march_boxes.as<unsigned char>();
+  queues.stats = reinterpret_cast<unsigned long long*>(dev_block);
+  if (!sharded) queues.counter[0] = reinterpret_cast<unsigned*>(dev_block + 24);
+  const FoldLayer* fold_dev = reinterpret_cast<const FoldLayer*>(dev_block + off_fold);
+  trace.mark("tables");
+
+  auto try_cuda = [&](cudaError_t e, const char* what) {
+    return (e == cudaSuccess) ? AMRVR_OK
+                              : fail(ctx, AMRVR_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+  };
+  auto try_launch = [&](int e, const char* what) {
+    return (e == 0) ? AMRVR_OK
+                    : fail(ctx, AMRVR_ERR_CUDA,
+                           std::string(what) + ": " + cudaGetErrorString(static_cast<cudaError_t>(e)));
+  };
+  int st = try_cuda(cudaMemcpyAsync(dev_block, block, off_fold, cudaMemcpyHostToDevice, ctx->stream),
+                    "parameter copy");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[1], ctx->stream), "event");
+  if (st == AMRVR_OK)
+    st = try_launch(launch_raymarch(frame, queues, reinterpret_cast<const MarchBox*>(dev_block + off_items),
+                                    scene->bricks.as<uint8_t>(),
+                                    reinterpret_cast<const float*>(dev_block + kParamHeader),
+                                    params->count_samples != 0, ctx->stream, &ctx->launches),
+                    "march");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[2], ctx->stream), "event");
+  trace.mark("march_enqueue");
+
   // ---- fold table of my piece, in the reference's blend order with its run ids
-  // (DirectSendBase.cpp:363-407)
+  // (DirectSendBase.cpp:363-407); built while the march runs
   std::vector<int> blend_order(static_cast<size_t>(n));
   layer_order(n, scene->global.data(), *camera, nullptr, blend_order.data());
   std::vector<FoldLayer> fold;
@@ -2752,64 +2809,27 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
       fold.push_back(F);
     }
   }
-  const int my_begin = pbegin[queues.mine], my_end = pend[queues.mine];
   OverlayEdges edges{};
   const bool overlay = bytes_mode && params->draw_bounding_box && n > 0;
   if (overlay) make_overlay_edges(G.tmin, G.tmax, *camera, 1, W, H, edges);
-
-  // ---- one parameter block: [header | tables | items | fold table | overlay edges]
-  const size_t tables_bytes = tables.size() * sizeof(float);
-  const size_t items_bytes = items.size() * sizeof(MarchBox);
   const size_t fold_bytes = fold.size() * sizeof(FoldLayer);
-  const size_t off_items = kParamHeader + tables_bytes;
-  const size_t off_fold = off_items + items_bytes;
-  const size_t off_edges = off_fold + fold_bytes;
-  const size_t block_bytes = off_edges + sizeof(OverlayEdges);
-  unsigned char* block = nullptr;
-  {
-    const int st = param_staging(ctx, block_bytes, &block);
-    if (st != AMRVR_OK) return bail(st);
-  }
-  std::memset(block, 0, kParamHeader);
-  if (tables_bytes) std::memcpy(block + kParamHeader, tables.data(), tables_bytes);
-  if (items_bytes) std::memcpy(block + off_items, items.data(), items_bytes);
   if (fold_bytes) std::memcpy(block + off_fold, fold.data(), fold_bytes);
   std::memcpy(block + off_edges, &edges, sizeof(OverlayEdges));
-  if (ctx->march_boxes.reserve(block_bytes) != cudaSuccess ||
-      ctx->fold_bins.reserve(std::max<size_t>(
-          fold_scratch_bytes(static_cast<int>(fold.size()), RW, my_begin, my_end), 256)) != cudaSuccess)
-    return bail(fail(ctx, AMRVR_ERR_CUDA, "parameter block allocation failed"));
-  unsigned char* dev_block = ctx->march_boxes.as<unsigned char>();
-  queues.stats = reinterpret_cast<unsigned long long*>(dev_block);
-  if (!sharded) queues.counter[0] = reinterpret_cast<unsigned*>(dev_block + 24);
-  const FoldLayer* fold_dev = reinterpret_cast<const FoldLayer*>(dev_block + off_fold);
-  trace.mark("tables");
-
-  auto try_cuda = [&](cudaError_t e, const char* what) {
-    return (e == cudaSuccess) ? AMRVR_OK
-                              : fail(ctx, AMRVR_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
-  };
-  auto try_launch = [&](int e, const char* what) {
-    return (e == 0) ? AMRVR_OK
-                    : fail(ctx, AMRVR_ERR_CUDA,
-                           std::string(what) + ": " + cudaGetErrorString(static_cast<cudaError_t>(e)));
-  };
-  int st = try_cuda(cudaMemcpyAsync(dev_block, block, block_bytes, cudaMemcpyHostToDevice, ctx->stream),
-                    "parameter copy");
-  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->param_copied, ctx->stream), "event");
+  // on the aux stream, beside the march; the fold waits for it
+  if (st == AMRVR_OK && ctx->bin_done == nullptr)
+    st = try_cuda(cudaEventCreateWithFlags(&ctx->bin_done, cudaEventDisableTiming), "event");
+  if (st == AMRVR_OK)
+    st = try_cuda(cudaMemcpyAsync(dev_block + off_fold, block + off_fold, block_bytes - off_fold,
+                                  cudaMemcpyHostToDevice, ctx->aux),
+                  "fold table copy");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->param_copied, ctx->aux), "event");
   if (st == AMRVR_OK)
     st = try_launch(launch_fold_bin(fold_dev, static_cast<int>(fold.size()), RW, my_begin, my_end,
-                                    ctx->fold_bins.ptr, ctx->stream, &ctx->launches),
+                                    ctx->fold_bins.ptr, ctx->aux, &ctx->launches),
                     "fold_bin");
-  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[1], ctx->stream), "event");
-  if (st == AMRVR_OK)
-    st = try_launch(launch_raymarch(frame, queues, reinterpret_cast<const MarchBox*>(dev_block + off_items),
-                                    scene->bricks.as<uint8_t>(),
-                                    reinterpret_cast<const float*>(dev_block + kParamHeader),
-                                    params->count_samples != 0, ctx->stream, &ctx->launches),
-                    "march");
-  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[2], ctx->stream), "event");
-  trace.mark("march_enqueue");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->bin_done, ctx->aux), "event");
+  if (st == AMRVR_OK) st = try_cuda(cudaStreamWaitEvent(ctx->stream, ctx->bin_done, 0), "wait");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[6], ctx->stream), "event");
 
   // ---- fold (+ bytes) of my piece
   FoldSync sync{};
@@ -2890,12 +2910,12 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   trace.mark("post_enqueue");
 
   // ---- statistics and the barrier time-out word come back with one small copy
-  if (cudaMemcpyAsync(ctx->frame_stats_host, dev_block, 24, cudaMemcpyDeviceToHost, ctx->stream) !=
+  if (cudaMemcpyAsync(ctx->frame_stats_host, dev_block, kParamHeader, cudaMemcpyDeviceToHost, ctx->stream) !=
       cudaSuccess)
     return bail(fail(ctx, AMRVR_ERR_CUDA, "statistics readback failed"));
-  ctx->frame_stats_host[3] = 0;
+  ctx->frame_stats_host[8] = 0;
   if (sharded &&
-      cudaMemcpyAsync(ctx->frame_stats_host + 3, static_cast<uint32_t*>(ctx->sym_flags.local) + kCtlError,
+      cudaMemcpyAsync(ctx->frame_stats_host + 8, static_cast<uint32_t*>(ctx->sym_flags.local) + kCtlError,
                       sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess)
     return bail(fail(ctx, AMRVR_ERR_CUDA, "statistics readback failed"));
   if (cudaStreamSynchronize(ctx->stream) != cudaSuccess) {
@@ -2906,10 +2926,10 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   trace.mark("final_sync");
   st = join_order(ctx, &order);
   if (st != AMRVR_OK) return st;
-  if (sharded && static_cast<uint32_t>(ctx->frame_stats_host[3]) != 0) {
+  if (sharded && static_cast<uint32_t>(ctx->frame_stats_host[8]) != 0) {
     ctx->poisoned = true;
     return fail(ctx, AMRVR_ERR_RUNTIME,
-                static_cast<uint32_t>(ctx->frame_stats_host[3]) == 2u
+                static_cast<uint32_t>(ctx->frame_stats_host[8]) == 2u
                     ? "a peer rank gave up in the middle of the frame"
                     : "a peer GPU did not reach the frame barrier within 10 s");
   }
@@ -2920,10 +2940,17 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
     stats->stolen_tiles = static_cast<int64_t>(ctx->frame_stats_host[2]);
     stats->tiles = tiles;
     stats->fragment_pixels = my_rays;
+    if (ctx->frame_stats_host[6] != 0) {  // the march ran: its time line on the device clock
+      stats->march_span_ns = static_cast<int64_t>(ctx->frame_stats_host[6] - ~ctx->frame_stats_host[5]);
+      stats->march_cta_busy_ns = static_cast<int64_t>(ctx->frame_stats_host[4]);
+      stats->march_table_ns = static_cast<int64_t>(ctx->frame_stats_host[7]);
+      stats->march_ctas = static_cast<int64_t>(ctx->frame_stats_host[3] >> 32);
+    }
     stats->order_ms = order.host_ms;  // beside the march, on the helper thread: host wall time
     cudaEventElapsedTime(&stats->march_ms, ev[1], ev[2]);
-    cudaEventElapsedTime(&stats->fold_ms, ev[2], ev[3]);
-    cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[4]);  // fold + both hand-shakes
+    cudaEventElapsedTime(&stats->pre_ms, ev[0], ev[1]);
+    cudaEventElapsedTime(&stats->fold_ms, ev[6], ev[3]);       // the fold kernel (it starts with the hand-shake)
+    cudaEventElapsedTime(&stats->composite_ms, ev[2], ev[4]);  // fold table copy + bin + fold + final wait
     stats->gather_ms = 0.0f;
     cudaEventElapsedTime(&stats->post_ms, ev[4], ev[5]);
   }

@@ -181,6 +181,8 @@ struct MarchQueues {
   int32_t me, nranks;              // nranks > 0: the last CTA raises flag row `signal_row` on every rank
   int32_t tile_begin[kMaxPeers + 1];
   int32_t steal_order[kMaxPeers];
+  int32_t piece_begin[kMaxPeers + 1];  // queue q marches only pixels [piece_begin[q], piece_begin[q+1]):
+                                       // a piece may start or end inside a frame row
   unsigned* counter[kMaxPeers];    // next tile of queue q (relative to tile_begin[q])
   float* pool[kMaxPeers];
   unsigned* ctl[kMaxPeers];        // control block of rank r (hints, flags); [me] is the local one

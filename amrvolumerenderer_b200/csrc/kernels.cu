@@ -576,7 +576,15 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
 #ifndef AMRVR_MARCH_MIN_BLOCKS
 #define AMRVR_MARCH_MIN_BLOCKS 4
 #endif
+#ifndef AMRVR_MARCH_TIMELINE
+#define AMRVR_MARCH_TIMELINE 1  // thread 0 of every CTA times itself on %globaltimer (amrvr_frame_stats::march_*_ns)
+#endif
 
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned* p) {
   unsigned v;
   asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
@@ -650,7 +658,11 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
   const unsigned table_addr = smem_u32(s_table) + static_cast<unsigned>(lane % kTableCopies) * 16u;
   int have_box = -1, have_table = -1;
   unsigned nsamples = 0;
+  // thread 0 keeps the launch's time line (Q.stats[4..7]): CTA busy time, first start, last end, table staging
+  __shared__ unsigned long long s_t0, s_table_ns, s_stage_t;  // in shared memory: the march loop keeps its registers
   if (threadIdx.x == 0) {
+    s_t0 = AMRVR_MARCH_TIMELINE ? global_timer_ns() : 0ull;
+    s_table_ns = 0;
     s_cur = 0;
     s_pushed = s_stolen = 0;
     publish(0, claim_blocking());
@@ -664,7 +676,9 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
       const int* src = reinterpret_cast<const int*>(boxes + which);
       if (threadIdx.x < words) reinterpret_cast<int*>(&s_box)[threadIdx.x] = __ldg(src + threadIdx.x);
       const int table = __ldg(&boxes[which].table);
-      if (table != have_table) {
+      const bool restage = table != have_table;
+      if (restage) {
+        if (AMRVR_MARCH_TIMELINE && threadIdx.x == 0) s_stage_t = global_timer_ns();
         // consecutive threads write consecutive 16 B slots: conflict-free stores
         const float4* src4 = tables + table * AMRVR_COLOR_TABLE_SIZE;
         for (int slot = threadIdx.x; slot < AMRVR_COLOR_TABLE_SIZE * kTableCopies; slot += kMarchThreads)
@@ -673,6 +687,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
       }
       have_box = which;
       __syncthreads();
+      if (AMRVR_MARCH_TIMELINE && restage && threadIdx.x == 0) s_table_ns += global_timer_ns() - s_stage_t;
     }
     // the claim of the next tile: issued here, read after this thread's ray
     unsigned pend_t = 0;
@@ -689,7 +704,10 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
     const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
     const int rw = s_box.rw;
     // footprints are padded to 4-pixel column multiples: columns past the frame are not rays
-    const bool valid = x < rw && y < s_box.rh && s_box.rx0 + x < f.width;
+    // and the row a piece boundary cuts belongs to two queues: each marches its own pixels
+    const int pixel = (s_box.ry0 + y) * f.width + s_box.rx0 + x;
+    const bool valid = x < rw && y < s_box.rh && s_box.rx0 + x < f.width &&
+                       pixel >= Q.piece_begin[s_box.dest] && pixel < Q.piece_begin[s_box.dest + 1];
 
     const RayOut r = s_box.exact_recip
                          ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x,
@@ -735,6 +753,14 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
   if (threadIdx.x == 0) {
     if (s_pushed != 0) atomicAdd(Q.stats + 1, s_pushed);
     if (s_stolen != 0) atomicAdd(Q.stats + 2, s_stolen);
+#if AMRVR_MARCH_TIMELINE
+    const unsigned long long cta_t1 = global_timer_ns();
+    atomicAdd(Q.stats + 4, cta_t1 - s_t0);
+    atomicMax(Q.stats + 5, ~s_t0);  // ~ of the earliest start
+    atomicMax(Q.stats + 6, cta_t1);
+    if (s_table_ns != 0) atomicAdd(Q.stats + 7, s_table_ns);
+    if (blockIdx.x == 0) reinterpret_cast<unsigned*>(Q.stats)[7] = gridDim.x;  // beside the u32 tile counter
+#endif
     if (Q.nranks > 0) {
       // every thread's fragment stores precede the barrier the loop was left through
       __threadfence_system();
@@ -815,21 +841,40 @@ __device__ __forceinline__ void overlay_and_quantise(int px, int py, float c0, f
   }
 }
 
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
 
 constexpr int kBinThreads = 256;  // fold_bin_kernel
 constexpr int kFoldThreads = 128; // fold_layers_kernel: 4 warps, each 32 pixels x 2 rows
 constexpr int kFoldTileW = 32;
 constexpr int kFoldBandRows = 8;  // one CTA tile = 32 x 8 pixels; one band = 8 frame rows
-constexpr int kFoldDepth = 2;     // list entries in flight per thread (x 2 pixels each)
+constexpr int kFoldDepth = 2;     // (register variant) list entries in flight per thread (x 2 pixels each)
 constexpr int kFoldWarpList = 64; // per-warp list of matched layers (shared memory)
+#ifndef AMRVR_FOLD_RING
+#define AMRVR_FOLD_RING 4         // > 0: fragments travel through a per-thread ring of cp.async copies this deep
+                                  // (C4 fold on one B200: 0.0925 ms without, 0.0905 / 0.0823 / 0.0864 ms at depth 6 / 4 / 3)
+#endif
 #ifndef AMRVR_FOLD_MIN_BLOCKS
+#if AMRVR_FOLD_RING > 0
+#define AMRVR_FOLD_MIN_BLOCKS 6   // 28 KB of shared memory per CTA, <= 85 registers
+#else
 #define AMRVR_FOLD_MIN_BLOCKS 8   // 64 registers: 32 warps per SM keep the HBM pipe full
 #endif
+#endif
+constexpr int kFoldRing = AMRVR_FOLD_RING > 0 ? AMRVR_FOLD_RING : 1;
+
+// cp.async: global -> shared without a register in between.  A thread only ever
+// reads back what it copied itself, so cp.async.wait_group is all the
+// synchronisation the ring needs.
+__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int kPending>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(kPending) : "memory");
+}
 
 // A layer as one warp sees it: the address of the warp's first row inside the
 // layer (never dereferenced when that row lies outside the slice), the column
@@ -955,6 +1000,11 @@ template <bool kBytes>
 __global__ void __launch_bounds__(kFoldThreads, AMRVR_FOLD_MIN_BLOCKS)
 fold_layers_kernel(const __grid_constant__ FoldArgs A) {
   __shared__ __align__(16) FoldEntry s_list[kFoldThreads / 32][kFoldWarpList];
+#if AMRVR_FOLD_RING > 0
+  // ring slot of a thread: RGBA of its two pixels, then their depths (40 bytes)
+  __shared__ __align__(16) float4 s_ring_rgba[kFoldRing][2][kFoldThreads];
+  __shared__ float s_ring_depth[kFoldRing][2][kFoldThreads];
+#endif
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (A.sync.nranks > 0) {
@@ -1026,6 +1076,72 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
       nlist += __popc(ballot);
       __syncwarp();
       if (nlist <= kFoldWarpList - 32 && chunk + 32 < count) continue;  // room for another chunk
+#if AMRVR_FOLD_RING > 0
+      // fold the list through the ring: entry e + kFoldRing is requested when entry e has
+      // been blended, so kFoldRing layers x 2 pixels x 20 B per thread are in flight and no
+      // register waits for them; one (possibly empty) group per entry keeps the count fixed
+      auto covers = [&](const FoldEntry& E, bool& in0, bool& in1, int& cx) {
+        cx = px - E.x0;
+        const bool inx = cx >= 0 && cx < E.w;
+        in0 = live0 && inx && (E.rows & 1);
+        in1 = live1 && inx && (E.rows & 2);
+      };
+      auto request = [&](int e) {
+        if (e < nlist) {
+          const FoldEntry E = list[e];  // same address in every lane: broadcast
+          bool in0, in1;
+          int cx;
+          covers(E, in0, in1, cx);
+          const int slot = e % kFoldRing;
+#pragma unroll
+          for (int r = 0; r < 2; ++r) {
+            if (!(r == 0 ? in0 : in1)) continue;
+            float4* dst = &s_ring_rgba[slot][r][threadIdx.x];
+            float* dst_d = &s_ring_depth[slot][r][threadIdx.x];
+            if (E.rows & 4) {  // the reference's own layout: 5 floats per pixel, 4-byte aligned only
+              const float* q = E.row + (static_cast<long long>(r) * E.w + cx) * 5;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) cp_async_4(reinterpret_cast<float*>(dst) + k, q + k);
+              cp_async_4(dst_d, q + 4);
+            } else {
+              const float* rowp = E.row + static_cast<size_t>(r) * E.w * 5;
+              cp_async_16(dst, reinterpret_cast<const float4*>(rowp) + cx);
+              cp_async_4(dst_d, rowp + 4 * E.w + cx);
+            }
+          }
+        }
+        cp_async_commit();
+      };
+#pragma unroll
+      for (int e = 0; e < kFoldRing; ++e) request(e);
+      for (int e = 0; e < nlist; ++e) {
+        cp_async_wait<kFoldRing - 1>();
+        const FoldEntry E = list[e];
+        bool in0, in1;
+        int cx;
+        covers(E, in0, in1, cx);
+        const int slot = e % kFoldRing;
+        Px5 f0 = transparent_px(), f1 = f0;
+        if (in0) {
+          const float4 c = s_ring_rgba[slot][0][threadIdx.x];
+          f0 = Px5{c.x, c.y, c.z, c.w, s_ring_depth[slot][0][threadIdx.x]};
+        }
+        if (in1) {
+          const float4 c = s_ring_rgba[slot][1][threadIdx.x];
+          f1 = Px5{c.x, c.y, c.z, c.w, s_ring_depth[slot][1][threadIdx.x]};
+        }
+        if (E.run != cur_run) {  // uniform: the run closes (DirectSendBase.cpp:441-445)
+          acc0 = blend_depth_swap(acc0, run0);
+          acc1 = blend_depth_swap(acc1, run1);
+          run0 = run1 = transparent_px();
+          cur_run = E.run;
+        }
+        run0 = blend_depth_swap(run0, f0);  // :413-426
+        run1 = blend_depth_swap(run1, f1);
+        request(e + kFoldRing);  // after the slot's values were used
+      }
+      cp_async_wait<0>();
+#else
       // fold the list: all loads of a batch are issued before its first blend
       for (int e0 = 0; e0 < nlist; e0 += kFoldDepth) {
         Px5 f0[kFoldDepth], f1[kFoldDepth];
@@ -1056,6 +1172,7 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
           run1 = blend_depth_swap(run1, f1[k]);
         }
       }
+#endif
       nlist = 0;
       __syncwarp();  // the list is rewritten by the next chunk
     }

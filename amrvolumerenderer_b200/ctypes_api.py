@@ -131,6 +131,12 @@ class FrameStats(C.Structure):
         ("stolen_tiles", C.c_int64),
         ("tiles", C.c_int64),
         ("fragment_pixels", C.c_int64),
+        ("march_span_ns", C.c_int64),
+        ("march_cta_busy_ns", C.c_int64),
+        ("march_table_ns", C.c_int64),
+        ("march_ctas", C.c_int64),
+        ("pre_ms", C.c_float),
+        ("pad_", C.c_float),
     ]
 
 
@@ -331,7 +337,8 @@ def load_library(path: os.PathLike | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = Path(path) if path is not None else LIB_PATH
+    # AMRVR_LIB: another build of the same library (tools/march_sweep.py compares variants)
+    p = Path(path) if path is not None else Path(os.environ.get("AMRVR_LIB") or LIB_PATH)
     if not p.exists():
         raise LibraryMissingError(
             f"{p} not found: build the CUDA extension first "

@@ -516,6 +516,7 @@ def main():
     keys = ("march_ms", "order_ms", "composite_ms", "fold_ms", "gather_ms", "post_ms")
     stage = {k: [] for k in keys}
     pushed, stolen = [], []
+    span_ns, busy_ns, table_ns = [], [], []
     barrier()
     sampler.start()
     for _ in range(args.steps):
@@ -532,12 +533,21 @@ def main():
             stage[k].append(getattr(res["stats"], k))
         pushed.append(res["stats"].exchanged_bytes)
         stolen.append(res["stats"].stolen_tiles)
+        span_ns.append(res["stats"].march_span_ns)
+        busy_ns.append(res["stats"].march_cta_busy_ns)
+        table_ns.append(res["stats"].march_table_ns)
     clocks = sampler.finish()
     launches = ctx.kernel_launches - launches0
     mine = {"rank": rank, "frame_ms": float(np.mean(frame_ms)),
             **{k: float(np.mean(v)) for k, v in stage.items()},
             "pushed_bytes": float(np.mean(pushed)), "stolen_tiles": float(np.mean(stolen)),
             "fragment_pixels": int(res["stats"].fragment_pixels), "tiles": int(res["stats"].tiles)}
+    ctas = max(int(res["stats"].march_ctas), 1)
+    # the march launch on the device clock: first CTA start -> last CTA end, how much of
+    # (span x CTAs) the CTAs were resident, and the time a CTA spent staging transfer tables
+    mine["march_span_ms"] = float(np.mean(span_ns)) * 1e-6
+    mine["march_cta_resident_frac"] = float(np.mean(busy_ns)) / max(float(np.mean(span_ns)) * ctas, 1.0)
+    mine["march_table_ms_per_cta"] = float(np.mean(table_ns)) * 1e-6 / ctas
     per_rank = gather_all(mine)
     ms_per_step = max(r["frame_ms"] for r in per_rank)
 
@@ -685,7 +695,9 @@ def main():
                               "fragment_bytes_read": rd, "bytes_written": wr,
                               "hbm_GBps": (rd + wr) / (r["fold_ms"] * 1e-3) / 1e9 if r["fold_ms"] > 0 else None,
                               "pushed_bytes": r["pushed_bytes"], "stolen_tiles": r["stolen_tiles"],
-                              "march_ms": r["march_ms"],
+                              "march_ms": r["march_ms"], "march_span_ms": r["march_span_ms"],
+                              "march_cta_resident_frac": r["march_cta_resident_frac"],
+                              "march_table_ms_per_cta": r["march_table_ms_per_cta"],
                               "push_GBps": r["pushed_bytes"] / (r["march_ms"] * 1e-3) / 1e9
                               if r["march_ms"] > 0 else None})
         link_peak = None

@@ -518,6 +518,14 @@ typedef struct amrvr_frame_stats {
   int64_t stolen_tiles;    /* march tiles this rank took from other GPUs' queues (sharded frame) */
   int64_t tiles;           /* march tiles of the whole frame */
   int64_t fragment_pixels; /* (pixel, layer) fragments stored for this rank's piece */
+  /* time line of this rank's march launch on the device clock (globaltimer) */
+  int64_t march_span_ns;     /* first CTA start -> last CTA end */
+  int64_t march_cta_busy_ns; /* sum over CTAs of (end - start) */
+  int64_t march_table_ns;    /* sum over CTAs of the time spent staging transfer tables */
+  int64_t march_ctas;        /* CTAs of the launch */
+  float pre_ms;              /* entry of amrvr_render_frame -> the march's parameters are on the device
+                                (host planning + one small copy; the GPU idles meanwhile) */
+  float pad_;
 } amrvr_frame_stats;
 
 /* a1-a17 in one call = VolumeRenderer::renderSingleTrial

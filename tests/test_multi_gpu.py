@@ -66,7 +66,6 @@ def test_eight_ranks(case):
     _run(8, case)
 
 
-@pytest.mark.xfail(reason="first multi-GPU run pending (added with no GPU budget left)", strict=False)
 def test_render_under_torchrun(tmp_path):
     """render() without a context on 2 ranks (Context.from_env) against the
     same plotfile rendered by one rank; worker: tests/mp_render_worker.py."""

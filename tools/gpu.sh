@@ -65,8 +65,11 @@ c5one)
   for w in C5-4 C5-8 C5-16; do bench 1 $w ${w}_n1 --steps 10 --no-cpu-baseline; done
   line C5-4_n1 C5-8_n1 C5-16_n1
   ;;
+twotests)
+  timeout 500 python -m pytest tests/test_multi_gpu.py tests/test_dropin.py -m gpu -q > gpurun_out/${TAG}_pytest_gpu_2.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/${TAG}_pytest_gpu_2.log
+  ;;
 two)
-  timeout 400 python -m pytest tests/test_multi_gpu.py tests/test_dropin.py -m gpu -x -q > gpurun_out/${TAG}_pytest_gpu_2.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/${TAG}_pytest_gpu_2.log
+  timeout 500 python -m pytest tests/test_multi_gpu.py tests/test_dropin.py -m gpu -q > gpurun_out/${TAG}_pytest_gpu_2.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/${TAG}_pytest_gpu_2.log
   bench 2 C4 C4_n2
   for w in C5-4 C5-8 C5-16; do bench 2 $w ${w}_n2 --steps 10 --no-cpu-baseline; done
   line C4_n2 C5-4_n2 C5-8_n2 C5-16_n2
@@ -75,6 +78,10 @@ four)
   bench 4 C4 C4_n4
   for w in C5-4 C5-8 C5-16; do bench 4 $w ${w}_n4 --steps 10 --no-cpu-baseline; done
   line C4_n4 C5-4_n4 C5-8_n4 C5-16_n4
+  ;;
+eightc4)
+  bench 8 C4 C4_n8 --no-cpu-baseline
+  line C4_n8
   ;;
 eight)
   bench 8 C4 C4_n8
