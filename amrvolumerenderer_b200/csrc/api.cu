@@ -122,6 +122,7 @@ struct amrvr_ctx {
   cudaStream_t stream = nullptr;
   cudaStream_t aux = nullptr;  // visibility ordering: runs beside the march, never waits for it
   cudaStream_t copy = nullptr;  // host->device FAB copies of amrvr_scene_upload, ahead of the quantise
+  cudaStream_t quant = nullptr; // quantise launches of an asynchronous upload (amrvr_scene_upload_async)
   cudaEvent_t copy_ev[4] = {};  // copy-group fences (round-robin)
   cudaEvent_t copy_start = nullptr;
   int64_t launches = 0;
@@ -191,6 +192,12 @@ struct amrvr_scene {
   std::vector<uint64_t> global_brick_off;
   std::vector<MarchBox> march_const_global;  // like march_const, for every global box
   cudaEvent_t up0 = nullptr, up1 = nullptr;  // around the FAB copies + quantise launches of the upload
+  // asynchronous upload (amrvr_scene_upload_async, one rank): the bricks arrive group by
+  // group; group_ready[g] fires when the bricks of copy group g are quantised, box_group[b]
+  // is the group of local box b.  A frame marches the boxes of a group as soon as it is there.
+  bool pending = false;
+  std::vector<cudaEvent_t> group_ready;
+  std::vector<int> box_group;
   int64_t fab_bytes = 0, fab_cells = 0;
   float range_min = 0.f, range_max = 1.f;
   // MarchBox fields that depend on the box alone (corners, cell sizes, exactness
@@ -631,6 +638,7 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->copy, cudaStreamNonBlocking));
+  CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->quant, cudaStreamNonBlocking));
   for (auto& e : ctx->copy_ev) CUDA_TRY(nullptr, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   CUDA_TRY(nullptr, cudaEventCreateWithFlags(&ctx->copy_start, cudaEventDisableTiming));
   for (auto& e : ctx->ev) CUDA_TRY(nullptr, cudaEventCreate(&e));
@@ -689,6 +697,7 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
   cudaStreamDestroy(ctx->aux);
+  if (ctx->quant != nullptr) cudaStreamDestroy(ctx->quant);
   cudaStreamDestroy(ctx->copy);
   for (auto& e : ctx->copy_ev)
     if (e != nullptr) cudaEventDestroy(e);
@@ -800,7 +809,10 @@ int stage_boxes(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes, std::vector<
 // (in-situ) are quantised in place with a single launch.
 int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                   const amrvr_scalar_transform& transform, float range_min, float range_max,
-                  amrvr_scene& scene) {
+                  amrvr_scene& scene, bool async_groups = false) {
+  // asynchronous: quantise launches go to their own stream and leave one event per group
+  cudaStream_t qstream = async_groups ? ctx->quant : ctx->stream;
+  if (async_groups) scene.box_group.assign(static_cast<size_t>(nboxes), 0);
   struct Item {
     int box;
     bool on_device;
@@ -847,11 +859,13 @@ int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
     J.nz = B.dims[2];
     J.pad = 0;
   }
-  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->quant_jobs.ptr, jobs.data(), jobs.size() * sizeof(QuantJob),
-                                cudaMemcpyHostToDevice, ctx->stream));
-  // the staging buffer may still be read by work queued on the main stream
+  // the staging buffer and the job table may still be read by work queued on the main stream
   CUDA_TRY(ctx, cudaEventRecord(ctx->copy_start, ctx->stream));
   CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->copy, ctx->copy_start, 0));
+  if (async_groups) CUDA_TRY(ctx, cudaStreamWaitEvent(qstream, ctx->copy_start, 0));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->quant_jobs.ptr, jobs.data(), jobs.size() * sizeof(QuantJob),
+                                cudaMemcpyHostToDevice, qstream));
+  if (async_groups) CUDA_TRY(ctx, cudaStreamSynchronize(qstream));  // `jobs` is a local
 
   const size_t group_bytes = 16u << 20;
   size_t first = 0, in_group = 0, max_cells = 0;
@@ -861,12 +875,20 @@ int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
     if (copied) {
       cudaEvent_t ev = ctx->copy_ev[fence++ & 3];
       CUDA_TRY(ctx, cudaEventRecord(ev, ctx->copy));
-      CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ev, 0));
+      CUDA_TRY(ctx, cudaStreamWaitEvent(qstream, ev, 0));
     }
     LAUNCH_TRY(ctx, launch_brick_quantise_batch(ctx->quant_jobs.as<QuantJob>() + first,
                                                 static_cast<int>(end - first),
                                                 static_cast<long long>(max_cells), transform, range_min,
-                                                range_max, ctx->stream, &ctx->launches));
+                                                range_max, qstream, &ctx->launches));
+    if (async_groups) {
+      cudaEvent_t ready = nullptr;
+      CUDA_TRY(ctx, take_event(ctx, &ready));
+      scene.group_ready.push_back(ready);  // owned by the scene from here on
+      CUDA_TRY(ctx, cudaEventRecord(ready, qstream));
+      const int g = static_cast<int>(scene.group_ready.size()) - 1;
+      for (size_t i = first; i < end; ++i) scene.box_group[static_cast<size_t>(items[i].box)] = g;
+    }
     first = end;
     in_group = 0;
     max_cells = 0;
@@ -1036,9 +1058,44 @@ int gather_box_table(amrvr_ctx* ctx, const std::vector<amrvr_box_record>& mine,
 
 }  // namespace
 
+namespace {
+// waits for an asynchronous upload (no-op otherwise); every entry point that reads
+// the bricks calls it, except the single-rank frame, which marches group by group
+int wait_upload(amrvr_ctx* ctx, const amrvr_scene* scene) {
+  if (scene == nullptr || !scene->pending) return AMRVR_OK;
+  amrvr_scene* sc = const_cast<amrvr_scene*>(scene);
+  if (!sc->group_ready.empty()) CUDA_TRY(ctx, cudaEventSynchronize(sc->group_ready.back()));
+  sc->pending = false;
+  return AMRVR_OK;
+}
+int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                      const amrvr_scalar_transform* transform, float range_min, float range_max,
+                      amrvr_scene** out, bool want_async);
+}  // namespace
+
 extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                                   const amrvr_scalar_transform* transform, float range_min,
                                   float range_max, amrvr_scene** out) {
+  return scene_upload_impl(ctx, nboxes, boxes, transform, range_min, range_max, out, false);
+}
+
+extern "C" int amrvr_scene_upload_async(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                                        const amrvr_scalar_transform* transform, float range_min,
+                                        float range_max, amrvr_scene** out) {
+  return scene_upload_impl(ctx, nboxes, boxes, transform, range_min, range_max, out, true);
+}
+
+extern "C" int amrvr_scene_wait(amrvr_ctx* ctx, amrvr_scene* scene) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, scene != nullptr, "scene is NULL");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return wait_upload(ctx, scene);
+}
+
+namespace {
+int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                      const amrvr_scalar_transform* transform, float range_min, float range_max,
+                      amrvr_scene** out, bool want_async) {
   if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
   REQUIRE(ctx, out != nullptr, "out is NULL");
   *out = nullptr;
@@ -1128,16 +1185,36 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
     scene->fab_cells += cells;
     scene->fab_bytes += cells * static_cast<int64_t>(sizeof(double));
   }
-  CUDA_TRY(ctx, cudaEventRecord(scene->up0, ctx->stream));
+  // asynchronous only where a frame can use it: one rank (a sharded scene is allgathered whole)
+  const bool async_groups = want_async && P == 1;
+  if (async_groups) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->quant));  // an earlier upload still reads the staging buffer
+  cudaStream_t qstream = async_groups ? ctx->quant : ctx->stream;
+  if (async_groups) {
+    CUDA_TRY(ctx, cudaEventRecord(ctx->copy_start, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(qstream, ctx->copy_start, 0));
+  }
+  CUDA_TRY(ctx, cudaEventRecord(scene->up0, qstream));
   {
-    const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene);
+    const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene, async_groups);
     if (st != AMRVR_OK) {
+      if (async_groups) {
+        cudaStreamSynchronize(ctx->copy);
+        cudaStreamSynchronize(ctx->quant);
+      }
+      for (cudaEvent_t e : scene->group_ready) cudaEventDestroy(e);
       scene->bricks.release();
       return st;
     }
   }
-  CUDA_TRY(ctx, cudaEventRecord(scene->up1, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(scene->up1, qstream));
   tr.mark("upload_enqueue");
+  if (async_groups) {
+    // returns with the copies in flight: the caller keeps the FABs alive until
+    // amrvr_scene_wait or the first frame of this scene has returned
+    scene->pending = !scene->group_ready.empty();
+    *out = scene.release();
+    return AMRVR_OK;
+  }
   if (scene->replicated)  // in place: every rank contributes its own slot
     NCCL_TRY(ctx, nccl_api().AllGather(scene->bricks.as<char>() + slot * ctx->rank, scene->bricks.ptr,
                                        slot, ncclChar, ctx->comm, ctx->stream));
@@ -1146,6 +1223,7 @@ extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* b
   *out = scene.release();
   return AMRVR_OK;
 }
+}  // namespace
 
 extern "C" int amrvr_scene_is_replicated(const amrvr_scene* scene) {
   return (scene != nullptr && scene->replicated) ? 1 : 0;
@@ -1396,7 +1474,15 @@ extern "C" int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene) {
   if (scene == nullptr) return AMRVR_OK;
   if (ctx != nullptr) {
     cudaSetDevice(ctx->device);
+    if (scene->pending) {
+      cudaStreamSynchronize(ctx->copy);
+      cudaStreamSynchronize(ctx->quant);
+    }
     cudaStreamSynchronize(ctx->stream);
+  }
+  for (cudaEvent_t e : scene->group_ready) {
+    if (ctx != nullptr && ctx->event_pool.size() < 64) ctx->event_pool.push_back(e);
+    else cudaEventDestroy(e);
   }
   if (ctx != nullptr && scene->bricks.ptr != nullptr && ctx->brick_pools.size() < 2) {
     ctx->brick_pools.push_back(scene->bricks);  // cudaMalloc/cudaFree cost more than the quantise
@@ -1430,6 +1516,7 @@ extern "C" int amrvr_scene_read_brick(amrvr_ctx* ctx, const amrvr_scene* scene, 
   const size_t cells = static_cast<size_t>(std::max(L.dims[0], 0)) * std::max(L.dims[1], 0) *
                        std::max(L.dims[2], 0);
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (wait_upload(ctx, scene) != AMRVR_OK) return AMRVR_ERR_CUDA;
   CUDA_TRY(ctx, cudaMemcpyAsync(dst, scene->bricks.as<uint8_t>() + L.brick_off, cells,
                                 cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1618,6 +1705,7 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
   REQUIRE(ctx, npts >= 0 && (npts == 0 || pts != nullptr), "bad colour map");
   REQUIRE(ctx, static_cast<int64_t>(width) * height < (1LL << 31), "frame too large");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (wait_upload(ctx, scene) != AMRVR_OK) return AMRVR_ERR_CUDA;
 
   const int n = static_cast<int>(scene->local.size());
   std::unique_ptr<amrvr_layers> L(new amrvr_layers);
@@ -2642,6 +2730,17 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   for (int g = 0; g < n; ++g) by_table[g] = g;
   std::stable_sort(by_table.begin(), by_table.end(),
                    [&](int a, int b) { return per_box[a].table < per_box[b].table; });
+  // a scene whose upload is still under way (one rank): boxes by copy group first, one
+  // march launch per group, each waiting only for its own group's bricks
+  const bool grouped = !sharded && scene->pending && !scene->group_ready.empty() &&
+                       scene->box_group.size() == static_cast<size_t>(n);
+  const int ngroups = grouped ? static_cast<int>(scene->group_ready.size()) : 0;
+  if (grouped)
+    std::stable_sort(by_table.begin(), by_table.end(),
+                     [&](int a, int b) { return scene->box_group[a] < scene->box_group[b]; });
+  else if (wait_upload(ctx, scene) != AMRVR_OK)
+    return bail(AMRVR_ERR_CUDA);
+  std::vector<int> group_tile_begin(static_cast<size_t>(ngroups) + 1, 0);
 
   trace.mark("boxconst");
   // ---- march items: queue p = the rows of every footprint that fall into piece p
@@ -2671,6 +2770,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
       M.tiles_x = (r.w + 15) / 16;
       M.tile_base = tiles;
       tiles += M.tiles_x * ((M.rh + 15) / 16);
+      if (grouped) group_tile_begin[static_cast<size_t>(scene->box_group[g]) + 1] = tiles;
       M.layer_off = pool_floats[p];
       M.dest = p;
       pool_floats[p] += static_cast<uint64_t>(M.rw) * M.rh * 5;
@@ -2682,6 +2782,8 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
     }
   }
   queues.tile_begin[P] = tiles;
+  for (int g = 1; g <= ngroups; ++g)  // groups without a visible box: empty ranges
+    group_tile_begin[g] = std::max(group_tile_begin[g], group_tile_begin[g - 1]);
   for (int p = 0; p < P; ++p) queues.piece_begin[p] = pbegin[p];
   queues.piece_begin[P] = npix;
   frame.nboxes = static_cast<int>(items.size());
@@ -2743,8 +2845,10 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   const size_t tables_bytes = tables.size() * sizeof(float);
   const size_t items_bytes = items.size() * sizeof(MarchBox);
   const size_t fold_bytes_max = static_cast<size_t>(n) * sizeof(FoldLayer);
+  const size_t counters_bytes = (static_cast<size_t>(ngroups) * sizeof(uint32_t) + 15) & ~size_t(15);
   const size_t off_items = kParamHeader + tables_bytes;
-  const size_t off_fold = off_items + items_bytes;
+  const size_t off_counters = off_items + items_bytes;  // tile counters of the per-group launches
+  const size_t off_fold = off_counters + counters_bytes;
   const size_t off_edges = off_fold + fold_bytes_max;
   const size_t block_bytes = off_edges + sizeof(OverlayEdges);
   unsigned char* block = nullptr;
@@ -2755,6 +2859,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   std::memset(block, 0, kParamHeader);
   if (tables_bytes) std::memcpy(block + kParamHeader, tables.data(), tables_bytes);
   if (items_bytes) std::memcpy(block + off_items, items.data(), items_bytes);
+  if (counters_bytes) std::memset(block + off_counters, 0, counters_bytes);
   if (ctx->march_boxes.reserve(block_bytes) != cudaSuccess ||
       ctx->fold_bins.reserve(std::max<size_t>(fold_scratch_bytes(n, RW, my_begin, my_end), 256)) != cudaSuccess)
     return bail(fail(ctx, AMRVR_ERR_CUDA, "parameter block allocation failed"));
@@ -2773,15 +2878,41 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
                     : fail(ctx, AMRVR_ERR_CUDA,
                            std::string(what) + ": " + cudaGetErrorString(static_cast<cudaError_t>(e)));
   };
-  int st = try_cuda(cudaMemcpyAsync(dev_block, block, off_fold, cudaMemcpyHostToDevice, ctx->stream),
-                    "parameter copy");
+  // While FAB copies fill the host-to-device copy engine a cudaMemcpyAsync would queue
+  // behind all of them: the march's parameters are then fetched by a small kernel that
+  // reads the pinned staging block across PCIe itself.
+  int st = grouped ? try_launch(launch_peer_copy(block, dev_block, off_fold,
+                                                 static_cast<int>((off_fold / 16 + 255) / 256), ctx->stream,
+                                                 &ctx->launches),
+                                "parameter fetch")
+                   : try_cuda(cudaMemcpyAsync(dev_block, block, off_fold, cudaMemcpyHostToDevice, ctx->stream),
+                              "parameter copy");
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[1], ctx->stream), "event");
-  if (st == AMRVR_OK)
-    st = try_launch(launch_raymarch(frame, queues, reinterpret_cast<const MarchBox*>(dev_block + off_items),
-                                    scene->bricks.as<uint8_t>(),
-                                    reinterpret_cast<const float*>(dev_block + kParamHeader),
-                                    params->count_samples != 0, ctx->stream, &ctx->launches),
-                    "march");
+  if (!grouped) {
+    if (st == AMRVR_OK)
+      st = try_launch(launch_raymarch(frame, queues, reinterpret_cast<const MarchBox*>(dev_block + off_items),
+                                      scene->bricks.as<uint8_t>(),
+                                      reinterpret_cast<const float*>(dev_block + kParamHeader),
+                                      params->count_samples != 0, ctx->stream, &ctx->launches),
+                      "march");
+  } else {
+    for (int g = 0; g < ngroups && st == AMRVR_OK; ++g) {
+      // the bricks of group g are quantised; later groups are still on PCIe
+      st = try_cuda(cudaStreamWaitEvent(ctx->stream, scene->group_ready[static_cast<size_t>(g)], 0), "wait");
+      MarchQueues q = queues;
+      q.tile_begin[0] = group_tile_begin[static_cast<size_t>(g)];
+      q.tile_begin[1] = group_tile_begin[static_cast<size_t>(g) + 1];
+      q.counter[0] = reinterpret_cast<unsigned*>(dev_block + off_counters) + g;
+      MarchFrame fr = frame;
+      fr.ntiles = q.tile_begin[1] - q.tile_begin[0];
+      if (st == AMRVR_OK && fr.ntiles > 0)
+        st = try_launch(launch_raymarch(fr, q, reinterpret_cast<const MarchBox*>(dev_block + off_items),
+                                        scene->bricks.as<uint8_t>(),
+                                        reinterpret_cast<const float*>(dev_block + kParamHeader),
+                                        params->count_samples != 0, ctx->stream, &ctx->launches),
+                        "march");
+    }
+  }
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[2], ctx->stream), "event");
   trace.mark("march_enqueue");
 
@@ -2924,6 +3055,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
     return fail(ctx, AMRVR_ERR_CUDA, std::string("frame failed: ") + cudaGetErrorString(cudaGetLastError()));
   }
   trace.mark("final_sync");
+  if (grouped) const_cast<amrvr_scene*>(scene)->pending = false;  // every group was waited for on the stream
   st = join_order(ctx, &order);
   if (st != AMRVR_OK) return st;
   if (sharded && static_cast<uint32_t>(ctx->frame_stats_host[8]) != 0) {

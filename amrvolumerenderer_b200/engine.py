@@ -153,17 +153,19 @@ class Context:
                                                   C.byref(total)))
         return counts, int(total.value)
 
-    def upload(self, cboxes, n, transform, scalar_range) -> "DeviceScene":
+    def upload(self, cboxes, n, transform, scalar_range, wait=True) -> "DeviceScene":
+        """wait=False: amrvr_scene_upload_async -- returns with the FAB copies in flight
+        (the arrays must stay alive and unchanged until the first frame or .wait())."""
         h = C.c_void_p()
-        self.check(self.lib.amrvr_scene_upload(self._h, n, cboxes, C.byref(transform),
-                                               float(scalar_range[0]), float(scalar_range[1]),
-                                               C.byref(h)))
+        fn = self.lib.amrvr_scene_upload if wait else self.lib.amrvr_scene_upload_async
+        self.check(fn(self._h, n, cboxes, C.byref(transform), float(scalar_range[0]),
+                      float(scalar_range[1]), C.byref(h)))
         return DeviceScene(self, h)
 
-    def upload_scene(self, scene) -> "DeviceScene":
+    def upload_scene(self, scene, wait=True) -> "DeviceScene":
         """scene: amrvolumerenderer_b200.scenes.Scene; uploads this rank's boxes."""
         cboxes, n, keep = scene.c_boxes(only_rank=self.rank if scene.nranks > 1 else None)
-        ds = self.upload(cboxes, n, scene.transform, scene.scalar_range)
+        ds = self.upload(cboxes, n, scene.transform, scene.scalar_range, wait=wait)
         ds._keep = keep
         return ds
 
@@ -259,6 +261,10 @@ class DeviceScene:
         if self._h:
             self.ctx.lib.amrvr_scene_free(self.ctx._h, self._h)
             self._h = C.c_void_p()
+
+    def wait(self):
+        """Blocks until an asynchronous upload has finished."""
+        self.ctx.check(self.ctx.lib.amrvr_scene_wait(self.ctx._h, self._h))
 
     @property
     def replicated(self) -> bool:

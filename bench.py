@@ -563,7 +563,10 @@ def main():
     for it in range(2 + min(args.steps, 10)):
         barrier()
         t0 = time.perf_counter()
-        ds2 = ctx.upload_scene(scene)
+        # one rank: the upload returns with the copies in flight and the frame marches each
+        # copy group as it lands (amrvr_scene_upload_async); several ranks: the bricks are
+        # allgathered after the upload, so it is waited for
+        ds2 = ctx.upload_scene(scene, wait=(world > 1))
         t1 = time.perf_counter()
         o2 = ctx.render_frame(ds2, camera, params, want_rgba=False)
         assert o2["rgb8"] is not None or rank != 0
@@ -641,7 +644,9 @@ def main():
                                    f"{W}x{H} AA{aa}, visibility graph on, boxes dealt "
                                    f"{DEAL} round-robin to {world} rank(s)",
                        "value_scope": "bricks resident in HBM, RGB8 frame left on the root GPU",
-                       "e2e_scope": "pinned host FABs -> upload+quantise -> frame -> RGB8 on the host",
+                       "e2e_scope": "pinned host FABs -> upload+quantise -> frame -> RGB8 on the host"
+                                    + ("; the frame marches each 16 MB copy group as it lands "
+                                       "(amrvr_scene_upload_async)" if world == 1 else ""),
                        "l2": "256 MiB buffer written between timed frames (L2 flush)",
                        "placement": ("bricks replicated on every GPU at upload; march tiles dealt by image "
                                      "piece, stolen across GPUs, fragments stored into the folding GPU's pool")

@@ -153,6 +153,19 @@ int amrvr_brick_stats(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                       double* min_value, double* max_value,
                       double* min_positive, int64_t* finite_count);
 
+/* amrvr_scene_upload without the final wait (one rank; with several ranks it is
+ * amrvr_scene_upload): returns while the FAB copies are still on PCIe.  The
+ * caller keeps the FABs alive and unchanged until amrvr_scene_wait() or the
+ * first amrvr_render_frame() of the scene has returned.  That first frame
+ * marches the boxes of a copy group as soon as the group is quantised, so the
+ * march hides behind the upload (the in-situ case of a known scalar range:
+ * SceneBuilder.cpp:160-187 hands the data over, VolumeRenderer.cpp:1103-1339
+ * renders it once).  Every other entry point waits for the upload first. */
+int amrvr_scene_upload_async(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                             const amrvr_scalar_transform* transform,
+                             float range_min, float range_max, amrvr_scene** out);
+int amrvr_scene_wait(amrvr_ctx* ctx, amrvr_scene* scene);
+
 /* K5.  Replaces the zero-copy Array4 views BuildSceneGeometry hands to the
  * painter (SceneBuilder.cpp:160-187): each FAB becomes a device-resident brick
  * of one byte per cell holding the colour-table index the reference computes

@@ -255,6 +255,39 @@ def test_frame_bytes_only_path(ctx, oracle, w, h):
     ds.free()
 
 
+def test_frame_of_a_scene_still_uploading(ctx):
+    """amrvr_scene_upload_async: the first frame marches copy group by copy group while
+    later groups are still on PCIe (46 MB of FABs = 3 groups here).  Same bricks, same
+    samples and the same pixels, bit for bit, as after a finished upload -- with and
+    without the float frame, and through the entry points that wait for the upload."""
+    scene = scenes.scene_c4(box_cells=32)
+    camera = scenes.make_camera()
+    params = _params(320, 240)
+    done = ctx.upload_scene(scene)
+    want = ctx.render_frame(done, camera, params)
+    want_rgb, want_f5, want_samples = want["rgb8"].copy(), want["final5"].copy(), want["stats"].samples
+    ncells = int(np.prod(scene.boxes[-1].dims))
+    want_brick = done.read_brick(len(scene.boxes) - 1, ncells)
+    done.free()
+    for want_rgba in (True, False):
+        ds = ctx.upload_scene(scene, wait=False)
+        got = ctx.render_frame(ds, camera, params, want_rgba=want_rgba)
+        assert np.array_equal(got["rgb8"], want_rgb)
+        if want_rgba:
+            assert np.array_equal(got["final5"], want_f5)
+        assert got["stats"].samples == want_samples
+        again = ctx.render_frame(ds, camera, params, want_rgba=False)  # the upload is over by now
+        assert np.array_equal(again["rgb8"], want_rgb)
+        ds.free()
+    ds = ctx.upload_scene(scene, wait=False)
+    assert np.array_equal(ds.read_brick(len(scene.boxes) - 1, ncells), want_brick)  # waits
+    ds.free()
+    ds = ctx.upload_scene(scene, wait=False)
+    ds.wait()
+    ds.free()
+    ctx.upload_scene(scene, wait=False).free()  # freed while the copies are in flight
+
+
 def test_frame_bytes_only_antialiased_and_empty(ctx, oracle):
     """AA > 1 keeps the downsample -> fused overlay+bytes pass; an empty scene gives a black frame."""
     scene = scenes.scene_c2(box_cells=8)
