@@ -117,6 +117,37 @@ def _ncu_issue(march_s, sm_clock_hz, n_sm=148):
         return None
 
 
+def nvlink_counters(index: int):
+    """NVLink data/raw byte counters of one GPU, summed over its links (NVML field values
+    138-141, KiB; hardware counters, not arithmetic).  None when NVML cannot give them."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(visible.split(",")[index]) if visible and visible.split(",")[index].isdigit() else index
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        ids = [(pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
+               (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF),
+               (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_TX, 0xFFFFFFFF),
+               (pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_RAW_RX, 0xFFFFFFFF)]
+        vals = pynvml.nvmlDeviceGetFieldValues(h, ids)
+        out = {}
+        for name, v in zip(("data_tx", "data_rx", "raw_tx", "raw_rx"), vals):
+            if v.nvmlReturn != 0:  # 3 = NVML_ERROR_NOT_SUPPORTED on the pool's boxes (seen in round 2)
+                return None
+            out[name] = int(v.value.ullVal) * 1024
+        return out
+    except Exception:
+        return None
+
+
+def _delta(after, before, per):
+    if after is None or before is None:
+        return None
+    return {k: (after[k] - before[k]) / per for k in after}
+
+
 class ClockSampler(threading.Thread):
     """SM clock and throttle reasons of one GPU while the timed region runs
     (NVML in-process, every 5 ms; nvidia-smi as the fallback)."""
@@ -518,6 +549,7 @@ def main():
     pushed, stolen = [], []
     span_ns, busy_ns, table_ns = [], [], []
     barrier()
+    link0 = nvlink_counters(local) if world > 1 else None
     sampler.start()
     for _ in range(args.steps):
         with torch.cuda.stream(stream):
@@ -537,6 +569,7 @@ def main():
         busy_ns.append(res["stats"].march_cta_busy_ns)
         table_ns.append(res["stats"].march_table_ns)
     clocks = sampler.finish()
+    link1 = nvlink_counters(local) if world > 1 else None
     launches = ctx.kernel_launches - launches0
     mine = {"rank": rank, "frame_ms": float(np.mean(frame_ms)),
             **{k: float(np.mean(v)) for k, v in stage.items()},
@@ -545,6 +578,9 @@ def main():
     ctas = max(int(res["stats"].march_ctas), 1)
     # the march launch on the device clock: first CTA start -> last CTA end, how much of
     # (span x CTAs) the CTAs were resident, and the time a CTA spent staging transfer tables
+    # NVLink bytes per frame as the hardware counted them over the timed frames (the frames'
+    # own barriers ride on NCCL and are in there too)
+    mine["nvlink_counted"] = _delta(link1, link0, args.steps)
     mine["march_span_ms"] = float(np.mean(span_ns)) * 1e-6
     mine["march_cta_resident_frac"] = float(np.mean(busy_ns)) / max(float(np.mean(span_ns)) * ctas, 1.0)
     mine["march_table_ms_per_cta"] = float(np.mean(table_ns)) * 1e-6 / ctas
@@ -554,9 +590,14 @@ def main():
     # ---- NVLink: measured per-GPU rate of plain stores / loads into the ring neighbour, all ranks at once
     link = None
     if world > 1 and replicated:
+        c0 = nvlink_counters(local)
         wr = ctx.peer_bandwidth(256 << 20, 1, True, 10)
+        c1 = nvlink_counters(local)
         rd = ctx.peer_bandwidth(256 << 20, 1, False, 10)
-        link = gather_all({"rank": rank, "write_GBps": wr, "read_GBps": rd})
+        c2 = nvlink_counters(local)
+        # the probe moves 11 x 256 MiB (warm-up + 10) each way: what the counters say about it
+        link = gather_all({"rank": rank, "write_GBps": wr, "read_GBps": rd,
+                           "counted_write_probe": _delta(c1, c0, 1), "counted_read_probe": _delta(c2, c1, 1)})
 
     # ---- end-to-end arm: pinned host FABs -> upload -> frame -> host RGB8
     e2e_ms, up_ms = [], []
@@ -701,6 +742,7 @@ def main():
                               "hbm_GBps": (rd + wr) / (r["fold_ms"] * 1e-3) / 1e9 if r["fold_ms"] > 0 else None,
                               "pushed_bytes": r["pushed_bytes"], "stolen_tiles": r["stolen_tiles"],
                               "march_ms": r["march_ms"], "march_span_ms": r["march_span_ms"],
+                              "nvlink_counted_bytes_per_frame": r.get("nvlink_counted"),
                               "march_cta_resident_frac": r["march_cta_resident_frac"],
                               "march_table_ms_per_cta": r["march_table_ms_per_cta"],
                               "push_GBps": r["pushed_bytes"] / (r["march_ms"] * 1e-3) / 1e9
@@ -712,7 +754,14 @@ def main():
                          "read_GBps_min": min(l["read_GBps"] for l in link),
                          "read_GBps_max": max(l["read_GBps"] for l in link),
                          "how": "256 MiB between ring neighbours, all ranks at once, plain 16 B loads/stores "
-                                "from 148x8 CTAs, CUDA events, 10 iterations"}
+                                "from 148x8 CTAs, CUDA events, 10 iterations",
+                         "counted_by_nvml": {"write_probe_rank0": link[0].get("counted_write_probe"),
+                                             "read_probe_rank0": link[0].get("counted_read_probe"),
+                                             "expected_bytes_each_way": 11 * (256 << 20),
+                                             "note": "NVML NVLink throughput counters (field values 138-141, all "
+                                                     "links of the GPU) around the two probes; null = NVML answers "
+                                                     "NOT_SUPPORTED on this box, the rates above are CUDA-event times "
+                                                     "of a copy kernel and pushed_bytes is counted by the march itself"}}
         line["composite"] = {
             "fold_ms_max_rank": max(r["fold_ms"] for r in per_rank),
             "composite_ms_max_rank": max(r["composite_ms"] for r in per_rank),
