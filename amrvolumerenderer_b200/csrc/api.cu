@@ -2666,9 +2666,8 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   if (ctx->frame_stats_host == nullptr)
     CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->frame_stats_host), 128));
 
-  OrderJob order;
-  start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
-  // from here on every return path joins the helper thread
+  OrderJob order;  // started right after the march is enqueued (waking the helper thread costs microseconds)
+  // every return path joins the helper thread
   auto bail = [&](int status) {
     if (order.on_thread) ctx->worker.wait();
     if (sharded) abort_sharded_frame(ctx);
@@ -2915,6 +2914,8 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   }
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[2], ctx->stream), "event");
   trace.mark("march_enqueue");
+  // the visibility ordering (BuildVisibilityOrderedGroup) runs beside the march on the helper thread
+  start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
 
   // ---- fold table of my piece, in the reference's blend order with its run ids
   // (DirectSendBase.cpp:363-407); built while the march runs

@@ -483,10 +483,16 @@ def main():
         dist.broadcast_object_list(box, src=0)
         nccl_id = box[0]
 
+    spin_us = float(os.environ.get("AMRVR_BENCH_SPIN_US", "0"))
+
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+        if spin_us > 0:  # experiment: keep the core busy after the collective's blocking wait
+            t_end = time.perf_counter() + spin_us * 1e-6
+            while time.perf_counter() < t_end:
+                pass
 
     def gather_all(obj):
         if world == 1:
@@ -544,7 +550,7 @@ def main():
     sampler = ClockSampler(local)
     launches0 = ctx.kernel_launches
     frame_ms = []
-    keys = ("march_ms", "order_ms", "composite_ms", "fold_ms", "gather_ms", "post_ms")
+    keys = ("pre_ms", "march_ms", "order_ms", "composite_ms", "fold_ms", "gather_ms", "post_ms")
     stage = {k: [] for k in keys}
     pushed, stolen = [], []
     span_ns, busy_ns, table_ns = [], [], []
@@ -741,7 +747,7 @@ def main():
                               "fragment_bytes_read": rd, "bytes_written": wr,
                               "hbm_GBps": (rd + wr) / (r["fold_ms"] * 1e-3) / 1e9 if r["fold_ms"] > 0 else None,
                               "pushed_bytes": r["pushed_bytes"], "stolen_tiles": r["stolen_tiles"],
-                              "march_ms": r["march_ms"], "march_span_ms": r["march_span_ms"],
+                              "pre_ms": r["pre_ms"], "march_ms": r["march_ms"], "march_span_ms": r["march_span_ms"],
                               "nvlink_counted_bytes_per_frame": r.get("nvlink_counted"),
                               "march_cta_resident_frac": r["march_cta_resident_frac"],
                               "march_table_ms_per_cta": r["march_table_ms_per_cta"],
