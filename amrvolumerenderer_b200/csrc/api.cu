@@ -1777,6 +1777,7 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
     M.ry0 = r.y0;
     M.rw = r.w;
     M.rh = r.h;
+    M.ry_first = r.y0;
     M.tiles_x = (r.w + 15) / 16;
     M.tile_base = tiles;
     tiles += M.tiles_x * ((r.h + 15) / 16);
@@ -1786,6 +1787,7 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
     rays += static_cast<int64_t>(r.w) * r.h;
   }
   frame.ntiles = tiles;
+  frame.strip_stride = 16;
   L->pool_floats = floats;
   L->stats.rays = rays;
   L->stats.fragment_pixels = rays;
@@ -1821,7 +1823,6 @@ extern "C" int amrvr_raymarch(amrvr_ctx* ctx, const amrvr_scene* scene, const am
   MarchQueues queues{};  // one queue, one pool: this rank's own boxes
   queues.nqueues = 1;
   queues.tile_begin[1] = tiles;
-  queues.piece_begin[1] = INT_MAX;  // every pixel of the frame
   queues.counter[0] = reinterpret_cast<unsigned*>(dev_block + 24);
   queues.pool[0] = L->pool.as<float>();
   queues.stats = counter;
@@ -2742,51 +2743,87 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   std::vector<int> group_tile_begin(static_cast<size_t>(ngroups) + 1, 0);
 
   trace.mark("boxconst");
-  // ---- march items: queue p = the rows of every footprint that fall into piece p
-  std::vector<int> pbegin(static_cast<size_t>(P)), pend(static_cast<size_t>(P));
-  for (int p = 0; p < P; ++p) piece_range(npix, p, P, &pbegin[p], &pend[p]);
+  // ---- march items.  One rank: one queue, a box's tiles cover its footprint from its top
+  // row.  Several ranks: the frame is STRIPED -- GPU q folds the 16-row strips k = q, q + P,
+  // ... of the frame and queue q holds, of every box, the tiles of those strips (QueueItem),
+  // so every GPU gets an even share of every footprint: the march and the fold balance
+  // without any tile changing hands, and stealing only evens out what is left.  Which
+  // pixels a rank folds is bookkeeping: the gathered frame does not depend on it (each
+  // pixel is folded once, in the reference's global layer order with its run structure;
+  // pixel ownership in the reference's sense is what amrvr_composite reports).
   std::vector<MarchBox> items;
-  items.reserve(static_cast<size_t>(n) * 2);
-  std::vector<int> my_item(static_cast<size_t>(n), -1);  // global box -> its item in MY queue
+  items.reserve(static_cast<size_t>(n));
+  std::vector<int> my_item(static_cast<size_t>(n), -1);  // global box -> its item
+  std::vector<int> item_box;                              // item -> global box
+  for (int k = 0; k < n; ++k) {
+    const int g = by_table[k];
+    const Rect& r = rects[g];
+    if (r.w <= 0 || r.h <= 0) continue;
+    MarchBox M = per_box[g];
+    M.rx0 = r.x0;
+    M.ry0 = r.y0;
+    M.rw = r.w;
+    M.rh = r.h;
+    M.tiles_x = (r.w + 15) / 16;
+    M.ry_first = r.y0;
+    M.dest = 0;
+    my_item[g] = static_cast<int>(items.size());
+    item_box.push_back(g);
+    items.push_back(M);
+  }
+  const int nb = static_cast<int>(items.size());
+  auto by_item_box = [&](int i) { return item_box[static_cast<size_t>(i)]; };
+  std::vector<QueueItem> qitems(sharded ? static_cast<size_t>(P) * nb : 0);
+  std::vector<uint64_t> my_layer_off(static_cast<size_t>(nb), 0);
+  std::vector<char> mine_has_rows(static_cast<size_t>(nb), 0);
   MarchQueues queues{};
   queues.nqueues = P;
   queues.mine = sharded ? me : 0;
   std::vector<uint64_t> pool_floats(static_cast<size_t>(P), 0);
   int tiles = 0;
   int64_t my_rays = 0;
-  for (int p = 0; p < P; ++p) {
-    queues.tile_begin[p] = tiles;
-    for (int k = 0; k < n; ++k) {
-      const int g = by_table[k];
-      const Rect& r = rects[g];
-      int s0, s1;
-      if (!slice_rows(r, pbegin[p], pend[p], RW, &s0, &s1)) continue;
-      MarchBox M = per_box[g];
-      M.rx0 = r.x0;
-      M.ry0 = s0;
-      M.rw = r.w;
-      M.rh = s1 - s0;
-      M.tiles_x = (r.w + 15) / 16;
-      M.tile_base = tiles;
-      tiles += M.tiles_x * ((M.rh + 15) / 16);
-      if (grouped) group_tile_begin[static_cast<size_t>(scene->box_group[g]) + 1] = tiles;
-      M.layer_off = pool_floats[p];
-      M.dest = p;
-      pool_floats[p] += static_cast<uint64_t>(M.rw) * M.rh * 5;
-      if (p == queues.mine) {
-        my_item[g] = static_cast<int>(items.size());
+  for (int q = 0; q < P; ++q) {
+    queues.tile_begin[q] = tiles;
+    for (int i = 0; i < nb; ++i) {
+      MarchBox& M = items[static_cast<size_t>(i)];
+      if (!sharded) {
+        M.tile_base = tiles;
+        tiles += M.tiles_x * ((M.rh + 15) / 16);
+        if (grouped) group_tile_begin[static_cast<size_t>(scene->box_group[by_item_box(i)]) + 1] = tiles;
+        M.layer_off = pool_floats[0];
+        pool_floats[0] += static_cast<uint64_t>(M.rw) * M.rh * 5;
+        my_layer_off[static_cast<size_t>(i)] = M.layer_off;
+        mine_has_rows[static_cast<size_t>(i)] = 1;
         my_rays += static_cast<int64_t>(M.rw) * M.rh;
+        continue;
       }
-      items.push_back(M);
+      const int y0 = M.ry0, y1 = M.ry0 + M.rh;  // footprint rows [y0, y1)
+      const int k0 = y0 >> 4, k1 = (y1 - 1) >> 4;
+      const int kf = k0 + (((q - k0) % P) + P) % P;  // first strip of GPU q that touches the footprint
+      const int ns = (kf > k1) ? 0 : (k1 - kf) / P + 1;
+      QueueItem& QI = qitems[static_cast<size_t>(q) * nb + i];
+      QI.tile_base = tiles;
+      QI.ry_first = kf * 16;
+      QI.layer_off = pool_floats[q];
+      tiles += ns * M.tiles_x;
+      pool_floats[q] += static_cast<uint64_t>(ns) * 16 * M.rw * 5;  // whole strips, 16 rows each
+      if (q == me) {
+        my_layer_off[static_cast<size_t>(i)] = QI.layer_off;
+        mine_has_rows[static_cast<size_t>(i)] = ns > 0;
+        for (int k = kf; k <= k1; k += P)
+          my_rays += static_cast<int64_t>(M.rw) * (std::min(16 * k + 16, y1) - std::max(16 * k, y0));
+      }
     }
   }
   queues.tile_begin[P] = tiles;
   for (int g = 1; g <= ngroups; ++g)  // groups without a visible box: empty ranges
     group_tile_begin[g] = std::max(group_tile_begin[g], group_tile_begin[g - 1]);
-  for (int p = 0; p < P; ++p) queues.piece_begin[p] = pbegin[p];
-  queues.piece_begin[P] = npix;
-  frame.nboxes = static_cast<int>(items.size());
+  frame.nboxes = nb;
   frame.ntiles = tiles;
+  frame.strip_stride = 16 * P;
+  // the rows this rank folds: strips me, me + P, ... (all rows on one rank)
+  const int strips_total = (RH + 15) / 16;
+  const int my_strips = sharded ? ((strips_total > me) ? (strips_total - 1 - me) / P + 1 : 0) : strips_total;
   {  // the other queues, heaviest first
     std::vector<int> others;
     for (int p = 0; p < P; ++p)
@@ -2806,7 +2843,8 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   float* pool_local = nullptr;
   if (sharded) {
     bool ok_a = true, ok_b = true, ok_c = true;
-    const size_t max_piece = static_cast<size_t>(npix) / P + static_cast<size_t>(npix) % P;
+    // the float piece of a rank: its strips one after the other, 16 rows each
+    const size_t max_piece = static_cast<size_t>((strips_total + P - 1) / P) * 16 * RW;
     int st = sym_reserve(ctx, ctx->sym_pool, std::max<size_t>(most_floats * sizeof(float), 256), &ok_a);
     if (st == AMRVR_OK) st = sym_reserve(ctx, ctx->sym_piece, std::max<size_t>(max_piece * 20, 256), &ok_b);
     if (st == AMRVR_OK && bytes_mode)
@@ -2840,13 +2878,17 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   // ---- one parameter block: [header | tables | items | fold table | overlay edges].  The
   // march needs the first three only: they are copied and the march is launched BEFORE
   // the host builds the fold table, which then travels while the march runs.
-  const int my_begin = pbegin[queues.mine], my_end = pend[queues.mine];
+  const int my_begin = 0, my_end = npix;  // one rank: every pixel; striped: FoldStrips says which rows
+  const FoldStrips strips{P, me, RH};
+  const FoldStrips* my_strips_arg = sharded ? &strips : nullptr;
   const size_t tables_bytes = tables.size() * sizeof(float);
   const size_t items_bytes = items.size() * sizeof(MarchBox);
+  const size_t qitems_bytes = qitems.size() * sizeof(QueueItem);
   const size_t fold_bytes_max = static_cast<size_t>(n) * sizeof(FoldLayer);
   const size_t counters_bytes = (static_cast<size_t>(ngroups) * sizeof(uint32_t) + 15) & ~size_t(15);
   const size_t off_items = kParamHeader + tables_bytes;
-  const size_t off_counters = off_items + items_bytes;  // tile counters of the per-group launches
+  const size_t off_qitems = off_items + items_bytes;      // striped frame: [queue][box] table
+  const size_t off_counters = off_qitems + qitems_bytes;  // tile counters of the per-group launches
   const size_t off_fold = off_counters + counters_bytes;
   const size_t off_edges = off_fold + fold_bytes_max;
   const size_t block_bytes = off_edges + sizeof(OverlayEdges);
@@ -2858,12 +2900,15 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   std::memset(block, 0, kParamHeader);
   if (tables_bytes) std::memcpy(block + kParamHeader, tables.data(), tables_bytes);
   if (items_bytes) std::memcpy(block + off_items, items.data(), items_bytes);
+  if (qitems_bytes) std::memcpy(block + off_qitems, qitems.data(), qitems_bytes);
   if (counters_bytes) std::memset(block + off_counters, 0, counters_bytes);
   if (ctx->march_boxes.reserve(block_bytes) != cudaSuccess ||
-      ctx->fold_bins.reserve(std::max<size_t>(fold_scratch_bytes(n, RW, my_begin, my_end), 256)) != cudaSuccess)
+      ctx->fold_bins.reserve(std::max<size_t>(fold_scratch_bytes(n, RW, my_begin, my_end, my_strips_arg), 256)) !=
+          cudaSuccess)
     return bail(fail(ctx, AMRVR_ERR_CUDA, "parameter block allocation failed"));
   unsigned char* dev_block = ctx->march_boxes.as<unsigned char>();
   queues.stats = reinterpret_cast<unsigned long long*>(dev_block);
+  queues.queue_items = sharded ? reinterpret_cast<const QueueItem*>(dev_block + off_qitems) : nullptr;
   if (!sharded) queues.counter[0] = reinterpret_cast<unsigned*>(dev_block + 24);
   const FoldLayer* fold_dev = reinterpret_cast<const FoldLayer*>(dev_block + off_fold);
   trace.mark("tables");
@@ -2929,13 +2974,13 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
       const int g = blend_order[pos];
       if (pos == 0 || scene->global[g].owner != prev_owner) ++run;
       prev_owner = scene->global[g].owner;
-      if (my_item[g] < 0) continue;
+      if (my_item[g] < 0 || !mine_has_rows[static_cast<size_t>(my_item[g])]) continue;
       const MarchBox& M = items[static_cast<size_t>(my_item[g])];
       FoldLayer F{};
-      F.base = pool_local + M.layer_off;
+      F.base = pool_local + my_layer_off[static_cast<size_t>(my_item[g])];
       F.x0 = M.rx0;
       F.w = M.rw;
-      F.row0 = M.ry0;
+      F.row0 = M.ry0;  // the footprint's rows; a striped layer stores this rank's strips of them
       F.row1 = M.ry0 + M.rh;
       F.run = run;
       fold.push_back(F);
@@ -2957,7 +3002,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->param_copied, ctx->aux), "event");
   if (st == AMRVR_OK)
     st = try_launch(launch_fold_bin(fold_dev, static_cast<int>(fold.size()), RW, my_begin, my_end,
-                                    ctx->fold_bins.ptr, ctx->aux, &ctx->launches),
+                                    ctx->fold_bins.ptr, ctx->aux, &ctx->launches, my_strips_arg),
                     "fold_bin");
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->bin_done, ctx->aux), "event");
   if (st == AMRVR_OK) st = try_cuda(cudaStreamWaitEvent(ctx->stream, ctx->bin_done, 0), "wait");
@@ -2987,7 +3032,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   if (st == AMRVR_OK)
     st = try_launch(launch_fold(fold_dev, static_cast<int>(fold.size()), RW, my_begin, my_end, piece_dst,
                                 ctx->fold_bins.ptr, ctx->stream, &ctx->launches,
-                                fb.rgb8 != nullptr ? &fb : nullptr, sharded ? &sync : nullptr),
+                                fb.rgb8 != nullptr ? &fb : nullptr, sharded ? &sync : nullptr, my_strips_arg),
                     "fold");
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[3], ctx->stream), "event");
   if (st == AMRVR_OK && sharded)
@@ -3005,12 +3050,27 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
                              (!sharded && !single_bytes);
     if (sharded && need_floats) {
       // the root pulls the float pieces over NVLink (ImageColorOnly::Gather)
-      for (int p = 0; p < P; ++p)
-        if (pend[p] > pbegin[p])
-          if (cudaMemcpyAsync(ctx->full.as<float>() + static_cast<size_t>(pbegin[p]) * 5,
-                              ctx->sym_piece.peer[p], static_cast<size_t>(pend[p] - pbegin[p]) * 20,
+      // rank p's piece holds its strips p, p + P, ... one after the other: one pitched copy per
+      // rank puts them where they belong, then the last (partial) strip of the frame by itself
+      const size_t strip_bytes = static_cast<size_t>(16) * RW * 20;
+      for (int p = 0; p < P; ++p) {
+        const int mine_p = (strips_total > p) ? (strips_total - 1 - p) / P + 1 : 0;
+        if (mine_p <= 0) continue;
+        const int last_k = p + (mine_p - 1) * P;  // the rank's last strip may be cut by the frame's end
+        const int full_strips = (16 * last_k + 16 <= RH) ? mine_p : mine_p - 1;
+        char* dst = reinterpret_cast<char*>(ctx->full.as<float>()) + static_cast<size_t>(p) * strip_bytes;
+        const char* src = static_cast<const char*>(ctx->sym_piece.peer[p]);
+        if (full_strips > 0 &&
+            cudaMemcpy2DAsync(dst, strip_bytes * P, src, strip_bytes, strip_bytes, static_cast<size_t>(full_strips),
                               cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess)
-            return bail(fail(ctx, AMRVR_ERR_CUDA, "piece gather failed"));
+          return bail(fail(ctx, AMRVR_ERR_CUDA, "piece gather failed"));
+        if (full_strips < mine_p &&
+            cudaMemcpyAsync(dst + static_cast<size_t>(full_strips) * strip_bytes * P,
+                            src + static_cast<size_t>(full_strips) * strip_bytes,
+                            static_cast<size_t>(RH - 16 * last_k) * RW * 20, cudaMemcpyDeviceToDevice,
+                            ctx->stream) != cudaSuccess)
+          return bail(fail(ctx, AMRVR_ERR_CUDA, "piece gather failed"));
+      }
     }
     if (fb.rgb8 != nullptr && !(sharded && !bytes_mode)) {
       // the bytes are complete (the fold wrote overlay + RGB8)

@@ -141,7 +141,20 @@ struct MarchBox {
   uint64_t brick_off;  // byte offset into the brick pool
   uint64_t layer_off;  // float offset into the fragment pool of destination `dest`
   int32_t dest;        // which pool the fragments go to (MarchQueues::pool index)
-  int32_t pad;
+  int32_t ry_first;    // frame row of the item's first tile row (== ry0 unless the frame is striped)
+};
+
+// A frame striped over P GPUs (MarchFrame::strip_stride == 16 * P): GPU q folds the
+// 16-row strips k = q, q + P, ... of the frame, so march queue q holds, of every box,
+// the tiles of the strips k % P == q that its footprint rows [ry0, ry0 + rh) touch --
+// every GPU gets an even share of every footprint.  Per (queue, box) only these three
+// numbers differ; boxes[] then holds one MarchBox per box (its tile_base / layer_off /
+// dest / ry_first are filled in shared memory from queue_items[q * nboxes + box]).
+// A layer of queue q stores its strips one after the other, 16 rows each.
+struct QueueItem {
+  int32_t tile_base;   // first tile id of (queue, box); equal to the next one's when it has no tile
+  int32_t ry_first;    // first frame row of the first strip: 16 * (first k >= ry0 / 16 with k % P == q)
+  uint64_t layer_off;  // float offset into pool[q]
 };
 
 struct MarchFrame {
@@ -149,6 +162,8 @@ struct MarchFrame {
   float tan_half, aspect, inv_w, inv_h;
   int32_t width, height;
   int32_t nboxes, ntiles;
+  int32_t strip_stride;  // rows from one tile row of an item to the next: 16, or 16 * P when the frame is striped
+  int32_t pad;
 };
 
 // Peer-memory exchange (one box, NVLink/NVSwitch): pointers to the same buffer on
@@ -181,8 +196,7 @@ struct MarchQueues {
   int32_t me, nranks;              // nranks > 0: the last CTA raises flag row `signal_row` on every rank
   int32_t tile_begin[kMaxPeers + 1];
   int32_t steal_order[kMaxPeers];
-  int32_t piece_begin[kMaxPeers + 1];  // queue q marches only pixels [piece_begin[q], piece_begin[q+1]):
-                                       // a piece may start or end inside a frame row
+  const QueueItem* queue_items;    // striped frame: [nqueues][nboxes]; nullptr: boxes[] are the items of one queue
   unsigned* counter[kMaxPeers];    // next tile of queue q (relative to tile_begin[q])
   float* pool[kMaxPeers];
   unsigned* ctl[kMaxPeers];        // control block of rank r (hints, flags); [me] is the local one
@@ -227,8 +241,14 @@ int launch_brick_quantise_batch(const QuantJob* jobs_dev, int njobs, long long m
 int launch_raymarch(const MarchFrame& frame, const MarchQueues& queues, const MarchBox* boxes_dev,
                     const uint8_t* bricks, const float* tables, bool count_samples, void* stream,
                     int64_t* launches);
+// Rows a rank folds in a frame striped over `p` GPUs: the 16-row strips g, g + p, ... of a
+// frame `height` rows high (see QueueItem).  nullptr / p <= 1: the pixel range the caller gives.
+struct FoldStrips {
+  int p, g, height;
+};
 // scratch: fold_scratch_bytes() of device memory (per-band layer lists)
-size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end);
+size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end,
+                          const FoldStrips* strips = nullptr);
 // Byte epilogue of the fold: overlay edges in device memory (nullptr: no
 // overlay), frame height, RGB8 frame (top row first; may be the root's frame on
 // another GPU -- every rank writes the bytes of its own piece).
@@ -253,12 +273,14 @@ struct FoldSync {
 // depends on the frame plan only, never on pixel data, so a frame launches it
 // BEFORE the march and the march hides it.
 int launch_fold_bin(const FoldLayer* layers_dev, int nlayers, int width, int pixel_begin,
-                    int pixel_end, void* scratch, void* stream, int64_t* launches);
+                    int pixel_end, void* scratch, void* stream, int64_t* launches,
+                    const FoldStrips* strips = nullptr);
 // Pass 2: the fold proper over the lists pass 1 left in `scratch`.
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int pixel_begin, int pixel_end, float* piece5, void* scratch,
                 void* stream, int64_t* launches,
-                const FoldBytes* bytes = nullptr, const FoldSync* sync = nullptr);
+                const FoldBytes* bytes = nullptr, const FoldSync* sync = nullptr,
+                const FoldStrips* strips = nullptr);
 // Wait (on the stream) until flag row `row` of the own control block holds
 // `epoch` from every rank; raises the time-out word instead of hanging.
 int launch_peer_wait(const PeerPtrs& ctl, int me, int nranks, int row, uint32_t epoch,

@@ -602,7 +602,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
                        const float4* __restrict__ tables) {
   __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE * kTableCopies];
   __shared__ MarchBox s_box;
-  __shared__ int s_tile[2], s_which[2];
+  __shared__ int s_tile[2], s_which[2], s_queue[2];  // mailbox: tile id, its box (item), its queue
 
   // ---- thread 0 only; its bookkeeping lives in shared memory so that the march
   // loop keeps its registers.  The try order is the own queue, then steal_order[].
@@ -641,22 +641,32 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
     return tile;
   };
   auto publish = [&](int slot, int tile) {
-    int lo = 0;
+    int lo = 0, q = 0;
     if (tile >= 0) {  // last item whose first tile is <= tile
       int hi = f.nboxes - 1;
-      while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (__ldg(&boxes[mid].tile_base) <= tile) lo = mid; else hi = mid - 1;
+      if (Q.queue_items != nullptr) {  // striped frame: the items of the queue the tile came from
+        q = queue_at(s_cur);
+        const QueueItem* items = Q.queue_items + static_cast<size_t>(q) * f.nboxes;
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (__ldg(&items[mid].tile_base) <= tile) lo = mid; else hi = mid - 1;
+        }
+      } else {
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (__ldg(&boxes[mid].tile_base) <= tile) lo = mid; else hi = mid - 1;
+        }
       }
       if (s_cur > 0) ++s_stolen;
     }
     s_tile[slot] = tile;
     s_which[slot] = lo;
+    s_queue[slot] = q;
   };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned table_addr = smem_u32(s_table) + static_cast<unsigned>(lane % kTableCopies) * 16u;
-  int have_box = -1, have_table = -1;
+  int have_box = -1, have_queue = -1, have_table = -1;
   unsigned nsamples = 0;
   // thread 0 keeps the launch's time line (Q.stats[4..7]): CTA busy time, first start, last end, table staging
   __shared__ unsigned long long s_t0, s_table_ns, s_stage_t;  // in shared memory: the march loop keeps its registers
@@ -669,12 +679,28 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
   }
   for (int it = 0;; ++it) {
     __syncthreads();  // mailbox slot it&1 is written; everyone is done with the previous tile
-    const int tile = s_tile[it & 1], which = s_which[it & 1];
+    const int tile = s_tile[it & 1], which = s_which[it & 1], queue = s_queue[it & 1];
     if (tile < 0) break;
-    if (which != have_box) {  // uniform across the CTA
-      const int words = sizeof(MarchBox) / 4;
+    if (which != have_box || queue != have_queue) {  // uniform across the CTA
+      static_assert(sizeof(MarchBox) == 128 && offsetof(MarchBox, layer_off) == 112,
+                    "words 28..31 (layer_off, dest, ry_first) and tile_base are the item's");
+      constexpr int kTileBaseWord = offsetof(MarchBox, tile_base) / 4;
       const int* src = reinterpret_cast<const int*>(boxes + which);
-      if (threadIdx.x < words) reinterpret_cast<int*>(&s_box)[threadIdx.x] = __ldg(src + threadIdx.x);
+      if (Q.queue_items == nullptr) {
+        if (threadIdx.x < 32) reinterpret_cast<int*>(&s_box)[threadIdx.x] = __ldg(src + threadIdx.x);
+      } else {
+        // striped frame: the box, then what (queue, box) adds to it
+        if (threadIdx.x < 28 && threadIdx.x != kTileBaseWord)
+          reinterpret_cast<int*>(&s_box)[threadIdx.x] = __ldg(src + threadIdx.x);
+        if (threadIdx.x == 32) {
+          const QueueItem* item = Q.queue_items + static_cast<size_t>(queue) * f.nboxes + which;
+          s_box.tile_base = __ldg(&item->tile_base);
+          s_box.ry_first = __ldg(&item->ry_first);
+          s_box.layer_off = __ldg(&item->layer_off);
+          s_box.dest = queue;
+        }
+      }
+      have_queue = queue;
       const int table = __ldg(&boxes[which].table);
       const bool restage = table != have_table;
       if (restage) {
@@ -698,22 +724,24 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
       if (cur < Q.nqueues) pend_t = atomicAdd(Q.counter[queue_at(cur)], 1u);
     }
 
+    // tile row ty of an item starts at frame row ry_first + ty * strip_stride (the next strip
+    // of the same GPU when the frame is striped) and is row 16 * ty of the stored layer
     const int local_tile = tile - s_box.tile_base;
     const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
     const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
-    const int y = ty * kTile + (warp >> 1) * 4 + (lane >> 3);
+    const int y_in = (warp >> 1) * 4 + (lane >> 3);
+    const int y = ty * kTile + y_in;                                    // row of the layer
+    const int frame_y = s_box.ry_first + ty * f.strip_stride + y_in;    // row of the frame
     const int rw = s_box.rw;
-    // footprints are padded to 4-pixel column multiples: columns past the frame are not rays
-    // and the row a piece boundary cuts belongs to two queues: each marches its own pixels
-    const int pixel = (s_box.ry0 + y) * f.width + s_box.rx0 + x;
-    const bool valid = x < rw && y < s_box.rh && s_box.rx0 + x < f.width &&
-                       pixel >= Q.piece_begin[s_box.dest] && pixel < Q.piece_begin[s_box.dest + 1];
+    // footprints are padded to 4-pixel column multiples: columns past the frame are not rays;
+    // a strip may begin above the footprint or end below it
+    const bool valid = x < rw && s_box.rx0 + x < f.width && frame_y >= s_box.ry0 &&
+                       frame_y < s_box.ry0 + s_box.rh;
 
     const RayOut r = s_box.exact_recip
-                         ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x,
-                                                   s_box.ry0 + y, valid)
-                         : march_ray<kCount, false>(f, s_box, bricks, table_addr, s_box.rx0 + x,
-                                                    s_box.ry0 + y, valid);
+                         ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x, frame_y, valid)
+                         : march_ray<kCount, false>(f, s_box, bricks, table_addr, s_box.rx0 + x, frame_y,
+                                                    valid);
 
     // host epilogue of the reference (:939-955)
     float4 out = make_float4(clamp01(r.r), clamp01(r.g), clamp01(r.b), clamp01(r.a));
@@ -729,7 +757,8 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
     if (threadIdx.x == 0) {
       if (Q.nranks > 0 && s_box.dest != Q.me) {
         const int w = min(min(kTile, rw - tx * kTile), f.width - s_box.rx0 - tx * kTile);
-        const int h = min(kTile, s_box.rh - ty * kTile);
+        const int top = s_box.ry_first + ty * f.strip_stride;
+        const int h = min(top + kTile, s_box.ry0 + s_box.rh) - max(top, s_box.ry0);
         if (w > 0 && h > 0) s_pushed += 20ull * static_cast<unsigned>(w * h);
       }
       int next = -1;
@@ -907,11 +936,18 @@ __device__ __forceinline__ Px5 fold_load(const FoldEntry& E, int r, int cx) {
   return Px5{c.x, c.y, c.z, c.w, __ldcg(rowp + 4 * E.w + cx)};
 }
 
+// First frame row of band `band` of the rows a rank folds.  Contiguous rows (strip_p == 1):
+// first_row + 8 * band.  Striped frame (strip_p = P GPUs, first_row = 16 * rank): the rank's
+// strips are 16 rows every 16 * P rows, two bands each.
+__device__ __forceinline__ int fold_band_row(int first_row, int strip_p, int band) {
+  return first_row + (band >> 1) * 2 * kFoldBandRows * strip_p + (band & 1) * kFoldBandRows;
+}
+
 // Pass 1: one CTA per band of 8 frame rows filters the globally ordered layer
 // table down to the layers whose rows touch the band (ordered compaction, so
 // the list keeps the blend order).  band_lists[band * nlayers + i], band_counts[band].
 __global__ void __launch_bounds__(kBinThreads)
-fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row,
+fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row, int strip_p,
                 int* __restrict__ band_lists, int* __restrict__ band_counts,
                 int2* __restrict__ band_xspan) {
   __shared__ int s_warp_count[kBinThreads / 32];
@@ -923,7 +959,7 @@ fold_bin_kernel(const FoldLayer* __restrict__ layers, int nlayers, int first_row
   __syncthreads();
   int xmin = INT_MAX, xmax = INT_MIN;  // union of the x ranges of the band's layers
   const int band = blockIdx.x;
-  const int y0 = first_row + band * kFoldBandRows, y1 = y0 + kFoldBandRows;  // [y0, y1)
+  const int y0 = fold_band_row(first_row, strip_p, band), y1 = y0 + kFoldBandRows;  // [y0, y1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int* list = band_lists + static_cast<size_t>(band) * nlayers;
   int written = 0;
@@ -974,6 +1010,7 @@ struct FoldArgs {
   const int* band_counts;
   const int2* band_xspan;
   int first_row, bands, width, height;
+  int strip_p, strip_g;  // striped frame: GPUs and this rank (layers then hold the rank's strips, 16 rows each); else 1, 0
   int pixel_begin, pixel_end;
   float* piece5;
   const OverlayEdges* edges;
@@ -1035,7 +1072,7 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
   for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int band = tile / tiles_x;
     const int tile_x0 = (tile - band * tiles_x) * kFoldTileW;
-    const int y0 = A.first_row + band * kFoldBandRows + 2 * warp, y1 = y0 + 1;
+    const int y0 = fold_band_row(A.first_row, A.strip_p, band) + 2 * warp, y1 = y0 + 1;
     const int px = tile_x0 + lane;
     const long long p0 = static_cast<long long>(y0) * A.width + px;
     const long long p1 = p0 + A.width;
@@ -1064,7 +1101,13 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
       const unsigned ballot = __ballot_sync(0xffffffffu, keep);
       if (keep) {
         FoldEntry E;
-        E.row = L.base + (static_cast<long long>(y0) - L.row0) * L.w * 5;
+        long long layer_row = static_cast<long long>(y0) - L.row0;
+        if (A.strip_p > 1) {  // the layer stores this rank's strips one after the other, 16 rows each
+          const int k0 = L.row0 >> 4;
+          const int kf = k0 + (((A.strip_g - k0) % A.strip_p) + A.strip_p) % A.strip_p;
+          layer_row = static_cast<long long>(((y0 >> 4) - kf) / A.strip_p) * 16 + (y0 & 15);
+        }
+        E.row = L.base + layer_row * L.w * 5;
         E.x0 = L.x0;
         E.w = L.w;
         E.rows = ((y0 >= L.row0 && y0 < L.row1) ? 1 : 0) | ((y1 >= L.row0 && y1 < L.row1) ? 2 : 0) |
@@ -1202,6 +1245,10 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
                                      static_cast<long long>(kFoldTileW));
         const float* src = s_out + 160 * r;
         float* dst = A.piece5 + (row_first - A.pixel_begin) * 5;
+        if (A.strip_p > 1) {  // the piece holds this rank's strips one after the other
+          const long long local_row = static_cast<long long>(band >> 1) * 16 + (band & 1) * kFoldBandRows + 2 * warp + r;
+          dst = A.piece5 + (local_row * A.width + tile_x0) * 5;
+        }
 #pragma unroll
         for (int j = 0; j < 5; ++j) {
           const int fl = lane + 32 * j;  // float within the row segment
@@ -1788,11 +1835,27 @@ int launch_raymarch(const MarchFrame& frame, const MarchQueues& queues, const Ma
   return static_cast<int>(cudaGetLastError());
 }
 
-size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end) {
-  if (pixel_end <= pixel_begin || width <= 0) return 0;
-  const int first_row = pixel_begin / width, last_row = (pixel_end - 1) / width;
-  const size_t bands = static_cast<size_t>((last_row - first_row) / kFoldBandRows + 1);
-  return bands * (static_cast<size_t>(std::max(nlayers, 1)) + 3) * sizeof(int);
+namespace {
+// first row and number of 8-row bands of the rows a rank folds
+void fold_rows(int width, int pixel_begin, int pixel_end, const FoldStrips* strips, int* first_row,
+               int* bands) {
+  if (strips != nullptr && strips->p > 1) {
+    const int total = (strips->height + 15) / 16;
+    const int mine = (total > strips->g) ? (total - 1 - strips->g) / strips->p + 1 : 0;
+    *first_row = 16 * strips->g;
+    *bands = 2 * mine;
+    return;
+  }
+  *first_row = pixel_begin / width;
+  *bands = (pixel_end > pixel_begin) ? ((pixel_end - 1) / width - *first_row) / kFoldBandRows + 1 : 0;
+}
+}  // namespace
+
+size_t fold_scratch_bytes(int nlayers, int width, int pixel_begin, int pixel_end, const FoldStrips* strips) {
+  if (width <= 0) return 0;
+  int first_row = 0, bands = 0;
+  fold_rows(width, pixel_begin, pixel_end, strips, &first_row, &bands);
+  return static_cast<size_t>(bands) * (static_cast<size_t>(std::max(nlayers, 1)) + 3) * sizeof(int);
 }
 
 namespace {
@@ -1802,11 +1865,10 @@ struct FoldScratch {
   int* band_counts;
   int* band_lists;
 };
-FoldScratch fold_scratch_layout(void* scratch, int width, int pixel_begin, int pixel_end) {
+FoldScratch fold_scratch_layout(void* scratch, int width, int pixel_begin, int pixel_end,
+                                const FoldStrips* strips) {
   FoldScratch L;
-  L.first_row = pixel_begin / width;
-  const int last_row = (pixel_end - 1) / width;
-  L.bands = (last_row - L.first_row) / kFoldBandRows + 1;
+  fold_rows(width, pixel_begin, pixel_end, strips, &L.first_row, &L.bands);
   L.band_xspan = static_cast<int2*>(scratch);
   L.band_counts = reinterpret_cast<int*>(L.band_xspan + L.bands);
   L.band_lists = L.band_counts + L.bands;
@@ -1830,19 +1892,28 @@ int fold_grid_size(bool bytes) {
 }  // namespace
 
 int launch_fold_bin(const FoldLayer* layers_dev, int nlayers, int width, int pixel_begin,
-                    int pixel_end, void* scratch, void* stream, int64_t* launches) {
-  if (pixel_end <= pixel_begin) return 0;
-  const FoldScratch L = fold_scratch_layout(scratch, width, pixel_begin, pixel_end);
+                    int pixel_end, void* scratch, void* stream, int64_t* launches,
+                    const FoldStrips* strips) {
+  const bool striped = strips != nullptr && strips->p > 1;
+  if (!striped && pixel_end <= pixel_begin) return 0;
+  const FoldScratch L = fold_scratch_layout(scratch, width, pixel_begin, pixel_end, strips);
+  if (L.bands <= 0) return 0;
   fold_bin_kernel<<<L.bands, kBinThreads, 0, as_stream(stream)>>>(layers_dev, nlayers, L.first_row,
-                                                                  L.band_lists, L.band_counts,
-                                                                  L.band_xspan);
+                                                                  striped ? strips->p : 1, L.band_lists,
+                                                                  L.band_counts, L.band_xspan);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }
 
 int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
                 int pixel_begin, int pixel_end, float* piece5, void* scratch, void* stream,
-                int64_t* launches, const FoldBytes* bytes, const FoldSync* sync) {
+                int64_t* launches, const FoldBytes* bytes, const FoldSync* sync,
+                const FoldStrips* strips) {
+  const bool striped = strips != nullptr && strips->p > 1;
+  if (striped) {  // whole rows; rows past the frame are masked by the pixel range
+    pixel_begin = 0;
+    pixel_end = width * strips->height;
+  }
   const int npix = pixel_end - pixel_begin;
   const bool sharded = sync != nullptr && sync->nranks > 0;
   if (npix <= 0 && !sharded) return 0;
@@ -1852,8 +1923,10 @@ int launch_fold(const FoldLayer* layers_dev, int nlayers, int width,
   A.width = width;
   A.pixel_begin = pixel_begin;
   A.pixel_end = pixel_end;
+  A.strip_p = striped ? strips->p : 1;
+  A.strip_g = striped ? strips->g : 0;
   if (npix > 0) {
-    const FoldScratch L = fold_scratch_layout(scratch, width, pixel_begin, pixel_end);
+    const FoldScratch L = fold_scratch_layout(scratch, width, pixel_begin, pixel_end, strips);
     A.first_row = L.first_row;
     A.bands = L.bands;
     A.band_xspan = L.band_xspan;
