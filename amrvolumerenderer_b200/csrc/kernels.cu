@@ -576,6 +576,9 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
 #ifndef AMRVR_MARCH_MIN_BLOCKS
 #define AMRVR_MARCH_MIN_BLOCKS 4
 #endif
+#ifndef AMRVR_MARCH_FIRST_PUBLISHES
+#define AMRVR_MARCH_FIRST_PUBLISHES 1  // 1: the first warp through with a tile claims and looks up the next one
+#endif
 #ifndef AMRVR_MARCH_TIMELINE
 #define AMRVR_MARCH_TIMELINE 1  // thread 0 of every CTA times itself on %globaltimer (amrvr_frame_stats::march_*_ns)
 #endif
@@ -603,6 +606,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
   __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE * kTableCopies];
   __shared__ MarchBox s_box;
   __shared__ int s_tile[2], s_which[2], s_queue[2];  // mailbox: tile id, its box (item), its queue
+  __shared__ int s_taken[2];  // mailbox slot: a warp has taken on filling it (AMRVR_MARCH_FIRST_PUBLISHES)
 
   // ---- thread 0 only; its bookkeeping lives in shared memory so that the march
   // loop keeps its registers.  The try order is the own queue, then steal_order[].
@@ -675,6 +679,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
     s_table_ns = 0;
     s_cur = 0;
     s_pushed = s_stolen = 0;
+    s_taken[0] = s_taken[1] = 0;
     publish(0, claim_blocking());
   }
   for (int it = 0;; ++it) {
@@ -715,6 +720,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
       __syncthreads();
       if (AMRVR_MARCH_TIMELINE && restage && threadIdx.x == 0) s_table_ns += global_timer_ns() - s_stage_t;
     }
+#if !AMRVR_MARCH_FIRST_PUBLISHES
     // the claim of the next tile: issued here, read after this thread's ray
     unsigned pend_t = 0;
     if (threadIdx.x == 0) {
@@ -723,6 +729,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
       s_cur = cur;
       if (cur < Q.nqueues) pend_t = atomicAdd(Q.counter[queue_at(cur)], 1u);
     }
+#endif
 
     // tile row ty of an item starts at frame row ry_first + ty * strip_stride (the next strip
     // of the same GPU when the frame is striped) and is row 16 * ty of the stored layer
@@ -754,6 +761,23 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
     }
     if (kCount) nsamples += r.nsamples;
 
+#if AMRVR_MARCH_FIRST_PUBLISHES
+    // The FIRST warp through with its patch claims the next tile and looks its item up (an
+    // atomic, possibly on another GPU, and a binary search: several dependent round trips)
+    // while the other warps are still marching; with thread 0 doing it after its own ray,
+    // every tile whose slowest patch was warp 0's paid for it in full.
+    if (lane == 0 && atomicExch(&s_taken[(it + 1) & 1], 1) == 0) {
+      if (Q.nranks > 0 && s_box.dest != Q.me) {
+        const int w = min(min(kTile, rw - tx * kTile), f.width - s_box.rx0 - tx * kTile);
+        const int top = s_box.ry_first + ty * f.strip_stride;
+        const int h = min(top + kTile, s_box.ry0 + s_box.rh) - max(top, s_box.ry0);
+        if (w > 0 && h > 0) s_pushed += 20ull * static_cast<unsigned>(w * h);
+      }
+      publish((it + 1) & 1, claim_blocking());
+      s_taken[it & 1] = 0;  // free for iteration it + 2; nobody looks at it before the next barrier
+    }
+  }
+#else
     if (threadIdx.x == 0) {
       if (Q.nranks > 0 && s_box.dest != Q.me) {
         const int w = min(min(kTile, rw - tx * kTile), f.width - s_box.rx0 - tx * kTile);
@@ -774,6 +798,7 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
       publish((it + 1) & 1, next);
     }
   }
+#endif
   if (kCount) {
     for (int off = 16; off > 0; off >>= 1) nsamples += __shfl_down_sync(0xffffffffu, nsamples, off);
     if (lane == 0 && nsamples != 0)
