@@ -631,7 +631,12 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
                 std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
                     std::to_string(prop.minor) + "; this library carries sm_100a code only");
   CUDA_TRY(nullptr, cudaSetDevice(cuda_device));
-  std::unique_ptr<amrvr_ctx> ctx(new amrvr_ctx);
+  // every early return below releases what has been created so far (streams, events, the
+  // NCCL communicator, peer mappings): amrvr_ctx_destroy copes with a half-built context
+  struct Destroy {
+    void operator()(amrvr_ctx* c) const { amrvr_ctx_destroy(c); }
+  };
+  std::unique_ptr<amrvr_ctx, Destroy> ctx(new amrvr_ctx);
   ctx->device = cuda_device;
   ctx->rank = rank;
   ctx->nranks = nranks;
@@ -673,7 +678,7 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
 extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   if (ctx == nullptr) return;
   cudaSetDevice(ctx->device);
-  cudaStreamSynchronize(ctx->stream);
+  if (ctx->stream != nullptr) cudaStreamSynchronize(ctx->stream);
   for (SymBuffer* b : {&ctx->sym_flags, &ctx->sym_pool, &ctx->sym_piece, &ctx->sym_rgb8})
     sym_release(*b, ctx->rank);
   if (ctx->peer_error_host != nullptr) cudaFreeHost(ctx->peer_error_host);
@@ -695,10 +700,8 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (auto& e : ctx->ev)
     if (e != nullptr) cudaEventDestroy(e);
   for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
-  cudaStreamDestroy(ctx->stream);
-  cudaStreamDestroy(ctx->aux);
-  if (ctx->quant != nullptr) cudaStreamDestroy(ctx->quant);
-  cudaStreamDestroy(ctx->copy);
+  for (cudaStream_t st : {ctx->stream, ctx->aux, ctx->quant, ctx->copy})
+    if (st != nullptr) cudaStreamDestroy(st);
   for (auto& e : ctx->copy_ev)
     if (e != nullptr) cudaEventDestroy(e);
   if (ctx->copy_start != nullptr) cudaEventDestroy(ctx->copy_start);
@@ -2667,7 +2670,13 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   if (ctx->frame_stats_host == nullptr)
     CUDA_TRY(ctx, cudaMallocHost(reinterpret_cast<void**>(&ctx->frame_stats_host), 128));
 
-  OrderJob order;  // started right after the march is enqueued (waking the helper thread costs microseconds)
+  // The visibility ordering runs beside the march on the helper thread.  Small tables: it is
+  // started right after the march is enqueued (waking the thread costs microseconds of the
+  // frame's head).  Tables that go to the device back end take about as long as the march
+  // itself (C5: 4096 boxes), so they start first.
+  OrderJob order;
+  const bool order_first = n >= ctx->order_device_min;
+  if (order_first) start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
   // every return path joins the helper thread
   auto bail = [&](int status) {
     if (order.on_thread) ctx->worker.wait();
@@ -2959,8 +2968,7 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   }
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[2], ctx->stream), "event");
   trace.mark("march_enqueue");
-  // the visibility ordering (BuildVisibilityOrderedGroup) runs beside the march on the helper thread
-  start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
+  if (!order_first) start_order(ctx, scene, camera, G.aspect, params->use_visibility_graph != 0, &order);
 
   // ---- fold table of my piece, in the reference's blend order with its run ids
   // (DirectSendBase.cpp:363-407); built while the march runs

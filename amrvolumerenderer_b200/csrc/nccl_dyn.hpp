@@ -49,6 +49,7 @@ struct NcclApi {
                     bind(GroupStart, "ncclGroupStart") && bind(GroupEnd, "ncclGroupEnd") &&
                     bind(GetErrorString, "ncclGetErrorString");
     if (!ok) {
+      dlclose(handle);
       handle = nullptr;
       return "NCCL library lacks a required symbol";
     }
