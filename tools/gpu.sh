@@ -7,7 +7,7 @@
 #   gpurun --timeout 600 -- 'bash tools/gpu.sh c5one'            # C5 sweep at one GPU
 #   gpurun --gpus 2 --timeout 420 -- 'bash tools/gpu.sh two'     # multi-rank parity + C4/C5 lines
 #   gpurun --gpus 4 --timeout 300 -- 'bash tools/gpu.sh four'
-#   gpurun --gpus 8 --timeout 300 -- 'bash tools/gpu.sh eight'
+#   gpurun --gpus 8 --timeout 300 -- 'bash tools/gpu.sh eight'   # (eighttests: the 8-rank parity cases)
 # TAG (env) prefixes the output files under gpurun_out/ (default r2).
 mkdir -p gpurun_out
 TAG=${TAG:-r2}
@@ -43,7 +43,9 @@ case "$1" in
 one)
   timeout 900 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_pytest_gpu_1.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/${TAG}_pytest_gpu_1.log
   bench 1 C4 C4_n1
-  line C4_n1
+  bench 1 C3 C3_n1 --no-cpu-baseline --steps 10
+  bench 1 C2 C2_n1 --no-cpu-baseline --steps 10
+  line C4_n1 C3_n1 C2_n1
   ;;
 launches)
   bench 1 C4 C4_n1 --steps 2 --warmup 3
@@ -82,6 +84,9 @@ four)
 eightc4)
   bench 8 C4 C4_n8 --no-cpu-baseline
   line C4_n8
+  ;;
+eighttests)
+  timeout 500 python -m pytest tests/test_multi_gpu.py -m gpu -q -k "eight_ranks" > gpurun_out/${TAG}_pytest_gpu_8.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/${TAG}_pytest_gpu_8.log
   ;;
 eight)
   bench 8 C4 C4_n8
