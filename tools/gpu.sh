@@ -81,6 +81,14 @@ four)
   for w in C5-4 C5-8 C5-16; do bench 4 $w ${w}_n4 --steps 10 --no-cpu-baseline; done
   line C4_n4 C5-4_n4 C5-8_n4 C5-16_n4
   ;;
+twoc4)
+  bench 2 C4 C4_n2 --no-cpu-baseline
+  line C4_n2
+  ;;
+fourc4)
+  bench 4 C4 C4_n4 --no-cpu-baseline
+  line C4_n4
+  ;;
 eightc4)
   bench 8 C4 C4_n8 --no-cpu-baseline
   line C4_n8
