@@ -1228,6 +1228,37 @@ int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
 }
 }  // namespace
 
+extern "C" int amrvr_stripe_plan_host(int nranks, int nboxes, const int32_t* rects, int32_t* tile_base,
+                                      int32_t* ry_first, uint64_t* layer_off, int32_t* queue_tile_begin,
+                                      uint64_t* pool_floats) {
+  if (nranks < 1 || nranks > kMaxPeers || nboxes < 0 || (nboxes > 0 && rects == nullptr) ||
+      tile_base == nullptr || ry_first == nullptr || layer_off == nullptr || queue_tile_begin == nullptr ||
+      pool_floats == nullptr)
+    return fail(nullptr, AMRVR_ERR_INVALID, "bad argument");
+  std::vector<int32_t> ry0(static_cast<size_t>(nboxes)), rh(static_cast<size_t>(nboxes)), rw(static_cast<size_t>(nboxes));
+  for (int b = 0; b < nboxes; ++b) {
+    ry0[static_cast<size_t>(b)] = rects[4 * b + 1];
+    rw[static_cast<size_t>(b)] = rects[4 * b + 2];
+    rh[static_cast<size_t>(b)] = rects[4 * b + 3];
+    if (rw[static_cast<size_t>(b)] <= 0 || rh[static_cast<size_t>(b)] <= 0 || ry0[static_cast<size_t>(b)] < 0)
+      return fail(nullptr, AMRVR_ERR_INVALID, "empty footprint or negative row");
+  }
+  std::vector<QueueItem> items(static_cast<size_t>(nranks) * std::max(nboxes, 1));
+  stripe_plan(nranks, nboxes, ry0.data(), rh.data(), rw.data(), items.data(), queue_tile_begin, pool_floats);
+  for (size_t i = 0; i < static_cast<size_t>(nranks) * nboxes; ++i) {
+    tile_base[i] = items[i].tile_base;
+    ry_first[i] = items[i].ry_first;
+    layer_off[i] = items[i].layer_off;
+  }
+  return AMRVR_OK;
+}
+
+extern "C" int64_t amrvr_stripe_layer_row_host(int nranks, int rank, int row0, int y) {
+  if (nranks < 1 || rank < 0 || rank >= nranks) return -1;
+  if (((y >> 4) % nranks) != rank || (y >> 4) < stripe_first_strip(nranks, rank, row0)) return -1;
+  return stripe_layer_row(nranks, rank, row0, y);
+}
+
 extern "C" int amrvr_scene_is_replicated(const amrvr_scene* scene) {
   return (scene != nullptr && scene->replicated) ? 1 : 0;
 }
@@ -2791,37 +2822,36 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   std::vector<uint64_t> pool_floats(static_cast<size_t>(P), 0);
   int tiles = 0;
   int64_t my_rays = 0;
-  for (int q = 0; q < P; ++q) {
-    queues.tile_begin[q] = tiles;
+  if (!sharded) {
+    queues.tile_begin[0] = 0;
     for (int i = 0; i < nb; ++i) {
       MarchBox& M = items[static_cast<size_t>(i)];
-      if (!sharded) {
-        M.tile_base = tiles;
-        tiles += M.tiles_x * ((M.rh + 15) / 16);
-        if (grouped) group_tile_begin[static_cast<size_t>(scene->box_group[by_item_box(i)]) + 1] = tiles;
-        M.layer_off = pool_floats[0];
-        pool_floats[0] += static_cast<uint64_t>(M.rw) * M.rh * 5;
-        my_layer_off[static_cast<size_t>(i)] = M.layer_off;
-        mine_has_rows[static_cast<size_t>(i)] = 1;
-        my_rays += static_cast<int64_t>(M.rw) * M.rh;
-        continue;
-      }
-      const int y0 = M.ry0, y1 = M.ry0 + M.rh;  // footprint rows [y0, y1)
-      const int k0 = y0 >> 4, k1 = (y1 - 1) >> 4;
-      const int kf = k0 + (((q - k0) % P) + P) % P;  // first strip of GPU q that touches the footprint
-      const int ns = (kf > k1) ? 0 : (k1 - kf) / P + 1;
-      QueueItem& QI = qitems[static_cast<size_t>(q) * nb + i];
-      QI.tile_base = tiles;
-      QI.ry_first = kf * 16;
-      QI.layer_off = pool_floats[q];
-      tiles += ns * M.tiles_x;
-      pool_floats[q] += static_cast<uint64_t>(ns) * 16 * M.rw * 5;  // whole strips, 16 rows each
-      if (q == me) {
-        my_layer_off[static_cast<size_t>(i)] = QI.layer_off;
-        mine_has_rows[static_cast<size_t>(i)] = ns > 0;
-        for (int k = kf; k <= k1; k += P)
-          my_rays += static_cast<int64_t>(M.rw) * (std::min(16 * k + 16, y1) - std::max(16 * k, y0));
-      }
+      M.tile_base = tiles;
+      tiles += M.tiles_x * ((M.rh + 15) / 16);
+      if (grouped) group_tile_begin[static_cast<size_t>(scene->box_group[by_item_box(i)]) + 1] = tiles;
+      M.layer_off = pool_floats[0];
+      pool_floats[0] += static_cast<uint64_t>(M.rw) * M.rh * 5;
+      my_layer_off[static_cast<size_t>(i)] = M.layer_off;
+      mine_has_rows[static_cast<size_t>(i)] = 1;
+      my_rays += static_cast<int64_t>(M.rw) * M.rh;
+    }
+  } else {
+    std::vector<int32_t> ry0(static_cast<size_t>(nb)), rh(static_cast<size_t>(nb)), rw(static_cast<size_t>(nb));
+    for (int i = 0; i < nb; ++i) {
+      ry0[static_cast<size_t>(i)] = items[static_cast<size_t>(i)].ry0;
+      rh[static_cast<size_t>(i)] = items[static_cast<size_t>(i)].rh;
+      rw[static_cast<size_t>(i)] = items[static_cast<size_t>(i)].rw;
+    }
+    stripe_plan(P, nb, ry0.data(), rh.data(), rw.data(), qitems.data(), queues.tile_begin, pool_floats.data());
+    tiles = queues.tile_begin[P];
+    for (int i = 0; i < nb; ++i) {  // what this rank folds of every box
+      const MarchBox& M = items[static_cast<size_t>(i)];
+      const int y0 = M.ry0, y1 = M.ry0 + M.rh;
+      const int ns = stripe_count(P, me, y0, y1);
+      my_layer_off[static_cast<size_t>(i)] = qitems[static_cast<size_t>(me) * nb + i].layer_off;
+      mine_has_rows[static_cast<size_t>(i)] = ns > 0;
+      for (int k = stripe_first_strip(P, me, y0), j = 0; j < ns; ++j, k += P)
+        my_rays += static_cast<int64_t>(M.rw) * (std::min(16 * k + 16, y1) - std::max(16 * k, y0));
     }
   }
   queues.tile_begin[P] = tiles;

@@ -392,6 +392,25 @@ void layer_order(int nglobal, const amrvr_box_record* recs, const amrvr_camera& 
   });
 }
 
+void stripe_plan(int p, int nboxes, const int32_t* ry0, const int32_t* rh, const int32_t* rw,
+                 QueueItem* qitems, int32_t* tile_begin, uint64_t* pool_floats) {
+  int tiles = 0;
+  for (int q = 0; q < p; ++q) {
+    tile_begin[q] = tiles;
+    pool_floats[q] = 0;
+    for (int b = 0; b < nboxes; ++b) {
+      const int ns = stripe_count(p, q, ry0[b], ry0[b] + rh[b]);
+      QueueItem& item = qitems[static_cast<size_t>(q) * nboxes + b];
+      item.tile_base = tiles;
+      item.ry_first = 16 * stripe_first_strip(p, q, ry0[b]);
+      item.layer_off = pool_floats[q];
+      tiles += ns * ((rw[b] + 15) / 16);
+      pool_floats[q] += static_cast<uint64_t>(ns) * 16 * rw[b] * 5;  // whole strips, 16 rows each
+    }
+  }
+  tile_begin[p] = tiles;
+}
+
 void piece_range(int num_pixels, int piece, int num_pieces, int* begin, int* end) {
   const int each = num_pixels / num_pieces;
   *begin = each * piece;

@@ -157,6 +157,37 @@ struct QueueItem {
   uint64_t layer_off;  // float offset into pool[q]
 };
 
+#if defined(__CUDACC__)
+#define AMRVR_HD __host__ __device__
+#else
+#define AMRVR_HD
+#endif
+
+// ---- striped frame arithmetic, shared by the host plan, the fold kernel and the CPU tests.
+// Frame rows come in 16-row strips; strip k is folded by GPU k % P.
+// First strip >= the one holding `row0` that GPU g folds.
+AMRVR_HD inline int stripe_first_strip(int p, int g, int row0) {
+  const int k0 = row0 >> 4;
+  return k0 + (((g - k0) % p) + p) % p;
+}
+// Number of strips of GPU g that touch rows [row0, row1).
+AMRVR_HD inline int stripe_count(int p, int g, int row0, int row1) {
+  if (row1 <= row0) return 0;
+  const int kf = stripe_first_strip(p, g, row0), k1 = (row1 - 1) >> 4;
+  return (kf > k1) ? 0 : (k1 - kf) / p + 1;
+}
+// Row of GPU g's layer (its strips of a footprint starting at row0, one after the other,
+// 16 rows each) that holds frame row y; y must lie in one of g's strips.
+AMRVR_HD inline long long stripe_layer_row(int p, int g, int row0, int y) {
+  return static_cast<long long>(((y >> 4) - stripe_first_strip(p, g, row0)) / p) * 16 + (y & 15);
+}
+// Plan of a striped frame: for every (queue q, box b) the first tile id, the first frame
+// row of the queue's first strip of the box and the float offset of the box's strips in
+// pool q; tile_begin[q] / pool_floats[q] per queue.  Boxes: footprint rows [ry0, ry0 + rh),
+// padded width rw.  qitems: [p * nboxes].
+void stripe_plan(int p, int nboxes, const int32_t* ry0, const int32_t* rh, const int32_t* rw,
+                 QueueItem* qitems, int32_t* tile_begin /*[p + 1]*/, uint64_t* pool_floats /*[p]*/);
+
 struct MarchFrame {
   float eye[3], fwd[3], right[3], up[3];
   float tan_half, aspect, inv_w, inv_h;

@@ -1127,11 +1127,8 @@ fold_layers_kernel(const __grid_constant__ FoldArgs A) {
       if (keep) {
         FoldEntry E;
         long long layer_row = static_cast<long long>(y0) - L.row0;
-        if (A.strip_p > 1) {  // the layer stores this rank's strips one after the other, 16 rows each
-          const int k0 = L.row0 >> 4;
-          const int kf = k0 + (((A.strip_g - k0) % A.strip_p) + A.strip_p) % A.strip_p;
-          layer_row = static_cast<long long>(((y0 >> 4) - kf) / A.strip_p) * 16 + (y0 & 15);
-        }
+        // striped: the layer stores this rank's strips one after the other, 16 rows each
+        if (A.strip_p > 1) layer_row = stripe_layer_row(A.strip_p, A.strip_g, L.row0, y0);
         E.row = L.base + layer_row * L.w * 5;
         E.x0 = L.x0;
         E.w = L.w;

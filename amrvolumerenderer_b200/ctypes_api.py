@@ -255,6 +255,9 @@ def _declare(lib):
         "amrvr_brick_stats": (C.c_int, [vp, i32, _P(Box), _P(C.c_double), _P(C.c_double),
                                         _P(C.c_double), _P(i64)]),
         "amrvr_scene_upload": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),
+        "amrvr_stripe_plan_host": (C.c_int, [i32, i32, _P(C.c_int32), _P(C.c_int32), _P(C.c_int32),
+                                             _P(C.c_uint64), _P(C.c_int32), _P(C.c_uint64)]),
+        "amrvr_stripe_layer_row_host": (C.c_int64, [i32, i32, i32, i32]),
         "amrvr_scene_upload_async": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),
         "amrvr_scene_wait": (C.c_int, [vp, vp]),
         "amrvr_scene_free": (C.c_int, [vp, vp]),

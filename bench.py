@@ -483,16 +483,10 @@ def main():
         dist.broadcast_object_list(box, src=0)
         nccl_id = box[0]
 
-    spin_us = float(os.environ.get("AMRVR_BENCH_SPIN_US", "0"))
-
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        if spin_us > 0:  # experiment: keep the core busy after the collective's blocking wait
-            t_end = time.perf_counter() + spin_us * 1e-6
-            while time.perf_counter() < t_end:
-                pass
 
     def gather_all(obj):
         if world == 1:

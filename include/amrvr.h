@@ -388,6 +388,22 @@ int amrvr_layer_order_host(int nglobal, const amrvr_box_record* records,
                            const amrvr_camera* camera, float* depth_hints,
                            int* order);
 
+/* [host-only] The plan of a frame striped over the GPUs of a box (one rank per GPU):
+ * GPU q folds the 16-row strips q, q + nranks, ... of the frame and its march queue
+ * holds, of every box, the tiles of those strips.  rects: x0, y0, w (padded to 4), h of
+ * every visible footprint.  Out, indexed [q * nboxes + b]: first tile id, first frame row
+ * of the queue's first strip of the box, float offset of the box's strips in pool q (a
+ * layer stores them one after the other, 16 rows each); queue_tile_begin[nranks + 1],
+ * pool_floats[nranks].  Where the reference deals a CONTIGUOUS piece to every rank
+ * (DirectSendBase.cpp:59-74) this deals strips: which pixels a rank folds does not change
+ * a pixel of the gathered frame. */
+int amrvr_stripe_plan_host(int nranks, int nboxes, const int32_t* rects,
+                           int32_t* tile_base, int32_t* ry_first, uint64_t* layer_off,
+                           int32_t* queue_tile_begin, uint64_t* pool_floats);
+/* [host-only] row of rank's layer of a footprint starting at row0 that holds frame row y
+ * (-1: not a row of this rank) -- the address arithmetic of the fold kernel. */
+int64_t amrvr_stripe_layer_row_host(int nranks, int rank, int row0, int y);
+
 /* [host-only] a12.  getPieceRange (DirectSendBase.cpp:59-74). */
 int amrvr_piece_range(int num_pixels, int piece, int num_pieces, int* begin,
                       int* end);

@@ -251,3 +251,70 @@ def test_documents_name_only_entry_points_the_header_declares():
                 assert any(d.startswith(name) for d in declared), (doc, name)
             else:
                 assert name in declared, (doc, name)
+
+
+@pytest.mark.parametrize("nranks", [1, 2, 3, 4, 8])
+def test_stripe_plan_against_a_row_by_row_model(nranks):
+    """The plan of a frame striped over the GPUs of a box (amrvr_stripe_plan_host, the
+    arithmetic frame_fused and the fold kernel share): GPU q folds the 16-row strips
+    q, q + P, ... -- every footprint row belongs to exactly one (queue, tile row), the
+    march's store row equals the fold's read row, layers of one pool do not overlap."""
+    lib = api.load_library()
+    rng = np.random.default_rng(700 + nranks)
+    height, nb = 333, 41
+    rects = np.zeros((nb, 4), np.int32)
+    for b in range(nb):
+        h = int(rng.integers(1, 120))
+        y0 = int(rng.integers(0, height - h + 1))
+        w = 4 * int(rng.integers(1, 40))
+        rects[b] = (4 * int(rng.integers(0, 50)), y0, w, h)
+    rects[0] = (0, 16, 16, 16)   # exactly one strip
+    rects[1] = (0, 15, 4, 2)     # two rows in two strips
+    rects[2] = (0, 0, 8, height)  # the whole frame height
+    n = nranks * nb
+    tile_base, ry_first = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    layer_off, pool = np.zeros(n, np.uint64), np.zeros(nranks, np.uint64)
+    qbegin = np.zeros(nranks + 1, np.int32)
+    P32, P64 = C.POINTER(C.c_int32), C.POINTER(C.c_uint64)
+    st = lib.amrvr_stripe_plan_host(nranks, nb, rects.ctypes.data_as(P32), tile_base.ctypes.data_as(P32),
+                                    ry_first.ctypes.data_as(P32), layer_off.ctypes.data_as(P64),
+                                    qbegin.ctypes.data_as(P32), pool.ctypes.data_as(P64))
+    assert st == 0
+    tiles, covered = 0, np.zeros((nb, height), np.int32)
+    for q in range(nranks):
+        assert qbegin[q] == tiles
+        floats = 0
+        for b in range(nb):
+            _, y0, w, h = (int(v) for v in rects[b])
+            ks = [k for k in range(y0 >> 4, ((y0 + h - 1) >> 4) + 1) if k % nranks == q]
+            i = q * nb + b
+            assert tile_base[i] == tiles and layer_off[i] == floats
+            k = y0 >> 4
+            while k % nranks != q:
+                k += 1
+            assert ry_first[i] == 16 * k
+            for j, ks_j in enumerate(ks):  # tile row j of (queue, box), as the march walks it
+                top = int(ry_first[i]) + j * 16 * nranks
+                assert top == 16 * ks_j
+                for y_in in range(16):
+                    y = top + y_in
+                    if y0 <= y < y0 + h:
+                        covered[b, y] += 1
+                        # the march stores this row at layer row 16 j + y_in; the fold looks it up here
+                        assert lib.amrvr_stripe_layer_row_host(nranks, q, y0, y) == 16 * j + y_in
+            for y in range(y0, y0 + h):  # rows of other ranks are not this rank's
+                if (y >> 4) % nranks != q:
+                    assert lib.amrvr_stripe_layer_row_host(nranks, q, y0, y) == -1
+            tiles += len(ks) * ((w + 15) // 16)
+            floats += len(ks) * 16 * w * 5
+        assert pool[q] == floats
+    assert qbegin[nranks] == tiles
+    for b in range(nb):
+        y0, h = int(rects[b, 1]), int(rects[b, 3])
+        assert (covered[b, y0:y0 + h] == 1).all() and covered[b].sum() == h
+    # the rows a rank folds partition the frame
+    owner = np.array([(y >> 4) % nranks for y in range(height)])
+    assert sorted(np.unique(owner)) == list(range(min(nranks, (height + 15) // 16)))
+    assert lib.amrvr_stripe_plan_host(0, nb, rects.ctypes.data_as(P32), tile_base.ctypes.data_as(P32),
+                                      ry_first.ctypes.data_as(P32), layer_off.ctypes.data_as(P64),
+                                      qbegin.ctypes.data_as(P32), pool.ctypes.data_as(P64)) != 0

@@ -230,6 +230,21 @@ def test_frame_c4_small(ctx, oracle):
     _check_frame(ctx, oracle, scenes.scene_c4(box_cells=8), scenes.make_camera(), _params(128, 128))
 
 
+def test_frame_stats_carry_the_march_time_line(ctx):
+    """amrvr_frame_stats: stage times from CUDA events and the march's own time line on the
+    device clock (first CTA start -> last CTA end, CTA residency, table staging)."""
+    scene = scenes.scene_c4(box_cells=8)
+    ds = ctx.upload_scene(scene)
+    st = ctx.render_frame(ds, scenes.make_camera(), _params(128, 128), want_rgba=False)["stats"]
+    assert st.tiles > 0 and st.fragment_pixels > 0 and st.samples > 0
+    assert st.march_ctas > 0 and st.march_span_ns > 0
+    assert 0 < st.march_cta_busy_ns <= st.march_span_ns * st.march_ctas
+    assert 0 <= st.march_table_ns <= st.march_cta_busy_ns
+    assert st.march_ms > 0 and st.fold_ms > 0 and st.pre_ms >= 0 and st.composite_ms >= st.fold_ms
+    assert st.march_span_ns * 1e-6 <= st.march_ms * 1.5 + 0.05  # the two clocks agree
+    ds.free()
+
+
 def test_frame_ragged_width(ctx, oracle):
     """Width not a multiple of 4 or 16: padded footprints overhang the frame."""
     _check_frame(ctx, oracle, scenes.scene_c2(box_cells=8), scenes.make_camera(), _params(101, 67))
