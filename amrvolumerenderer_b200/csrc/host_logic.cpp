@@ -394,19 +394,37 @@ void layer_order(int nglobal, const amrvr_box_record* recs, const amrvr_camera& 
 
 void stripe_plan(int p, int nboxes, const int32_t* ry0, const int32_t* rh, const int32_t* rw,
                  QueueItem* qitems, int32_t* tile_begin, uint64_t* pool_floats) {
+  // per box, once: first strip k0, k0 % p, and how its nk strips deal out over p queues
+  // (queue q gets base, plus one when it is among the first `rem` after k0 % p) -- the
+  // same numbers as stripe_first_strip / stripe_count, without a division per (queue, box)
+  struct PerBox {
+    int32_t k0, r0, base, rem, tiles_x;
+    uint64_t strip_floats;
+  };
+  std::vector<PerBox> pb(static_cast<size_t>(std::max(nboxes, 0)));
+  for (int b = 0; b < nboxes; ++b) {
+    const int k0 = ry0[b] >> 4, k1 = (ry0[b] + rh[b] - 1) >> 4;
+    const int nk = (rh[b] > 0) ? k1 - k0 + 1 : 0;
+    pb[static_cast<size_t>(b)] = PerBox{k0, k0 % p, nk / p, nk % p, (rw[b] + 15) / 16,
+                                        static_cast<uint64_t>(16) * rw[b] * 5};
+  }
   int tiles = 0;
   for (int q = 0; q < p; ++q) {
     tile_begin[q] = tiles;
-    pool_floats[q] = 0;
+    uint64_t floats = 0;
+    QueueItem* row = qitems + static_cast<size_t>(q) * nboxes;
     for (int b = 0; b < nboxes; ++b) {
-      const int ns = stripe_count(p, q, ry0[b], ry0[b] + rh[b]);
-      QueueItem& item = qitems[static_cast<size_t>(q) * nboxes + b];
-      item.tile_base = tiles;
-      item.ry_first = 16 * stripe_first_strip(p, q, ry0[b]);
-      item.layer_off = pool_floats[q];
-      tiles += ns * ((rw[b] + 15) / 16);
-      pool_floats[q] += static_cast<uint64_t>(ns) * 16 * rw[b] * 5;  // whole strips, 16 rows each
+      const PerBox& B = pb[static_cast<size_t>(b)];
+      int a = q - B.r0;  // how many strips after k0 the queue's first one lies
+      if (a < 0) a += p;
+      const int ns = B.base + (a < B.rem ? 1 : 0);
+      row[b].tile_base = tiles;
+      row[b].ry_first = 16 * (B.k0 + a);
+      row[b].layer_off = floats;
+      tiles += ns * B.tiles_x;
+      floats += static_cast<uint64_t>(ns) * B.strip_floats;  // whole strips, 16 rows each
     }
+    pool_floats[q] = floats;
   }
   tile_begin[p] = tiles;
 }
