@@ -316,7 +316,14 @@ def reference_arm(args, workload):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload, "sample": f"{sw}x{sh} frame of the {W}x{H} workload",
+        # the same workload string as the GPU arm prints at this N; what is timed per step is
+        # the bounded sample named beside it
+        "config": {"workload": f"{workload}: {len(scene.boxes)} boxes, {scene.total_cells()} cells, "
+                               f"{W}x{H} AA{aa}, visibility graph on, boxes dealt {DEAL} round-robin to "
+                               f"{args.gpus} rank(s)",
+                   "sample": f"{sw}x{sh} frame of the {W}x{H} workload, {P} ranks-as-threads "
+                             "(the reference's dense layers make the full frame 14.8 GB and ~20 s: "
+                             "one is timed in full_size_check)",
                    "boxes": len(scene.boxes), "cells": scene.total_cells()},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": P, "host_cores": cores, "kind": kind,
                          "sample": f"{workload} scene, {sw}x{sh} render size, {P} ranks-as-threads on "
