@@ -2668,24 +2668,26 @@ void abort_sharded_frame(amrvr_ctx* ctx) {
 }
 
 // One rank, or every GPU of an NVLink box with the bricks replicated: the whole
-// frame is four launches per GPU and no collective call.
-//   copy    one parameter block (tables, march items, fold table, overlay edges)
-//   bin     per-band layer lists of this GPU's piece (needs the plan only)
-//   march   queue per image piece, own piece first, then tiles of the others with
-//           the fragments stored into their GPU's pool over NVLink; last CTA
-//           raises "march finished" on every GPU
-//   fold    waits for every GPU's flag, folds the piece from LOCAL memory in the
-//           reference's order and run structure, writes overlay + bytes straight
-//           into the root's frame (and the float piece beside it); last CTA
-//           raises "piece finished"
-//   wait    every GPU waits for all pieces (the root's frame is complete; pools
+// frame is a handful of launches per GPU and no collective call.
+//   copy    parameter block, first part (tables, one MarchBox per box, queue items)
+//   march   one queue per GPU: the tiles of the 16-row frame strips that GPU folds
+//           (stripe_plan); own queue first, then tiles of the others with the
+//           fragments stored into their GPU's pool over NVLink; last CTA raises
+//           "march finished" on every GPU
+//   (beside the march, second stream: the host builds the fold table, it is copied
+//    and binned into per-band layer lists)
+//   fold    waits for every GPU's flag, folds this GPU's strips from LOCAL memory in
+//           the reference's order and run structure, writes overlay + bytes straight
+//           into the root's frame (and the float rows beside them); last CTA raises
+//           "rows finished"
+//   wait    every GPU waits for all of them (the root's frame is complete; pools
 //           and queue counters are free for the next frame)
-// Piece p (getPieceRange(N, p, P), DirectSendBase.cpp:59-74) is folded on GPU p.
-// Which rank the REFERENCE would let own piece p -- rank_order[p] from the
-// visibility graph -- does not change a pixel of the gathered frame
-// (SURVEY.md fact 8), so the ordering runs beside the march on the helper thread
-// and is reported (amrvr_ctx_last_rank_order); amrvr_composite, the
-// Compositor::compose seam, places pieces by it.
+// Which pixels a rank folds does not change a pixel of the gathered frame, and
+// neither does which rank the REFERENCE would let own piece p -- rank_order[p]
+// from the visibility graph -- so the ordering runs beside the
+// march on the helper thread and is reported (amrvr_ctx_last_rank_order);
+// amrvr_composite, the Compositor::compose seam, deals the reference's contiguous
+// pieces (getPieceRange, DirectSendBase.cpp:59-74) by it.
 int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* camera,
                 const amrvr_frame_params* params, const amrvr_colormap_pt* pts, int npts, int root,
                 float* rgba5_host, uint8_t* rgb8_host, amrvr_frame_stats* stats,
