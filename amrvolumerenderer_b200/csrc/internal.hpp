@@ -218,9 +218,8 @@ struct PeerPtrs {
 
 // The tiles of one march launch, as up to kMaxPeers queues.  A single-GPU march
 // has one queue.  A frame sharded over the GPUs of a box has one queue per
-// image piece: queue q holds every (box, tile) whose rows lie in piece q, its
-// fragments go to pool[q] (the GPU that folds piece q) and its tile counter
-// lives on that GPU.  A GPU drains `mine` first and then helps with the other
+// GPU: queue q holds every (box, tile) of the frame strips GPU q folds, its
+// fragments go to pool[q] and its tile counter lives on that GPU.  A GPU drains `mine` first and then helps with the other
 // queues in `steal_order`, writing the fragments of those tiles across NVLink.
 struct MarchQueues {
   int32_t nqueues, mine;

@@ -561,18 +561,19 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
 // moves on to the next AMR level.
 //
 // Queues (MarchQueues): one for a single-GPU march.  A frame sharded over the
-// GPUs of a box has one queue per image piece; every GPU holds every brick, so
-// any GPU can march any tile.  A CTA drains its own GPU's queue first (the
-// fragments stay in local HBM) and then takes tiles from the other queues,
-// heaviest first, storing those fragments straight into the pool of the GPU
-// that folds the piece -- posted NVLink stores from an issue-bound kernel, the
-// exchange of DirectSendBase::PostSends/PostReceives (DirectSendBase.cpp:76-177)
-// overlapped with the march tile by tile.  The claim of the next tile is an
-// atomic on the owning GPU's counter: thread 0 issues it BEFORE marching its ray
-// and reads the answer AFTER, so the NVLink round trip of a remote claim hides
-// behind the march of the current tile.  "hints" keep CTAs from probing queues
-// another CTA already found drained.  The last CTA to finish raises this rank's
-// flag on every GPU: that is the barrier the fold of the piece waits on.
+// GPUs of a box has one queue per GPU -- the tiles of the 16-row frame strips
+// that GPU folds (QueueItem, internal.hpp); every GPU holds every brick, so any
+// GPU can march any tile.  A CTA drains its own GPU's queue first (the fragments
+// stay in local HBM) and then takes tiles from the other queues, heaviest first,
+// storing those fragments straight into the pool of the GPU that folds them --
+// posted NVLink stores from an issue-bound kernel, the exchange of
+// DirectSendBase::PostSends/PostReceives (DirectSendBase.cpp:76-177) overlapped
+// with the march tile by tile.  The claim of the next tile is an atomic on the
+// owning GPU's counter, issued by the first warp that is through with the current
+// tile, so its round trip (NVLink for a remote queue) and the look-up of the
+// tile's item hide behind the warps still marching.  "hints" keep CTAs from
+// probing queues another CTA already found drained.  The last CTA to finish
+// raises this rank's flag on every GPU: that is what the folds wait for.
 #ifndef AMRVR_MARCH_MIN_BLOCKS
 #define AMRVR_MARCH_MIN_BLOCKS 4
 #endif
