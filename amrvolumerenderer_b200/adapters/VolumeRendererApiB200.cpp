@@ -434,9 +434,11 @@ int Render(const AmrData& data, const RenderOptions& options) {
   amrvr_ctx* ctx = scene.ctx;
   amrvr_scene* uploaded = nullptr;
   amrvr_b200::check(ctx,
-                    amrvr_scene_upload(ctx, summary.nboxes, scene.boxes.data(), &summary.transform, rangeMin,
-                                       rangeMax, &uploaded),
-                    "amrvr_scene_upload");
+                    // the statistics pass of amrvr_scene_build left these FABs in the staging
+                    // buffer: host MultiFabs cross PCIe once, not twice
+                    amrvr_scene_upload_staged(ctx, summary.nboxes, scene.boxes.data(), &summary.transform,
+                                              rangeMin, rangeMax, &uploaded),
+                    "amrvr_scene_upload_staged");
   amrvr_frame_params params{};
   params.width = options.width;
   params.height = options.height;

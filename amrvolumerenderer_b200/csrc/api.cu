@@ -134,6 +134,11 @@ struct amrvr_ctx {
   cudaEvent_t ev[8] = {};
   // per-frame parameter blocks and scratch
   DeviceBuffer stage;        // FAB doubles waiting for quantisation
+  // what stage_boxes left in `stage` (one 64-bit word per descriptor field and box); valid
+  // until anything else writes the staging buffer -- amrvr_scene_upload_staged quantises
+  // straight from it instead of copying the same FABs a second time
+  std::vector<uint64_t> staged_key;
+  bool staged_valid = false;
   DeviceBuffer quant_jobs;   // QuantJob[] of the upload in flight
   DeviceBuffer march_boxes;  // MarchBox[]
   DeviceBuffer tables;       // float[ntables*1024]
@@ -195,6 +200,7 @@ struct amrvr_scene {
   // asynchronous upload (amrvr_scene_upload_async, one rank): the bricks arrive group by
   // group; group_ready[g] fires when the bricks of copy group g are quantised, box_group[b]
   // is the group of local box b.  A frame marches the boxes of a group as soon as it is there.
+  bool staged_reuse = false;  // amrvr_scene_upload_staged found the FABs in the staging buffer: no copy
   bool pending = false;
   std::vector<cudaEvent_t> group_ready;
   std::vector<int> box_group;
@@ -754,7 +760,29 @@ struct StagedBox {
 
 // Make the valid region of every box device-visible.  Host FABs are copied
 // into ctx->stage (compacted, no ghost cells); device FABs are used in place.
+// identity of a list of FAB views: pointers, extents, strides (not the corners: scene_build rescales them)
+std::vector<uint64_t> staging_key(int nboxes, const amrvr_box* boxes) {
+  std::vector<uint64_t> key;
+  key.reserve(static_cast<size_t>(std::max(nboxes, 0)) * 14 + 1);
+  key.push_back(static_cast<uint64_t>(nboxes));
+  for (int b = 0; b < nboxes; ++b) {
+    const amrvr_box& B = boxes[b];
+    key.push_back(reinterpret_cast<uintptr_t>(B.data));
+    for (int d = 0; d < 3; ++d) {
+      key.push_back(static_cast<uint64_t>(static_cast<uint32_t>(B.dims[d])));
+      key.push_back(static_cast<uint64_t>(static_cast<uint32_t>(B.lo[d])));
+      key.push_back(static_cast<uint64_t>(static_cast<uint32_t>(B.begin[d])));
+    }
+    key.push_back(static_cast<uint64_t>(B.jstride));
+    key.push_back(static_cast<uint64_t>(B.kstride));
+    key.push_back(static_cast<uint64_t>(B.nstride));
+    key.push_back(static_cast<uint64_t>(static_cast<uint32_t>(B.component)));
+  }
+  return key;
+}
+
 int stage_boxes(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes, std::vector<StagedBox>& out) {
+  ctx->staged_valid = false;
   out.resize(static_cast<size_t>(std::max(nboxes, 0)));
   size_t need = 0;
   std::vector<char> on_device(out.size(), 0);
@@ -801,6 +829,8 @@ int stage_boxes(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes, std::vector<
     }
     out[b] = StagedBox{dst, nx, static_cast<int64_t>(nx) * ny};
   }
+  ctx->staged_key = staging_key(nboxes, boxes);  // same offsets as upload_bricks lays the FABs out
+  ctx->staged_valid = true;
   return AMRVR_OK;
 }
 
@@ -812,7 +842,13 @@ int stage_boxes(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes, std::vector<
 // (in-situ) are quantised in place with a single launch.
 int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                   const amrvr_scalar_transform& transform, float range_min, float range_max,
-                  amrvr_scene& scene, bool async_groups = false) {
+                  amrvr_scene& scene, bool async_groups = false, bool reuse_staged = false) {
+  // reuse_staged: the caller asserts that the FABs are the ones the last amrvr_brick_stats /
+  // amrvr_scene_build of this context staged and have not changed since: when the views
+  // match, their doubles are still in the staging buffer and nothing is copied
+  const bool staged = reuse_staged && !async_groups && ctx->staged_valid &&
+                      ctx->staged_key == staging_key(nboxes, boxes);
+  ctx->staged_valid = false;  // an upload that copies overwrites the staging buffer
   // asynchronous: quantise launches go to their own stream and leave one event per group
   cudaStream_t qstream = async_groups ? ctx->quant : ctx->stream;
   if (async_groups) scene.box_group.assign(static_cast<size_t>(nboxes), 0);
@@ -910,7 +946,7 @@ int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
   for (size_t i = 0; i < items.size(); ++i) {
     const Item& it = items[i];
     const amrvr_box& B = boxes[it.box];
-    if (!it.on_device) {
+    if (!it.on_device && !staged) {
       const int nx = B.dims[0], ny = B.dims[1], nz = B.dims[2];
       const double* src = B.data + (B.lo[0] - B.begin[0]) + (B.lo[1] - B.begin[1]) * B.jstride +
                           (B.lo[2] - B.begin[2]) * B.kstride + B.component * B.nstride;
@@ -958,6 +994,11 @@ int upload_bricks(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
   {
     const int st = flush_run();
     if (st != AMRVR_OK) return st;
+  }
+  if (staged) {  // the buffer still holds exactly these FABs
+    ctx->staged_key = staging_key(nboxes, boxes);
+    ctx->staged_valid = true;
+    scene.staged_reuse = true;
   }
   return flush(items.size(), group_copied);
 }
@@ -1073,7 +1114,7 @@ int wait_upload(amrvr_ctx* ctx, const amrvr_scene* scene) {
 }
 int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                       const amrvr_scalar_transform* transform, float range_min, float range_max,
-                      amrvr_scene** out, bool want_async);
+                      amrvr_scene** out, bool want_async, bool reuse_staged = false);
 }  // namespace
 
 extern "C" int amrvr_scene_upload(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
@@ -1088,6 +1129,16 @@ extern "C" int amrvr_scene_upload_async(amrvr_ctx* ctx, int nboxes, const amrvr_
   return scene_upload_impl(ctx, nboxes, boxes, transform, range_min, range_max, out, true);
 }
 
+extern "C" int amrvr_scene_upload_staged(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                                         const amrvr_scalar_transform* transform, float range_min,
+                                         float range_max, amrvr_scene** out) {
+  return scene_upload_impl(ctx, nboxes, boxes, transform, range_min, range_max, out, false, true);
+}
+
+extern "C" int amrvr_scene_upload_was_staged(const amrvr_scene* scene) {
+  return (scene != nullptr && scene->staged_reuse) ? 1 : 0;
+}
+
 extern "C" int amrvr_scene_wait(amrvr_ctx* ctx, amrvr_scene* scene) {
   if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
   REQUIRE(ctx, scene != nullptr, "scene is NULL");
@@ -1098,7 +1149,7 @@ extern "C" int amrvr_scene_wait(amrvr_ctx* ctx, amrvr_scene* scene) {
 namespace {
 int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                       const amrvr_scalar_transform* transform, float range_min, float range_max,
-                      amrvr_scene** out, bool want_async) {
+                      amrvr_scene** out, bool want_async, bool reuse_staged) {
   if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
   REQUIRE(ctx, out != nullptr, "out is NULL");
   *out = nullptr;
@@ -1198,7 +1249,8 @@ int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
   }
   CUDA_TRY(ctx, cudaEventRecord(scene->up0, qstream));
   {
-    const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene, async_groups);
+    const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene, async_groups,
+                                 reuse_staged);
     if (st != AMRVR_OK) {
       if (async_groups) {
         cudaStreamSynchronize(ctx->copy);

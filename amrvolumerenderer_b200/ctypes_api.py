@@ -260,6 +260,8 @@ def _declare(lib):
         "amrvr_stripe_layer_row_host": (C.c_int64, [i32, i32, i32, i32]),
         "amrvr_scene_upload_async": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),
         "amrvr_scene_wait": (C.c_int, [vp, vp]),
+        "amrvr_scene_upload_staged": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),
+        "amrvr_scene_upload_was_staged": (C.c_int, [vp]),
         "amrvr_scene_free": (C.c_int, [vp, vp]),
         "amrvr_scene_build": (C.c_int, [vp, i32, _P(Level), i32, i32, i32, i32, i32, _P(Box), i32,
                                         _P(SceneSummary)]),

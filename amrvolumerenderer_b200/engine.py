@@ -153,11 +153,15 @@ class Context:
                                                   C.byref(total)))
         return counts, int(total.value)
 
-    def upload(self, cboxes, n, transform, scalar_range, wait=True) -> "DeviceScene":
+    def upload(self, cboxes, n, transform, scalar_range, wait=True, staged=False) -> "DeviceScene":
         """wait=False: amrvr_scene_upload_async -- returns with the FAB copies in flight
-        (the arrays must stay alive and unchanged until the first frame or .wait())."""
+        (the arrays must stay alive and unchanged until the first frame or .wait()).
+        staged=True: amrvr_scene_upload_staged -- reuse what the last scene_build /
+        brick_stats of this context left in the staging buffer (unchanged FABs)."""
         h = C.c_void_p()
         fn = self.lib.amrvr_scene_upload if wait else self.lib.amrvr_scene_upload_async
+        if staged:
+            fn = self.lib.amrvr_scene_upload_staged
         self.check(fn(self._h, n, cboxes, C.byref(transform), float(scalar_range[0]),
                       float(scalar_range[1]), C.byref(h)))
         return DeviceScene(self, h)
@@ -261,6 +265,11 @@ class DeviceScene:
         if self._h:
             self.ctx.lib.amrvr_scene_free(self.ctx._h, self._h)
             self._h = C.c_void_p()
+
+    @property
+    def was_staged(self) -> bool:
+        """True when amrvr_scene_upload_staged found the FABs in the staging buffer."""
+        return bool(self.ctx.lib.amrvr_scene_upload_was_staged(self._h))
 
     def wait(self):
         """Blocks until an asynchronous upload has finished."""

@@ -166,6 +166,19 @@ int amrvr_scene_upload_async(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                              float range_min, float range_max, amrvr_scene** out);
 int amrvr_scene_wait(amrvr_ctx* ctx, amrvr_scene* scene);
 
+/* amrvr_scene_upload for the in-situ call sequence (VolumeRendererApi.cpp:80-124, 257-395:
+ * BuildSceneGeometry, then the painter reads the same FABs): amrvr_scene_build /
+ * amrvr_brick_stats already moved the host FABs into the context's staging buffer to
+ * reduce their statistics.  When `boxes` are the views that call staged last (same
+ * pointers, extents, strides; nothing else used the staging buffer since) and the caller
+ * asserts that their contents have not changed, the bricks are quantised from the staged
+ * doubles and nothing crosses PCIe a second time; otherwise this is amrvr_scene_upload.
+ * amrvr_scene_upload_was_staged tells which happened. */
+int amrvr_scene_upload_staged(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
+                              const amrvr_scalar_transform* transform,
+                              float range_min, float range_max, amrvr_scene** out);
+int amrvr_scene_upload_was_staged(const amrvr_scene* scene);
+
 /* K5.  Replaces the zero-copy Array4 views BuildSceneGeometry hands to the
  * painter (SceneBuilder.cpp:160-187): each FAB becomes a device-resident brick
  * of one byte per cell holding the colour-table index the reference computes

@@ -60,6 +60,41 @@ def test_scene_build_ghost_cells_and_components(ctx, oracle):
     ds.free()
 
 
+def test_upload_reuses_what_scene_build_staged(ctx, oracle):
+    """amrvr_scene_upload_staged (the in-situ sequence of VolumeRendererApi.cpp:80-124 + 257-395):
+    the statistics pass of amrvr_scene_build left the host FABs in the staging buffer, the
+    upload quantises from there -- same bytes as a plain upload, with ghost cells and a
+    component offset; any other list of views falls back to the copying upload."""
+    scene = scenes.scene_c3(box_cells=6)
+    levels, nlevels, keep = scenes.c_levels(scene, ghost=2, ncomp=3, component=1)
+    want_boxes, want, status = oracle.scene_build(levels, nlevels, component=1)
+    assert status == 0
+    boxes, summary = ctx.scene_build(levels, nlevels, component=1)
+    rng = tuple(summary.scalar_range)
+    staged = ctx.upload(boxes, summary.nboxes, summary.transform, rng, staged=True)
+    assert staged.was_staged
+    again = ctx.upload(boxes, summary.nboxes, summary.transform, rng, staged=True)  # the buffer still holds them
+    assert again.was_staged
+    plain = ctx.upload(boxes, summary.nboxes, summary.transform, rng)
+    assert not plain.was_staged
+    for b in range(summary.nboxes):
+        w = oracle.quantize_box(want_boxes[b], want.transform, *want.scalar_range)
+        assert np.array_equal(staged.read_brick(b, w.size), w)
+        assert np.array_equal(again.read_brick(b, w.size), w)
+        assert np.array_equal(plain.read_brick(b, w.size), w)
+    # a plain upload used the staging buffer for itself: the next staged call must copy
+    after_plain = ctx.upload(boxes, summary.nboxes, summary.transform, rng, staged=True)
+    assert not after_plain.was_staged
+    # other views (one box fewer) than the ones staged: copies as well, and is right
+    boxes2, summary2 = ctx.scene_build(levels, nlevels, component=1)
+    fewer = ctx.upload(boxes2, summary2.nboxes - 1, summary2.transform, rng, staged=True)
+    assert not fewer.was_staged
+    w = oracle.quantize_box(want_boxes[0], want.transform, *want.scalar_range)
+    assert np.array_equal(fewer.read_brick(0, w.size), w)
+    for ds in (staged, again, plain, after_plain, fewer):
+        ds.free()
+
+
 @pytest.mark.parametrize("case,bins", [("c3_two_levels", 64), ("c2prime_rescaled", 7), ("c3_log_poisoned", 256),
                                        ("c2_raw_range", 1000), ("c1", 1), ("c4_level_window", 20000)])
 def test_histogram_bit_exact(ctx, oracle, case, bins):
