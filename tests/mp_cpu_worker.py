@@ -123,6 +123,51 @@ def check_context_from_env(rank, world):
     assert ids[0] is not None and len(ids[0]) == api.NCCL_ID_BYTES and all(i == ids[0] for i in ids)
 
 
+def check_striped_plan(rank, world):
+    """A frame striped over the ranks (amrvr_stripe_plan_host): every rank computes the same
+    plan (the peer-mapped pools grow collectively, so the sizes must agree without a
+    message), the rows the ranks fold partition the frame, and what rank r holds of every
+    footprint is exactly the rows of r's strips."""
+    import ctypes as C
+    import zlib
+
+    lib = api.load_library()
+    height, nb = 270, 23
+    rng = np.random.default_rng(99)  # the same footprints on every rank
+    rects = np.zeros((nb, 4), np.int32)
+    for b in range(nb):
+        h = int(rng.integers(1, 100))
+        rects[b] = (4 * int(rng.integers(0, 30)), int(rng.integers(0, height - h + 1)),
+                    4 * int(rng.integers(1, 30)), h)
+    n = world * nb
+    tile_base, ry_first = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    layer_off, pool = np.zeros(n, np.uint64), np.zeros(world, np.uint64)
+    qbegin = np.zeros(world + 1, np.int32)
+    P32, P64 = C.POINTER(C.c_int32), C.POINTER(C.c_uint64)
+    assert lib.amrvr_stripe_plan_host(world, nb, rects.ctypes.data_as(P32), tile_base.ctypes.data_as(P32),
+                                      ry_first.ctypes.data_as(P32), layer_off.ctypes.data_as(P64),
+                                      qbegin.ctypes.data_as(P32), pool.ctypes.data_as(P64)) == 0
+    digest = zlib.crc32(tile_base.tobytes() + ry_first.tobytes() + layer_off.tobytes() + pool.tobytes()
+                        + qbegin.tobytes())
+    digests = [None] * world
+    dist.all_gather_object(digests, digest)
+    assert all(d == digests[0] for d in digests)
+    mine = [y for y in range(height) if (y >> 4) % world == rank]
+    rows = [None] * world
+    dist.all_gather_object(rows, mine)
+    assert sorted(y for r in rows for y in r) == list(range(height))
+    held = 0
+    for b in range(nb):
+        y0, h = int(rects[b, 1]), int(rects[b, 3])
+        for y in range(y0, y0 + h):
+            row = lib.amrvr_stripe_layer_row_host(world, rank, y0, y)
+            assert (row >= 0) == (y in mine)
+            held += row >= 0
+    total = torch.tensor([held])
+    dist.all_reduce(total)
+    assert int(total.item()) == int(rects[:, 3].sum())
+
+
 def main():
     dist.init_process_group("gloo")
     rank, world = dist.get_rank(), dist.get_world_size()
@@ -167,6 +212,7 @@ def main():
         assert covered[0][0] == 0 and covered[-1][1] == w * h
         assert all(a[1] == c[0] for a, c in zip(covered, covered[1:]))
     check_input_side(rank, world)
+    check_striped_plan(rank, world)
     check_context_from_env(rank, world)
     dist.barrier()
     if rank == 0:
