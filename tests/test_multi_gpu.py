@@ -40,6 +40,9 @@ def _run(nranks, case, exchange=None):
     if exchange is not None:
         env["AMRVR_EXCHANGE"] = exchange  # "nccl": pack + alltoallv instead of peer-memory loads
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
+    if p.returncode != 0 and "EADDRINUSE" in p.stderr:  # the port found free was taken meanwhile: once more
+        cmd[cmd.index("--master-port") + 1] = str(_free_port())
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env, cwd=ROOT)
     tail = (p.stdout + p.stderr)[-3000:]
     assert p.returncode == 0, tail
     assert "OK" in p.stdout, tail
