@@ -577,9 +577,6 @@ __device__ __forceinline__ RayOut march_ray(const MarchFrame& f, const MarchBox&
 #ifndef AMRVR_MARCH_MIN_BLOCKS
 #define AMRVR_MARCH_MIN_BLOCKS 4
 #endif
-#ifndef AMRVR_MARCH_FIRST_PUBLISHES
-#define AMRVR_MARCH_FIRST_PUBLISHES 1  // 1: the first warp through with a tile claims and looks up the next one
-#endif
 #ifndef AMRVR_MARCH_TIMELINE
 #define AMRVR_MARCH_TIMELINE 1  // thread 0 of every CTA times itself on %globaltimer (amrvr_frame_stats::march_*_ns)
 #endif
@@ -605,9 +602,9 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
                        const unsigned char* __restrict__ bricks,
                        const float4* __restrict__ tables) {
   __shared__ float4 s_table[AMRVR_COLOR_TABLE_SIZE * kTableCopies];
-  __shared__ MarchBox s_box;
+  __shared__ MarchBox s_box[2];                      // mailbox: the box parameters of the slot's tile
   __shared__ int s_tile[2], s_which[2], s_queue[2];  // mailbox: tile id, its box (item), its queue
-  __shared__ int s_taken[2];  // mailbox slot: a warp has taken on filling it (AMRVR_MARCH_FIRST_PUBLISHES)
+  __shared__ int s_taken[2];                         // mailbox slot: a warp has taken on filling it
 
   // ---- thread 0 only; its bookkeeping lives in shared memory so that the march
   // loop keeps its registers.  The try order is the own queue, then steal_order[].
@@ -671,135 +668,115 @@ raymarch_bricks_kernel(const __grid_constant__ MarchFrame f, const __grid_consta
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned table_addr = smem_u32(s_table) + static_cast<unsigned>(lane % kTableCopies) * 16u;
-  int have_box = -1, have_queue = -1, have_table = -1;
+  int have_table = -1;
   unsigned nsamples = 0;
   // thread 0 keeps the launch's time line (Q.stats[4..7]): CTA busy time, first start, last end, table staging
   __shared__ unsigned long long s_t0, s_table_ns, s_stage_t;  // in shared memory: the march loop keeps its registers
+
+  // One warp fills mailbox slot `slot`: lane 0 claims a tile and looks its item up (an
+  // atomic, possibly on another GPU, and a binary search: several dependent round trips),
+  // then the warp copies the item's box parameters into the slot's MarchBox -- so the CTA
+  // finds everything for its next tile in shared memory after ONE barrier.
+  auto fill_slot = [&](int slot) {
+    if (lane == 0) publish(slot, claim_blocking());
+    __syncwarp();
+    const int tile = *reinterpret_cast<volatile int*>(&s_tile[slot]);
+    if (tile < 0) return;
+    const int which = *reinterpret_cast<volatile int*>(&s_which[slot]);
+    const int queue = *reinterpret_cast<volatile int*>(&s_queue[slot]);
+    static_assert(sizeof(MarchBox) == 128 && offsetof(MarchBox, layer_off) == 112,
+                  "words 28..31 (layer_off, dest, ry_first) and tile_base are the item's");
+    constexpr int kTileBaseWord = offsetof(MarchBox, tile_base) / 4;
+    const int* src = reinterpret_cast<const int*>(boxes + which);
+    int* dst = reinterpret_cast<int*>(&s_box[slot]);
+    if (Q.queue_items == nullptr) {
+      dst[lane] = __ldg(src + lane);
+    } else {
+      // striped frame: the box, then what (queue, box) adds to it
+      if (lane < 28 && lane != kTileBaseWord) dst[lane] = __ldg(src + lane);
+      if (lane == 31) {
+        const QueueItem* item = Q.queue_items + static_cast<size_t>(queue) * f.nboxes + which;
+        s_box[slot].tile_base = __ldg(&item->tile_base);
+        s_box[slot].ry_first = __ldg(&item->ry_first);
+        s_box[slot].layer_off = __ldg(&item->layer_off);
+        s_box[slot].dest = queue;
+      }
+    }
+  };
+
   if (threadIdx.x == 0) {
     s_t0 = AMRVR_MARCH_TIMELINE ? global_timer_ns() : 0ull;
     s_table_ns = 0;
     s_cur = 0;
     s_pushed = s_stolen = 0;
     s_taken[0] = s_taken[1] = 0;
-    publish(0, claim_blocking());
   }
+  __syncthreads();
+  if (warp == 0) fill_slot(0);
   for (int it = 0;; ++it) {
-    __syncthreads();  // mailbox slot it&1 is written; everyone is done with the previous tile
-    const int tile = s_tile[it & 1], which = s_which[it & 1], queue = s_queue[it & 1];
+    __syncthreads();  // mailbox slot it&1 is filled; everyone is done with the previous tile
+    const int tile = s_tile[it & 1];
     if (tile < 0) break;
-    if (which != have_box || queue != have_queue) {  // uniform across the CTA
-      static_assert(sizeof(MarchBox) == 128 && offsetof(MarchBox, layer_off) == 112,
-                    "words 28..31 (layer_off, dest, ry_first) and tile_base are the item's");
-      constexpr int kTileBaseWord = offsetof(MarchBox, tile_base) / 4;
-      const int* src = reinterpret_cast<const int*>(boxes + which);
-      if (Q.queue_items == nullptr) {
-        if (threadIdx.x < 32) reinterpret_cast<int*>(&s_box)[threadIdx.x] = __ldg(src + threadIdx.x);
-      } else {
-        // striped frame: the box, then what (queue, box) adds to it
-        if (threadIdx.x < 28 && threadIdx.x != kTileBaseWord)
-          reinterpret_cast<int*>(&s_box)[threadIdx.x] = __ldg(src + threadIdx.x);
-        if (threadIdx.x == 32) {
-          const QueueItem* item = Q.queue_items + static_cast<size_t>(queue) * f.nboxes + which;
-          s_box.tile_base = __ldg(&item->tile_base);
-          s_box.ry_first = __ldg(&item->ry_first);
-          s_box.layer_off = __ldg(&item->layer_off);
-          s_box.dest = queue;
-        }
-      }
-      have_queue = queue;
-      const int table = __ldg(&boxes[which].table);
-      const bool restage = table != have_table;
-      if (restage) {
-        if (AMRVR_MARCH_TIMELINE && threadIdx.x == 0) s_stage_t = global_timer_ns();
-        // consecutive threads write consecutive 16 B slots: conflict-free stores
-        const float4* src4 = tables + table * AMRVR_COLOR_TABLE_SIZE;
-        for (int slot = threadIdx.x; slot < AMRVR_COLOR_TABLE_SIZE * kTableCopies; slot += kMarchThreads)
-          s_table[slot] = __ldg(src4 + (slot / kTableCopies));
-        have_table = table;
-      }
-      have_box = which;
+    const MarchBox& B = s_box[it & 1];
+    const int table = B.table;
+    if (table != have_table) {  // uniform across the CTA; once per AMR level and queue
+      if (AMRVR_MARCH_TIMELINE && threadIdx.x == 0) s_stage_t = global_timer_ns();
+      // consecutive threads write consecutive 16 B slots: conflict-free stores
+      const float4* src4 = tables + table * AMRVR_COLOR_TABLE_SIZE;
+      for (int slot = threadIdx.x; slot < AMRVR_COLOR_TABLE_SIZE * kTableCopies; slot += kMarchThreads)
+        s_table[slot] = __ldg(src4 + (slot / kTableCopies));
+      have_table = table;
       __syncthreads();
-      if (AMRVR_MARCH_TIMELINE && restage && threadIdx.x == 0) s_table_ns += global_timer_ns() - s_stage_t;
+      if (AMRVR_MARCH_TIMELINE && threadIdx.x == 0) s_table_ns += global_timer_ns() - s_stage_t;
     }
-#if !AMRVR_MARCH_FIRST_PUBLISHES
-    // the claim of the next tile: issued here, read after this thread's ray
-    unsigned pend_t = 0;
-    if (threadIdx.x == 0) {
-      int cur = s_cur;
-      while (cur < Q.nqueues && known_drained(queue_at(cur))) ++cur;
-      s_cur = cur;
-      if (cur < Q.nqueues) pend_t = atomicAdd(Q.counter[queue_at(cur)], 1u);
-    }
-#endif
 
     // tile row ty of an item starts at frame row ry_first + ty * strip_stride (the next strip
     // of the same GPU when the frame is striped) and is row 16 * ty of the stored layer
-    const int local_tile = tile - s_box.tile_base;
-    const int tx = local_tile % s_box.tiles_x, ty = local_tile / s_box.tiles_x;
+    const int local_tile = tile - B.tile_base;
+    const int tx = local_tile % B.tiles_x, ty = local_tile / B.tiles_x;
     const int x = tx * kTile + (warp & 1) * 8 + (lane & 7);
     const int y_in = (warp >> 1) * 4 + (lane >> 3);
-    const int y = ty * kTile + y_in;                                    // row of the layer
-    const int frame_y = s_box.ry_first + ty * f.strip_stride + y_in;    // row of the frame
-    const int rw = s_box.rw;
+    const int y = ty * kTile + y_in;                               // row of the layer
+    const int frame_y = B.ry_first + ty * f.strip_stride + y_in;   // row of the frame
+    const int rw = B.rw;
     // footprints are padded to 4-pixel column multiples: columns past the frame are not rays;
     // a strip may begin above the footprint or end below it
-    const bool valid = x < rw && s_box.rx0 + x < f.width && frame_y >= s_box.ry0 &&
-                       frame_y < s_box.ry0 + s_box.rh;
+    const bool valid = x < rw && B.rx0 + x < f.width && frame_y >= B.ry0 && frame_y < B.ry0 + B.rh;
 
-    const RayOut r = s_box.exact_recip
-                         ? march_ray<kCount, true>(f, s_box, bricks, table_addr, s_box.rx0 + x, frame_y, valid)
-                         : march_ray<kCount, false>(f, s_box, bricks, table_addr, s_box.rx0 + x, frame_y,
-                                                    valid);
+    const RayOut r = B.exact_recip
+                         ? march_ray<kCount, true>(f, B, bricks, table_addr, B.rx0 + x, frame_y, valid)
+                         : march_ray<kCount, false>(f, B, bricks, table_addr, B.rx0 + x, frame_y, valid);
 
     // host epilogue of the reference (:939-955)
     float4 out = make_float4(clamp01(r.r), clamp01(r.g), clamp01(r.b), clamp01(r.a));
     float depth = r.depth;
     if (!isfinite(depth) || out.w <= 0.0f) depth = INFINITY;
     if (valid) {
-      float* row = Q.pool[s_box.dest] + s_box.layer_off + static_cast<size_t>(y) * rw * 5;
+      float* row = Q.pool[B.dest] + B.layer_off + static_cast<size_t>(y) * rw * 5;
       reinterpret_cast<float4*>(row)[x] = out;
       row[4 * rw + x] = depth;
     }
     if (kCount) nsamples += r.nsamples;
 
-#if AMRVR_MARCH_FIRST_PUBLISHES
-    // The FIRST warp through with its patch claims the next tile and looks its item up (an
-    // atomic, possibly on another GPU, and a binary search: several dependent round trips)
-    // while the other warps are still marching; with thread 0 doing it after its own ray,
-    // every tile whose slowest patch was warp 0's paid for it in full.
-    if (lane == 0 && atomicExch(&s_taken[(it + 1) & 1], 1) == 0) {
-      if (Q.nranks > 0 && s_box.dest != Q.me) {
-        const int w = min(min(kTile, rw - tx * kTile), f.width - s_box.rx0 - tx * kTile);
-        const int top = s_box.ry_first + ty * f.strip_stride;
-        const int h = min(top + kTile, s_box.ry0 + s_box.rh) - max(top, s_box.ry0);
-        if (w > 0 && h > 0) s_pushed += 20ull * static_cast<unsigned>(w * h);
-      }
-      publish((it + 1) & 1, claim_blocking());
-      s_taken[it & 1] = 0;  // free for iteration it + 2; nobody looks at it before the next barrier
-    }
-  }
-#else
-    if (threadIdx.x == 0) {
-      if (Q.nranks > 0 && s_box.dest != Q.me) {
-        const int w = min(min(kTile, rw - tx * kTile), f.width - s_box.rx0 - tx * kTile);
-        const int top = s_box.ry_first + ty * f.strip_stride;
-        const int h = min(top + kTile, s_box.ry0 + s_box.rh) - max(top, s_box.ry0);
-        if (w > 0 && h > 0) s_pushed += 20ull * static_cast<unsigned>(w * h);
-      }
-      int next = -1;
-      if (s_cur < Q.nqueues) {
-        const int pend_q = queue_at(s_cur);
-        next = tile_of(pend_q, pend_t);
-        if (next < 0) {
-          mark_drained(pend_q);
-          ++s_cur;
-          next = claim_blocking();
+    // The FIRST warp through with its patch fills the other mailbox slot while the rest are
+    // still marching; with thread 0 doing it after its own ray, every tile whose slowest
+    // patch was warp 0's paid for the claim and the look-up in full.
+    int taker = 0;
+    if (lane == 0) taker = (atomicExch(&s_taken[(it + 1) & 1], 1) == 0) ? 1 : 0;
+    taker = __shfl_sync(0xffffffffu, taker, 0);
+    if (taker) {
+      if (lane == 0) {
+        if (Q.nranks > 0 && B.dest != Q.me) {  // fragment bytes of this tile that left the GPU
+          const int w = min(min(kTile, rw - tx * kTile), f.width - B.rx0 - tx * kTile);
+          const int top = B.ry_first + ty * f.strip_stride;
+          const int h = min(top + kTile, B.ry0 + B.rh) - max(top, B.ry0);
+          if (w > 0 && h > 0) s_pushed += 20ull * static_cast<unsigned>(w * h);
         }
+        s_taken[it & 1] = 0;  // free for iteration it + 2; nobody looks at it before the next barrier
       }
-      publish((it + 1) & 1, next);
+      fill_slot((it + 1) & 1);
     }
   }
-#endif
   if (kCount) {
     for (int off = 16; off > 0; off >>= 1) nsamples += __shfl_down_sync(0xffffffffu, nsamples, off);
     if (lane == 0 && nsamples != 0)
