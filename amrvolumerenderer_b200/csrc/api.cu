@@ -139,6 +139,7 @@ struct amrvr_ctx {
   // straight from it instead of copying the same FABs a second time
   std::vector<uint64_t> staged_key;
   bool staged_valid = false;
+  bool async_upload_inflight = false;  // an amrvr_scene_upload_async may still read `stage` / `quant_jobs`
   DeviceBuffer quant_jobs;   // QuantJob[] of the upload in flight
   DeviceBuffer march_boxes;  // MarchBox[]
   DeviceBuffer tables;       // float[ntables*1024]
@@ -760,6 +761,17 @@ struct StagedBox {
 
 // Make the valid region of every box device-visible.  Host FABs are copied
 // into ctx->stage (compacted, no ghost cells); device FABs are used in place.
+// The staging buffer and the quantise job table are shared by every upload / statistics pass
+// of a context: anything that is about to overwrite them first lets an asynchronous upload
+// that may still be reading them finish.
+int drain_async_upload(amrvr_ctx* ctx) {
+  if (!ctx->async_upload_inflight) return AMRVR_OK;
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copy));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->quant));
+  ctx->async_upload_inflight = false;
+  return AMRVR_OK;
+}
+
 // identity of a list of FAB views: pointers, extents, strides (not the corners: scene_build rescales them)
 std::vector<uint64_t> staging_key(int nboxes, const amrvr_box* boxes) {
   std::vector<uint64_t> key;
@@ -782,6 +794,7 @@ std::vector<uint64_t> staging_key(int nboxes, const amrvr_box* boxes) {
 }
 
 int stage_boxes(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes, std::vector<StagedBox>& out) {
+  if (drain_async_upload(ctx) != AMRVR_OK) return AMRVR_ERR_CUDA;
   ctx->staged_valid = false;
   out.resize(static_cast<size_t>(std::max(nboxes, 0)));
   size_t need = 0;
@@ -1241,7 +1254,7 @@ int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
   }
   // asynchronous only where a frame can use it: one rank (a sharded scene is allgathered whole)
   const bool async_groups = want_async && P == 1;
-  if (async_groups) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->quant));  // an earlier upload still reads the staging buffer
+  if (drain_async_upload(ctx) != AMRVR_OK) return AMRVR_ERR_CUDA;  // an earlier one still reads the staging buffer
   cudaStream_t qstream = async_groups ? ctx->quant : ctx->stream;
   if (async_groups) {
     CUDA_TRY(ctx, cudaEventRecord(ctx->copy_start, ctx->stream));
@@ -1267,6 +1280,7 @@ int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
     // returns with the copies in flight: the caller keeps the FABs alive until
     // amrvr_scene_wait or the first frame of this scene has returned
     scene->pending = !scene->group_ready.empty();
+    ctx->async_upload_inflight = scene->pending;
     *out = scene.release();
     return AMRVR_OK;
   }
