@@ -21,6 +21,7 @@ AMRVR_ERR_CUDA = 3
 AMRVR_ERR_NCCL = 4
 COLOR_TABLE_SIZE = 256
 NCCL_ID_BYTES = 128
+BRICK_STATS_STATIC_MAX_BOXES = 4096  # AMRVR_BRICK_STATS_STATIC_MAX_BOXES
 
 PKG_DIR = Path(__file__).resolve().parent
 REPO_ROOT = PKG_DIR.parent
@@ -254,6 +255,8 @@ def _declare(lib):
         "amrvr_peer_bandwidth": (C.c_int, [vp, C.c_size_t, i32, i32, i32, _P(f32)]),
         "amrvr_brick_stats": (C.c_int, [vp, i32, _P(Box), _P(C.c_double), _P(C.c_double),
                                         _P(C.c_double), _P(i64)]),
+        "amrvr_brick_stats_static": (C.c_int, [i32, vp, i32, _P(Box), _P(C.c_double), _P(C.c_double),
+                                               _P(C.c_double), _P(i64)]),
         "amrvr_scene_upload": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),
         "amrvr_stripe_plan_host": (C.c_int, [i32, i32, _P(C.c_int32), _P(C.c_int32), _P(C.c_int32),
                                              _P(C.c_uint64), _P(C.c_int32), _P(C.c_uint64)]),

@@ -328,6 +328,27 @@ class Layers:
         return out
 
 
+# -------------------------------------------- calls that need no context
+
+def brick_stats_static(cboxes, n, device: int = 0, stream: int | None = None):
+    """amrvr_brick_stats_static: (min, max, min positive, finite count) of FABs that are
+    already in device memory, reduced without a Context and without any device allocation.
+
+    For hosts that cannot let a library allocate on the GPU (an in-situ simulation whose
+    arena already holds the device's memory, a time loop that bans cudaMalloc): the
+    reduction's partial records sit in a fixed array inside libamrvr_b200.so.  One call
+    at a time per GPU (all calls share that array), at most
+    ``api.BRICK_STATS_STATIC_MAX_BOXES`` boxes, device-resident data only -- anything
+    else raises AmrvrError.  ``stream`` is a raw cudaStream_t (None = default stream)."""
+    lib = api.load_library()
+    lo, hi, lp = C.c_double(), C.c_double(), C.c_double()
+    cnt = C.c_int64()
+    _check(lib, None, lib.amrvr_brick_stats_static(int(device), C.c_void_p(stream or None), int(n),
+                                                   cboxes, C.byref(lo), C.byref(hi), C.byref(lp),
+                                                   C.byref(cnt)))
+    return lo.value, hi.value, lp.value, cnt.value
+
+
 # ------------------------------------------------------------ host-only calls
 
 def color_table(alpha_scale, norm, rmin, rmax, colormap=None) -> np.ndarray:

@@ -153,6 +153,29 @@ int amrvr_brick_stats(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
                       double* min_value, double* max_value,
                       double* min_positive, int64_t* finite_count);
 
+/* No counterpart in the reference.  amrvr_brick_stats for callers that cannot allocate device
+ * memory: it needs no amrvr_ctx and calls neither cudaMalloc nor cudaFree nor anything else that
+ * allocates.  Meant for in-situ hosts (an AMReX run whose arena already holds almost all of the
+ * GPU's memory, or any code that bans allocation inside its time loop): there a cudaMalloc made by
+ * a library can fail outright, and the matching cudaFree makes the whole device wait.
+ * The per-CTA partial records of the reduction live in one fixed array in device memory that every
+ * GPU loading this library holds from load to exit (about 2 MiB).  Consequences:
+ *   - at most AMRVR_BRICK_STATS_STATIC_MAX_BOXES boxes per call (AMRVR_ERR_INVALID beyond that);
+ *   - every box's `data` must be device (or managed) memory -- a host FAB would need a staging
+ *     buffer, so it is refused with AMRVR_ERR_INVALID instead;
+ *   - all calls on one GPU share that array: calls that overlap on the GPU (two streams, two
+ *     threads) race and return garbage.  The call waits for `stream` before returning, so calls
+ *     issued one after another are fine; nothing has to be cleared between them;
+ *   - the first call on each GPU looks up the array's device address and keeps it; make that
+ *     first call outside any stream capture.
+ * cuda_device is made current.  stream is a cudaStream_t (NULL = the default stream).  Results are
+ * host pointers (any may be NULL) and equal amrvr_brick_stats' bit for bit.  Errors are read with
+ * amrvr_last_error(NULL). */
+#define AMRVR_BRICK_STATS_STATIC_MAX_BOXES 4096
+int amrvr_brick_stats_static(int cuda_device, void* stream, int nboxes,
+                             const amrvr_box* boxes, double* min_value, double* max_value,
+                             double* min_positive, int64_t* finite_count);
+
 /* amrvr_scene_upload without the final wait (one rank; with several ranks it is
  * amrvr_scene_upload): returns while the FAB copies are still on PCIe.  The
  * caller keeps the FABs alive and unchanged until amrvr_scene_wait() or the
