@@ -121,6 +121,8 @@ struct amrvr_ctx {
   int device = 0, rank = 0, nranks = 1;
   cudaStream_t stream = nullptr;
   cudaStream_t aux = nullptr;  // visibility ordering: runs beside the march, never waits for it
+  cudaStream_t plan = nullptr; // fold table copy + fold_bin of a frame: beside the march, and apart from `aux`,
+                               // which the helper thread may be driving (ordering of >= 1024 boxes) at the same time
   cudaStream_t copy = nullptr;  // host->device FAB copies of amrvr_scene_upload, ahead of the quantise
   cudaStream_t quant = nullptr; // quantise launches of an asynchronous upload (amrvr_scene_upload_async)
   cudaEvent_t copy_ev[4] = {};  // copy-group fences (round-robin)
@@ -140,6 +142,7 @@ struct amrvr_ctx {
   std::vector<uint64_t> staged_key;
   bool staged_valid = false;
   bool async_upload_inflight = false;  // an amrvr_scene_upload_async may still read `stage` / `quant_jobs`
+  const amrvr_scene* async_upload_owner = nullptr;  // the scene of that upload (cleared with the flag)
   DeviceBuffer quant_jobs;   // QuantJob[] of the upload in flight
   DeviceBuffer march_boxes;  // MarchBox[]
   DeviceBuffer tables;       // float[ntables*1024]
@@ -164,7 +167,7 @@ struct amrvr_ctx {
   unsigned char* param_host = nullptr;  // pinned staging of the per-frame march parameter block
   size_t param_host_bytes = 0;
   cudaEvent_t param_copied = nullptr;   // the last copy out of param_host has completed
-  cudaEvent_t bin_done = nullptr;       // frame_fused: fold table copied and binned on the aux stream
+  cudaEvent_t bin_done = nullptr;       // frame_fused: fold table copied and binned on the plan stream
   uint8_t* last_rgb8 = nullptr;         // RGB8 frame of the last amrvr_render_frame (root)
   DeviceBuffer frame_pool;              // fragment pool of single-rank fused frames
   std::vector<int> last_rank_order;     // visibility order of the last frame (BuildVisibilityOrderedGroup)
@@ -649,6 +652,7 @@ extern "C" int amrvr_ctx_create(int cuda_device, int rank, int nranks, const voi
   ctx->nranks = nranks;
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
+  CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->plan, cudaStreamNonBlocking));
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->copy, cudaStreamNonBlocking));
   CUDA_TRY(nullptr, cudaStreamCreateWithFlags(&ctx->quant, cudaStreamNonBlocking));
   for (auto& e : ctx->copy_ev) CUDA_TRY(nullptr, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -707,7 +711,7 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (auto& e : ctx->ev)
     if (e != nullptr) cudaEventDestroy(e);
   for (cudaEvent_t e : ctx->event_pool) cudaEventDestroy(e);
-  for (cudaStream_t st : {ctx->stream, ctx->aux, ctx->quant, ctx->copy})
+  for (cudaStream_t st : {ctx->stream, ctx->aux, ctx->plan, ctx->quant, ctx->copy})
     if (st != nullptr) cudaStreamDestroy(st);
   for (auto& e : ctx->copy_ev)
     if (e != nullptr) cudaEventDestroy(e);
@@ -769,7 +773,15 @@ int drain_async_upload(amrvr_ctx* ctx) {
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->copy));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->quant));
   ctx->async_upload_inflight = false;
+  ctx->async_upload_owner = nullptr;
   return AMRVR_OK;
+}
+
+// the asynchronous upload of `scene` is known to be complete: nothing reads the staging buffer any more
+void async_upload_done(amrvr_ctx* ctx, const amrvr_scene* scene) {
+  if (ctx->async_upload_owner != scene) return;  // a later upload owns the flag
+  ctx->async_upload_inflight = false;
+  ctx->async_upload_owner = nullptr;
 }
 
 // identity of a list of FAB views: pointers, extents, strides (not the corners: scene_build rescales them)
@@ -1123,6 +1135,7 @@ int wait_upload(amrvr_ctx* ctx, const amrvr_scene* scene) {
   amrvr_scene* sc = const_cast<amrvr_scene*>(scene);
   if (!sc->group_ready.empty()) CUDA_TRY(ctx, cudaEventSynchronize(sc->group_ready.back()));
   sc->pending = false;
+  async_upload_done(ctx, scene);
   return AMRVR_OK;
 }
 int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
@@ -1172,7 +1185,17 @@ int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
     for (int d = 0; d < 3; ++d)
       REQUIRE(ctx, boxes[b].dims[d] <= (1 << 20), "box dimension exceeds 2^20 cells");
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  std::unique_ptr<amrvr_scene> scene(new amrvr_scene);
+  // every failure return below hands the half-built scene to amrvr_scene_free: streams drained,
+  // events back in the pool, the brick pool (possibly a recycled multi-GB one) back in brick_pools
+  struct Abandon {
+    amrvr_ctx* ctx;
+    void operator()(amrvr_scene* s) const {
+      if (s == nullptr) return;
+      s->pending = true;  // copies of an asynchronous upload may be in flight
+      amrvr_scene_free(ctx, s);
+    }
+  };
+  std::unique_ptr<amrvr_scene, Abandon> scene(new amrvr_scene, Abandon{ctx});
   scene->range_min = range_min;
   scene->range_max = range_max;
   scene->local.resize(static_cast<size_t>(nboxes));
@@ -1264,15 +1287,7 @@ int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
   {
     const int st = upload_bricks(ctx, nboxes, boxes, *transform, range_min, range_max, *scene, async_groups,
                                  reuse_staged);
-    if (st != AMRVR_OK) {
-      if (async_groups) {
-        cudaStreamSynchronize(ctx->copy);
-        cudaStreamSynchronize(ctx->quant);
-      }
-      for (cudaEvent_t e : scene->group_ready) cudaEventDestroy(e);
-      scene->bricks.release();
-      return st;
-    }
+    if (st != AMRVR_OK) return st;
   }
   CUDA_TRY(ctx, cudaEventRecord(scene->up1, qstream));
   tr.mark("upload_enqueue");
@@ -1281,6 +1296,7 @@ int scene_upload_impl(amrvr_ctx* ctx, int nboxes, const amrvr_box* boxes,
     // amrvr_scene_wait or the first frame of this scene has returned
     scene->pending = !scene->group_ready.empty();
     ctx->async_upload_inflight = scene->pending;
+    ctx->async_upload_owner = scene->pending ? scene.get() : nullptr;
     *out = scene.release();
     return AMRVR_OK;
   }
@@ -1579,6 +1595,7 @@ extern "C" int amrvr_scene_free(amrvr_ctx* ctx, amrvr_scene* scene) {
       cudaStreamSynchronize(ctx->quant);
     }
     cudaStreamSynchronize(ctx->stream);
+    async_upload_done(ctx, scene);  // waited for above if it was still pending
   }
   for (cudaEvent_t e : scene->group_ready) {
     if (ctx != nullptr && ctx->event_pool.size() < 64) ctx->event_pool.push_back(e);
@@ -3098,19 +3115,19 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
   const size_t fold_bytes = fold.size() * sizeof(FoldLayer);
   if (fold_bytes) std::memcpy(block + off_fold, fold.data(), fold_bytes);
   std::memcpy(block + off_edges, &edges, sizeof(OverlayEdges));
-  // on the aux stream, beside the march; the fold waits for it
+  // on the plan stream, beside the march; the fold waits for it
   if (st == AMRVR_OK && ctx->bin_done == nullptr)
     st = try_cuda(cudaEventCreateWithFlags(&ctx->bin_done, cudaEventDisableTiming), "event");
   if (st == AMRVR_OK)
     st = try_cuda(cudaMemcpyAsync(dev_block + off_fold, block + off_fold, block_bytes - off_fold,
-                                  cudaMemcpyHostToDevice, ctx->aux),
+                                  cudaMemcpyHostToDevice, ctx->plan),
                   "fold table copy");
-  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->param_copied, ctx->aux), "event");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->param_copied, ctx->plan), "event");
   if (st == AMRVR_OK)
     st = try_launch(launch_fold_bin(fold_dev, static_cast<int>(fold.size()), RW, my_begin, my_end,
-                                    ctx->fold_bins.ptr, ctx->aux, &ctx->launches, my_strips_arg),
+                                    ctx->fold_bins.ptr, ctx->plan, &ctx->launches, my_strips_arg),
                     "fold_bin");
-  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->bin_done, ctx->aux), "event");
+  if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ctx->bin_done, ctx->plan), "event");
   if (st == AMRVR_OK) st = try_cuda(cudaStreamWaitEvent(ctx->stream, ctx->bin_done, 0), "wait");
   if (st == AMRVR_OK) st = try_cuda(cudaEventRecord(ev[6], ctx->stream), "event");
 
@@ -3222,7 +3239,10 @@ int frame_fused(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_camera* ca
     return fail(ctx, AMRVR_ERR_CUDA, std::string("frame failed: ") + cudaGetErrorString(cudaGetLastError()));
   }
   trace.mark("final_sync");
-  if (grouped) const_cast<amrvr_scene*>(scene)->pending = false;  // every group was waited for on the stream
+  if (grouped) {  // every group was waited for on the stream
+    const_cast<amrvr_scene*>(scene)->pending = false;
+    async_upload_done(ctx, scene);
+  }
   st = join_order(ctx, &order);
   if (st != AMRVR_OK) return st;
   if (sharded && static_cast<uint32_t>(ctx->frame_stats_host[8]) != 0) {
