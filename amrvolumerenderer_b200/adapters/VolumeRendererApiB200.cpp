@@ -23,6 +23,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <fstream>
 #include <iomanip>
 #include <iostream>
@@ -433,12 +434,19 @@ int Render(const AmrData& data, const RenderOptions& options) {
 
   amrvr_ctx* ctx = scene.ctx;
   amrvr_scene* uploaded = nullptr;
+  // The statistics pass of amrvr_scene_build left these FABs in the staging buffer: host MultiFabs
+  // cross PCIe once, not twice.  The staged copy is recognised by pointers, extents and strides only,
+  // so NOTHING may touch the MultiFabs between buildScene (amrvr_scene_build) above and this call --
+  // no FillBoundary, no reallocation at the same address: the doubles quantised here would be the
+  // stale staged ones.  AMRVR_DEBUG_STAGED=1 prints which path the upload took.
   amrvr_b200::check(ctx,
-                    // the statistics pass of amrvr_scene_build left these FABs in the staging
-                    // buffer: host MultiFabs cross PCIe once, not twice
                     amrvr_scene_upload_staged(ctx, summary.nboxes, scene.boxes.data(), &summary.transform,
                                               rangeMin, rangeMax, &uploaded),
                     "amrvr_scene_upload_staged");
+  if (const char* debugStaged = std::getenv("AMRVR_DEBUG_STAGED"); debugStaged != nullptr && debugStaged[0] == '1')
+    std::fprintf(stderr, "[amrvr] api::Render rank %d: bricks quantised from %s\n", scene.rank,
+                 amrvr_scene_upload_was_staged(uploaded) ? "the doubles amrvr_scene_build staged (no second PCIe pass)"
+                                                         : "a fresh copy of the FABs");
   amrvr_frame_params params{};
   params.width = options.width;
   params.height = options.height;
