@@ -391,12 +391,31 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
         recs, n, [min(float(r.min_corner[d]) for r in recs[:n]) for d in range(3)],
         [max(float(r.max_corner[d]) for r in recs[:n]) for d in range(3)])
     layers = ctx.raymarch(ds, camera, rw, rh, params.box_transparency, ref_d)
-    begin, end, _piece = ctx.composite(ds, layers, camera, order)
+    begin, end, piece = ctx.composite(ds, layers, camera, order)
+    # ... and its pixels: the pieces the NCCL exchange + fold left on every rank, gathered on rank 0
+    # (a12 content + a14), against the oracle's frame without the overlay, before any downsample
+    full = ctx.gather(piece, begin, end, rw * rh, root=0)
     spans = [None] * world
     if world > 1:
         dist.all_gather_object(spans, (rank, begin, end))
     else:
         spans = [(0, begin, end)]
+    # at N > 1 one more frame with replication switched off for this upload: every rank marches its
+    # own boxes and the fragments cross with NCCL (the path a scene too large to replicate takes)
+    got_os, ds_os = None, None
+    if world > 1:
+        keep = os.environ.get("AMRVR_REPLICATE_MAX_MB")
+        os.environ["AMRVR_REPLICATE_MAX_MB"] = "0"
+        try:
+            ds_os = ctx.upload_scene(scene)
+        finally:
+            if keep is None:
+                del os.environ["AMRVR_REPLICATE_MAX_MB"]
+            else:
+                os.environ["AMRVR_REPLICATE_MAX_MB"] = keep
+        got_os = ctx.render_frame(ds_os, camera, params)
+        samples_os = torch.tensor([got_os["stats"].samples], dtype=torch.int64, device=device)
+        dist.all_reduce(samples_os)
     out = None
     if rank == 0:
         from oracle.oracle import Oracle, Ref, RefUnavailable, read_ppm
@@ -417,6 +436,22 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
                "ownership_equal": bool(own_ok),
                "samples_equal": bool(int(samples.item()) == int(want["samples"])),
                "max_abs_rgba": err, "max_lsb": lsb, "against": "oracle, same rank count and box->rank map"}
+        dense = np.frombuffer(ctx.read_device(full, rw * rh * 20), np.float32).reshape(rh, rw, 5)
+        bare = api.FrameParams(width=rw, height=rh, box_transparency=params.box_transparency, antialiasing=1,
+                               use_visibility_graph=1, count_samples=0, draw_bounding_box=0)
+        want_bare = orc.render_frame(scene, camera, bare)
+        out["seam_piece_max_abs_rgba"] = float(np.abs(dense[..., :4] - want_bare["final5"][..., :4]).max())
+        out["seam"] = ("amrvr_raymarch -> amrvr_composite (pack + ncclSend/Recv + fold) -> amrvr_gather at "
+                       f"{rw}x{rh}, vs the oracle's frame without overlay")
+        ctx.lib.amrvr_device_free(ctx._h, full)
+        if got_os is not None:
+            out["object_space_frame"] = {
+                "replicated": bool(ds_os.replicated),
+                "max_abs_rgba": float(np.abs(got_os["final5"][..., :4] - want["final5"][..., :4]).max()),
+                "max_lsb": int(np.abs(got_os["rgb8"].astype(int) - want["rgb8"].astype(int)).max()),
+                "samples_equal": bool(int(samples_os.item()) == int(want["samples"])),
+                "path": "AMRVR_REPLICATE_MAX_MB=0 for one upload: boxes marched by their owner, "
+                        "fragments exchanged with NCCL, same frame"}
         try:  # the reference's own frame: real VolumeRenderer::renderScene, ranks as threads
             ref = Ref()
             ref.render_scene(scene, camera, params, "/tmp/amrvr_bench_parity.ppm")
@@ -425,11 +460,26 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
         except (RefUnavailable, OSError) as exc:
             out["reference_ppm_max_lsb"] = None
             out["reference_ppm_note"] = f"oracle/_ref unavailable: {exc}"
+        osf = out.get("object_space_frame")
         out["ok"] = bool(out["rank_order_equal"] and out["ownership_equal"] and out["samples_equal"] and
                          err <= RGBA_TOL and lsb <= LSB_TOL and
+                         out["seam_piece_max_abs_rgba"] <= RGBA_TOL and
+                         (osf is None or (not osf["replicated"] and osf["samples_equal"] and
+                                          osf["max_abs_rgba"] <= RGBA_TOL and osf["max_lsb"] <= LSB_TOL)) and
                          (out["reference_ppm_max_lsb"] is None or out["reference_ppm_max_lsb"] <= LSB_TOL))
+        eq = lambda flag: "equal" if flag else "DIFFERENT"
+        out["summary"] = (
+            f"{world} rank(s) {out['size']} vs oracle: order {eq(out['rank_order_equal'])}, ownership "
+            f"{eq(out['ownership_equal'])}, samples {eq(out['samples_equal'])}, max|dRGBA| {err:.3g}, "
+            f"LSB {lsb}, reference PPM LSB {out['reference_ppm_max_lsb']}, compose-seam piece (NCCL "
+            f"exchange + gather) max|d| {out['seam_piece_max_abs_rgba']:.3g}"
+            + (f", object-space frame (unreplicated, NCCL) max|d| {osf['max_abs_rgba']:.3g} LSB "
+               f"{osf['max_lsb']} samples {eq(osf['samples_equal'])}" if osf else "")
+            + (" -- OK" if out["ok"] else " -- BROKEN"))
     layers.free()
     ds.free()
+    if ds_os is not None:
+        ds_os.free()
     return out
 
 
@@ -701,7 +751,8 @@ def main():
                        if replicated else "one rank" if world == 1 else "boxes marched by their owner, NCCL exchange",
                        "samples_per_frame": total_samples,
                        "frames_per_s": 1e3 / ms_per_step,
-                       "stage_ms": stage_ms},
+                       "stage_ms": stage_ms,
+                       "parity": parity["summary"] if parity else "not run (--no-parity)"},
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": total_samples / (e2e_ms_mean * 1e-3) / 1e9, "unit": UNIT,
                     "ms_per_step": e2e_ms_mean, "frames_per_s": 1e3 / e2e_ms_mean,
@@ -798,6 +849,7 @@ def main():
                 line["cpu_baseline"] = cpu_baseline(args.workload)
             except Exception as exc:  # the oracle always exists; report rather than hide
                 line["cpu_baseline"] = {"error": repr(exc)}
+        line["parity"] = line.pop("parity")  # last in the line: a tail of stdout still shows it
         print(json.dumps(line), flush=True)
         fail = (parity is not None and not parity["ok"]) or \
                (full_check is not None and full_check.get("ok") is False)
