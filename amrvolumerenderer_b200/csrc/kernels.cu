@@ -10,16 +10,21 @@
 //   raymarch_bricks_kernel      K1  all (box, 16x16 pixel tile) pairs of a rank, one launch,
 //                                   persistent CTAs pulling tiles from a counter
 //   fold_bin_kernel             K6  per 8-row band: the ordered list of layers touching it
-//   fold_layers_kernel          K6  per-pixel run-structured depth-swap 'over'; reads peer
-//                                   GPUs' fragments over NVLink; <true>: overlay + RGB8 epilogue
+//   fold_layers_kernel          K6  per-pixel run-structured depth-swap 'over' of a rank's rows; the
+//                                   fragments of those rows lie in the rank's OWN pool (the march of
+//                                   whichever GPU took the tile stored them there over NVLink);
+//                                   <true>: overlay + RGB8 epilogue (into the root's frame over NVLink)
 //   pack_slices_kernel          C6  row slices into per-destination send buffers (NCCL path)
-//   peer_barrier_kernel             flag barrier across the GPUs of one box, with time-out
+//   peer_wait_kernel                closes a sharded frame: waits for every GPU's fold flag, time-out
+//   peer_barrier_kernel             flag barrier across the GPUs of one box, with time-out (set-up paths)
+//   peer_copy_kernel                load/store copy between peers (amrvr_peer_bandwidth, the NVLink probe)
 //   post_piece_kernel               overlay + bytes of a piece into the root's RGB8 frame
 //   downsample_kernel           K8  box filter
 //   overlay_kernel                  wireframe coverage on the float frame
 //   quantize_rgb8_kernel            float -> byte, rows flipped
 //   order_rank_kernel           K7  single-CTA LSD radix sort of box depth keys
 //   order_pairs_kernel          K7  all-pairs face-adjacency test
+//   order_count_kernel          K7  per-box count of boxes in front (priority of the Kahn peel)
 #include <cuda_runtime.h>
 
 #include <algorithm>

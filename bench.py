@@ -52,7 +52,17 @@ WORKLOADS = {
     "C5-8": (functools.partial(scenes.scene_c5, n=8), 4096, 4096, 1, 0.0),
     "C5-16": (functools.partial(scenes.scene_c5, n=16), 4096, 4096, 1, 0.0),
 }
-DEAL = "skewed"  # box i -> rank (i + i div P) mod P over the (level, k, j, i) order
+# Box -> rank map of the synthetic scenes.  "skewed": box i -> rank (i + i div P) mod P over the
+# (level, k, j, i) order; "chunks": contiguous chunks of ceil(n/P) boxes, the rule SURVEY.md 8(d) writes
+# down for C3/C4 (AMRVR_BENCH_DEAL=chunks selects it).  With replicated bricks the march is dealt by image
+# strips, so the rule no longer moves the march; it changes the same-owner run structure the fold follows
+# (the reference's blend fold is not associative: the oracle gets the same map) and the FAB bytes each
+# rank uploads -- chunks give one rank a whole refinement level, skewed gives every rank near and far boxes.
+DEAL = os.environ.get("AMRVR_BENCH_DEAL", "skewed")
+DEAL_TEXT = {"skewed": "skewed round-robin (i + i div P) mod P [SURVEY 8(d) names contiguous chunks: "
+                       "AMRVR_BENCH_DEAL=chunks]",
+             "chunks": "in contiguous chunks of ceil(n/P) (SURVEY 8(d))",
+             "round_robin": "round-robin i mod P"}[DEAL]
 NVLINK_NOMINAL_GBPS = 900.0  # NVLink 5, per direction per GPU (B200_PROFILING.md)
 RGBA_TOL = 1e-4  # north_star: float RGBA within 1e-4 absolute per channel
 LSB_TOL = 1      # north_star: 8-bit output within 1 LSB
@@ -319,7 +329,7 @@ def reference_arm(args, workload):
         # the same workload string as the GPU arm prints at this N; what is timed per step is
         # the bounded sample named beside it
         "config": {"workload": f"{workload}: {len(scene.boxes)} boxes, {scene.total_cells()} cells, "
-                               f"{W}x{H} AA{aa}, visibility graph on, boxes dealt {DEAL} round-robin to "
+                               f"{W}x{H} AA{aa}, visibility graph on, boxes dealt {DEAL_TEXT} to "
                                f"{args.gpus} rank(s)",
                    "sample": f"{sw}x{sh} frame of the {W}x{H} workload, {P} ranks-as-threads "
                              "(the reference's dense layers make the full frame 14.8 GB and ~20 s: "
@@ -740,7 +750,7 @@ def main():
             "data": "synthetic",
             "config": {"workload": f"{args.workload}: {len(scene.boxes)} boxes, {cells} cells, "
                                    f"{W}x{H} AA{aa}, visibility graph on, boxes dealt "
-                                   f"{DEAL} round-robin to {world} rank(s)",
+                                   f"{DEAL_TEXT} to {world} rank(s)",
                        "value_scope": "bricks resident in HBM, RGB8 frame left on the root GPU",
                        "e2e_scope": "pinned host FABs -> upload+quantise -> frame -> RGB8 on the host"
                                     + ("; the frame marches each 16 MB copy group as it lands "
