@@ -493,6 +493,61 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
     return out
 
 
+def composite_seam(ctx, dist, dscene, scene, camera, workload, world, rank, stream, flush, steps, gather_all):
+    """N > 1, untimed part of the line: the Compositor::compose seam on RANK-OWNED layers at the
+    workload's full render size (BASELINE.json configs[4] words the compositor sweep this way):
+    every rank marches its own boxes (amrvr_raymarch), then amrvr_composite = host plan + pack
+    kernel + grouped ncclSend/ncclRecv of the row slices other pieces need + fold.  Device time
+    from CUDA events on the ctx stream around the call, host time around call + synchronise;
+    bytes from amrvr_exchange_plan_host (every rank derives the same plan)."""
+    import torch
+    from amrvolumerenderer_b200.engine import exchange_plan_host, reference_sample_distance
+
+    _, W, H, aa, transp = WORKLOADS[workload]
+    root = int(round(aa ** 0.5))
+    rw, rh = W * root, H * root
+    recs, n = scene.records()
+    order, _ = ctx.order_boxes(dscene, camera, W / H)
+    ref_d = reference_sample_distance(
+        recs, n, [min(float(r.min_corner[d]) for r in recs[:n]) for d in range(3)],
+        [max(float(r.max_corner[d]) for r in recs[:n]) for d in range(3)])
+    layers = ctx.raymarch(dscene, camera, rw, rh, transp, ref_d)
+    send, recv, _span = exchange_plan_host(world, rank, recs, n, camera, rw, rh, order)
+    sent = int(4 * (send.sum() - send[rank]))
+    received = int(4 * (recv.sum() - recv[rank]))
+    dev_ms, host_ms = [], []
+    for it in range(2 + steps):
+        flush.fill_(it & 0xFF)
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(stream)
+        ctx.composite(dscene, layers, camera, order)
+        e1.record(stream)
+        ctx.synchronize()
+        t1 = time.perf_counter()
+        if it >= 2:
+            dev_ms.append(e0.elapsed_time(e1))
+            host_ms.append((t1 - t0) * 1e3)
+    layers.free()
+    rows = gather_all({"rank": rank, "device_ms": float(np.mean(dev_ms)), "host_ms": float(np.mean(host_ms)),
+                       "sent_bytes": sent, "received_bytes": received})
+    if rank != 0:
+        return None
+    worst = max(r["device_ms"] for r in rows)
+    return {"what": f"amrvr_raymarch (own boxes) -> amrvr_composite at {rw}x{rh}, {n} layers owned by "
+                    f"{world} ranks, mean of {steps} calls after 2 warm-up, L2 flushed between calls",
+            "device_ms_max_rank": worst, "host_ms_max_rank": max(r["host_ms"] for r in rows),
+            "sent_bytes_per_rank": [r["sent_bytes"] for r in rows],
+            "sent_GBps_per_rank_over_device_ms": [r["sent_bytes"] / (r["device_ms"] * 1e-3) / 1e9 for r in rows],
+            "aggregate_GBps": sum(r["sent_bytes"] for r in rows) / (worst * 1e-3) / 1e9,
+            "per_rank": rows,
+            "note": "device_ms spans pack + NCCL exchange + fold_bin + fold of one call; the rate divides the "
+                    "bytes a rank SENDS by that whole time, so it is a lower bound on the link rate during "
+                    "the exchange itself"}
+
+
 def full_size_check(scene, camera, workload, rgb8):
     """N=1, once, untimed: the timed frame itself (full size) against the oracle's."""
     from oracle.oracle import Oracle
@@ -522,6 +577,8 @@ def main():
     ap.add_argument("--workload", default="C4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-seam", action="store_true",
+                    help="skip the untimed compose-seam measurement on rank-owned layers (N > 1)")
     ap.add_argument("--no-full-size", action="store_true",
                     help="skip the one full-size comparison with the oracle (N=1) / full-size reference frame")
     args = ap.parse_args()
@@ -665,6 +722,12 @@ def main():
         # the probe moves 11 x 256 MiB (warm-up + 10) each way: what the counters say about it
         link = gather_all({"rank": rank, "write_GBps": wr, "read_GBps": rd,
                            "counted_write_probe": _delta(c1, c0, 1), "counted_read_probe": _delta(c2, c1, 1)})
+
+    # ---- the compose seam on rank-owned layers (N > 1): the path that exchanges fragments with NCCL
+    seam = None
+    if world > 1 and not args.no_seam:
+        seam = composite_seam(ctx, dist, dscene, scene, camera, args.workload, world, rank, stream, flush,
+                              min(args.steps, 10), gather_all)
 
     # ---- end-to-end arm: pinned host FABs -> upload -> frame -> host RGB8
     e2e_ms, up_ms = [], []
@@ -850,6 +913,12 @@ def main():
                     "the same rank; push_GBps = fragment bytes this rank's march stored into other GPUs' "
                     "pools / its own march time -- the exchange rides on the march, it has no time of its own",
         }
+        if seam is not None:
+            peak_w = link_peak["write_GBps_min"] if link_peak else None
+            seam["nvlink_measured_write_GBps"] = peak_w
+            seam["frac_of_measured_write_peak_per_rank"] = (
+                [g / peak_w for g in seam["sent_GBps_per_rank_over_device_ms"]] if peak_w else None)
+            line["composite_seam"] = seam
         if dev_fabs is not None:
             line["e2e_device_fabs"] = dev_fabs
         if full_check is not None:
