@@ -162,6 +162,9 @@ struct amrvr_ctx {
   // peer-memory exchange (nranks > 1 on one NVLink box; off -> NCCL alltoallv)
   bool peer_ok = false;
   SymBuffer sym_flags, sym_pool, sym_piece, sym_rgb8;
+  SymBuffer sym_recv;  // amrvr_composite with peer access: every rank's receive pool, written by its peers
+  cudaEvent_t seam_ev[4] = {};  // that composite on the stream: entry, pools free, slices stored, slices arrived
+  bool seam_timed = false;
   uint32_t barrier_epoch = 0;
   uint32_t* peer_error_host = nullptr;  // pinned copy of the barrier time-out flag
   unsigned char* param_host = nullptr;  // pinned staging of the per-frame march parameter block
@@ -690,7 +693,7 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   if (ctx == nullptr) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream != nullptr) cudaStreamSynchronize(ctx->stream);
-  for (SymBuffer* b : {&ctx->sym_flags, &ctx->sym_pool, &ctx->sym_piece, &ctx->sym_rgb8})
+  for (SymBuffer* b : {&ctx->sym_flags, &ctx->sym_pool, &ctx->sym_piece, &ctx->sym_rgb8, &ctx->sym_recv})
     sym_release(*b, ctx->rank);
   if (ctx->peer_error_host != nullptr) cudaFreeHost(ctx->peer_error_host);
   if (ctx->param_host != nullptr) cudaFreeHost(ctx->param_host);
@@ -716,6 +719,8 @@ extern "C" void amrvr_ctx_destroy(amrvr_ctx* ctx) {
   for (auto& e : ctx->copy_ev)
     if (e != nullptr) cudaEventDestroy(e);
   if (ctx->copy_start != nullptr) cudaEventDestroy(ctx->copy_start);
+  for (auto& e : ctx->seam_ev)
+    if (e != nullptr) cudaEventDestroy(e);
   ctx->quant_jobs.release();
   delete ctx;
 }
@@ -2091,20 +2096,35 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
   std::vector<uint64_t> send_off(P + 1, 0), recv_off(P + 1, 0);
   std::vector<CopyJob> jobs;
   std::vector<uint64_t> recv_slot(static_cast<size_t>(n), 0);  // float offset in recv_buf per global box
+  // With peer access the slices are not packed and sent: one kernel reads them out of the layer pool and
+  // stores them straight into the destination rank's receive pool over NVLink (fused pack + push), between
+  // two flag barriers.  AMRVR_EXCHANGE=nccl (no peer mapping) keeps pack + grouped ncclSend/ncclRecv.
+  const bool push = P > 1 && ctx->peer_ok;
+  float* recv_base = nullptr;
   if (P > 1) {
     std::vector<uint64_t> send_len(P, 0), recv_len(P, 0);
+    // len[q * P + o]: floats rank q receives from rank o (every rank derives the whole matrix)
+    std::vector<uint64_t> len(static_cast<size_t>(P) * P, 0);
     for (int g = 0; g < n; ++g) {
       const int owner = scene->global[g].owner;
       const Rect& r = plan.rects[g];
       int s0, s1;
-      if (owner == me) {
-        for (int q = 0; q < P; ++q) {
-          if (q == me || !slice_rows(r, plan.begin[q], plan.end[q], W, &s0, &s1)) continue;
-          send_len[q] += static_cast<uint64_t>(s1 - s0) * r.w * 5;
-        }
-      } else if (slice_rows(r, my_begin, my_end, W, &s0, &s1)) {
-        recv_len[owner] += static_cast<uint64_t>(s1 - s0) * r.w * 5;
+      for (int q = 0; q < P; ++q) {
+        if (q == owner || !slice_rows(r, plan.begin[q], plan.end[q], W, &s0, &s1)) continue;
+        len[static_cast<size_t>(q) * P + owner] += static_cast<uint64_t>(s1 - s0) * r.w * 5;
       }
+    }
+    uint64_t max_recv = 0;
+    std::vector<uint64_t> my_off_at(P, 0);  // where my slices start in rank q's receive pool
+    for (int q = 0; q < P; ++q) {
+      uint64_t total = 0;
+      for (int o = 0; o < P; ++o) {
+        if (o == me) my_off_at[q] = total;
+        total += len[static_cast<size_t>(q) * P + o];
+      }
+      max_recv = std::max(max_recv, total);
+      send_len[q] = len[static_cast<size_t>(q) * P + me];
+      recv_len[q] = len[static_cast<size_t>(me) * P + q];
     }
     for (int q = 0; q < P; ++q) {
       send_off[q + 1] = send_off[q] + send_len[q];
@@ -2125,7 +2145,9 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
           uint64_t left = static_cast<uint64_t>(s1 - s0) * r.w * 5;
           while (left > 0) {
             const uint32_t c = static_cast<uint32_t>(std::min<uint64_t>(left, kChunk));
-            jobs.push_back(CopyJob{src, send_cur[q], c, 0});
+            jobs.push_back(push ? CopyJob{src, my_off_at[q] + (send_cur[q] - send_off[q]), c,
+                                          static_cast<uint32_t>(q)}
+                                : CopyJob{src, send_cur[q], c, 0});
             src += c;
             send_cur[q] += c;
             left -= c;
@@ -2136,28 +2158,54 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
         recv_cur[owner] += static_cast<uint64_t>(s1 - s0) * r.w * 5;
       }
     }
-    CUDA_TRY(ctx, ctx->send_buf.reserve(std::max<uint64_t>(send_off[P], 4) * sizeof(float)));
-    CUDA_TRY(ctx, ctx->recv_buf.reserve(std::max<uint64_t>(recv_off[P], 4) * sizeof(float)));
     if (!jobs.empty()) {
       CUDA_TRY(ctx, ctx->copy_jobs.reserve(jobs.size() * sizeof(CopyJob)));
       CUDA_TRY(ctx, cudaMemcpyAsync(ctx->copy_jobs.ptr, jobs.data(), jobs.size() * sizeof(CopyJob),
                                     cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (push) {
+      // the pool is as large as the largest receiver needs, so every rank grows it in the same call
+      bool mapped = true;
+      const int st = sym_reserve(ctx, ctx->sym_recv, std::max<uint64_t>(max_recv, 4) * sizeof(float), &mapped);
+      if (st != AMRVR_OK) return st;
+      if (!mapped) return fail(ctx, AMRVR_ERR_CUDA, "peer mapping of the receive pool failed");
+      recv_base = static_cast<float*>(ctx->sym_recv.local);
+      for (auto& e : ctx->seam_ev)
+        if (e == nullptr) CUDA_TRY(ctx, cudaEventCreate(&e));
+      CUDA_TRY(ctx, cudaEventRecord(ctx->seam_ev[0], ctx->stream));
+      // nobody stores into a pool its owner may still be folding from (the previous composite)
+      int bst = peer_barrier(ctx, 3);
+      if (bst != AMRVR_OK) return bst;
+      CUDA_TRY(ctx, cudaEventRecord(ctx->seam_ev[1], ctx->stream));
+      LAUNCH_TRY(ctx, launch_push(ctx->copy_jobs.as<CopyJob>(), static_cast<int>(jobs.size()),
+                                  layers->pool.as<float>(), peer_ptrs(ctx->sym_recv), ctx->stream,
+                                  &ctx->launches));
+      CUDA_TRY(ctx, cudaEventRecord(ctx->seam_ev[2], ctx->stream));
+      // every peer's slices have arrived (the barrier kernel fences before it raises its flags)
+      bst = peer_barrier(ctx, 3);
+      if (bst != AMRVR_OK) return bst;
+      CUDA_TRY(ctx, cudaEventRecord(ctx->seam_ev[3], ctx->stream));
+      ctx->seam_timed = true;
+    } else {
+      CUDA_TRY(ctx, ctx->send_buf.reserve(std::max<uint64_t>(send_off[P], 4) * sizeof(float)));
+      CUDA_TRY(ctx, ctx->recv_buf.reserve(std::max<uint64_t>(recv_off[P], 4) * sizeof(float)));
+      recv_base = ctx->recv_buf.as<float>();
       LAUNCH_TRY(ctx, launch_pack(ctx->copy_jobs.as<CopyJob>(), static_cast<int>(jobs.size()),
                                   layers->pool.as<float>(), ctx->send_buf.as<float>(), ctx->stream,
                                   &ctx->launches));
+      NcclApi& nc = nccl_api();
+      NCCL_TRY(ctx, nc.GroupStart());
+      for (int q = 0; q < P; ++q) {
+        if (q == me) continue;
+        if (send_len[q] > 0)
+          NCCL_TRY(ctx, nc.Send(ctx->send_buf.as<float>() + send_off[q], send_len[q], ncclFloat, q,
+                                ctx->comm, ctx->stream));
+        if (recv_len[q] > 0)
+          NCCL_TRY(ctx, nc.Recv(ctx->recv_buf.as<float>() + recv_off[q], recv_len[q], ncclFloat, q,
+                                ctx->comm, ctx->stream));
+      }
+      NCCL_TRY(ctx, nc.GroupEnd());
     }
-    NcclApi& nc = nccl_api();
-    NCCL_TRY(ctx, nc.GroupStart());
-    for (int q = 0; q < P; ++q) {
-      if (q == me) continue;
-      if (send_len[q] > 0)
-        NCCL_TRY(ctx, nc.Send(ctx->send_buf.as<float>() + send_off[q], send_len[q], ncclFloat, q,
-                              ctx->comm, ctx->stream));
-      if (recv_len[q] > 0)
-        NCCL_TRY(ctx, nc.Recv(ctx->recv_buf.as<float>() + recv_off[q], recv_len[q], ncclFloat, q,
-                              ctx->comm, ctx->stream));
-    }
-    NCCL_TRY(ctx, nc.GroupEnd());
     if (exchanged_bytes) *exchanged_bytes = static_cast<int64_t>(send_off[P] * sizeof(float));
   } else if (exchanged_bytes) {
     *exchanged_bytes = 0;
@@ -2176,7 +2224,7 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
       F.base = layers->pool.as<float>() + layers->offs[g - scene->first_global] +
                static_cast<uint64_t>(s0 - r.y0) * r.w * 5;
     } else {
-      F.base = ctx->recv_buf.as<float>() + recv_slot[g];
+      F.base = recv_base + recv_slot[g];
     }
     F.x0 = r.x0;
     F.w = r.w;
@@ -2211,6 +2259,18 @@ int composite_impl(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers*
 }
 
 }  // namespace
+
+extern "C" int amrvr_ctx_last_composite_ms(amrvr_ctx* ctx, float* ms5) {
+  if (ctx == nullptr) return fail(nullptr, AMRVR_ERR_INVALID, "ctx is NULL");
+  REQUIRE(ctx, ms5 != nullptr, "ms5 is NULL");
+  REQUIRE(ctx, ctx->seam_timed, "no composite has pushed slices to peers on this ctx yet");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  const cudaEvent_t mark[6] = {ctx->seam_ev[0], ctx->seam_ev[1], ctx->seam_ev[2], ctx->seam_ev[3],
+                               ctx->ev[6], ctx->ev[7]};
+  for (int i = 0; i < 5; ++i) CUDA_TRY(ctx, cudaEventElapsedTime(&ms5[i], mark[i], mark[i + 1]));
+  return AMRVR_OK;
+}
 
 extern "C" int amrvr_composite(amrvr_ctx* ctx, const amrvr_scene* scene, const amrvr_layers* layers,
                                const amrvr_camera* camera, const int* rank_order,

@@ -249,7 +249,7 @@ struct FoldLayer {
 struct CopyJob {
   uint64_t src_off, dst_off;  // in floats
   uint32_t count;             // floats, multiple of 4
-  uint32_t pad;
+  uint32_t pad;               // push_slices_kernel: destination rank
 };
 
 // ------------------------------------------------------------ kernel launchers
@@ -325,6 +325,8 @@ int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst
 // flag row `which`, then wait until all nranks slots of the own row hold >= epoch.
 // Gives up after timeout_ns and raises *error_flag (own device memory) instead of
 // hanging the GPU.
+int launch_push(const CopyJob* jobs_dev, int njobs, const float* src, const PeerPtrs& recv, void* stream,
+                int64_t* launches);
 int launch_peer_barrier(const PeerPtrs& flags, int me, int nranks, int which, uint32_t epoch,
                         unsigned long long timeout_ns, uint32_t* error_flag, void* stream,
                         int64_t* launches);

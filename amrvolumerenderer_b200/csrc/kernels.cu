@@ -15,6 +15,7 @@
 //                                   whichever GPU took the tile stored them there over NVLink);
 //                                   <true>: overlay + RGB8 epilogue (into the root's frame over NVLink)
 //   pack_slices_kernel          C6  row slices into per-destination send buffers (NCCL path)
+//   push_slices_kernel          C6  the same slices stored straight into the destination GPU's receive pool
 //   peer_wait_kernel                closes a sharded frame: waits for every GPU's fold flag, time-out
 //   peer_barrier_kernel             flag barrier across the GPUs of one box, with time-out (set-up paths)
 //   peer_copy_kernel                load/store copy between peers (amrvr_peer_bandwidth, the NVLink probe)
@@ -1327,6 +1328,26 @@ pack_slices_kernel(const CopyJob* __restrict__ jobs, const float* __restrict__ s
   for (unsigned i = threadIdx.x; i < n4; i += blockDim.x) d[i] = s[i];
 }
 
+// Fused pack + push: the same row slices, stored straight into the receive pool of the rank whose piece
+// needs them (CopyJob::pad = destination rank, dst_off = offset inside THAT rank's pool) over NVLink.
+__global__ void __launch_bounds__(256)
+push_slices_kernel(const CopyJob* __restrict__ jobs, const float* __restrict__ src,
+                   const __grid_constant__ PeerPtrs recv) {
+  const CopyJob job = jobs[blockIdx.x];
+  const float4* s = reinterpret_cast<const float4*>(src + job.src_off);
+  float4* d = reinterpret_cast<float4*>(static_cast<float*>(recv.p[job.pad]) + job.dst_off);
+  const unsigned n4 = job.count >> 2;
+  unsigned i = threadIdx.x;
+  for (; i + 3 * 256 < n4; i += 4 * 256) {  // four 16 B loads in flight before the first remote store
+    const float4 a = __ldcs(s + i), b = __ldcs(s + i + 256), c = __ldcs(s + i + 512), e = __ldcs(s + i + 768);
+    d[i] = a;
+    d[i + 256] = b;
+    d[i + 512] = c;
+    d[i + 768] = e;
+  }
+  for (; i < n4; i += 256) d[i] = __ldcs(s + i);
+}
+
 // ------------------------------------------------------------------ K8, post
 
 // reference: VolumeRenderer/VolumeRenderer.cpp:479-528 (sum order dy-major, dx-minor)
@@ -1978,6 +1999,14 @@ int launch_pack(const CopyJob* jobs_dev, int njobs, const float* src, float* dst
                 int64_t* launches) {
   if (njobs <= 0) return 0;
   pack_slices_kernel<<<njobs, 256, 0, as_stream(stream)>>>(jobs_dev, src, dst);
+  ++*launches;
+  return static_cast<int>(cudaGetLastError());
+}
+
+int launch_push(const CopyJob* jobs_dev, int njobs, const float* src, const PeerPtrs& recv, void* stream,
+                int64_t* launches) {
+  if (njobs <= 0) return 0;
+  push_slices_kernel<<<njobs, 256, 0, as_stream(stream)>>>(jobs_dev, src, recv);
   ++*launches;
   return static_cast<int>(cudaGetLastError());
 }

@@ -257,6 +257,7 @@ def _declare(lib):
                                         _P(C.c_double), _P(i64)]),
         "amrvr_brick_stats_static": (C.c_int, [i32, vp, i32, _P(Box), _P(C.c_double), _P(C.c_double),
                                                _P(C.c_double), _P(i64)]),
+        "amrvr_ctx_last_composite_ms": (C.c_int, [vp, _P(f32)]),
         "amrvr_scene_upload": (C.c_int, [vp, i32, _P(Box), _P(ScalarTransform), f32, f32, _P(vp)]),
         "amrvr_stripe_plan_host": (C.c_int, [i32, i32, _P(C.c_int32), _P(C.c_int32), _P(C.c_int32),
                                              _P(C.c_uint64), _P(C.c_int32), _P(C.c_uint64)]),

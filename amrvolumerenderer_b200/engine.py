@@ -244,6 +244,13 @@ class Context:
                                             C.byref(piece)))
         return b.value, e.value, piece
 
+    def last_composite_ms(self):
+        """Device ms of the last composite that pushed slices to peers: (wait for free pools,
+        push kernel, wait for arrival, fold table copy + host gap, fold_bin + fold)."""
+        out = (C.c_float * 5)()
+        self.check(self.lib.amrvr_ctx_last_composite_ms(self._h, out))
+        return tuple(float(x) for x in out)
+
     def read_device(self, ptr, nbytes) -> bytes:
         buf = np.zeros(nbytes, np.uint8)
         self.check(self.lib.amrvr_copy_to_host(self._h, buf.ctypes.data_as(C.c_void_p), ptr, nbytes))

@@ -451,7 +451,7 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
                                use_visibility_graph=1, count_samples=0, draw_bounding_box=0)
         want_bare = orc.render_frame(scene, camera, bare)
         out["seam_piece_max_abs_rgba"] = float(np.abs(dense[..., :4] - want_bare["final5"][..., :4]).max())
-        out["seam"] = ("amrvr_raymarch -> amrvr_composite (pack + ncclSend/Recv + fold) -> amrvr_gather at "
+        out["seam"] = ("amrvr_raymarch -> amrvr_composite (slices pushed into the peers' receive pools, or NCCL; fold) -> amrvr_gather at "
                        f"{rw}x{rh}, vs the oracle's frame without overlay")
         ctx.lib.amrvr_device_free(ctx._h, full)
         if got_os is not None:
@@ -461,7 +461,7 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
                 "max_lsb": int(np.abs(got_os["rgb8"].astype(int) - want["rgb8"].astype(int)).max()),
                 "samples_equal": bool(int(samples_os.item()) == int(want["samples"])),
                 "path": "AMRVR_REPLICATE_MAX_MB=0 for one upload: boxes marched by their owner, "
-                        "fragments exchanged with NCCL, same frame"}
+                        "fragments exchanged through the compose seam, same frame"}
         try:  # the reference's own frame: real VolumeRenderer::renderScene, ranks as threads
             ref = Ref()
             ref.render_scene(scene, camera, params, "/tmp/amrvr_bench_parity.ppm")
@@ -481,9 +481,9 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
         out["summary"] = (
             f"{world} rank(s) {out['size']} vs oracle: order {eq(out['rank_order_equal'])}, ownership "
             f"{eq(out['ownership_equal'])}, samples {eq(out['samples_equal'])}, max|dRGBA| {err:.3g}, "
-            f"LSB {lsb}, reference PPM LSB {out['reference_ppm_max_lsb']}, compose-seam piece (NCCL "
-            f"exchange + gather) max|d| {out['seam_piece_max_abs_rgba']:.3g}"
-            + (f", object-space frame (unreplicated, NCCL) max|d| {osf['max_abs_rgba']:.3g} LSB "
+            f"LSB {lsb}, reference PPM LSB {out['reference_ppm_max_lsb']}, compose-seam piece (exchange "
+            f"+ fold + gather) max|d| {out['seam_piece_max_abs_rgba']:.3g}"
+            + (f", object-space frame (unreplicated, own boxes) max|d| {osf['max_abs_rgba']:.3g} LSB "
                f"{osf['max_lsb']} samples {eq(osf['samples_equal'])}" if osf else "")
             + (" -- OK" if out["ok"] else " -- BROKEN"))
     layers.free()
@@ -496,8 +496,9 @@ def parity_check(ctx, dist, scene, camera, workload, world, rank, device):
 def composite_seam(ctx, dist, dscene, scene, camera, workload, world, rank, stream, flush, steps, gather_all):
     """N > 1, untimed part of the line: the Compositor::compose seam on RANK-OWNED layers at the
     workload's full render size (BASELINE.json configs[4] words the compositor sweep this way):
-    every rank marches its own boxes (amrvr_raymarch), then amrvr_composite = host plan + pack
-    kernel + grouped ncclSend/ncclRecv of the row slices other pieces need + fold.  Device time
+    every rank marches its own boxes (amrvr_raymarch), then amrvr_composite = host plan + the row
+    slices other pieces need stored straight into their ranks' receive pools over NVLink
+    (push_slices_kernel between two flag barriers; pack + ncclSend/ncclRecv without peer access) + fold.  Device time
     from CUDA events on the ctx stream around the call, host time around call + synchronise;
     bytes from amrvr_exchange_plan_host (every rank derives the same plan)."""
     import torch
@@ -515,7 +516,8 @@ def composite_seam(ctx, dist, dscene, scene, camera, workload, world, rank, stre
     send, recv, _span = exchange_plan_host(world, rank, recs, n, camera, rw, rh, order)
     sent = int(4 * (send.sum() - send[rank]))
     received = int(4 * (recv.sum() - recv[rank]))
-    dev_ms, host_ms = [], []
+    dev_ms, host_ms, stages = [], [], []
+    pushing = os.environ.get("AMRVR_EXCHANGE") != "nccl"
     for it in range(2 + steps):
         flush.fill_(it & 0xFF)
         dist.barrier()
@@ -530,20 +532,32 @@ def composite_seam(ctx, dist, dscene, scene, camera, workload, world, rank, stre
         if it >= 2:
             dev_ms.append(e0.elapsed_time(e1))
             host_ms.append((t1 - t0) * 1e3)
+            if pushing:
+                try:
+                    stages.append(ctx.last_composite_ms())
+                except api.AmrvrError:  # no peer mapping on this box: the call took the NCCL path
+                    pushing = False
     layers.free()
+    stage = [float(x) for x in np.mean(np.array(stages), axis=0)] if stages else None
     rows = gather_all({"rank": rank, "device_ms": float(np.mean(dev_ms)), "host_ms": float(np.mean(host_ms)),
-                       "sent_bytes": sent, "received_bytes": received})
+                       "sent_bytes": sent, "received_bytes": received,
+                       "stage_ms": dict(zip(("wait_pools_free", "push_kernel", "wait_arrival", "table_copy_gap",
+                                             "fold_bin_and_fold"), stage)) if stage else None,
+                       "push_GBps": sent / (stage[1] * 1e-3) / 1e9 if stage and stage[1] > 0 else None})
     if rank != 0:
         return None
     worst = max(r["device_ms"] for r in rows)
     return {"what": f"amrvr_raymarch (own boxes) -> amrvr_composite at {rw}x{rh}, {n} layers owned by "
                     f"{world} ranks, mean of {steps} calls after 2 warm-up, L2 flushed between calls",
             "device_ms_max_rank": worst, "host_ms_max_rank": max(r["host_ms"] for r in rows),
+            "exchange": "push over NVLink (peer-mapped receive pools)" if rows[0]["stage_ms"]
+                        else "pack + ncclSend/ncclRecv",
+            "push_GBps_per_rank": [r["push_GBps"] for r in rows],
             "sent_bytes_per_rank": [r["sent_bytes"] for r in rows],
             "sent_GBps_per_rank_over_device_ms": [r["sent_bytes"] / (r["device_ms"] * 1e-3) / 1e9 for r in rows],
             "aggregate_GBps": sum(r["sent_bytes"] for r in rows) / (worst * 1e-3) / 1e9,
             "per_rank": rows,
-            "note": "device_ms spans pack + NCCL exchange + fold_bin + fold of one call; the rate divides the "
+            "note": "device_ms spans the host plan, barrier, push (or pack + NCCL), barrier, fold_bin and fold of one call; the rate divides the "
                     "bytes a rank SENDS by that whole time, so it is a lower bound on the link rate during "
                     "the exchange itself"}
 
@@ -723,7 +737,7 @@ def main():
         link = gather_all({"rank": rank, "write_GBps": wr, "read_GBps": rd,
                            "counted_write_probe": _delta(c1, c0, 1), "counted_read_probe": _delta(c2, c1, 1)})
 
-    # ---- the compose seam on rank-owned layers (N > 1): the path that exchanges fragments with NCCL
+    # ---- the compose seam on rank-owned layers (N > 1): the path that moves fragments between ranks
     seam = None
     if world > 1 and not args.no_seam:
         seam = composite_seam(ctx, dist, dscene, scene, camera, args.workload, world, rank, stream, flush,
@@ -918,6 +932,8 @@ def main():
             seam["nvlink_measured_write_GBps"] = peak_w
             seam["frac_of_measured_write_peak_per_rank"] = (
                 [g / peak_w for g in seam["sent_GBps_per_rank_over_device_ms"]] if peak_w else None)
+            seam["push_kernel_frac_of_measured_write_peak_per_rank"] = (
+                [g / peak_w if g else None for g in seam["push_GBps_per_rank"]] if peak_w else None)
             line["composite_seam"] = seam
         if dev_fabs is not None:
             line["e2e_device_fabs"] = dev_fabs

@@ -488,11 +488,23 @@ int amrvr_layers_read(amrvr_ctx* ctx, const amrvr_layers* layers, int layer,
  * (Common/Compositor.hpp:35-37, DirectSend/Base/DirectSendBase.cpp:316-458):
  * this rank's fully blended piece, pixels [*region_begin, *region_end) of the
  * row-major frame, 5 floats per pixel, left on the device
- * (*piece5_device, owned by ctx, valid until the next composite). Collective. */
+ * (*piece5_device, owned by ctx, valid until the next composite). Collective.
+ * The exchange of DirectSendBase.cpp:76-177, 400-446 (MPI_Isend/Irecv of layer pieces) is one
+ * kernel here when the GPUs of the box can map each other's memory: it reads the row slices
+ * another rank's piece needs out of the layer pool and stores them straight into that rank's
+ * receive pool over NVLink, between two flag barriers; without peer access (or with
+ * AMRVR_EXCHANGE=nccl) the slices are packed and travel with grouped ncclSend/ncclRecv. */
 int amrvr_composite(amrvr_ctx* ctx, const amrvr_scene* scene,
                     const amrvr_layers* layers, const amrvr_camera* camera,
                     const int* rank_order, int* region_begin, int* region_end,
                     float** piece5_device);
+/* Where the device time of the last amrvr_composite of this ctx went when it stored its slices
+ * into the peers' receive pools (nranks > 1 with peer access; AMRVR_ERR_INVALID otherwise):
+ * ms5 = { wait until every peer's pool is free, push_slices_kernel (this rank's stores over
+ * NVLink), wait until every peer's slices have arrived, fold table copy + host gap, fold_bin +
+ * fold }.  Waits for the ctx stream.  No reference counterpart (the reference times nothing
+ * inside DirectSendBase::compose). */
+int amrvr_ctx_last_composite_ms(amrvr_ctx* ctx, float* ms5);
 /* [host-only] The exchange amrvr_composite performs for `rank`, without doing
  * it: floats this rank sends to / receives from every other rank (row slices
  * of footprint layers that intersect the destination piece) and its own pixel
