@@ -553,6 +553,12 @@ def composite_seam(ctx, dist, dscene, scene, camera, workload, world, rank, stre
             "exchange": "push over NVLink (peer-mapped receive pools)" if rows[0]["stage_ms"]
                         else "pack + ncclSend/ncclRecv",
             "push_GBps_per_rank": [r["push_GBps"] for r in rows],
+            # what a rank RECEIVES over the time its peers' stores were in flight (its own push + the wait
+            # for arrival): with contiguous pieces the centre of the image receives most, and that GPU's
+            # ingress is the link that bounds the exchange
+            "ingress_GBps_per_rank": [
+                r["received_bytes"] / ((r["stage_ms"]["push_kernel"] + r["stage_ms"]["wait_arrival"]) * 1e-3) / 1e9
+                if r["stage_ms"] else None for r in rows],
             "sent_bytes_per_rank": [r["sent_bytes"] for r in rows],
             "sent_GBps_per_rank_over_device_ms": [r["sent_bytes"] / (r["device_ms"] * 1e-3) / 1e9 for r in rows],
             "aggregate_GBps": sum(r["sent_bytes"] for r in rows) / (worst * 1e-3) / 1e9,
@@ -932,6 +938,8 @@ def main():
             seam["nvlink_measured_write_GBps"] = peak_w
             seam["frac_of_measured_write_peak_per_rank"] = (
                 [g / peak_w for g in seam["sent_GBps_per_rank_over_device_ms"]] if peak_w else None)
+            seam["hottest_ingress_frac_of_measured_write_peak"] = (
+                max((g or 0.0) for g in seam["ingress_GBps_per_rank"]) / peak_w if peak_w else None)
             seam["push_kernel_frac_of_measured_write_peak_per_rank"] = (
                 [g / peak_w if g else None for g in seam["push_GBps_per_rank"]] if peak_w else None)
             line["composite_seam"] = seam
