@@ -558,7 +558,8 @@ def composite_seam(ctx, dist, dscene, scene, camera, workload, world, rank, stre
             # ingress is the link that bounds the exchange
             "ingress_GBps_per_rank": [
                 r["received_bytes"] / ((r["stage_ms"]["push_kernel"] + r["stage_ms"]["wait_arrival"]) * 1e-3) / 1e9
-                if r["stage_ms"] else None for r in rows],
+                if r["stage_ms"] and (r["stage_ms"]["push_kernel"] + r["stage_ms"]["wait_arrival"]) > 0 else None
+                for r in rows],
             "sent_bytes_per_rank": [r["sent_bytes"] for r in rows],
             "sent_GBps_per_rank_over_device_ms": [r["sent_bytes"] / (r["device_ms"] * 1e-3) / 1e9 for r in rows],
             "aggregate_GBps": sum(r["sent_bytes"] for r in rows) / (worst * 1e-3) / 1e9,
